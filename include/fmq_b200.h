@@ -1,0 +1,248 @@
+/*
+ * fmq_b200.h — C ABI of the B200-native keyed window-aggregate + alert engine.
+ *
+ * This is the drop-in boundary for the ONE hot path of the Flink monitoring quickstart
+ * (reference = /root/reference, Jax-Rene/monitor-systam-flink-quickstart): what a Flink
+ * `OneInputStreamOperator` / `KeyedProcessFunction` shim (JNI / Panama / ctypes / C++) binds.
+ * Plain C: pointers, sizes, POD structs.  No C++ types, no torch types, no exceptions cross it.
+ *
+ * Data model: one micro-batch = n events in three columns
+ *     ts[n]  : int64   event time, epoch milliseconds, ts >= 0
+ *     key[n] : uint64  dictionary-encoded key (host, channel, or host<<32|metric);
+ *                      0xFFFFFFFFFFFFFFFF is reserved
+ *     val[n] : float64 (FMQ_VAL_F64) or int64 (FMQ_VAL_I64)
+ * Watermarks arrive only at micro-batch boundaries: every record of batch b is judged against
+ * the watermark in force after batch b-1 (deterministic replacement of Flink's 200 ms
+ * wall-clock watermark timer, chapter3/README.md:379-386).
+ *
+ * Threading contract (inherited from Flink's operator model): one handle per operator
+ * subtask, calls on one handle are serialised by the caller; different handles may be used
+ * concurrently from different threads.  Each handle owns one CUDA stream and all of its
+ * device state.
+ *
+ * All functions return an fmq_status (0 = OK).  A human-readable message for the last
+ * failure on a handle is available from fmq_last_error().
+ */
+#ifndef FMQ_B200_H
+#define FMQ_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FMQ_ABI_VERSION 1
+
+typedef enum fmq_status {
+    FMQ_OK = 0,
+    FMQ_ERR_BAD_ARG = 1,        /* null pointer, bad enum, size not a multiple of slide ...   */
+    FMQ_ERR_TABLE_FULL = 2,     /* key directory is full (raise table_capacity)               */
+    FMQ_ERR_RING_OVERFLOW = 3,  /* open event-time span exceeds pane_ring panes               */
+    FMQ_ERR_OUTPUT_OVERFLOW = 4,/* an output buffer filled up before it was polled            */
+    FMQ_ERR_CUDA = 5,           /* a CUDA call failed; see fmq_last_error                     */
+    FMQ_ERR_BAD_TS = 6,         /* negative timestamp or reserved key seen                    */
+    FMQ_ERR_NO_DEVICE = 7,      /* no usable CUDA device: there is NO CPU fallback            */
+    FMQ_ERR_POISONED = 8        /* a previous sticky error invalidated this handle's state    */
+} fmq_status;
+
+typedef enum fmq_value_type { FMQ_VAL_F64 = 0, FMQ_VAL_I64 = 1 } fmq_value_type;
+typedef enum fmq_mem        { FMQ_MEM_HOST = 0, FMQ_MEM_DEVICE = 1 } fmq_mem;
+typedef enum fmq_cmp        { FMQ_CMP_GT = 0, FMQ_CMP_LT = 1, FMQ_CMP_GE = 2, FMQ_CMP_LE = 3 } fmq_cmp;
+
+/* aggregate mask bits (count is always maintained: a window fires only if count > 0) */
+#define FMQ_AGG_COUNT 1u
+#define FMQ_AGG_SUM   2u
+#define FMQ_AGG_MIN   4u
+#define FMQ_AGG_MAX   8u
+
+/* which fired-window quantity the window alert expression is evaluated on */
+typedef enum fmq_alert_source {
+    FMQ_ALERT_NONE = 0,
+    FMQ_ALERT_SUM = 1,   /* (double)sum * mul / div0 / div1 / div2   BandwidthMonitor.java:39    */
+    FMQ_ALERT_AVG = 2,   /* count == 0 ? 0.0 : sum / count           ComputeCpuAvg.java:49       */
+    FMQ_ALERT_MIN = 3,
+    FMQ_ALERT_MAX = 4,
+    FMQ_ALERT_COUNT = 5
+} fmq_alert_source;
+
+/* watermark_after value meaning "derive it from the data": wm = max(wm, maxTsSeen - bound)
+ * (BoundedOutOfOrdernessTimestampExtractor, chapter3/README.md:379-396). */
+#define FMQ_WM_AUTO INT64_MIN
+/* watermark that fires every remaining window (Flink's end-of-input Watermark(Long.MAX_VALUE)) */
+#define FMQ_WM_FINAL INT64_MAX
+
+/*
+ * Job description.  One POD replaces the reference's hard-coded DSL chain
+ *   keyBy(k).timeWindow(size[,slide]).reduce/aggregate(...).map(...).filter(...)
+ * (chapter3/.../BandwidthMonitorWithEventTime.java:45-55, chapter2/.../ComputeCpuAvg.java:27-31),
+ * the un-keyed filter (chapter1/.../Main.java:27-32) and the keyed ValueState operators
+ * (chapter2/.../ComputeCpuMax.java:26 and the consecutive-breach rule of BASELINE.json).
+ * Zero-initialise, set struct_size = sizeof(fmq_config), then fill in what the job uses.
+ */
+typedef struct fmq_config {
+    uint32_t struct_size;
+    int32_t  device;                 /* CUDA device ordinal                                      */
+    int32_t  value_type;             /* fmq_value_type                                           */
+    int32_t  reserved0;
+
+    /* --- event-time window aggregation (A2, A3, A5, A5f) --- */
+    int32_t  window_enabled;
+    uint32_t agg_mask;               /* FMQ_AGG_*                                                */
+    int64_t  window_size_ms;         /* Time.minutes(5) -> 300000                                */
+    int64_t  window_slide_ms;        /* == size for tumbling; size % slide must be 0             */
+    int64_t  window_offset_ms;       /* 0 <= offset < slide; timeWindow(...) uses 0              */
+    int64_t  max_out_of_orderness_ms;/* bound of BoundedOutOfOrdernessTimestampExtractor         */
+    int32_t  emit_fired;             /* 1: every fired (key, window) row is emitted              */
+
+    /* --- alert on fired windows (A6 ii/iii) --- */
+    int32_t  walert_source;          /* fmq_alert_source                                         */
+    int32_t  walert_op;              /* fmq_cmp                                                  */
+    int32_t  reserved1;
+    double   walert_mul;             /* 8.0                                                      */
+    double   walert_div0;            /* 60     (use 1.0 for "no division")                       */
+    double   walert_div1;            /* 1024                                                     */
+    double   walert_div2;            /* 1024                                                     */
+    double   walert_threshold;       /* 100.0                                                    */
+
+    /* --- per-event threshold filter (A6 i, chapter1 Main.java:31) --- */
+    int32_t  efilter_enabled;
+    int32_t  efilter_op;             /* fmq_cmp; the reference uses strict >                     */
+    double   efilter_threshold;      /* 90                                                       */
+
+    /* --- keyed ValueState operators (A7), per-key arrival order --- */
+    int32_t  rolling_max_enabled;    /* keyBy(0).max(2): one output per input                    */
+    int32_t  consec_n;               /* 0 = off; N consecutive over-threshold readings           */
+    int32_t  consec_op;              /* fmq_cmp, strict > by default                             */
+    int32_t  consec_reset_on_fire;   /* 1: counter returns to 0 after an alert                   */
+    double   consec_threshold;
+
+    /* --- capacities (all device memory is allocated once, in fmq_create) --- */
+    uint64_t table_capacity;         /* key-directory slots; rounded up to a power of two        */
+    uint32_t pane_ring;              /* open panes kept per key; rounded up to a power of two    */
+    uint32_t reserved2;
+    uint64_t max_batch;              /* largest n accepted by fmq_push_batch                     */
+    uint64_t fired_capacity;         /* fired rows buffered between polls                        */
+    uint64_t walert_capacity;        /* window-alert rows buffered between polls                 */
+    uint64_t ealert_capacity;        /* per-event filter rows buffered between polls             */
+    uint64_t calert_capacity;        /* consecutive-breach alert rows buffered between polls     */
+} fmq_config;
+
+/* one fired (key, window): 48 B per row */
+typedef struct fmq_fired_cols {
+    uint64_t* key;
+    int64_t*  window_end;            /* exclusive end; Flink's record timestamp is window_end-1  */
+    int64_t*  count;
+    void*     sum;                   /* double* or int64_t* according to value_type              */
+    void*     min;
+    void*     max;
+} fmq_fired_cols;
+
+/* one window alert: the fired rows that pass the alert expression, 24 B per row */
+typedef struct fmq_walert_cols {
+    uint64_t* key;
+    int64_t*  window_end;
+    double*   value;                 /* the evaluated expression, e.g. Mbps                      */
+} fmq_walert_cols;
+
+/* one event row (per-event filter output, consecutive-breach alert): 24 B per row */
+typedef struct fmq_event_cols {
+    int64_t*  ts;
+    uint64_t* key;
+    void*     val;                   /* double* or int64_t*                                      */
+} fmq_event_cols;
+
+typedef struct fmq_counters {
+    uint64_t events_in;
+    uint64_t late_dropped;           /* WindowOperator.numLateRecordsDropped                     */
+    uint64_t windows_fired;          /* fired (key, window) pairs                                */
+    uint64_t window_alerts;
+    uint64_t event_alerts;
+    uint64_t consec_alerts;
+    uint64_t keys;                   /* distinct keys in the directory                           */
+    int64_t  watermark;              /* current watermark                                        */
+    uint64_t gpu_launches;           /* kernels launched by this handle so far                   */
+} fmq_counters;
+
+typedef struct fmq_handle fmq_handle;
+
+/* Library / build identification; usable without a GPU. */
+int32_t     fmq_abi_version(void);
+const char* fmq_build_info(void);
+
+/* Replaces: operator construction + open() (OneInputStreamOperator#open) for the DSL chain at
+ * BandwidthMonitorWithEventTime.java:45-55 / ComputeCpuAvg.java:27-31 / ComputeCpuMax.java:26 /
+ * Main.java:27-32.  Allocates every device buffer the handle will ever use. */
+int32_t fmq_create(const fmq_config* cfg, fmq_handle** out);
+
+/* Replaces: a run of WindowOperator#processElement / StreamFilter#processElement /
+ * StreamGroupedReduce#processElement calls followed by one processWatermark(watermark_after)
+ * (call stack SURVEY.md §3.1).  `mem` says where ts/key/val live (host or device pointers).
+ * Asynchronous on the handle's stream; results become visible through the poll functions. */
+int32_t fmq_push_batch(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val,
+                       size_t n, int64_t watermark_after, int32_t mem);
+
+/* Replaces: processWatermark(wm) with no records (and Watermark(Long.MAX_VALUE) at end of a
+ * finite source when wm == FMQ_WM_FINAL). */
+int32_t fmq_flush(fmq_handle* h, int64_t watermark);
+
+/* Replaces: Output#collect of fired window results (WindowOperator#emitWindowContents).
+ * Copies up to `cap` rows into caller buffers (`mem` says host or device); *n_out = rows copied,
+ * *n_left = rows still buffered.  Row order is unspecified (compare as sets). */
+int32_t fmq_poll_fired(fmq_handle* h, const fmq_fired_cols* out, size_t cap, int32_t mem,
+                       size_t* n_out, size_t* n_left);
+/* Replaces: the chained map + filter after the window (BandwidthMonitorWithEventTime.java:48-55). */
+int32_t fmq_poll_window_alerts(fmq_handle* h, const fmq_walert_cols* out, size_t cap, int32_t mem,
+                               size_t* n_out, size_t* n_left);
+/* Replaces: StreamFilter output of Main.java:27-32 (rows in arrival order within a batch). */
+int32_t fmq_poll_event_alerts(fmq_handle* h, const fmq_event_cols* out, size_t cap, int32_t mem,
+                              size_t* n_out, size_t* n_left);
+/* Replaces: KeyedProcessFunction output of the consecutive-breach rule. */
+int32_t fmq_poll_consec_alerts(fmq_handle* h, const fmq_event_cols* out, size_t cap, int32_t mem,
+                               size_t* n_out, size_t* n_left);
+/* Replaces: StreamGroupedReduce output of keyBy(0).max(2) (ComputeCpuMax.java:26): the rolling
+ * per-key maximum after each record of the LAST pushed batch, in that batch's input order. */
+int32_t fmq_poll_rolling_max(fmq_handle* h, void* out, size_t cap, int32_t mem, size_t* n_out);
+
+/* Replaces: Flink metric group of the operator (numLateRecordsDropped etc.).  Synchronises. */
+int32_t fmq_get_counters(fmq_handle* h, fmq_counters* out);
+
+/* Keyed-state inspection for parity tests ("state transitions" in BASELINE.json): looks up
+ * n keys; found[i] = 0/1, consec[i] = breach counter, rolling[i] = rolling max bits. */
+int32_t fmq_get_key_state(fmq_handle* h, const uint64_t* keys, size_t n, int32_t* found,
+                          int32_t* consec, void* rolling);
+
+/* Blocks until all work queued on the handle has finished. */
+int32_t fmq_synchronize(fmq_handle* h);
+/* Device time in ms of the last fmq_push_batch / fmq_flush kernel chain (CUDA events on the
+ * handle's stream); synchronises. */
+int32_t fmq_last_device_ms(fmq_handle* h, float* ms);
+/* Raw cudaStream_t of the handle, for callers that enqueue their own device work. */
+void*   fmq_stream(fmq_handle* h);
+
+const char* fmq_last_error(fmq_handle* h);   /* h may be NULL: last create() failure */
+/* Replaces: OneInputStreamOperator#close / dispose. */
+int32_t fmq_destroy(fmq_handle* h);
+
+/* keyBy routing (A4).  fmq_owner_of: the GPU-side routing function owner = mix64(key) % world.
+ * fmq_flink_key_group / fmq_flink_subtask: Flink 1.8 KeyGroupRangeAssignment restated
+ * (murmurHash(key.hashCode()) % maxParallelism; kg * p / maxParallelism), pinned by golden G8. */
+uint32_t fmq_owner_of(uint64_t key, uint32_t world);
+int32_t  fmq_java_string_hash(const char* utf8, size_t len);
+int32_t  fmq_flink_key_group(int32_t key_hash, int32_t max_parallelism);
+int32_t  fmq_flink_subtask(int32_t key_group, int32_t parallelism, int32_t max_parallelism);
+
+/* Multi-GPU keyBy exchange, device side (A4): stable partition of a device-resident batch into
+ * `world` contiguous buckets by fmq_owner_of.  counts[world] is written to HOST memory.
+ * All pointers except counts are device pointers; runs on the handle's stream and
+ * synchronises before returning (the counts are needed to size the all-to-all). */
+int32_t fmq_partition_by_owner(fmq_handle* h, const int64_t* ts, const uint64_t* key,
+                               const void* val, size_t n, uint32_t world,
+                               int64_t* ts_out, uint64_t* key_out, void* val_out,
+                               uint64_t* counts);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FMQ_B200_H */

@@ -1,0 +1,345 @@
+"""ctypes binding of the C ABI declared in ``include/fmq_b200.h``.
+
+This is the thinnest possible layer: POD structs, symbol signatures, and an ``Engine`` class that
+turns numpy arrays / CUDA tensors into the pointers the ABI wants.  It is what a Python caller
+(and the parity tests) use; a Flink shim would bind the same symbols through JNI or Panama
+(see INTEGRATION.md).  There is no CPU fallback: if the CUDA library is missing or no device is
+usable, construction fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+
+FMQ_VAL_F64, FMQ_VAL_I64 = 0, 1
+FMQ_MEM_HOST, FMQ_MEM_DEVICE = 0, 1
+FMQ_CMP_GT, FMQ_CMP_LT, FMQ_CMP_GE, FMQ_CMP_LE = 0, 1, 2, 3
+FMQ_AGG_COUNT, FMQ_AGG_SUM, FMQ_AGG_MIN, FMQ_AGG_MAX = 1, 2, 4, 8
+FMQ_ALERT_NONE, FMQ_ALERT_SUM, FMQ_ALERT_AVG, FMQ_ALERT_MIN, FMQ_ALERT_MAX, FMQ_ALERT_COUNT = range(6)
+FMQ_WM_AUTO = -(2 ** 63)
+FMQ_WM_FINAL = 2 ** 63 - 1
+
+STATUS_NAMES = {0: "OK", 1: "BAD_ARG", 2: "TABLE_FULL", 3: "RING_OVERFLOW", 4: "OUTPUT_OVERFLOW",
+                5: "CUDA", 6: "BAD_TS", 7: "NO_DEVICE", 8: "POISONED"}
+
+
+class FmqConfig(C.Structure):
+    """Mirror of ``struct fmq_config`` (include/fmq_b200.h)."""
+    _fields_ = [
+        ("struct_size", C.c_uint32), ("device", C.c_int32), ("value_type", C.c_int32), ("reserved0", C.c_int32),
+        ("window_enabled", C.c_int32), ("agg_mask", C.c_uint32),
+        ("window_size_ms", C.c_int64), ("window_slide_ms", C.c_int64), ("window_offset_ms", C.c_int64),
+        ("max_out_of_orderness_ms", C.c_int64), ("emit_fired", C.c_int32),
+        ("walert_source", C.c_int32), ("walert_op", C.c_int32), ("reserved1", C.c_int32),
+        ("walert_mul", C.c_double), ("walert_div0", C.c_double), ("walert_div1", C.c_double),
+        ("walert_div2", C.c_double), ("walert_threshold", C.c_double),
+        ("efilter_enabled", C.c_int32), ("efilter_op", C.c_int32), ("efilter_threshold", C.c_double),
+        ("rolling_max_enabled", C.c_int32), ("consec_n", C.c_int32), ("consec_op", C.c_int32),
+        ("consec_reset_on_fire", C.c_int32), ("consec_threshold", C.c_double),
+        ("table_capacity", C.c_uint64), ("pane_ring", C.c_uint32), ("reserved2", C.c_uint32),
+        ("max_batch", C.c_uint64), ("fired_capacity", C.c_uint64), ("walert_capacity", C.c_uint64),
+        ("ealert_capacity", C.c_uint64), ("calert_capacity", C.c_uint64),
+    ]
+
+
+class FmqFiredCols(C.Structure):
+    _fields_ = [("key", C.c_void_p), ("window_end", C.c_void_p), ("count", C.c_void_p),
+                ("sum", C.c_void_p), ("min", C.c_void_p), ("max", C.c_void_p)]
+
+
+class FmqWAlertCols(C.Structure):
+    _fields_ = [("key", C.c_void_p), ("window_end", C.c_void_p), ("value", C.c_void_p)]
+
+
+class FmqEventCols(C.Structure):
+    _fields_ = [("ts", C.c_void_p), ("key", C.c_void_p), ("val", C.c_void_p)]
+
+
+class FmqCounters(C.Structure):
+    _fields_ = [("events_in", C.c_uint64), ("late_dropped", C.c_uint64), ("windows_fired", C.c_uint64),
+                ("window_alerts", C.c_uint64), ("event_alerts", C.c_uint64), ("consec_alerts", C.c_uint64),
+                ("keys", C.c_uint64), ("watermark", C.c_int64), ("gpu_launches", C.c_uint64)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+def make_config(**kw) -> FmqConfig:
+    """Zero-initialised config with ``struct_size`` set; keyword arguments override fields."""
+    cfg = FmqConfig()
+    cfg.struct_size = C.sizeof(FmqConfig)
+    cfg.emit_fired = 1
+    for k, v in kw.items():
+        if not hasattr(cfg, k):
+            raise AttributeError(f"fmq_config has no field {k!r}")
+        setattr(cfg, k, v)
+    return cfg
+
+
+class FmqError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"fmq status {status} ({STATUS_NAMES.get(status, '?')}): {msg}")
+        self.status = status
+
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libfmq_b200.so")
+_lib = None
+
+
+def library_path() -> str:
+    return _LIB_PATH
+
+
+def load_library() -> C.CDLL:
+    """Load ``libfmq_b200.so`` (built in-tree by ``__graft_entry__.build()``).  Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        raise FileNotFoundError(
+            f"{_LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "— there is no CPU fallback for the hot path")
+    lib = C.CDLL(_LIB_PATH)
+    _declare(lib, "fmq_")
+    _lib = lib
+    return lib
+
+
+def _declare(lib, p: str, has_mem: bool = True):
+    """Attach argtypes/restype for every entry point; `p` is the symbol prefix."""
+    vp, sz, i32, i64 = C.c_void_p, C.c_size_t, C.c_int32, C.c_int64
+    psz = C.POINTER(C.c_size_t)
+    mem = [i32] if has_mem else []
+
+    def sig(name, args, res=i32):
+        f = getattr(lib, p + name)
+        f.argtypes, f.restype = args, res
+    sig("create", [C.POINTER(FmqConfig), C.POINTER(vp)])
+    sig("push_batch", [vp, vp, vp, vp, sz, i64] + mem)
+    sig("flush", [vp, i64])
+    sig("poll_fired", [vp, C.POINTER(FmqFiredCols), sz] + mem + [psz, psz])
+    sig("poll_window_alerts", [vp, C.POINTER(FmqWAlertCols), sz] + mem + [psz, psz])
+    sig("poll_event_alerts", [vp, C.POINTER(FmqEventCols), sz] + mem + [psz, psz])
+    sig("poll_consec_alerts", [vp, C.POINTER(FmqEventCols), sz] + mem + [psz, psz])
+    sig("poll_rolling_max", [vp, vp, sz] + mem + [psz])
+    sig("get_counters", [vp, C.POINTER(FmqCounters)])
+    sig("get_key_state", [vp, vp, sz, vp, vp, vp])
+    sig("destroy", [vp])
+    if has_mem:   # product-only entry points
+        sig("abi_version", [])
+        sig("build_info", [], C.c_char_p)
+        sig("synchronize", [vp])
+        sig("last_device_ms", [vp, C.POINTER(C.c_float)])
+        sig("stream", [vp], vp)
+        sig("last_error", [vp], C.c_char_p)
+        sig("owner_of", [C.c_uint64, C.c_uint32], C.c_uint32)
+        sig("java_string_hash", [C.c_char_p, sz])
+        sig("flink_key_group", [i32, i32])
+        sig("flink_subtask", [i32, i32, i32])
+        sig("partition_by_owner", [vp, vp, vp, vp, sz, C.c_uint32, vp, vp, vp, vp])
+
+
+def _ptr(a) -> int:
+    """Raw address of a numpy array or torch tensor (host or device)."""
+    if a is None:
+        return 0
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()          # torch.Tensor
+
+
+def _is_device(a) -> bool:
+    return (not isinstance(a, np.ndarray)) and hasattr(a, "is_cuda") and a.is_cuda
+
+
+@dataclass
+class Fired:
+    key: np.ndarray
+    window_end: np.ndarray
+    count: np.ndarray
+    sum: np.ndarray
+    min: np.ndarray
+    max: np.ndarray
+
+    def __len__(self):
+        return len(self.key)
+
+
+@dataclass
+class WindowAlerts:
+    key: np.ndarray
+    window_end: np.ndarray
+    value: np.ndarray
+
+    def __len__(self):
+        return len(self.key)
+
+
+@dataclass
+class EventRows:
+    ts: np.ndarray
+    key: np.ndarray
+    val: np.ndarray
+
+    def __len__(self):
+        return len(self.key)
+
+
+class EngineBase:
+    """Shared driver for anything exporting the fmq-shaped ABI (the product, and — in tests only —
+    the CPU oracle, which exports the same calls under the ``orc_`` prefix without ``mem``)."""
+
+    def __init__(self, lib, prefix: str, cfg: FmqConfig, has_mem: bool):
+        self._lib, self._p, self._has_mem = lib, prefix, has_mem
+        self.cfg = cfg
+        self._vdtype = np.float64 if cfg.value_type == FMQ_VAL_F64 else np.int64
+        h = C.c_void_p()
+        st = self._f("create")(C.byref(cfg), C.byref(h))
+        if st != 0:
+            raise FmqError(st, self._err(None))
+        self._h = h
+
+    def _f(self, name):
+        return getattr(self._lib, self._p + name)
+
+    def _err(self, h) -> str:
+        if not self._has_mem:
+            return "oracle error"
+        m = self._lib.fmq_last_error(h)
+        return m.decode() if m else ""
+
+    def _check(self, st):
+        if st != 0:
+            raise FmqError(st, self._err(self._h))
+
+    # --- ingest -------------------------------------------------------------------------------
+    def push_batch(self, ts, key, val, watermark_after: int = FMQ_WM_AUTO):
+        n = len(ts)
+        assert len(key) == n and len(val) == n
+        dev = _is_device(ts)
+        if not dev:
+            ts = np.ascontiguousarray(ts, dtype=np.int64)
+            key = np.ascontiguousarray(key, dtype=np.uint64)
+            val = np.ascontiguousarray(val, dtype=self._vdtype)
+        args = [self._h, _ptr(ts), _ptr(key), _ptr(val), n, watermark_after]
+        if self._has_mem:
+            args.append(FMQ_MEM_DEVICE if dev else FMQ_MEM_HOST)
+        self._check(self._f("push_batch")(*args))
+
+    def flush(self, watermark: int = FMQ_WM_FINAL):
+        self._check(self._f("flush")(self._h, watermark))
+
+    # --- outputs ------------------------------------------------------------------------------
+    def _poll_loop(self, name, make_cols, chunk):
+        parts = []
+        while True:
+            cols, arrays = make_cols(chunk)
+            n_out, n_left = C.c_size_t(0), C.c_size_t(0)
+            args = [self._h, C.byref(cols), chunk]
+            if self._has_mem:
+                args.append(FMQ_MEM_HOST)
+            args += [C.byref(n_out), C.byref(n_left)]
+            self._check(self._f(name)(*args))
+            parts.append([a[: n_out.value] for a in arrays])
+            if n_left.value == 0:
+                break
+        return [np.concatenate([p[i] for p in parts]) for i in range(len(parts[0]))]
+
+    def poll_fired(self, chunk: int = 1 << 20) -> Fired:
+        def mk(c):
+            arrs = [np.empty(c, np.uint64), np.empty(c, np.int64), np.empty(c, np.int64),
+                    np.empty(c, self._vdtype), np.empty(c, self._vdtype), np.empty(c, self._vdtype)]
+            return FmqFiredCols(*[a.ctypes.data for a in arrs]), arrs
+        return Fired(*self._poll_loop("poll_fired", mk, chunk))
+
+    def poll_window_alerts(self, chunk: int = 1 << 20) -> WindowAlerts:
+        def mk(c):
+            arrs = [np.empty(c, np.uint64), np.empty(c, np.int64), np.empty(c, np.float64)]
+            return FmqWAlertCols(*[a.ctypes.data for a in arrs]), arrs
+        return WindowAlerts(*self._poll_loop("poll_window_alerts", mk, chunk))
+
+    def _poll_events(self, name, chunk) -> EventRows:
+        def mk(c):
+            arrs = [np.empty(c, np.int64), np.empty(c, np.uint64), np.empty(c, self._vdtype)]
+            return FmqEventCols(*[a.ctypes.data for a in arrs]), arrs
+        return EventRows(*self._poll_loop(name, mk, chunk))
+
+    def poll_event_alerts(self, chunk: int = 1 << 20) -> EventRows:
+        return self._poll_events("poll_event_alerts", chunk)
+
+    def poll_consec_alerts(self, chunk: int = 1 << 20) -> EventRows:
+        return self._poll_events("poll_consec_alerts", chunk)
+
+    def poll_rolling_max(self, n: int) -> np.ndarray:
+        out = np.empty(n, self._vdtype)
+        n_out = C.c_size_t(0)
+        args = [self._h, out.ctypes.data, n]
+        if self._has_mem:
+            args.append(FMQ_MEM_HOST)
+        args.append(C.byref(n_out))
+        self._check(self._f("poll_rolling_max")(*args))
+        return out[: n_out.value]
+
+    def counters(self) -> dict:
+        c = FmqCounters()
+        self._check(self._f("get_counters")(self._h, C.byref(c)))
+        return c.as_dict()
+
+    def key_state(self, keys):
+        keys = np.ascontiguousarray(keys, dtype=np.uint64)
+        n = len(keys)
+        found, consec, rolling = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, self._vdtype)
+        self._check(self._f("get_key_state")(self._h, keys.ctypes.data, n, found.ctypes.data,
+                                             consec.ctypes.data, rolling.ctypes.data))
+        return found, consec, rolling
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._f("destroy")(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Engine(EngineBase):
+    """One native handle of libfmq_b200 = one operator subtask on one GPU."""
+
+    def __init__(self, cfg: Optional[FmqConfig] = None, **kw):
+        lib = load_library()
+        super().__init__(lib, "fmq_", cfg if cfg is not None else make_config(**kw), has_mem=True)
+
+    def synchronize(self):
+        self._check(self._lib.fmq_synchronize(self._h))
+
+    def last_device_ms(self) -> float:
+        ms = C.c_float(0)
+        self._check(self._lib.fmq_last_device_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    @property
+    def stream(self) -> int:
+        return self._lib.fmq_stream(self._h) or 0
+
+    @property
+    def handle(self):
+        return self._h
+
+    def partition_by_owner(self, ts, key, val, world: int, ts_out, key_out, val_out) -> np.ndarray:
+        counts = np.zeros(world, np.uint64)
+        self._check(self._lib.fmq_partition_by_owner(self._h, _ptr(ts), _ptr(key), _ptr(val), len(ts), world,
+                                                     _ptr(ts_out), _ptr(key_out), _ptr(val_out), counts.ctypes.data))
+        return counts
