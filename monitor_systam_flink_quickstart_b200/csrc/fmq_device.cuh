@@ -1,0 +1,178 @@
+// Device-side building blocks shared by all kernels of libfmq_b200 (sm_100a only).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace fmq {
+
+typedef unsigned long long u64;
+typedef long long i64;
+typedef unsigned int u32;
+
+constexpr u64 KEY_EMPTY = 0xFFFFFFFFFFFFFFFFull;
+constexpr u32 SLOT_INVALID = 0xFFFFFFFFu;
+constexpr i64 I64_MIN_ = (i64)0x8000000000000000ull;
+constexpr i64 I64_MAX_ = (i64)0x7FFFFFFFFFFFFFFFull;
+
+// sticky error bits kept in DevState::err_flags
+constexpr u32 ERRB_TABLE_FULL = 1u, ERRB_RING = 2u, ERRB_OUTPUT = 4u, ERRB_BAD_INPUT = 8u;
+
+// One accumulator cell per (ring pane, key slot): 32 B = exactly one L2 sector, so the add pair
+// {cnt,sum} and the max pair {mx,mn} of one event each travel as ONE sector request when issued
+// from adjacent lanes of the same RED instruction (measured: tools/micro_atomics.cu).
+// All-zero bytes are the identity of every field.
+struct __align__(32) Acc32 {
+    u64 cnt;   // F64 jobs: count kept as a double (exact to 2^53) so cnt and sum share red.add.f64
+    u64 sum;   // double bits or int64 (wraps like Java long)
+    u64 mx;    // order-preserving encoding, see enc_max
+    u64 mn;    // complement of the encoding, so min is also a red.max.u64
+};
+
+// Per-handle device-resident scalar state.  Everything a kernel needs to know about "where the
+// stream is" lives here, so a push never needs a host round trip.
+struct DevState {
+    // event-time position
+    i64 wm;                 // current watermark (INT64_MIN before the first one)
+    i64 cur_max_ts;         // BoundedOutOfOrdernessTimestampExtractor.currentMaxTimestamp
+    i64 last_emitted_wm;    // .lastEmittedWatermark
+    i64 batch_max_ts;       // max ts of the batch being ingested (reset by plan)
+    // ingest parameters derived from wm by the plan kernel
+    i64 origin_ts;          // records with ts < origin_ts are late (all their windows have fired)
+    i64 origin_pane;        // absolute pane index whose start is origin_ts
+    int anchored;           // 0 while wm == INT64_MIN (nothing can be late)
+    int pad0;
+    i64 min_pane, max_pane; // absolute pane range currently holding data (min > max: none)
+    // fire plan for the current watermark advance
+    i64 fire_first_end;     // exclusive end of the first window to fire
+    i64 fire_count;         // number of consecutive window ends (step = slide)
+    i64 expire_lo, expire_hi; // absolute panes to clear after firing (lo > hi: none)
+    // counters
+    u64 events_in, late_dropped, windows_fired, window_alerts, event_alerts, consec_alerts, keys;
+    // output cursors (rows appended since the last full drain)
+    u64 n_fired, n_walert, n_ealert, n_calert;
+    u32 err_flags;
+    u32 pad1;
+};
+
+__host__ __device__ __forceinline__ u64 mix64(u64 x) {
+    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull; x ^= x >> 27; x *= 0x94d049bb133111ebull; x ^= x >> 31; return x;
+}
+
+// ---- order-preserving encodings -------------------------------------------------------------
+// f64: total order  -NaN.. < -inf < .. < -0.0 < +0.0 < .. < +inf ; NaN is forced to the top for
+// BOTH max and min so that it propagates like java.lang.Math.max/min.  i64: bias to unsigned.
+__device__ __forceinline__ u64 order_f64(double v) {
+    u64 b = (u64)__double_as_longlong(v);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double unorder_f64(u64 u) {
+    u64 b = (u >> 63) ? (u ^ 0x8000000000000000ull) : ~u;
+    return __longlong_as_double((i64)b);
+}
+template <typename V> struct IsF64 { static constexpr bool value = false; };
+template <> struct IsF64<double> { static constexpr bool value = true; };
+template <typename V> struct Codec;
+template <> struct Codec<double> {
+    static __device__ __forceinline__ u64 enc_max(double v) { return (v != v) ? ~0ull : order_f64(v); }
+    static __device__ __forceinline__ u64 enc_min(double v) { return (v != v) ? ~0ull : ~order_f64(v); }
+    static __device__ __forceinline__ u64 dec_max(u64 u) { return (u64)__double_as_longlong(unorder_f64(u)); }
+    static __device__ __forceinline__ u64 dec_min(u64 u) { return u == ~0ull ? 0x7FFFFFFFFFFFFFFFull : (u64)__double_as_longlong(unorder_f64(~u)); }
+    static __device__ __forceinline__ double as_double(u64 bits) { return __longlong_as_double((i64)bits); }
+    static __device__ __forceinline__ double from_bits(u64 bits) { return __longlong_as_double((i64)bits); }
+    // Double.compareTo order (NaN canonical and greatest, -0.0 < +0.0): used by rolling max
+    static __device__ __forceinline__ u64 cmp_key(double v) { return (v != v) ? ~0ull : order_f64(v); }
+};
+template <> struct Codec<i64> {
+    static __device__ __forceinline__ u64 enc_max(i64 v) { return (u64)v ^ 0x8000000000000000ull; }
+    static __device__ __forceinline__ u64 enc_min(i64 v) { return ~((u64)v ^ 0x8000000000000000ull); }
+    static __device__ __forceinline__ u64 dec_max(u64 u) { return u ^ 0x8000000000000000ull; }
+    static __device__ __forceinline__ u64 dec_min(u64 u) { return (~u) ^ 0x8000000000000000ull; }
+    static __device__ __forceinline__ double as_double(u64 bits) { return (double)(i64)bits; }
+    static __device__ __forceinline__ i64 from_bits(u64 bits) { return (i64)bits; }
+    static __device__ __forceinline__ u64 cmp_key(i64 v) { return (u64)v ^ 0x8000000000000000ull; }
+};
+
+__device__ __forceinline__ bool cmp_op(double v, int op, double thr) {
+    switch (op) { case 0: return v > thr; case 1: return v < thr; case 2: return v >= thr; default: return v <= thr; }
+}
+
+// ---- streaming loads: the event columns are read exactly once ---------------------------------
+// sm_100 has 256-bit global loads; only they accept the direct .L2::evict_first qualifier, which
+// keeps the one-pass event stream from pushing the L2-resident accumulator table out.
+__device__ __forceinline__ ulonglong4 ldg_stream_v4(const void* p) {
+    ulonglong4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.b64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ u64 ldg_stream(const void* p) {
+    u64 r;
+    asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(r) : "l"(p));
+    return r;
+}
+
+// ---- key directory: open addressing, linear probing, keys are never removed ---------------------
+// `cap` is any size >= 32 (not a power of two on purpose: 1.5x the key count keeps one pane of
+// accumulators at 48 MB for 1 M keys, well inside the 126 MB L2).  home = mulhi(hash, cap).
+// Returns the slot of `key`, inserting it if absent.  Stale L1 data cannot mislead the probe: a
+// slot only ever changes EMPTY -> key, and the CAS that claims it is resolved in L2.
+__device__ __forceinline__ u32 dir_find_or_insert(u64* __restrict__ dkeys, u64 cap, u64 key, DevState* st) {
+    u64 h = __umul64hi(mix64(key), cap);
+    for (u64 probe = 0; probe < cap; ++probe) {
+        u64 k = __ldcg(dkeys + h);
+        if (k == key) return (u32)h;
+        if (k == KEY_EMPTY) {
+            u64 old = atomicCAS(dkeys + h, KEY_EMPTY, key);
+            if (old == KEY_EMPTY) { atomicAdd(&st->keys, 1ull); return (u32)h; }
+            if (old == key) return (u32)h;
+        }
+        h = (h + 1 == cap) ? 0 : h + 1;
+    }
+    atomicOr(&st->err_flags, ERRB_TABLE_FULL);
+    return SLOT_INVALID;
+}
+__device__ __forceinline__ u32 dir_find(const u64* __restrict__ dkeys, u64 cap, u64 key) {
+    u64 h = __umul64hi(mix64(key), cap);
+    for (u64 probe = 0; probe < cap; ++probe) {
+        u64 k = __ldcg(dkeys + h);
+        if (k == key) return (u32)h;
+        if (k == KEY_EMPTY) return SLOT_INVALID;
+        h = (h + 1 == cap) ? 0 : h + 1;
+    }
+    return SLOT_INVALID;
+}
+
+// ---- warp-aggregated append: one atomic per warp, rows of a warp land contiguously --------------
+// Must be called by all 32 lanes.  Returns the row index for lanes with pred, or ~0 when the
+// buffer is full (and raises the sticky overflow flag).
+__device__ __forceinline__ u64 warp_append(bool pred, u64* counter, u64 cap, DevState* st) {
+    unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0) return ~0ull;
+    unsigned lane = threadIdx.x & 31;
+    int leader = __ffs(m) - 1;
+    u64 base = 0;
+    if ((int)lane == leader) base = atomicAdd(counter, (u64)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (!pred) return ~0ull;
+    u64 row = base + __popc(m & ((1u << lane) - 1));
+    if (row >= cap) { atomicOr(&st->err_flags, ERRB_OUTPUT); return ~0ull; }
+    return row;
+}
+
+__device__ __forceinline__ i64 warp_max_i64(i64 v) {
+    for (int o = 16; o > 0; o >>= 1) { i64 t = __shfl_xor_sync(0xffffffffu, v, o); v = t > v ? t : v; }
+    return v;
+}
+__device__ __forceinline__ i64 warp_min_i64(i64 v) {
+    for (int o = 16; o > 0; o >>= 1) { i64 t = __shfl_xor_sync(0xffffffffu, v, o); v = t < v ? t : v; }
+    return v;
+}
+__device__ __forceinline__ u64 warp_sum_u64(u64 v) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// floor division for possibly negative numerators, positive divisor
+__host__ __device__ __forceinline__ i64 floor_div(i64 a, i64 b) { i64 q = a / b; return (a % b != 0 && a < 0) ? q - 1 : q; }
+
+}  // namespace fmq

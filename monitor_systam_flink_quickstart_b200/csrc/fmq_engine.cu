@@ -1,0 +1,467 @@
+// libfmq_b200: host side of the C ABI declared in include/fmq_b200.h.
+// One handle = one operator subtask = one CUDA stream + all device state.  No CPU fallback:
+// without a usable device fmq_create fails with FMQ_ERR_NO_DEVICE.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <new>
+#include "../../include/fmq_b200.h"
+#include "fmq_device.cuh"
+#include "fmq_window.cuh"
+#include "fmq_sort.cuh"
+#include "fmq_keyed.cuh"
+
+using namespace fmq;
+
+#define FMQ_STR2(x) #x
+#define FMQ_STR(x) FMQ_STR2(x)
+
+static thread_local std::string g_create_err;
+
+struct fmq_handle {
+    fmq_config cfg;
+    int device = 0, num_sms = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_copy = nullptr;
+    std::string err;
+    int sticky = 0;                      // sticky fmq_status once the device state is invalid
+    // geometry
+    WindowGeom g{};
+    u64 capacity = 0; u32 ring = 0; u32 slot_bits = 0;
+    size_t max_batch = 0;
+    // device state
+    DevState* d_st = nullptr; DevState* h_st = nullptr;   // h_st: pinned mirror
+    u64* d_keys = nullptr; Acc32* d_acc = nullptr; u32* d_kflags = nullptr; u64* d_kmax = nullptr;
+    // staging for host-resident inputs
+    i64* d_in_ts = nullptr; u64* d_in_key = nullptr; u64* d_in_val = nullptr;
+    // outputs
+    u64 *f_key = nullptr, *f_sum = nullptr, *f_min = nullptr, *f_max = nullptr; i64 *f_wend = nullptr, *f_count = nullptr; u64 f_cap = 0;
+    u64* wa_key = nullptr; i64* wa_wend = nullptr; double* wa_val = nullptr; u64 wa_cap = 0;
+    i64* ea_ts = nullptr; u64 *ea_key = nullptr, *ea_val = nullptr; u64 ea_cap = 0;
+    i64* ca_ts = nullptr; u64 *ca_key = nullptr, *ca_val = nullptr; u64 ca_cap = 0;
+    u64* d_rolling = nullptr; size_t rolling_n = 0;
+    size_t cur_fired = 0, cur_walert = 0, cur_ealert = 0, cur_calert = 0;   // host read cursors
+    // keyed-path / partition scratch
+    u32 *d_slot[2] = {nullptr, nullptr}, *d_idx[2] = {nullptr, nullptr};
+    u32* d_counts = nullptr; u32* d_tiles = nullptr; size_t counts_len = 0, tiles_len = 0;
+    uint64_t launches = 0;
+};
+
+#define CU(h, call)                                                                                   \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess) {                                                                      \
+            (h)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                            \
+            return FMQ_ERR_CUDA;                                                                      \
+        }                                                                                             \
+    } while (0)
+
+static int set_err(fmq_handle* h, int st, const char* msg) { if (h) h->err = msg; else g_create_err = msg; return st; }
+
+template <typename T> static cudaError_t dalloc(T** p, size_t count) { return cudaMalloc((void**)p, count * sizeof(T)); }
+
+static bool keyed_enabled(const fmq_config& c) { return c.rolling_max_enabled || c.consec_n > 0; }
+
+extern "C" {
+
+int32_t fmq_abi_version(void) { return FMQ_ABI_VERSION; }
+const char* fmq_build_info(void) { return "libfmq_b200 sm_100a (CUDA " FMQ_STR(CUDART_VERSION) ") hashed key directory + pane ring, no CPU fallback"; }
+
+const char* fmq_last_error(fmq_handle* h) { return h ? h->err.c_str() : g_create_err.c_str(); }
+
+static void free_all(fmq_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    void* ptrs[] = {h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
+                    h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
+                    h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
+                    h->d_slot[0], h->d_slot[1], h->d_idx[0], h->d_idx[1], h->d_counts, h->d_tiles};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    if (h->h_st) cudaFreeHost(h->h_st);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->ev_copy) cudaEventDestroy(h->ev_copy);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
+    if (!cfg || !out) return set_err(nullptr, FMQ_ERR_BAD_ARG, "null argument");
+    *out = nullptr;
+    if (cfg->struct_size != sizeof(fmq_config)) return set_err(nullptr, FMQ_ERR_BAD_ARG, "fmq_config.struct_size mismatch");
+    if (cfg->value_type != FMQ_VAL_F64 && cfg->value_type != FMQ_VAL_I64) return set_err(nullptr, FMQ_ERR_BAD_ARG, "bad value_type");
+    if (cfg->window_enabled) {
+        if (cfg->window_size_ms <= 0 || cfg->window_slide_ms <= 0) return set_err(nullptr, FMQ_ERR_BAD_ARG, "window size/slide must be positive");
+        if (cfg->window_size_ms % cfg->window_slide_ms != 0) return set_err(nullptr, FMQ_ERR_BAD_ARG, "window_size_ms must be a multiple of window_slide_ms (pane pre-aggregation)");
+        if (cfg->window_offset_ms < 0 || cfg->window_offset_ms >= cfg->window_slide_ms) return set_err(nullptr, FMQ_ERR_BAD_ARG, "need 0 <= window_offset_ms < window_slide_ms");
+        if (cfg->max_out_of_orderness_ms < 0) return set_err(nullptr, FMQ_ERR_BAD_ARG, "max_out_of_orderness_ms cannot be negative");   // chapter3/README.md:356-359
+    }
+    if (cfg->consec_n < 0) return set_err(nullptr, FMQ_ERR_BAD_ARG, "consec_n cannot be negative");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return set_err(nullptr, FMQ_ERR_NO_DEVICE, "no CUDA device visible (this library has no CPU fallback)"); }
+    if (cfg->device < 0 || cfg->device >= ndev) return set_err(nullptr, FMQ_ERR_NO_DEVICE, "device ordinal out of range");
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, cfg->device) != cudaSuccess) return set_err(nullptr, FMQ_ERR_CUDA, "cudaGetDeviceProperties failed");
+    if (prop.major < 10) return set_err(nullptr, FMQ_ERR_NO_DEVICE, "kernels are built for sm_100a only");
+
+    fmq_handle* h = new (std::nothrow) fmq_handle();
+    if (!h) return set_err(nullptr, FMQ_ERR_BAD_ARG, "out of host memory");
+    h->cfg = *cfg; h->device = cfg->device; h->num_sms = prop.multiProcessorCount;
+    auto fail = [&](int st, const std::string& m) { g_create_err = m; free_all(h); return st; };
+#define CUC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(FMQ_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+    CUC(cudaSetDevice(h->device));
+    CUC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CUC(cudaEventCreate(&h->ev0)); CUC(cudaEventCreate(&h->ev1)); CUC(cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming));
+
+    h->capacity = cfg->table_capacity ? cfg->table_capacity : (1u << 20);
+    if (h->capacity < 32) h->capacity = 32;
+    if (h->capacity >= 0xFFFFFFF0ull) return fail(FMQ_ERR_BAD_ARG, "table_capacity must be < 2^32");
+    u32 ring = cfg->pane_ring ? cfg->pane_ring : 8; u32 r2 = 1; while (r2 < ring) r2 <<= 1; h->ring = r2;
+    h->slot_bits = 1; while ((1ull << h->slot_bits) < h->capacity) h->slot_bits++;
+    h->max_batch = cfg->max_batch ? (size_t)cfg->max_batch : ((size_t)1 << 22);
+    if (h->max_batch >= 0xFFFFFFF0ull) return fail(FMQ_ERR_BAD_ARG, "max_batch must be < 2^32");
+    h->g.size = cfg->window_size_ms; h->g.slide = cfg->window_slide_ms; h->g.off = cfg->window_offset_ms;
+    h->g.ring_mask = h->ring - 1; h->g.agg_mask = cfg->agg_mask | FMQ_AGG_COUNT; h->g.capacity = h->capacity;
+    h->g.slide32 = (cfg->window_slide_ms > 0 && cfg->window_slide_ms < 0x100000000ll) ? (u32)cfg->window_slide_ms : 0;
+    h->g.panes_per_window = cfg->window_enabled ? (u32)(cfg->window_size_ms / cfg->window_slide_ms) : 0;
+    if (cfg->window_enabled && h->g.panes_per_window >= h->ring) return fail(FMQ_ERR_BAD_ARG, "pane_ring must exceed window_size_ms / window_slide_ms");
+
+    CUC(dalloc(&h->d_st, 1)); CUC(cudaMallocHost((void**)&h->h_st, sizeof(DevState)));
+    DevState init; memset(&init, 0, sizeof(init));
+    init.wm = I64_MIN_; init.cur_max_ts = I64_MIN_ + cfg->max_out_of_orderness_ms; init.last_emitted_wm = I64_MIN_; init.batch_max_ts = I64_MIN_;
+    init.min_pane = I64_MAX_; init.max_pane = I64_MIN_; init.expire_lo = 1; init.expire_hi = 0;
+    CUC(cudaMemcpy(h->d_st, &init, sizeof(init), cudaMemcpyHostToDevice));
+    CUC(dalloc(&h->d_keys, h->capacity)); CUC(cudaMemset(h->d_keys, 0xFF, h->capacity * 8));
+    if (cfg->window_enabled) { CUC(dalloc(&h->d_acc, (size_t)h->ring * h->capacity)); CUC(cudaMemset(h->d_acc, 0, (size_t)h->ring * h->capacity * sizeof(Acc32))); }
+    CUC(dalloc(&h->d_in_ts, h->max_batch)); CUC(dalloc(&h->d_in_key, h->max_batch)); CUC(dalloc(&h->d_in_val, h->max_batch));
+    if (cfg->window_enabled && cfg->emit_fired) {
+        h->f_cap = cfg->fired_capacity ? cfg->fired_capacity : (2 * h->capacity > (1u << 20) ? 2 * h->capacity : (1u << 20));
+        CUC(dalloc(&h->f_key, h->f_cap)); CUC(dalloc(&h->f_wend, h->f_cap)); CUC(dalloc(&h->f_count, h->f_cap));
+        CUC(dalloc(&h->f_sum, h->f_cap)); CUC(dalloc(&h->f_min, h->f_cap)); CUC(dalloc(&h->f_max, h->f_cap));
+    }
+    if (cfg->window_enabled && cfg->walert_source != FMQ_ALERT_NONE) {
+        h->wa_cap = cfg->walert_capacity ? cfg->walert_capacity : (2 * h->capacity > (1u << 20) ? 2 * h->capacity : (1u << 20));
+        CUC(dalloc(&h->wa_key, h->wa_cap)); CUC(dalloc(&h->wa_wend, h->wa_cap)); CUC(dalloc(&h->wa_val, h->wa_cap));
+    }
+    if (cfg->efilter_enabled) {
+        h->ea_cap = cfg->ealert_capacity ? cfg->ealert_capacity : h->max_batch;
+        CUC(dalloc(&h->ea_ts, h->ea_cap)); CUC(dalloc(&h->ea_key, h->ea_cap)); CUC(dalloc(&h->ea_val, h->ea_cap));
+    }
+    if (keyed_enabled(*cfg)) {
+        CUC(dalloc(&h->d_kflags, h->capacity)); CUC(cudaMemset(h->d_kflags, 0, h->capacity * 4));
+        CUC(dalloc(&h->d_kmax, h->capacity)); CUC(cudaMemset(h->d_kmax, 0, h->capacity * 8));
+        for (int k = 0; k < 2; ++k) { CUC(dalloc(&h->d_slot[k], h->max_batch)); CUC(dalloc(&h->d_idx[k], h->max_batch)); }
+        if (cfg->rolling_max_enabled) CUC(dalloc(&h->d_rolling, h->max_batch));
+        if (cfg->consec_n > 0) {
+            h->ca_cap = cfg->calert_capacity ? cfg->calert_capacity : h->max_batch;
+            CUC(dalloc(&h->ca_ts, h->ca_cap)); CUC(dalloc(&h->ca_key, h->ca_cap)); CUC(dalloc(&h->ca_val, h->ca_cap));
+        }
+    }
+    // radix counter matrix (keyed path and owner partition)
+    h->counts_len = (size_t)RS_DIGITS * rs_num_chunks(h->max_batch);
+    h->tiles_len = (h->counts_len + SCAN_TILE - 1) / SCAN_TILE;
+    CUC(dalloc(&h->d_counts, h->counts_len)); CUC(dalloc(&h->d_tiles, h->tiles_len));
+    CUC(cudaDeviceSynchronize());
+#undef CUC
+    *out = h;
+    return FMQ_OK;
+}
+
+int32_t fmq_destroy(fmq_handle* h) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    free_all(h);
+    return FMQ_OK;
+}
+
+}  // extern "C"
+
+// ---- internal helpers ----------------------------------------------------------------------------
+static int launch_check(fmq_handle* h, const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { h->err = std::string(what) + ": " + cudaGetErrorString(e); return FMQ_ERR_CUDA; }
+    h->launches++;
+    return FMQ_OK;
+}
+#define LAUNCHED(h, what) do { int s_ = launch_check(h, what); if (s_) return s_; } while (0)
+
+static int exclusive_scan_counts(fmq_handle* h, size_t len) {
+    const u32 ntiles = (u32)((len + SCAN_TILE - 1) / SCAN_TILE);
+    scan_tile_sums<<<ntiles, SCAN_THREADS, 0, h->stream>>>(h->d_counts, len, h->d_tiles); LAUNCHED(h, "scan_tile_sums");
+    scan_tile_offsets<<<1, SCAN_THREADS, 0, h->stream>>>(h->d_tiles, ntiles); LAUNCHED(h, "scan_tile_offsets");
+    scan_apply<<<ntiles, SCAN_THREADS, 0, h->stream>>>(h->d_counts, len, h->d_tiles); LAUNCHED(h, "scan_apply");
+    return FMQ_OK;
+}
+
+template <typename DigitFn, typename Emit>
+static int multisplit(fmq_handle* h, size_t n, DigitFn digit, Emit emit) {
+    const u32 nchunks = rs_num_chunks(n);
+    const u32 nblocks = (nchunks + RS_WARPS - 1) / RS_WARPS;
+    rs_hist_kernel<<<nblocks, RS_THREADS, 0, h->stream>>>(n, nchunks, digit, h->d_counts); LAUNCHED(h, "rs_hist_kernel");
+    int s = exclusive_scan_counts(h, (size_t)RS_DIGITS * nchunks); if (s) return s;
+    rs_scatter_kernel<<<nblocks, RS_THREADS, 0, h->stream>>>(n, nchunks, digit, emit, h->d_counts); LAUNCHED(h, "rs_scatter_kernel");
+    return FMQ_OK;
+}
+
+static int status_from_flags(fmq_handle* h, u32 flags) {
+    if (!flags) return FMQ_OK;
+    int st; const char* m;
+    if (flags & ERRB_TABLE_FULL) { st = FMQ_ERR_TABLE_FULL; m = "key directory full: raise fmq_config.table_capacity"; }
+    else if (flags & ERRB_RING) { st = FMQ_ERR_RING_OVERFLOW; m = "open event-time span exceeds pane_ring panes: raise fmq_config.pane_ring or push smaller batches"; }
+    else if (flags & ERRB_OUTPUT) { st = FMQ_ERR_OUTPUT_OVERFLOW; m = "an output buffer overflowed before it was polled: poll more often or raise its capacity"; }
+    else { st = FMQ_ERR_BAD_TS; m = "negative timestamp or reserved key (0xFFFFFFFFFFFFFFFF) in input"; }
+    h->err = m; h->sticky = st;
+    return st;
+}
+
+// synchronise the stream and refresh the pinned mirror of DevState
+static int sync_state(fmq_handle* h) {
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaMemcpyAsync(h->h_st, h->d_st, sizeof(DevState), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return status_from_flags(h, h->h_st->err_flags);
+}
+
+template <typename V>
+static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n, int64_t wm_after) {
+    const fmq_config& c = h->cfg;
+    if (n > 0 && (c.window_enabled || c.efilter_enabled)) {
+        IngestArgs a{};
+        a.ts = ts; a.key = key; a.val = val; a.n = n; a.st = h->d_st; a.dkeys = h->d_keys; a.acc = h->d_acc; a.g = h->g;
+        a.window_enabled = c.window_enabled; a.vec32 = ((((uintptr_t)ts | (uintptr_t)key | (uintptr_t)val) & 31) == 0);
+        a.efilter_enabled = c.efilter_enabled; a.efilter_op = c.efilter_op; a.efilter_thr = c.efilter_threshold;
+        a.ea_ts = h->ea_ts; a.ea_key = h->ea_key; a.ea_val = h->ea_val; a.ea_cap = h->ea_cap;
+        const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
+        size_t blocks = (n + tile - 1) / tile; const size_t maxb = (size_t)h->num_sms * 8;
+        if (blocks > maxb) blocks = maxb;
+        ingest_kernel<V><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a); LAUNCHED(h, "ingest_kernel");
+    }
+    if (n > 0 && keyed_enabled(c)) {
+        const unsigned gb = (unsigned)((n + 255) / 256 < (size_t)h->num_sms * 8 ? (n + 255) / 256 : (size_t)h->num_sms * 8);
+        resolve_slots_kernel<<<gb, 256, 0, h->stream>>>(key, n, h->d_keys, h->capacity, h->d_st, h->d_slot[0], h->d_idx[0]); LAUNCHED(h, "resolve_slots_kernel");
+        int cur = 0;
+        for (u32 shift = 0; shift < h->slot_bits; shift += 8) {
+            SlotDigit dg{h->d_slot[cur], shift};
+            MovePair mv{h->d_slot[cur], h->d_idx[cur], h->d_slot[cur ^ 1], h->d_idx[cur ^ 1]};
+            int s = multisplit(h, n, dg, mv); if (s) return s;
+            cur ^= 1;
+        }
+        KeyedArgs k{};
+        k.slot_sorted = h->d_slot[cur]; k.idx_sorted = h->d_idx[cur]; k.n = n; k.ts = ts; k.key = key; k.val = val; k.st = h->d_st;
+        k.kflags = h->d_kflags; k.kmax = h->d_kmax; k.rolling_enabled = c.rolling_max_enabled; k.rolling_out = h->d_rolling;
+        k.consec_n = c.consec_n; k.consec_op = c.consec_op; k.consec_reset = c.consec_reset_on_fire; k.consec_thr = c.consec_threshold;
+        k.ca_ts = h->ca_ts; k.ca_key = h->ca_key; k.ca_val = h->ca_val; k.ca_cap = h->ca_cap;
+        keyed_apply_kernel<V><<<gb, 256, 0, h->stream>>>(k); LAUNCHED(h, "keyed_apply_kernel");
+        h->rolling_n = c.rolling_max_enabled ? n : 0;
+    } else if (keyed_enabled(c)) {
+        h->rolling_n = 0;
+    }
+    PlanArgs p{h->d_st, h->g, c.max_out_of_orderness_ms, wm_after, (u64)n, c.window_enabled, wm_after == FMQ_WM_AUTO};
+    plan_kernel<<<1, 32, 0, h->stream>>>(p); LAUNCHED(h, "plan_kernel");
+    if (c.window_enabled) {
+        FireArgs f{};
+        f.st = h->d_st; f.dkeys = h->d_keys; f.acc = h->d_acc; f.g = h->g; f.emit_fired = c.emit_fired;
+        f.walert_source = c.walert_source; f.walert_op = c.walert_op;
+        f.mul = c.walert_mul == 0.0 ? 1.0 : c.walert_mul; f.d0 = c.walert_div0 == 0.0 ? 1.0 : c.walert_div0;
+        f.d1 = c.walert_div1 == 0.0 ? 1.0 : c.walert_div1; f.d2 = c.walert_div2 == 0.0 ? 1.0 : c.walert_div2; f.thr = c.walert_threshold;
+        f.f_key = h->f_key; f.f_wend = h->f_wend; f.f_count = h->f_count; f.f_sum = h->f_sum; f.f_min = h->f_min; f.f_max = h->f_max; f.f_cap = h->f_cap;
+        f.wa_key = h->wa_key; f.wa_wend = h->wa_wend; f.wa_val = h->wa_val; f.wa_cap = h->wa_cap;
+        size_t blocks = (h->capacity + FIRE_THREADS - 1) / FIRE_THREADS; const size_t maxb = (size_t)h->num_sms * 8;
+        if (blocks > maxb) blocks = maxb;
+        fire_kernel<V><<<(unsigned)blocks, FIRE_THREADS, 0, h->stream>>>(f); LAUNCHED(h, "fire_kernel");
+        commit_kernel<<<1, 32, 0, h->stream>>>(h->d_st); LAUNCHED(h, "commit_kernel");
+    }
+    return FMQ_OK;
+}
+
+extern "C" {
+
+int32_t fmq_push_batch(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val, size_t n, int64_t wm_after, int32_t mem) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (n > 0 && (!ts || !key || !val)) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
+    if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
+    if (mem != FMQ_MEM_HOST && mem != FMQ_MEM_DEVICE) return set_err(h, FMQ_ERR_BAD_ARG, "bad mem");
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaEventRecord(h->ev0, h->stream));
+    const i64* dts = (const i64*)ts; const u64* dkey = (const u64*)key; const void* dval = val;
+    if (mem == FMQ_MEM_HOST && n > 0) {
+        CU(h, cudaMemcpyAsync(h->d_in_ts, ts, n * 8, cudaMemcpyHostToDevice, h->stream));
+        CU(h, cudaMemcpyAsync(h->d_in_key, key, n * 8, cudaMemcpyHostToDevice, h->stream));
+        CU(h, cudaMemcpyAsync(h->d_in_val, val, n * 8, cudaMemcpyHostToDevice, h->stream));
+        CU(h, cudaEventRecord(h->ev_copy, h->stream));
+        dts = h->d_in_ts; dkey = h->d_in_key; dval = h->d_in_val;
+    } else if (n > 0 && (((uintptr_t)ts | (uintptr_t)key | (uintptr_t)val) & 7)) {
+        return set_err(h, FMQ_ERR_BAD_ARG, "device columns must be 8-byte aligned (32-byte alignment enables 256-bit loads)");
+    }
+    int s = (h->cfg.value_type == FMQ_VAL_F64) ? run_chain<double>(h, dts, dkey, dval, n, wm_after)
+                                               : run_chain<i64>(h, dts, dkey, dval, n, wm_after);
+    if (s) return s;
+    CU(h, cudaEventRecord(h->ev1, h->stream));
+    // the caller owns host columns only for the duration of this call: wait for the H2D copies
+    if (mem == FMQ_MEM_HOST && n > 0) CU(h, cudaEventSynchronize(h->ev_copy));
+    return FMQ_OK;
+}
+
+int32_t fmq_flush(fmq_handle* h, int64_t watermark) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (watermark == FMQ_WM_AUTO) return set_err(h, FMQ_ERR_BAD_ARG, "flush needs an explicit watermark");
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaEventRecord(h->ev0, h->stream));
+    int s = (h->cfg.value_type == FMQ_VAL_F64) ? run_chain<double>(h, nullptr, nullptr, nullptr, 0, watermark)
+                                               : run_chain<i64>(h, nullptr, nullptr, nullptr, 0, watermark);
+    if (s) return s;
+    CU(h, cudaEventRecord(h->ev1, h->stream));
+    return FMQ_OK;
+}
+
+// copies rows [cur, cur+take) of `ncols` 8-byte columns to the caller; resets the device cursor
+// when everything has been drained
+static int drain_cols(fmq_handle* h, void* const* dcols, void* const* ocols, int ncols, u64 DevState::*counter, size_t* cursor,
+                      size_t cap, int32_t mem, size_t* n_out, size_t* n_left) {
+    if (!n_out) return set_err(h, FMQ_ERR_BAD_ARG, "n_out is null");
+    if (h->sticky) return FMQ_ERR_POISONED;
+    int s = sync_state(h); if (s) return s;
+    const size_t total = (size_t)(h->h_st->*counter);
+    const size_t avail = total > *cursor ? total - *cursor : 0;
+    const size_t take = avail < cap ? avail : cap;
+    const cudaMemcpyKind kind = mem == FMQ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    if (take > 0) {
+        for (int c = 0; c < ncols; ++c) {
+            if (!ocols[c] || !dcols[c]) continue;
+            CU(h, cudaMemcpyAsync(ocols[c], (const char*)dcols[c] + *cursor * 8, take * 8, kind, h->stream));
+        }
+    }
+    *cursor += take;
+    if (n_left) *n_left = avail - take;
+    if (avail - take == 0 && total > 0) {
+        const size_t off = (size_t)((char*)&(h->d_st->*counter) - (char*)h->d_st);
+        CU(h, cudaMemsetAsync((char*)h->d_st + off, 0, 8, h->stream));
+        *cursor = 0;
+    }
+    CU(h, cudaStreamSynchronize(h->stream));
+    *n_out = take;
+    return FMQ_OK;
+}
+
+int32_t fmq_poll_fired(fmq_handle* h, const fmq_fired_cols* o, size_t cap, int32_t mem, size_t* n_out, size_t* n_left) {
+    if (!h || !o) return FMQ_ERR_BAD_ARG;
+    void* d[6] = {h->f_key, h->f_wend, h->f_count, h->f_sum, h->f_min, h->f_max};
+    void* c[6] = {o->key, o->window_end, o->count, o->sum, o->min, o->max};
+    return drain_cols(h, d, c, 6, &DevState::n_fired, &h->cur_fired, cap, mem, n_out, n_left);
+}
+int32_t fmq_poll_window_alerts(fmq_handle* h, const fmq_walert_cols* o, size_t cap, int32_t mem, size_t* n_out, size_t* n_left) {
+    if (!h || !o) return FMQ_ERR_BAD_ARG;
+    void* d[3] = {h->wa_key, h->wa_wend, h->wa_val};
+    void* c[3] = {o->key, o->window_end, o->value};
+    return drain_cols(h, d, c, 3, &DevState::n_walert, &h->cur_walert, cap, mem, n_out, n_left);
+}
+int32_t fmq_poll_event_alerts(fmq_handle* h, const fmq_event_cols* o, size_t cap, int32_t mem, size_t* n_out, size_t* n_left) {
+    if (!h || !o) return FMQ_ERR_BAD_ARG;
+    void* d[3] = {h->ea_ts, h->ea_key, h->ea_val};
+    void* c[3] = {o->ts, o->key, o->val};
+    return drain_cols(h, d, c, 3, &DevState::n_ealert, &h->cur_ealert, cap, mem, n_out, n_left);
+}
+int32_t fmq_poll_consec_alerts(fmq_handle* h, const fmq_event_cols* o, size_t cap, int32_t mem, size_t* n_out, size_t* n_left) {
+    if (!h || !o) return FMQ_ERR_BAD_ARG;
+    void* d[3] = {h->ca_ts, h->ca_key, h->ca_val};
+    void* c[3] = {o->ts, o->key, o->val};
+    return drain_cols(h, d, c, 3, &DevState::n_calert, &h->cur_calert, cap, mem, n_out, n_left);
+}
+int32_t fmq_poll_rolling_max(fmq_handle* h, void* out, size_t cap, int32_t mem, size_t* n_out) {
+    if (!h || !n_out) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    int s = sync_state(h); if (s) return s;
+    const size_t take = h->rolling_n < cap ? h->rolling_n : cap;
+    if (take > 0) {
+        if (!out) return set_err(h, FMQ_ERR_BAD_ARG, "out is null");
+        CU(h, cudaMemcpyAsync(out, h->d_rolling, take * 8, mem == FMQ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+    }
+    *n_out = take;
+    return FMQ_OK;
+}
+
+int32_t fmq_get_counters(fmq_handle* h, fmq_counters* out) {
+    if (!h || !out) return FMQ_ERR_BAD_ARG;
+    int s = sync_state(h);
+    const DevState& d = *h->h_st;
+    out->events_in = d.events_in; out->late_dropped = d.late_dropped; out->windows_fired = d.windows_fired;
+    out->window_alerts = d.window_alerts; out->event_alerts = d.event_alerts; out->consec_alerts = d.consec_alerts;
+    out->keys = d.keys; out->watermark = d.wm; out->gpu_launches = h->launches;
+    return s;
+}
+
+int32_t fmq_get_key_state(fmq_handle* h, const uint64_t* keys, size_t n, int32_t* found, int32_t* consec, void* rolling) {
+    if (!h || (n && (!keys || !found || !consec || !rolling))) return FMQ_ERR_BAD_ARG;
+    if (!keyed_enabled(h->cfg)) return set_err(h, FMQ_ERR_BAD_ARG, "no keyed state operator is enabled");
+    if (n == 0) return FMQ_OK;
+    CU(h, cudaSetDevice(h->device));
+    u64* dk = nullptr; int *df = nullptr, *dc = nullptr; u64* dr = nullptr;
+    CU(h, dalloc(&dk, n)); CU(h, dalloc(&df, n)); CU(h, dalloc(&dc, n)); CU(h, dalloc(&dr, n));
+    CU(h, cudaMemcpyAsync(dk, keys, n * 8, cudaMemcpyHostToDevice, h->stream));
+    key_state_lookup_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(dk, n, h->d_keys, h->capacity, h->d_kflags, h->d_kmax, df, dc, dr);
+    LAUNCHED(h, "key_state_lookup_kernel");
+    CU(h, cudaMemcpyAsync(found, df, n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaMemcpyAsync(consec, dc, n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaMemcpyAsync(rolling, dr, n * 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    cudaFree(dk); cudaFree(df); cudaFree(dc); cudaFree(dr);
+    return FMQ_OK;
+}
+
+int32_t fmq_synchronize(fmq_handle* h) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return FMQ_OK;
+}
+int32_t fmq_last_device_ms(fmq_handle* h, float* ms) {
+    if (!h || !ms) return FMQ_ERR_BAD_ARG;
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaEventSynchronize(h->ev1));
+    CU(h, cudaEventElapsedTime(ms, h->ev0, h->ev1));
+    return FMQ_OK;
+}
+void* fmq_stream(fmq_handle* h) { return h ? (void*)h->stream : nullptr; }
+
+// ---- keyBy routing ---------------------------------------------------------------------------------
+uint32_t fmq_owner_of(uint64_t key, uint32_t world) { return world ? (uint32_t)(mix64(key) % world) : 0; }
+int32_t fmq_java_string_hash(const char* s, size_t len) {
+    uint32_t hsh = 0; for (size_t i = 0; i < len; i++) hsh = 31u * hsh + (uint8_t)s[i]; return (int32_t)hsh;   // ASCII keys
+}
+static int32_t flink_murmur(int32_t in) {                      // org.apache.flink.util.MathUtils#murmurHash
+    uint32_t c = (uint32_t)in;
+    c *= 0xcc9e2d51u; c = (c << 15) | (c >> 17); c *= 0x1b873593u;
+    c = (c << 13) | (c >> 19); c = c * 5u + 0xe6546b64u;
+    c ^= 4u; c ^= c >> 16; c *= 0x85ebca6bu; c ^= c >> 13; c *= 0xc2b2ae35u; c ^= c >> 16;
+    int32_t s = (int32_t)c;
+    return s >= 0 ? s : (s != INT32_MIN ? -s : 0);
+}
+int32_t fmq_flink_key_group(int32_t key_hash, int32_t max_parallelism) { return max_parallelism > 0 ? flink_murmur(key_hash) % max_parallelism : 0; }
+int32_t fmq_flink_subtask(int32_t key_group, int32_t parallelism, int32_t max_parallelism) { return max_parallelism > 0 ? key_group * parallelism / max_parallelism : 0; }
+
+int32_t fmq_partition_by_owner(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val, size_t n, uint32_t world,
+                               int64_t* ts_out, uint64_t* key_out, void* val_out, uint64_t* counts) {
+    if (!h || !counts || world == 0 || world > RS_DIGITS) return h ? set_err(h, FMQ_ERR_BAD_ARG, "need 1 <= world <= 256") : FMQ_ERR_BAD_ARG;
+    if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
+    for (uint32_t w = 0; w < world; ++w) counts[w] = 0;
+    if (n == 0) return FMQ_OK;
+    if (!ts || !key || !val || !ts_out || !key_out || !val_out) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
+    CU(h, cudaSetDevice(h->device));
+    OwnerDigit dg{(const u64*)key, world};
+    MoveEvent3 mv{(const u64*)ts, (const u64*)key, (const u64*)val, (u64*)ts_out, (u64*)key_out, (u64*)val_out};
+    int s = multisplit(h, n, dg, mv); if (s) return s;
+    // bucket starts = scanned offsets of chunk 0 for each digit
+    const u32 nchunks = rs_num_chunks(n);
+    u32 starts[RS_DIGITS];
+    CU(h, cudaMemcpy2DAsync(starts, 4, h->d_counts, (size_t)nchunks * 4, 4, world, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    for (uint32_t w = 0; w < world; ++w) counts[w] = (w + 1 < world ? starts[w + 1] : (u32)n) - starts[w];
+    return FMQ_OK;
+}
+
+}  // extern "C"

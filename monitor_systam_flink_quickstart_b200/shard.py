@@ -1,0 +1,105 @@
+"""keyBy across GPUs: one process per GPU, every rank owns the state of the keys
+with ``mix64(key) % world == rank``.
+
+Per micro-batch each rank (1) splits its slice of the batch into ``world`` owner buckets with the
+CUDA multi-split kernel behind ``fmq_partition_by_owner`` (stable, so per-key arrival order
+survives), (2) exchanges the bucket sizes, (3) moves the three 8-byte columns with a
+variable-size all-to-all over NCCL (NVLink 5 / NVSwitch), buckets concatenated in source-rank
+order, (4) agrees on the watermark with an all-reduce(max) of the per-rank max timestamp — the
+reference has ONE watermark assigner in front of the keyBy (BandwidthMonitorWithEventTime.java:30-45),
+so every rank must judge lateness against the same value — and (5) pushes what it received into
+its own engine.  The union of the ranks' outputs equals the single-GPU output.
+
+The exchange is written against ``torch.distributed`` only, so the same code runs over ``gloo``
+on CPU tensors in the world_size-2 tests (with a CPU partitioner and the CPU oracle injected as
+the engine — test doubles; the product default is the CUDA engine and fails without a GPU).
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional
+
+import numpy as np
+
+from . import capi
+
+_M1, _M2 = np.uint64(0xBF58476D1CE4E5B9), np.uint64(0x94D049BB133111EB)
+I64_MIN = -(2 ** 63)
+
+
+def mix64_numpy(x: np.ndarray) -> np.ndarray:
+    x = x.astype(np.uint64, copy=True)
+    x ^= x >> np.uint64(30); x *= _M1
+    x ^= x >> np.uint64(27); x *= _M2
+    x ^= x >> np.uint64(31)
+    return x
+
+
+def owner_of_numpy(key: np.ndarray, world: int) -> np.ndarray:
+    """Host restatement of ``fmq_owner_of`` (mix64(key) % world)."""
+    return (mix64_numpy(key) % np.uint64(world)).astype(np.int64)
+
+
+class ShardedOperator:
+    """One rank of the keyBy-sharded operator.
+
+    engine      : this rank's engine (capi.Engine on its GPU)
+    partition   : callable(ts, key, val, world) -> (ts_b, key_b, val_b, counts[world]) bucketed by owner;
+                  default = the CUDA multi-split of the engine
+    """
+
+    def __init__(self, engine, rank: int, world: int, bound_ms: int, group=None,
+                 partition: Optional[Callable] = None, auto_watermark: bool = True):
+        import torch.distributed as dist
+        self.dist = dist
+        self.engine, self.rank, self.world, self.group = engine, rank, world, group
+        self.bound = bound_ms
+        self.auto_watermark = auto_watermark
+        self._partition = partition or self._cuda_partition
+        self.cur_max_ts = I64_MIN + bound_ms
+        self.wm = I64_MIN
+        self.shuffle_bytes_sent = 0
+        self._bufs = None
+
+    # -- step 1: owner buckets on the GPU ------------------------------------------------------
+    def _cuda_partition(self, ts, key, val, world):
+        import torch
+        outs = [torch.empty_like(t) for t in (ts, key, val)]
+        counts = self.engine.partition_by_owner(ts, key, val, world, *outs)
+        return outs[0], outs[1], outs[2], counts.astype(np.int64)
+
+    def process_batch(self, ts, key, val, watermark_after: Optional[int] = None):
+        """ts/key/val: this rank's slice of the micro-batch (torch tensors; int64 bit patterns for
+        key, int64 or float64 for val).  Returns the number of records this rank now owns."""
+        import torch
+        dist, W = self.dist, self.world
+        n = int(ts.numel())
+        local_max = int(ts.max().item()) if n else I64_MIN
+        ts_b, key_b, val_b, counts = self._partition(ts, key, val, W)
+        # -- step 2: bucket sizes (W x W matrix, 8 B each) --
+        send_counts = torch.as_tensor(np.asarray(counts, dtype=np.int64), device=ts.device)
+        recv_counts = torch.empty_like(send_counts)
+        dist.all_to_all_single(recv_counts, send_counts, group=self.group)
+        rc = recv_counts.cpu().tolist(); sc = [int(c) for c in counts]
+        n_recv = sum(rc)
+        # -- step 3: variable-size all-to-all of the three columns --
+        outs = []
+        for col in (ts_b, key_b, val_b):
+            out = torch.empty(n_recv, dtype=col.dtype, device=col.device)
+            dist.all_to_all_single(out, col, output_split_sizes=rc, input_split_sizes=sc, group=self.group)
+            outs.append(out)
+        self.shuffle_bytes_sent += 24 * (n - sc[self.rank])
+        # -- step 4: one watermark for the whole job --
+        if watermark_after is None:
+            m = torch.tensor([local_max], dtype=torch.int64, device=ts.device)
+            dist.all_reduce(m, op=dist.ReduceOp.MAX, group=self.group)
+            self.cur_max_ts = max(self.cur_max_ts, int(m.item()))
+            pot = self.cur_max_ts - self.bound
+            if pot >= self.wm:
+                self.wm = pot
+            watermark_after = self.wm
+        # -- step 5: keyed operator on the records this rank owns --
+        self.engine.push_batch(outs[0], outs[1], outs[2], watermark_after)
+        return n_recv
+
+    def flush(self, wm: int = capi.FMQ_WM_FINAL):
+        self.engine.flush(wm)

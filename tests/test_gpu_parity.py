@@ -1,0 +1,274 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle on the same seeded
+inputs.  Bit-exact for counts, integer sums, min/max, alert tuples, late-drop counts and keyed
+state; double sums within 1e-9 relative (BASELINE.json north_star; atomics reorder the adds)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from monitor_systam_flink_quickstart_b200 import capi
+from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy
+from monitor_systam_flink_quickstart_b200.text import KeyDictionary, parse_cpu_line, parse_flow_line
+from oracle_lib import (OracleEngine, assert_events_equal, assert_fired_equal, sort_fired, sort_walerts)
+
+pytestmark = pytest.mark.gpu
+G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "readme_sessions.json"), encoding="utf-8"))
+SMALL = dict(table_capacity=1 << 12, pane_ring=128, max_batch=1 << 16)
+
+
+def pair(**kw):
+    okw = {k: v for k, v in kw.items()}
+    return capi.Engine(**kw), OracleEngine(**okw)
+
+
+def compare_all(gpu, cpu, agg_mask=15, rtol=1e-9):
+    assert_fired_equal(gpu.poll_fired(), cpu.poll_fired(), f64_sum_rtol=rtol, agg_mask=agg_mask)
+    if gpu.cfg.walert_source:
+        a, b = sort_walerts(gpu.poll_window_alerts()), sort_walerts(cpu.poll_window_alerts())
+        np.testing.assert_array_equal(a.key, b.key); np.testing.assert_array_equal(a.window_end, b.window_end)
+        np.testing.assert_allclose(a.value, b.value, rtol=rtol, atol=0)
+    if gpu.cfg.efilter_enabled:
+        assert_events_equal(gpu.poll_event_alerts(), cpu.poll_event_alerts())
+    if gpu.cfg.consec_n:
+        assert_events_equal(gpu.poll_consec_alerts(), cpu.poll_consec_alerts())
+    cg, cc = gpu.counters(), cpu.counters()
+    for k in ("events_in", "late_dropped", "windows_fired", "window_alerts", "event_alerts", "consec_alerts", "watermark"):
+        assert cg[k] == cc[k], (k, cg, cc)
+
+
+# ---- the reference's own golden sessions, through the CUDA path ---------------------------------
+def test_g1_filter_gpu():
+    d = KeyDictionary()
+    e = capi.Engine(efilter_enabled=1, efilter_op=capi.FMQ_CMP_GT, efilter_threshold=90.0, **SMALL)
+    rows = [parse_cpu_line(l) for l in G["G1_filter"]["input"]]
+    e.push_batch(np.array([r[0] * 1000 for r in rows], np.int64), np.array([d.encode(r[1]) for r in rows], np.uint64),
+                 np.array([r[3] for r in rows]))
+    out = e.poll_event_alerts()
+    assert out.val.tolist() == [99.2] and d.decode(out.key[0]) == "10.8.22.1"
+
+
+def test_g3_rolling_max_gpu():
+    e = capi.Engine(rolling_max_enabled=1, **SMALL)
+    rows = [parse_cpu_line(l) for l in G["G3_rolling_max"]["input"]]
+    e.push_batch(np.array([r[0] * 1000 for r in rows], np.int64), np.zeros(3, np.uint64), np.array([r[3] for r in rows]))
+    assert e.poll_rolling_max(3).tolist() == [80.5, 80.5, 99.9]
+
+
+def test_g4_avg_gpu():
+    d = KeyDictionary()
+    e = capi.Engine(window_enabled=1, agg_mask=3, window_size_ms=60000, window_slide_ms=60000,
+                    walert_source=capi.FMQ_ALERT_AVG, walert_op=capi.FMQ_CMP_GT, walert_threshold=-1.0, **SMALL)
+    rows = [parse_cpu_line(l) for l in G["G4_avg"]["input"]]
+    ts = 1563452040000 + np.arange(4, dtype=np.int64) * 1000
+    e.push_batch(ts, np.array([d.encode(r[1]) for r in rows], np.uint64), np.array([r[3] for r in rows]), 0)
+    e.flush()
+    a = e.poll_window_alerts()
+    got = {d.decode(k): v for k, v in zip(a.key, a.value)}
+    # a 3-term double sum in a different order may differ in the last bit; the README value is the
+    # sequential one — accept 1 ulp here, exactness of the sequential order is the oracle's job
+    assert abs(got["10.8.22.1"] - 86.26666666666667) <= 2e-14 and got["10.8.22.2"] == 20.2
+
+
+def test_g6_g7_bandwidth_gpu():
+    kw = dict(value_type=capi.FMQ_VAL_I64, window_enabled=1, agg_mask=3, window_size_ms=300000, window_slide_ms=5000,
+              max_out_of_orderness_ms=60000, walert_source=capi.FMQ_ALERT_SUM, walert_op=capi.FMQ_CMP_LT, walert_mul=8.0,
+              walert_div0=60.0, walert_div1=1024.0, walert_div2=1024.0, walert_threshold=100.0, **SMALL)
+    e = capi.Engine(**kw)
+    d = KeyDictionary()
+    for t, ch, flow in [parse_flow_line(l) for l in G["G7_event_time"]["input"]]:
+        e.push_batch(np.array([t], np.int64), np.array([d.encode(ch)], np.uint64), np.array([flow], np.int64))
+    f = sort_fired(e.poll_fired())
+    assert f.sum.tolist() == [10000] * 12 + [10100] * 12 + [10200] * 36
+    assert e.counters()["late_dropped"] == 1
+    a = e.poll_window_alerts()
+    assert {0.0012715657552083333, 0.0012969970703125} <= set(a.value.tolist()) and len(a) == 60   # bit-exact doubles
+    e.flush()
+    assert sort_fired(e.poll_fired()).sum.tolist() == [200] * 24 + [100] * 48
+    # G6: tumbling long sum 11200 and its filter value
+    kw.update(window_size_ms=60000, window_slide_ms=60000)
+    e = capi.Engine(**kw)
+    rows = [parse_flow_line(l) for l in G["G6_sum"]["input"]]
+    e.push_batch(1566957600000 + np.arange(4, dtype=np.int64) * 1000, np.zeros(4, np.uint64), np.array([r[2] for r in rows], np.int64), 0)
+    e.flush()
+    assert e.poll_fired().sum.tolist() == [11200] and e.poll_window_alerts().value.tolist() == [0.0014241536458333333]
+
+
+# ---- seeded streams ------------------------------------------------------------------------------
+CONFIGS = {
+    "c3_tumbling_f64": (dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=10_000, max_out_of_orderness_ms=5000,
+                             walert_source=capi.FMQ_ALERT_AVG, walert_op=capi.FMQ_CMP_GT, walert_threshold=50.0,
+                             efilter_enabled=1, efilter_threshold=90.0),
+                        StreamSpec(n_keys=3000, events_per_ms=3, late_frac_ppm=20000)),
+    "c4_sliding_i64": (dict(value_type=capi.FMQ_VAL_I64, window_enabled=1, agg_mask=15, window_size_ms=60_000, window_slide_ms=10_000,
+                            window_offset_ms=2500, max_out_of_orderness_ms=5000, walert_source=capi.FMQ_ALERT_SUM, walert_op=capi.FMQ_CMP_LT,
+                            walert_mul=8.0, walert_div0=60.0, walert_div1=1024.0, walert_div2=1024.0, walert_threshold=2.5),
+                       StreamSpec(n_keys=4096, events_per_ms=2, value_type="i64", key_kind="host_metric", late_frac_ppm=20000, late_extra_ms=90000)),
+    "count_only": (dict(window_enabled=1, agg_mask=1, window_size_ms=3000, window_slide_ms=1000, max_out_of_orderness_ms=0, emit_fired=1),
+                   StreamSpec(n_keys=100, events_per_ms=1, jitter_ms=0, late_frac_ppm=0)),
+}
+
+
+@pytest.mark.parametrize("name", list(CONFIGS))
+@pytest.mark.parametrize("batch", [1000, 37_001])
+def test_window_parity_seeded(name, batch):
+    kw, spec = CONFIGS[name]
+    gpu, cpu = pair(**kw, **SMALL)
+    total = 150_000
+    for s in range(0, total, batch):
+        n = min(batch, total - s)
+        ts, key, val = generate_numpy(spec, s, n)
+        gpu.push_batch(ts, key, val); cpu.push_batch(ts, key, val)
+        if (s // batch) % 3 == 1:                      # interleave polls with pushes
+            compare_all(gpu, cpu, agg_mask=kw["agg_mask"])
+    gpu.flush(); cpu.flush()
+    compare_all(gpu, cpu, agg_mask=kw["agg_mask"])
+    assert cpu.counters()["windows_fired"] > 0
+
+
+def test_explicit_watermarks_and_empty_batches():
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=5000, window_slide_ms=5000, **SMALL)
+    gpu, cpu = pair(**kw)
+    spec = StreamSpec(n_keys=50, events_per_ms=1, jitter_ms=8000, late_frac_ppm=0, t0=100_000)
+    wms = [capi.FMQ_WM_AUTO, 95_000, 90_000, 104_999, 105_000, capi.FMQ_WM_AUTO, 130_000]
+    for i, wm in enumerate(wms):
+        n = 0 if i == 2 else 4001
+        ts, key, val = generate_numpy(spec, i * 4001, n)
+        for e in (gpu, cpu):
+            e.push_batch(ts, key, val, wm)
+    compare_all(gpu, cpu)
+    for e in (gpu, cpu):
+        e.flush(150_000); e.flush(149_000); e.flush()
+    compare_all(gpu, cpu)
+
+
+def test_device_resident_and_misaligned_inputs():
+    import torch
+    kw, spec = CONFIGS["c3_tumbling_f64"]
+    gpu, cpu = pair(**kw, **SMALL)
+    ts, key, val = generate_numpy(spec, 0, 50_003)
+    dts, dkey, dval = (torch.from_numpy(x.view(np.int64) if x.dtype == np.uint64 else x).cuda() for x in (ts, key, val))
+    for lo, hi in [(0, 20_000), (20_001, 35_002), (35_002, 50_003)]:      # 8-byte-aligned-only slices too
+        gpu.push_batch(dts[lo:hi], dkey[lo:hi], dval[lo:hi])
+        cpu.push_batch(ts[lo:hi], key[lo:hi], val[lo:hi])
+    gpu.synchronize()
+    gpu.flush(); cpu.flush()
+    compare_all(gpu, cpu)
+
+
+def test_special_doubles_in_min_max():
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=1000, window_slide_ms=1000, **SMALL)
+    gpu, cpu = pair(**kw)
+    val = np.array([0.0, -0.0, 5.5, -3.25, np.inf, -np.inf, -0.0, 0.0, 1e-310, -1e-310], np.float64)
+    key = np.array([0, 0, 1, 1, 2, 2, 3, 3, 4, 4], np.uint64)
+    ts = np.full(10, 500, np.int64)
+    for e in (gpu, cpu):
+        e.push_batch(ts, key, val, 0); e.flush()
+    assert_fired_equal(gpu.poll_fired(), cpu.poll_fired(), agg_mask=12 | 1)      # min/max bit patterns incl. -0.0
+
+
+def test_int64_sum_wraps_like_java_long():
+    kw = dict(value_type=capi.FMQ_VAL_I64, window_enabled=1, agg_mask=15, window_size_ms=1000, window_slide_ms=1000, **SMALL)
+    gpu, cpu = pair(**kw)
+    val = np.array([2 ** 62, 2 ** 62, 2 ** 62, -5, -(2 ** 63), 7], np.int64)
+    key = np.array([1, 1, 1, 2, 2, 2], np.uint64)
+    for e in (gpu, cpu):
+        e.push_batch(np.full(6, 10, np.int64), key, val, 0); e.flush()
+    assert_fired_equal(gpu.poll_fired(), cpu.poll_fired())
+
+
+# ---- keyed ValueState operators ------------------------------------------------------------------
+@pytest.mark.parametrize("vt", ["f64", "i64"])
+@pytest.mark.parametrize("reset", [1, 0])
+def test_keyed_state_parity(vt, reset):
+    thr = 50.0 if vt == "f64" else 500_000.0
+    kw = dict(value_type=capi.FMQ_VAL_F64 if vt == "f64" else capi.FMQ_VAL_I64, rolling_max_enabled=1,
+              consec_n=3, consec_threshold=thr, consec_reset_on_fire=reset, **SMALL)
+    gpu, cpu = pair(**kw)
+    spec = StreamSpec(n_keys=700, events_per_ms=5, value_type=vt)
+    for b, n in enumerate([1, 5000, 33, 60_000, 0, 4097]):
+        ts, key, val = generate_numpy(spec, b * 70_000, n)
+        gpu.push_batch(ts, key, val); cpu.push_batch(ts, key, val)
+        np.testing.assert_array_equal(gpu.poll_rolling_max(n).view(np.uint64), cpu.poll_rolling_max(n).view(np.uint64))
+    assert_events_equal(gpu.poll_consec_alerts(), cpu.poll_consec_alerts())
+    keys = np.arange(0, 800, dtype=np.uint64)
+    fg, cg, rg = gpu.key_state(keys); fc, cc, rc = cpu.key_state(keys)
+    np.testing.assert_array_equal(fg, fc); np.testing.assert_array_equal(cg, cc)
+    np.testing.assert_array_equal(rg.view(np.uint64), rc.view(np.uint64))
+    assert gpu.counters()["consec_alerts"] == cpu.counters()["consec_alerts"] > 0
+
+
+def test_consecutive_rule_known_answers():
+    """6 consecutive overs -> 2 alerts with reset-on-fire; a dip resets the run."""
+    e = capi.Engine(consec_n=3, consec_threshold=90.0, consec_reset_on_fire=1, **SMALL)
+    v = np.array([95, 96, 97, 98, 99, 91, 10, 95, 95, 90.0, 95, 95, 95], np.float64)
+    e.push_batch(np.arange(13, dtype=np.int64), np.zeros(13, np.uint64), v)
+    a = e.poll_consec_alerts()
+    assert sorted(a.ts.tolist()) == [2, 5, 12]
+    e2 = capi.Engine(consec_n=3, consec_threshold=90.0, consec_reset_on_fire=0, **SMALL)
+    e2.push_batch(np.arange(13, dtype=np.int64), np.zeros(13, np.uint64), v)
+    assert sorted(e2.poll_consec_alerts().ts.tolist()) == [2, 3, 4, 5, 12]
+
+
+# ---- error behaviour -----------------------------------------------------------------------------
+def test_error_codes():
+    e = capi.Engine(window_enabled=1, agg_mask=3, window_size_ms=1000, window_slide_ms=1000, table_capacity=64, pane_ring=4, max_batch=1 << 12)
+    with pytest.raises(capi.FmqError) as ex:
+        e.push_batch(np.zeros(1 << 13, np.int64), np.zeros(1 << 13, np.uint64), np.zeros(1 << 13))
+    assert ex.value.status == 1                                           # larger than max_batch
+    e.push_batch(np.full(200, 5, np.int64), np.arange(200, dtype=np.uint64), np.ones(200))
+    with pytest.raises(capi.FmqError) as ex:
+        e.counters()
+    assert ex.value.status == 2 and "table_capacity" in str(ex.value)      # directory full -> sticky
+    with pytest.raises(capi.FmqError) as ex:
+        e.push_batch(np.zeros(1, np.int64), np.zeros(1, np.uint64), np.zeros(1))
+    assert ex.value.status == 8
+    e = capi.Engine(window_enabled=1, agg_mask=3, window_size_ms=1000, window_slide_ms=1000, table_capacity=64, pane_ring=4, max_batch=1 << 12)
+    e.push_batch(np.array([0, 10_000], np.int64), np.zeros(2, np.uint64), np.ones(2))   # 11 panes apart, ring of 4
+    with pytest.raises(capi.FmqError) as ex:
+        e.counters()
+    assert ex.value.status == 3
+    e = capi.Engine(window_enabled=1, agg_mask=3, window_size_ms=1000, window_slide_ms=1000, table_capacity=64, pane_ring=4, max_batch=1 << 12)
+    e.push_batch(np.array([-1], np.int64), np.zeros(1, np.uint64), np.ones(1))
+    with pytest.raises(capi.FmqError) as ex:
+        e.counters()
+    assert ex.value.status == 6
+    e = capi.Engine(efilter_enabled=1, efilter_threshold=0.5, ealert_capacity=10, max_batch=1 << 12)
+    e.push_batch(np.zeros(100, np.int64), np.zeros(100, np.uint64), np.ones(100))
+    with pytest.raises(capi.FmqError) as ex:
+        e.poll_event_alerts()
+    assert ex.value.status == 4
+
+
+def test_partial_polls_drain_everything():
+    kw, spec = CONFIGS["c3_tumbling_f64"]
+    gpu, cpu = pair(**kw, **SMALL)
+    ts, key, val = generate_numpy(spec, 0, 60_000)
+    gpu.push_batch(ts, key, val); cpu.push_batch(ts, key, val)
+    gpu.flush(); cpu.flush()
+    assert_fired_equal(gpu.poll_fired(chunk=777), cpu.poll_fired())
+    assert_events_equal(gpu.poll_event_alerts(chunk=100), cpu.poll_event_alerts())
+    assert len(gpu.poll_fired()) == 0
+
+
+# ---- keyBy exchange ------------------------------------------------------------------------------
+@pytest.mark.parametrize("world", [1, 2, 8])
+def test_partition_by_owner_is_a_stable_split(world):
+    import torch
+    e = capi.Engine(efilter_enabled=1, max_batch=1 << 17)
+    spec = StreamSpec(n_keys=5000, events_per_ms=5)
+    n = 100_003
+    ts, key, val = generate_numpy(spec, 0, n)
+    d = [torch.from_numpy(x.view(np.int64) if x.dtype == np.uint64 else x).cuda() for x in (ts, key, val)]
+    o = [torch.empty_like(x) for x in d]
+    counts = e.partition_by_owner(d[0], d[1], d[2], world, o[0], o[1], o[2])
+    lib = capi.load_library()
+    owner = np.array([lib.fmq_owner_of(int(k), world) for k in key[:2000]])
+    from monitor_systam_flink_quickstart_b200.shard import owner_of_numpy
+    own = owner_of_numpy(key, world)
+    np.testing.assert_array_equal(own[:2000], owner)
+    order = np.argsort(own, kind="stable")
+    np.testing.assert_array_equal(counts, np.bincount(own, minlength=world).astype(np.uint64))
+    np.testing.assert_array_equal(o[0].cpu().numpy(), ts[order])
+    np.testing.assert_array_equal(o[1].cpu().numpy().view(np.uint64), key[order])
+    np.testing.assert_array_equal(o[2].cpu().numpy(), val[order])
