@@ -1,0 +1,336 @@
+#!/usr/bin/env python
+"""bench.py — events/sec of the keyed window-aggregate + alert hot path on B200.
+
+Contract (see the task statement):  python bench.py --gpus N --steps K --warmup W
+prints ONE JSON line.  A "step" is one micro-batch of the hot path:
+    fmq_push_batch(ts, key, val, FMQ_WM_AUTO)  =  ingest (pane assign + late drop + per-event
+    filter + keyed accumulate) -> plan (watermark) -> fire (emit windows + alert) -> commit.
+Workload (BASELINE.json configs[2]): 10 s tumbling event-time window,
+count/sum(avg)/max per host, 1 M hosts, watermark bound 5 s with a late tail, alert avg > limit,
+plus the chapter1 per-event `> 90` filter; f64 values.
+
+  value : whole-job events/s, inputs already resident in HBM, CUDA events on the engine's stream
+  e2e   : same through the C ABI with pinned HOST columns (H2D inside the timed region) and the
+          step's fired rows / alerts read back to the host (D2H inside)
+  roofline : the ingest kernel, algorithmic bytes (24 B/event + 24 B/event-alert row) over its
+          measured launch time, against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline : the multi-thread C++ restatement of the Flink semantics (oracle/, kind "port")
+          on a bounded sample of the same workload, on this box's host cores
+
+--impl reference times that same CPU restatement (the reference's Flink job cannot run here: no
+JVM) with all host threads.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+N_KEYS = 1_000_000
+WINDOW_MS = 10_000
+BOUND_MS = 5_000
+AVG_LIMIT = 55.0
+EVENT_LIMIT = 90.0
+
+
+def workload_kwargs(capi, batch, n_keys=N_KEYS):
+    return dict(window_enabled=1, agg_mask=capi.FMQ_AGG_COUNT | capi.FMQ_AGG_SUM | capi.FMQ_AGG_MAX,
+                window_size_ms=WINDOW_MS, window_slide_ms=WINDOW_MS, max_out_of_orderness_ms=BOUND_MS,
+                walert_source=capi.FMQ_ALERT_AVG, walert_op=capi.FMQ_CMP_GT, walert_threshold=AVG_LIMIT,
+                efilter_enabled=1, efilter_op=capi.FMQ_CMP_GT, efilter_threshold=EVENT_LIMIT,
+                emit_fired=1, table_capacity=int(n_keys * 1.5), pane_ring=16, max_batch=batch)
+
+
+def stream_spec(StreamSpec):
+    # 1000 events/ms over 1 M hosts = one report per host per second; jitter <= bound, 0.1 % late tail
+    return StreamSpec(n_keys=N_KEYS, events_per_ms=1000, jitter_ms=BOUND_MS, late_frac_ppm=1000, late_extra_ms=25_000,
+                      value_type="f64", key_kind="uniform", seed=42)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.p = [], None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        sm, mx, reasons = [], None, set()
+        for t, line in self.rows:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                mx = float(f[1])
+                if t0 - 0.05 <= t <= t1 + 0.05:
+                    sm.append(float(f[0]))
+                    for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                        if v.lower().startswith("active"):
+                            reasons.add(name)
+            except ValueError:
+                continue
+        if not sm:   # region shorter than the sampling period: take every sample
+            sm = [float(l.split(",")[0]) for _, l in self.rows if l.split(",")[0].strip().replace(".", "").isdigit()]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic():
+    """dram bytes per ingest launch from the committed ncu --set full summary, if any."""
+    p = os.path.join(ROOT, "profiles", "ncu_ingest_latest.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get("dram_bytes_per_launch")
+        except Exception:
+            return None
+    return None
+
+
+# --------------------------------------------------------------------------------------------------
+def cpu_reference_run(steps, warmup, sample_events, threads, capi, ParallelOracle, StreamSpec, generate_numpy):
+    """The CPU restatement on host cores: `steps` timed steps of `sample_events` events each."""
+    kw = workload_kwargs(capi, sample_events)
+    spec = stream_spec(StreamSpec)
+    eng = ParallelOracle(threads=threads, **kw)
+    batches = [generate_numpy(spec, b * sample_events, sample_events) for b in range(warmup + steps)]
+    for b in range(warmup):
+        eng.push_batch(*batches[b]); eng.discard_outputs()
+    t0 = time.perf_counter()
+    for b in range(warmup, warmup + steps):
+        eng.push_batch(*batches[b]); eng.discard_outputs()
+    dt = time.perf_counter() - t0
+    c = eng.counters()
+    return steps * sample_events / dt, dt, c
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch-log2", type=int, default=24, help="events per micro-batch per GPU (log2)")
+    ap.add_argument("--cpu-sample-log2", type=int, default=21, help="events per step of the CPU baseline")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from monitor_systam_flink_quickstart_b200 import capi
+    from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy, generate_torch
+
+    # ---------------------------------------------------------------- reference arm (CPU) ---------
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        import __graft_entry__ as ge
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
+        from oracle_lib import ParallelOracle
+        threads = os.cpu_count() or 1
+        sample = 1 << args.cpu_sample_log2
+        v, dt, c = cpu_reference_run(args.steps, args.warmup, sample, threads, capi, ParallelOracle, StreamSpec, generate_numpy)
+        line = {"impl": "reference", "metric": "events/sec keyed window-agg+alert", "value": v, "unit": "events/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "C3 10s tumbling event-time count/avg/max per host + late drop + avg>limit alert + per-event >90 filter, 1M keys",
+                           "events_per_step": sample, "note": "CPU restatement of the Flink semantics (oracle/cpu_parallel.cpp); Flink itself cannot run here (no JVM)"},
+                "cpu_baseline": {"value": v, "unit": "events/s", "cores": threads, "kind": "port", "sample": f"{args.steps} steps x 2^{args.cpu_sample_log2} events"},
+                "e2e": {"value": v, "unit": "events/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    # ---------------------------------------------------------------- B200 arm --------------------
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    import __graft_entry__ as ge
+    if rank == 0:
+        ge.build()
+    if dist:
+        dist.barrier()
+
+    B = 1 << args.batch_log2
+    K, W = args.steps, args.warmup
+    spec = stream_spec(StreamSpec)
+    kw = workload_kwargs(capi, B * (2 if world > 1 else 1))
+    kw["device"] = local_rank
+    # outputs stay in HBM during the timed region (polled after it): size the buffers for K steps.
+    # ~1 fired row per 10 events (one report per host per second, 10 s windows), ~10 % event alerts.
+    per_rank_events = B * max(K, W)
+    kw["fired_capacity"] = int(per_rank_events * 0.125) + 4 * N_KEYS
+    kw["walert_capacity"] = kw["fired_capacity"]
+    kw["ealert_capacity"] = int(per_rank_events * 0.115) + 65536
+    eng = capi.Engine(**kw)
+    stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local_rank))
+
+    # synthetic inputs, resident in HBM before any timing: rank r owns slice r of every global batch
+    def dev_batch(step):
+        start = (step * world + rank) * B
+        ts, key, val = generate_torch(spec, start, B, device=f"cuda:{local_rank}")
+        return ts.contiguous(), key.contiguous(), val.contiguous()
+    batches = [dev_batch(s) for s in range(W + K)]
+    torch.cuda.synchronize()
+
+    sharded = None
+    if world > 1:
+        from monitor_systam_flink_quickstart_b200.shard import ShardedOperator
+        sharded = ShardedOperator(eng, rank, world, BOUND_MS)
+
+    def step(b):
+        if sharded:
+            sharded.process_batch(*batches[b])
+        else:
+            eng.push_batch(*batches[b])
+
+    def drain():
+        eng.synchronize()
+        f = eng.poll_fired(); a = eng.poll_window_alerts(); e = eng.poll_event_alerts()
+        return len(f), len(a), len(e)
+
+    for b in range(W):
+        step(b)
+    drain()
+    c0 = eng.counters()
+
+    # -------- timed region: device-resident inputs --------
+    if dist:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    time.sleep(0.25 if sampler else 0)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_wall0 = time.time()
+    ev0.record(stream)                    # every kernel, copy and collective of a step is ordered on the engine's stream
+    for b in range(W, W + K):
+        step(b)
+    ev1.record(stream)
+    eng.synchronize()
+    torch.cuda.synchronize()
+    t_wall1 = time.time()
+    if dist:
+        dist.barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+    # per-kernel timing of the ingest kernel over the timed pushes (CUDA events on the engine stream)
+    ing = [eng.push_timing(back)["ingest_ms"] for back in range(min(K, 64))]
+    fire = [eng.push_timing(back)["fire_ms"] for back in range(min(K, 64))]
+    c1 = eng.counters()
+    launches = c1["gpu_launches"] - c0["gpu_launches"]
+    if dist:
+        t = torch.tensor([ms], device=f"cuda:{local_rank}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        tot = torch.tensor([launches, c1["event_alerts"] - c0["event_alerts"], c1["late_dropped"] - c0["late_dropped"],
+                            c1["windows_fired"] - c0["windows_fired"]], device=f"cuda:{local_rank}", dtype=torch.int64)
+        dist.all_reduce(tot)
+        launches, n_ealert, n_late, n_fired = [int(x) for x in tot.tolist()]
+    else:
+        n_ealert = c1["event_alerts"] - c0["event_alerts"]; n_late = c1["late_dropped"] - c0["late_dropped"]
+        n_fired = c1["windows_fired"] - c0["windows_fired"]
+    drain()
+    value = world * B * K / (ms * 1e-3)
+
+    # -------- roofline of the dominant kernel (ingest), this rank --------
+    peak, peak_src = measured_peak()
+    ealert_rank = (c1["event_alerts"] - c0["event_alerts"]) / K
+    ing_events = B if not sharded else (c1["events_in"] - c0["events_in"]) / K
+    alg_bytes = 24.0 * ing_events + 24.0 * ealert_rank
+    ing_ms = float(np.mean(ing))
+    achieved = alg_bytes / (ing_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "ingest_kernel<double>", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": ncu_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                "avg_launch_ms": ing_ms, "fire_chain_ms": float(np.mean(fire)), "share_of_step": ing_ms * K / ms if not sharded else None}
+
+    # -------- e2e: host columns through the C ABI, outputs read back --------
+    e2e = None
+    if not args.no_e2e and not sharded:
+        e2e_steps = min(K, 4)
+        host = []
+        for s in range(e2e_steps):
+            ts, key, val = batches[W + s]
+            host.append(tuple(t.cpu().pin_memory() for t in (ts, key, val)))
+        eng2 = capi.Engine(**kw)
+        hw = tuple(t.cpu().pin_memory() for t in batches[0])
+        eng2.push_batch(hw[0].numpy(), hw[1].numpy().view(np.uint64), hw[2].numpy())
+        eng2.synchronize(); eng2.poll_fired(); eng2.poll_window_alerts(); eng2.poll_event_alerts()
+        d2h = 0
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for s in range(e2e_steps):
+            ts, key, val = host[s]
+            eng2.push_batch(ts.numpy(), key.numpy().view(np.uint64), val.numpy())
+            f = eng2.poll_fired(); a = eng2.poll_window_alerts(); e = eng2.poll_event_alerts()
+            d2h += 48 * len(f) + 24 * len(a) + 24 * len(e)
+        eng2.synchronize()
+        dt = time.perf_counter() - t0
+        e2e = {"value": e2e_steps * B / dt, "unit": "events/s", "h2d_bytes_per_step": 24 * B, "d2h_bytes_per_step": d2h // e2e_steps,
+               "steps": e2e_steps, "timing": "host wall clock around push(host columns)+poll, sync at both ends"}
+        eng2.close()
+
+    if rank != 0:
+        if dist:
+            dist.destroy_process_group()
+        return
+
+    # -------- CPU baseline on a bounded sample (rank 0, N = 1 only) --------
+    cpu_baseline = None
+    if not args.no_cpu_baseline and world == 1:
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
+        from oracle_lib import ParallelOracle
+        threads = os.cpu_count() or 1
+        v, dt, _ = cpu_reference_run(6, 1, 1 << args.cpu_sample_log2, threads, capi, ParallelOracle, StreamSpec, generate_numpy)
+        cpu_baseline = {"value": v, "unit": "events/s", "cores": threads, "kind": "port",
+                        "sample": f"6 steps x 2^{args.cpu_sample_log2} events of the same stream, {dt:.1f} s of CPU work"}
+
+    line = {"metric": "events/sec keyed window-agg+alert", "value": value, "unit": "events/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C3 10s tumbling event-time count/avg/max per host + late drop + avg>limit alert + per-event >90 filter, 1M keys",
+                       "events_per_step_per_gpu": B, "keys": N_KEYS, "window_ms": WINDOW_MS, "bound_ms": BOUND_MS,
+                       "l2": "inputs larger than L2 (each batch = 24 B x 2^%d = %.0f MB, read once)" % (args.batch_log2, 24 * B / 1e6),
+                       "parallelism": "1 GPU" if world == 1 else f"keyBy hash-sharded over {world} GPUs, NCCL all-to-all"},
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "step_counts": {"event_alert_rows": int(n_ealert), "late_dropped": int(n_late), "fired_rows": int(n_fired)}}
+    print(json.dumps(line))
+    if dist:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

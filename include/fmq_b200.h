@@ -195,7 +195,7 @@ int32_t fmq_poll_fired(fmq_handle* h, const fmq_fired_cols* out, size_t cap, int
 /* Replaces: the chained map + filter after the window (BandwidthMonitorWithEventTime.java:48-55). */
 int32_t fmq_poll_window_alerts(fmq_handle* h, const fmq_walert_cols* out, size_t cap, int32_t mem,
                                size_t* n_out, size_t* n_left);
-/* Replaces: StreamFilter output of Main.java:27-32 (rows in arrival order within a batch). */
+/* Replaces: StreamFilter output of Main.java:27-32 (row order unspecified, compare as sets). */
 int32_t fmq_poll_event_alerts(fmq_handle* h, const fmq_event_cols* out, size_t cap, int32_t mem,
                               size_t* n_out, size_t* n_left);
 /* Replaces: KeyedProcessFunction output of the consecutive-breach rule. */
@@ -218,6 +218,12 @@ int32_t fmq_synchronize(fmq_handle* h);
 /* Device time in ms of the last fmq_push_batch / fmq_flush kernel chain (CUDA events on the
  * handle's stream); synchronises. */
 int32_t fmq_last_device_ms(fmq_handle* h, float* ms);
+/* Measurement hook (no counterpart in the reference): device time of the push `back` calls ago
+ * (0 = latest; a ring of 64 is kept), split by stage with CUDA events on the handle's stream:
+ * ingest = H2D staging copies (host inputs only) + the window/filter kernel; keyed = ValueState
+ * chain; fire = plan + fire + commit.  Synchronises on that push. */
+int32_t fmq_get_push_timing(fmq_handle* h, uint32_t back, float* total_ms, float* ingest_ms,
+                            float* keyed_ms, float* fire_ms);
 /* Raw cudaStream_t of the handle, for callers that enqueue their own device work. */
 void*   fmq_stream(fmq_handle* h);
 

@@ -134,6 +134,8 @@ def _declare(lib, p: str, has_mem: bool = True):
         sig("build_info", [], C.c_char_p)
         sig("synchronize", [vp])
         sig("last_device_ms", [vp, C.POINTER(C.c_float)])
+        pf = C.POINTER(C.c_float)
+        sig("get_push_timing", [vp, C.c_uint32, pf, pf, pf, pf])
         sig("stream", [vp], vp)
         sig("last_error", [vp], C.c_char_p)
         sig("owner_of", [C.c_uint64, C.c_uint32], C.c_uint32)
@@ -329,6 +331,12 @@ class Engine(EngineBase):
         ms = C.c_float(0)
         self._check(self._lib.fmq_last_device_ms(self._h, C.byref(ms)))
         return ms.value
+
+    def push_timing(self, back: int = 0) -> dict:
+        """Device ms of the push `back` calls ago, by stage (CUDA events on the handle's stream)."""
+        t, i, k, f = C.c_float(0), C.c_float(0), C.c_float(0), C.c_float(0)
+        self._check(self._lib.fmq_get_push_timing(self._h, back, C.byref(t), C.byref(i), C.byref(k), C.byref(f)))
+        return {"total_ms": t.value, "ingest_ms": i.value, "keyed_ms": k.value, "fire_ms": f.value}
 
     @property
     def stream(self) -> int:

@@ -23,7 +23,11 @@ struct fmq_handle {
     fmq_config cfg;
     int device = 0, num_sms = 148;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_copy = nullptr;
+    cudaEvent_t ev_copy = nullptr;
+    // per-push stage timing: ring of event quadruples {start, after ingest, after keyed, end}
+    static constexpr int TIMING_RING = 64;
+    cudaEvent_t tev[TIMING_RING][4] = {};
+    uint64_t pushes = 0;
     std::string err;
     int sticky = 0;                      // sticky fmq_status once the device state is invalid
     // geometry
@@ -79,8 +83,7 @@ static void free_all(fmq_handle* h) {
                     h->d_slot[0], h->d_slot[1], h->d_idx[0], h->d_idx[1], h->d_counts, h->d_tiles};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->h_st) cudaFreeHost(h->h_st);
-    if (h->ev0) cudaEventDestroy(h->ev0);
-    if (h->ev1) cudaEventDestroy(h->ev1);
+    for (auto& q : h->tev) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
     if (h->ev_copy) cudaEventDestroy(h->ev_copy);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -112,7 +115,8 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
 #define CUC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(FMQ_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
     CUC(cudaSetDevice(h->device));
     CUC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-    CUC(cudaEventCreate(&h->ev0)); CUC(cudaEventCreate(&h->ev1)); CUC(cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming));
+    CUC(cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming));
+    for (auto& q : h->tev) for (cudaEvent_t& e : q) CUC(cudaEventCreate(&e));
 
     h->capacity = cfg->table_capacity ? cfg->table_capacity : (1u << 20);
     if (h->capacity < 32) h->capacity = 32;
@@ -227,6 +231,7 @@ static int sync_state(fmq_handle* h) {
 template <typename V>
 static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n, int64_t wm_after) {
     const fmq_config& c = h->cfg;
+    cudaEvent_t* tev = h->tev[h->pushes % fmq_handle::TIMING_RING];
     if (n > 0 && (c.window_enabled || c.efilter_enabled)) {
         IngestArgs a{};
         a.ts = ts; a.key = key; a.val = val; a.n = n; a.st = h->d_st; a.dkeys = h->d_keys; a.acc = h->d_acc; a.g = h->g;
@@ -238,6 +243,7 @@ static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* v
         if (blocks > maxb) blocks = maxb;
         ingest_kernel<V><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a); LAUNCHED(h, "ingest_kernel");
     }
+    CU(h, cudaEventRecord(tev[1], h->stream));
     if (n > 0 && keyed_enabled(c)) {
         const unsigned gb = (unsigned)((n + 255) / 256 < (size_t)h->num_sms * 8 ? (n + 255) / 256 : (size_t)h->num_sms * 8);
         resolve_slots_kernel<<<gb, 256, 0, h->stream>>>(key, n, h->d_keys, h->capacity, h->d_st, h->d_slot[0], h->d_idx[0]); LAUNCHED(h, "resolve_slots_kernel");
@@ -258,6 +264,7 @@ static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* v
     } else if (keyed_enabled(c)) {
         h->rolling_n = 0;
     }
+    CU(h, cudaEventRecord(tev[2], h->stream));
     PlanArgs p{h->d_st, h->g, c.max_out_of_orderness_ms, wm_after, (u64)n, c.window_enabled, wm_after == FMQ_WM_AUTO};
     plan_kernel<<<1, 32, 0, h->stream>>>(p); LAUNCHED(h, "plan_kernel");
     if (c.window_enabled) {
@@ -285,7 +292,7 @@ int32_t fmq_push_batch(fmq_handle* h, const int64_t* ts, const uint64_t* key, co
     if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
     if (mem != FMQ_MEM_HOST && mem != FMQ_MEM_DEVICE) return set_err(h, FMQ_ERR_BAD_ARG, "bad mem");
     CU(h, cudaSetDevice(h->device));
-    CU(h, cudaEventRecord(h->ev0, h->stream));
+    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][0], h->stream));
     const i64* dts = (const i64*)ts; const u64* dkey = (const u64*)key; const void* dval = val;
     if (mem == FMQ_MEM_HOST && n > 0) {
         CU(h, cudaMemcpyAsync(h->d_in_ts, ts, n * 8, cudaMemcpyHostToDevice, h->stream));
@@ -299,7 +306,8 @@ int32_t fmq_push_batch(fmq_handle* h, const int64_t* ts, const uint64_t* key, co
     int s = (h->cfg.value_type == FMQ_VAL_F64) ? run_chain<double>(h, dts, dkey, dval, n, wm_after)
                                                : run_chain<i64>(h, dts, dkey, dval, n, wm_after);
     if (s) return s;
-    CU(h, cudaEventRecord(h->ev1, h->stream));
+    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][3], h->stream));
+    h->pushes++;
     // the caller owns host columns only for the duration of this call: wait for the H2D copies
     if (mem == FMQ_MEM_HOST && n > 0) CU(h, cudaEventSynchronize(h->ev_copy));
     return FMQ_OK;
@@ -310,11 +318,12 @@ int32_t fmq_flush(fmq_handle* h, int64_t watermark) {
     if (h->sticky) return FMQ_ERR_POISONED;
     if (watermark == FMQ_WM_AUTO) return set_err(h, FMQ_ERR_BAD_ARG, "flush needs an explicit watermark");
     CU(h, cudaSetDevice(h->device));
-    CU(h, cudaEventRecord(h->ev0, h->stream));
+    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][0], h->stream));
     int s = (h->cfg.value_type == FMQ_VAL_F64) ? run_chain<double>(h, nullptr, nullptr, nullptr, 0, watermark)
                                                : run_chain<i64>(h, nullptr, nullptr, nullptr, 0, watermark);
     if (s) return s;
-    CU(h, cudaEventRecord(h->ev1, h->stream));
+    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][3], h->stream));
+    h->pushes++;
     return FMQ_OK;
 }
 
@@ -420,10 +429,19 @@ int32_t fmq_synchronize(fmq_handle* h) {
     return FMQ_OK;
 }
 int32_t fmq_last_device_ms(fmq_handle* h, float* ms) {
-    if (!h || !ms) return FMQ_ERR_BAD_ARG;
+    float in = 0, ke = 0, fi = 0;
+    return fmq_get_push_timing(h, 0, ms, &in, &ke, &fi);
+}
+int32_t fmq_get_push_timing(fmq_handle* h, uint32_t back, float* total_ms, float* ingest_ms, float* keyed_ms, float* fire_ms) {
+    if (!h || !total_ms || !ingest_ms || !keyed_ms || !fire_ms) return FMQ_ERR_BAD_ARG;
+    if (back >= fmq_handle::TIMING_RING || back >= h->pushes) return set_err(h, FMQ_ERR_BAD_ARG, "no such push in the timing ring");
     CU(h, cudaSetDevice(h->device));
-    CU(h, cudaEventSynchronize(h->ev1));
-    CU(h, cudaEventElapsedTime(ms, h->ev0, h->ev1));
+    cudaEvent_t* e = h->tev[(h->pushes - 1 - back) % fmq_handle::TIMING_RING];
+    CU(h, cudaEventSynchronize(e[3]));
+    CU(h, cudaEventElapsedTime(total_ms, e[0], e[3]));
+    CU(h, cudaEventElapsedTime(ingest_ms, e[0], e[1]));
+    CU(h, cudaEventElapsedTime(keyed_ms, e[1], e[2]));
+    CU(h, cudaEventElapsedTime(fire_ms, e[2], e[3]));
     return FMQ_OK;
 }
 void* fmq_stream(fmq_handle* h) { return h ? (void*)h->stream : nullptr; }

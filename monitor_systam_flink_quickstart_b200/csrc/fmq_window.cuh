@@ -99,19 +99,31 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_kernel(const __grid_con
                 vb_[e] = in_[e] ? ldg_stream(val + i + e) : 0;
             }
         }
+        // ---- A6-i: per-event threshold filter + compaction (Main.java:31), one reservation per tile;
+        //      rows keep arrival order inside the tile ----
+        if (a.efilter_enabled) {
+            u32 hits = 0;
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e) {
+                V v; memcpy(&v, &vb_[e], 8);
+                const bool ok = in_[e] && ts_[e] >= 0 && key_[e] != KEY_EMPTY;
+                if (ok && cmp_op((double)v, a.efilter_op, a.efilter_thr)) hits |= 1u << e;
+            }
+            const u32 nh = __popc(hits);
+            nea += nh;
+            u64 row = block_append<INGEST_THREADS>(nh, &st->n_ealert, a.ea_cap, st);
+            if (row != ~0ull) {
+#pragma unroll
+                for (int e = 0; e < INGEST_EPT; ++e)
+                    if (hits & (1u << e)) { a.ea_ts[row] = ts_[e]; a.ea_key[row] = key_[e]; a.ea_val[row] = vb_[e]; ++row; }
+            }
+        }
 #pragma unroll
         for (int e = 0; e < INGEST_EPT; ++e) {
             const i64 ts = ts_[e]; const u64 key = key_[e];
             V v; memcpy(&v, &vb_[e], 8);
             bool ok = in_[e];
             if (ok && (ts < 0 || key == KEY_EMPTY)) { err |= ERRB_BAD_INPUT; ok = false; }
-            // ---- A6-i: per-event threshold filter + compaction (Main.java:31) ----
-            if (a.efilter_enabled) {
-                const bool hit = ok && cmp_op((double)v, a.efilter_op, a.efilter_thr);
-                const u64 row = warp_append(hit, &st->n_ealert, a.ea_cap, st);
-                if (hit) nea++;
-                if (row != ~0ull) { a.ea_ts[row] = ts; a.ea_key[row] = key; a.ea_val[row] = vb_[e]; }
-            }
             if (!a.window_enabled) continue;
             bool valid = false; u64 idx = 0;
             if (ok) {
@@ -238,7 +250,7 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
     const u64 C = a.g.capacity;
     constexpr bool is_f64 = IsF64<V>::value;
     u64 fired_local = 0, alerts_local = 0;
-    const u64 nslots_rounded = (C + 31) & ~31ull;
+    const u64 nslots_rounded = (C + FIRE_THREADS - 1) / FIRE_THREADS * FIRE_THREADS;   // block-uniform trip count
     for (u64 slot = (u64)blockIdx.x * blockDim.x + threadIdx.x; slot < nslots_rounded; slot += (u64)gridDim.x * blockDim.x) {
         const bool live = slot < C && a.dkeys[slot] != KEY_EMPTY;
         const u64 key = live ? a.dkeys[slot] : 0;
@@ -262,8 +274,8 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
             const u64 sum_bits = is_f64 ? (u64)__double_as_longlong(sum_d) : sum_i;
             if (fired) fired_local++;
             if (a.emit_fired) {
-                const u64 row = warp_append(fired, &st->n_fired, a.f_cap, st);
-                if (row != ~0ull) {
+                const u64 row = block_append<FIRE_THREADS>(fired ? 1u : 0u, &st->n_fired, a.f_cap, st);
+                if (fired && row != ~0ull) {
                     a.f_key[row] = key; a.f_wend[row] = wend; a.f_count[row] = count; a.f_sum[row] = sum_bits;
                     a.f_min[row] = (a.g.agg_mask & 4u) ? Codec<V>::dec_min(mn) : 0;
                     a.f_max[row] = (a.g.agg_mask & 8u) ? Codec<V>::dec_max(mx) : 0;
@@ -286,8 +298,8 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
                     hit = cmp_op(v, a.walert_op, a.thr);
                 }
                 if (hit) alerts_local++;
-                const u64 row = warp_append(hit, &st->n_walert, a.wa_cap, st);
-                if (row != ~0ull) { a.wa_key[row] = key; a.wa_wend[row] = wend; a.wa_val[row] = v; }
+                const u64 row = block_append<FIRE_THREADS>(hit ? 1u : 0u, &st->n_walert, a.wa_cap, st);
+                if (hit && row != ~0ull) { a.wa_key[row] = key; a.wa_wend[row] = wend; a.wa_val[row] = v; }
             }
         }
         // cleanup: WindowOperator.clearAllState for panes whose last window has fired

@@ -69,7 +69,21 @@ class ShardedOperator:
 
     def process_batch(self, ts, key, val, watermark_after: Optional[int] = None):
         """ts/key/val: this rank's slice of the micro-batch (torch tensors; int64 bit patterns for
-        key, int64 or float64 for val).  Returns the number of records this rank now owns."""
+        key, int64 or float64 for val).  Returns the number of records this rank now owns.
+        On CUDA everything (multi-split kernels, NCCL, the engine's kernel chain) is ordered on the
+        engine's own stream, so no host synchronisation is needed between the steps beyond the
+        bucket-size read-back."""
+        import contextlib
+        import torch
+        ctx = contextlib.nullcontext()
+        if ts.is_cuda:
+            if getattr(self, "_ext", None) is None:
+                self._ext = torch.cuda.ExternalStream(self.engine.stream, device=ts.device)
+            ctx = torch.cuda.stream(self._ext)
+        with ctx:
+            return self._process_batch(ts, key, val, watermark_after)
+
+    def _process_batch(self, ts, key, val, watermark_after):
         import torch
         dist, W = self.dist, self.world
         n = int(ts.numel())
