@@ -48,9 +48,9 @@ def workload_kwargs(capi, batch, n_keys=N_KEYS):
                 emit_fired=1, table_capacity=int(n_keys * 1.5), pane_ring=16, max_batch=batch)
 
 
-def stream_spec(StreamSpec):
+def stream_spec(StreamSpec, n_keys=N_KEYS):
     # 1000 events/ms over 1 M hosts = one report per host per second; jitter <= bound, 0.1 % late tail
-    return StreamSpec(n_keys=N_KEYS, events_per_ms=1000, jitter_ms=BOUND_MS, late_frac_ppm=1000, late_extra_ms=25_000,
+    return StreamSpec(n_keys=n_keys, events_per_ms=1000, jitter_ms=BOUND_MS, late_frac_ppm=1000, late_extra_ms=25_000,
                       value_type="f64", key_kind="uniform", seed=42)
 
 
@@ -142,6 +142,11 @@ def main():
     ap.add_argument("--cpu-sample-log2", type=int, default=21, help="events per step of the CPU baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--keys", type=int, default=N_KEYS, help="experiment: number of distinct hosts")
+    ap.add_argument("--load", type=float, default=1.5, help="experiment: directory slots per key")
+    ap.add_argument("--key-mode", default="hashed", choices=["hashed", "dense"],
+                    help="hashed: arbitrary u64 keys through the hash directory; dense: dictionary ids index the table")
+    ap.add_argument("--no-efilter", action="store_true", help="experiment: drop the per-event filter from the workload")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -188,13 +193,21 @@ def main():
 
     B = 1 << args.batch_log2
     K, W = args.steps, args.warmup
-    spec = stream_spec(StreamSpec)
-    kw = workload_kwargs(capi, B * (2 if world > 1 else 1))
+    spec = stream_spec(StreamSpec, args.keys)
+    kw = workload_kwargs(capi, B * (2 if world > 1 else 1), args.keys)
+    kw["table_capacity"] = int(args.keys * args.load)
     kw["device"] = local_rank
+    if args.no_efilter:
+        kw["efilter_enabled"] = 0
+    if args.key_mode == "dense":
+        kw["key_mode"] = capi.FMQ_KEYS_DENSE
+        kw["table_capacity"] = args.keys
     # outputs stay in HBM during the timed region (polled after it): size the buffers for K steps.
     # ~1 fired row per 10 events (one report per host per second, 10 s windows), ~10 % event alerts.
     per_rank_events = B * max(K, W)
     kw["fired_capacity"] = int(per_rank_events * 0.125) + 4 * N_KEYS
+    if args.keys < N_KEYS:
+        kw["fired_capacity"] = int(per_rank_events * 0.125 * 4) + 4 * N_KEYS
     kw["walert_capacity"] = kw["fired_capacity"]
     kw["ealert_capacity"] = int(per_rank_events * 0.115) + 65536
     eng = capi.Engine(**kw)
@@ -322,7 +335,7 @@ def main():
     line = {"metric": "events/sec keyed window-agg+alert", "value": value, "unit": "events/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C3 10s tumbling event-time count/avg/max per host + late drop + avg>limit alert + per-event >90 filter, 1M keys",
-                       "events_per_step_per_gpu": B, "keys": N_KEYS, "window_ms": WINDOW_MS, "bound_ms": BOUND_MS,
+                       "events_per_step_per_gpu": B, "keys": args.keys, "key_mode": args.key_mode, "window_ms": WINDOW_MS, "bound_ms": BOUND_MS,
                        "l2": "inputs larger than L2 (each batch = 24 B x 2^%d = %.0f MB, read once)" % (args.batch_log2, 24 * B / 1e6),
                        "parallelism": "1 GPU" if world == 1 else f"keyBy hash-sharded over {world} GPUs, NCCL all-to-all"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,

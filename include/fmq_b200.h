@@ -49,6 +49,12 @@ typedef enum fmq_status {
 
 typedef enum fmq_value_type { FMQ_VAL_F64 = 0, FMQ_VAL_I64 = 1 } fmq_value_type;
 typedef enum fmq_mem        { FMQ_MEM_HOST = 0, FMQ_MEM_DEVICE = 1 } fmq_mem;
+/* How the uint64 key column indexes the device state.
+ * HASHED: arbitrary 64-bit keys, found through a bucketized hash directory (one extra memory access
+ *         per event).  DENSE: the caller's dictionary hands out ids 0..table_capacity-1 (what a shim
+ *         that dictionary-encodes String keys, SURVEY.md §8b, naturally produces) and the id IS the
+ *         table slot: no directory, no hashing.  An id >= table_capacity is an input error. */
+typedef enum fmq_key_mode   { FMQ_KEYS_HASHED = 0, FMQ_KEYS_DENSE = 1 } fmq_key_mode;
 typedef enum fmq_cmp        { FMQ_CMP_GT = 0, FMQ_CMP_LT = 1, FMQ_CMP_GE = 2, FMQ_CMP_LE = 3 } fmq_cmp;
 
 /* aggregate mask bits (count is always maintained: a window fires only if count > 0) */
@@ -85,7 +91,7 @@ typedef struct fmq_config {
     uint32_t struct_size;
     int32_t  device;                 /* CUDA device ordinal                                      */
     int32_t  value_type;             /* fmq_value_type                                           */
-    int32_t  reserved0;
+    int32_t  key_mode;               /* fmq_key_mode                                             */
 
     /* --- event-time window aggregation (A2, A3, A5, A5f) --- */
     int32_t  window_enabled;
@@ -119,7 +125,8 @@ typedef struct fmq_config {
     double   consec_threshold;
 
     /* --- capacities (all device memory is allocated once, in fmq_create) --- */
-    uint64_t table_capacity;         /* key-directory slots; rounded up to a power of two        */
+    uint64_t table_capacity;         /* key slots (any size; ~1.5x the key count when HASHED,
+                                        max id + 1 when DENSE)                                   */
     uint32_t pane_ring;              /* open panes kept per key; rounded up to a power of two    */
     uint32_t reserved2;
     uint64_t max_batch;              /* largest n accepted by fmq_push_batch                     */

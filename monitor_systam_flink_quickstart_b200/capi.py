@@ -17,6 +17,7 @@ import numpy as np
 
 FMQ_VAL_F64, FMQ_VAL_I64 = 0, 1
 FMQ_MEM_HOST, FMQ_MEM_DEVICE = 0, 1
+FMQ_KEYS_HASHED, FMQ_KEYS_DENSE = 0, 1
 FMQ_CMP_GT, FMQ_CMP_LT, FMQ_CMP_GE, FMQ_CMP_LE = 0, 1, 2, 3
 FMQ_AGG_COUNT, FMQ_AGG_SUM, FMQ_AGG_MIN, FMQ_AGG_MAX = 1, 2, 4, 8
 FMQ_ALERT_NONE, FMQ_ALERT_SUM, FMQ_ALERT_AVG, FMQ_ALERT_MIN, FMQ_ALERT_MAX, FMQ_ALERT_COUNT = range(6)
@@ -30,7 +31,7 @@ STATUS_NAMES = {0: "OK", 1: "BAD_ARG", 2: "TABLE_FULL", 3: "RING_OVERFLOW", 4: "
 class FmqConfig(C.Structure):
     """Mirror of ``struct fmq_config`` (include/fmq_b200.h)."""
     _fields_ = [
-        ("struct_size", C.c_uint32), ("device", C.c_int32), ("value_type", C.c_int32), ("reserved0", C.c_int32),
+        ("struct_size", C.c_uint32), ("device", C.c_int32), ("value_type", C.c_int32), ("key_mode", C.c_int32),
         ("window_enabled", C.c_int32), ("agg_mask", C.c_uint32),
         ("window_size_ms", C.c_int64), ("window_slide_ms", C.c_int64), ("window_offset_ms", C.c_int64),
         ("max_out_of_orderness_ms", C.c_int64), ("emit_fired", C.c_int32),
@@ -86,7 +87,8 @@ class FmqError(RuntimeError):
         self.status = status
 
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libfmq_b200.so")
+# FMQ_LIB_PATH lets a developer A/B-test another build of the SAME CUDA library (never a fallback)
+_LIB_PATH = os.environ.get("FMQ_LIB_PATH") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libfmq_b200.so")
 _lib = None
 
 

@@ -111,33 +111,83 @@ __device__ __forceinline__ u64 ldg_stream(const void* p) {
     return r;
 }
 
-// ---- key directory: open addressing, linear probing, keys are never removed ---------------------
-// `cap` is any size >= 32 (not a power of two on purpose: 1.5x the key count keeps one pane of
-// accumulators at 48 MB for 1 M keys, well inside the 126 MB L2).  home = mulhi(hash, cap).
-// Returns the slot of `key`, inserting it if absent.  Stale L1 data cannot mislead the probe: a
-// slot only ever changes EMPTY -> key, and the CAS that claims it is resolved in L2.
-__device__ __forceinline__ u32 dir_find_or_insert(u64* __restrict__ dkeys, u64 cap, u64 key, DevState* st) {
-    u64 h = __umul64hi(mix64(key), cap);
-    for (u64 probe = 0; probe < cap; ++probe) {
-        u64 k = __ldcg(dkeys + h);
-        if (k == key) return (u32)h;
-        if (k == KEY_EMPTY) {
-            u64 old = atomicCAS(dkeys + h, KEY_EMPTY, key);
-            if (old == KEY_EMPTY) { atomicAdd(&st->keys, 1ull); return (u32)h; }
-            if (old == key) return (u32)h;
+// ---- key directory: bucketized open addressing, keys are never removed ---------------------------
+// The directory is an array of 32-byte buckets of 4 keys; slot = 4 * bucket + position.  One
+// 256-bit load fetches a whole bucket in a single L2 sector request, so a lookup is normally ONE
+// dependent memory access (plain per-key linear probing at the same load factor cost ~11
+// serialised probes for the slowest lane of a warp — ncu, profiles/r01_notes.md).
+// home bucket = mulhi(mix64(key), nbuckets); `cap` (slots) is any multiple of 4.
+// Stale data cannot mislead the probe: a slot only ever changes EMPTY -> key, and the CAS that
+// claims it is resolved in L2 and returns the winner.  Buckets fill left to right and all
+// inserters of one key walk the same sequence, so a key can never be entered twice.
+__device__ __forceinline__ ulonglong4 ld_bucket(const u64* bucket) {
+    ulonglong4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.b64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w) : "l"(bucket) : "memory");
+    return r;
+}
+__device__ __forceinline__ u64 dir_home_bucket(u64 key, u64 nbuckets) { return __umul64hi(mix64(key), nbuckets); }
+
+// branch-free search of one loaded bucket: position 0..3 of `key`, or -1
+__device__ __forceinline__ int bucket_match(const ulonglong4& kv, u64 key) {
+    int j = -1;
+    j = (kv.w == key) ? 3 : j; j = (kv.z == key) ? 2 : j; j = (kv.y == key) ? 1 : j; j = (kv.x == key) ? 0 : j;
+    return j;
+}
+
+// Same as dir_resolve below but inlined into the ingest loop.
+__device__ __forceinline__ u32 dir_resolve_inline(u64* __restrict__ dkeys, u64 nbuckets, u64 key, u64 b, ulonglong4 kv, DevState* st) {
+    for (u64 probe = 0; probe < nbuckets; ++probe) {
+        const int j = bucket_match(kv, key);
+        if (j >= 0) return (u32)(b * 4 + j);
+        const u64 k4[4] = {kv.x, kv.y, kv.z, kv.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if (k4[q] == KEY_EMPTY) {                                   // first sight of this key: claim the slot
+                const u64 old = atomicCAS(dkeys + b * 4 + q, KEY_EMPTY, key);
+                if (old == KEY_EMPTY) { atomicAdd(&st->keys, 1ull); return (u32)(b * 4 + q); }
+                if (old == key) return (u32)(b * 4 + q);
+            }
         }
-        h = (h + 1 == cap) ? 0 : h + 1;
+        b = (b + 1 == nbuckets) ? 0 : b + 1;
+        kv = ld_bucket(dkeys + b * 4);
     }
     atomicOr(&st->err_flags, ERRB_TABLE_FULL);
     return SLOT_INVALID;
 }
+
+// Full lookup-or-insert starting at bucket `b` whose contents `kv` are already loaded (slow path:
+// first sight of a key, or a key that overflowed its home bucket).
+__device__ __noinline__ u32 dir_resolve(u64* __restrict__ dkeys, u64 nbuckets, u64 key, u64 b, ulonglong4 kv, DevState* st) {
+    for (u64 probe = 0; probe < nbuckets; ++probe) {
+        const u64 k4[4] = {kv.x, kv.y, kv.z, kv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            u64 k = k4[j];
+            if (k == KEY_EMPTY) {
+                k = atomicCAS(dkeys + b * 4 + j, KEY_EMPTY, key);
+                if (k == KEY_EMPTY) { atomicAdd(&st->keys, 1ull); return (u32)(b * 4 + j); }
+            }
+            if (k == key) return (u32)(b * 4 + j);
+        }
+        b = (b + 1 == nbuckets) ? 0 : b + 1;
+        kv = ld_bucket(dkeys + b * 4);
+    }
+    atomicOr(&st->err_flags, ERRB_TABLE_FULL);
+    return SLOT_INVALID;
+}
+__device__ __forceinline__ u32 dir_find_or_insert(u64* __restrict__ dkeys, u64 cap, u64 key, DevState* st) {
+    const u64 nb = cap >> 2, b = dir_home_bucket(key, nb);
+    return dir_resolve(dkeys, nb, key, b, ld_bucket(dkeys + b * 4), st);
+}
 __device__ __forceinline__ u32 dir_find(const u64* __restrict__ dkeys, u64 cap, u64 key) {
-    u64 h = __umul64hi(mix64(key), cap);
-    for (u64 probe = 0; probe < cap; ++probe) {
-        u64 k = __ldcg(dkeys + h);
-        if (k == key) return (u32)h;
-        if (k == KEY_EMPTY) return SLOT_INVALID;
-        h = (h + 1 == cap) ? 0 : h + 1;
+    const u64 nb = cap >> 2; u64 b = dir_home_bucket(key, nb);
+    for (u64 probe = 0; probe < nb; ++probe) {
+        const ulonglong4 kv = ld_bucket(dkeys + b * 4);
+        const u64 k4[4] = {kv.x, kv.y, kv.z, kv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { if (k4[j] == key) return (u32)(b * 4 + j); if (k4[j] == KEY_EMPTY) return SLOT_INVALID; }
+        b = (b + 1 == nb) ? 0 : b + 1;
     }
     return SLOT_INVALID;
 }

@@ -30,6 +30,7 @@ struct fmq_handle {
     uint64_t pushes = 0;
     std::string err;
     int sticky = 0;                      // sticky fmq_status once the device state is invalid
+    bool anchored_known = false;         // host knows a finite watermark is in force (device state is the authority)
     // geometry
     WindowGeom g{};
     u64 capacity = 0; u32 ring = 0; u32 slot_bits = 0;
@@ -101,6 +102,8 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
         if (cfg->max_out_of_orderness_ms < 0) return set_err(nullptr, FMQ_ERR_BAD_ARG, "max_out_of_orderness_ms cannot be negative");   // chapter3/README.md:356-359
     }
     if (cfg->consec_n < 0) return set_err(nullptr, FMQ_ERR_BAD_ARG, "consec_n cannot be negative");
+    if (cfg->consec_n > 0x3FFFFFFF) return set_err(nullptr, FMQ_ERR_BAD_ARG, "consec_n too large");
+    if (cfg->key_mode != FMQ_KEYS_HASHED && cfg->key_mode != FMQ_KEYS_DENSE) return set_err(nullptr, FMQ_ERR_BAD_ARG, "bad key_mode");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return set_err(nullptr, FMQ_ERR_NO_DEVICE, "no CUDA device visible (this library has no CPU fallback)"); }
     if (cfg->device < 0 || cfg->device >= ndev) return set_err(nullptr, FMQ_ERR_NO_DEVICE, "device ordinal out of range");
@@ -120,6 +123,7 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
 
     h->capacity = cfg->table_capacity ? cfg->table_capacity : (1u << 20);
     if (h->capacity < 32) h->capacity = 32;
+    h->capacity = (h->capacity + 3) & ~3ull;            // whole 4-key buckets
     if (h->capacity >= 0xFFFFFFF0ull) return fail(FMQ_ERR_BAD_ARG, "table_capacity must be < 2^32");
     u32 ring = cfg->pane_ring ? cfg->pane_ring : 8; u32 r2 = 1; while (r2 < ring) r2 <<= 1; h->ring = r2;
     h->slot_bits = 1; while ((1ull << h->slot_bits) < h->capacity) h->slot_bits++;
@@ -225,6 +229,7 @@ static int sync_state(fmq_handle* h) {
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaMemcpyAsync(h->h_st, h->d_st, sizeof(DevState), cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
+    if (h->h_st->anchored) h->anchored_known = true;
     return status_from_flags(h, h->h_st->err_flags);
 }
 
@@ -241,12 +246,26 @@ static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* v
         const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
         size_t blocks = (n + tile - 1) / tile; const size_t maxb = (size_t)h->num_sms * 8;
         if (blocks > maxb) blocks = maxb;
-        ingest_kernel<V><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a); LAUNCHED(h, "ingest_kernel");
+        // The kernels pick themselves on the device-resident stream position (no host round trip):
+        // the fast kernel returns at once unless a watermark anchors the pane origin, the generic
+        // one unless it does not.  Launches that are known to be no-ops are skipped.
+        const bool fast_geom = !c.window_enabled || (h->g.slide32 != 0 && (u64)h->ring * h->g.slide32 < 0x100000000ull);
+        const bool dense = c.key_mode == FMQ_KEYS_DENSE;
+        if (c.window_enabled && fast_geom) {
+            if (dense) ingest_fast_kernel<V, true><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a);
+            else       ingest_fast_kernel<V, false><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a);
+            LAUNCHED(h, "ingest_fast_kernel");
+        }
+        if (!c.window_enabled || !fast_geom || !h->anchored_known) {
+            if (dense) ingest_generic_kernel<V, true><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a);
+            else       ingest_generic_kernel<V, false><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a);
+            LAUNCHED(h, "ingest_generic_kernel");
+        }
     }
     CU(h, cudaEventRecord(tev[1], h->stream));
     if (n > 0 && keyed_enabled(c)) {
         const unsigned gb = (unsigned)((n + 255) / 256 < (size_t)h->num_sms * 8 ? (n + 255) / 256 : (size_t)h->num_sms * 8);
-        resolve_slots_kernel<<<gb, 256, 0, h->stream>>>(key, n, h->d_keys, h->capacity, h->d_st, h->d_slot[0], h->d_idx[0]); LAUNCHED(h, "resolve_slots_kernel");
+        resolve_slots_kernel<<<gb, 256, 0, h->stream>>>(key, n, h->d_keys, h->capacity, c.key_mode == FMQ_KEYS_DENSE, h->d_st, h->d_slot[0], h->d_idx[0]); LAUNCHED(h, "resolve_slots_kernel");
         int cur = 0;
         for (u32 shift = 0; shift < h->slot_bits; shift += 8) {
             SlotDigit dg{h->d_slot[cur], shift};
@@ -267,9 +286,10 @@ static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* v
     CU(h, cudaEventRecord(tev[2], h->stream));
     PlanArgs p{h->d_st, h->g, c.max_out_of_orderness_ms, wm_after, (u64)n, c.window_enabled, wm_after == FMQ_WM_AUTO};
     plan_kernel<<<1, 32, 0, h->stream>>>(p); LAUNCHED(h, "plan_kernel");
+    if (c.window_enabled && wm_after != FMQ_WM_AUTO && wm_after > INT64_MIN) h->anchored_known = true;
     if (c.window_enabled) {
         FireArgs f{};
-        f.st = h->d_st; f.dkeys = h->d_keys; f.acc = h->d_acc; f.g = h->g; f.emit_fired = c.emit_fired;
+        f.st = h->d_st; f.dkeys = h->d_keys; f.acc = h->d_acc; f.g = h->g; f.dense_keys = c.key_mode == FMQ_KEYS_DENSE; f.emit_fired = c.emit_fired;
         f.walert_source = c.walert_source; f.walert_op = c.walert_op;
         f.mul = c.walert_mul == 0.0 ? 1.0 : c.walert_mul; f.d0 = c.walert_div0 == 0.0 ? 1.0 : c.walert_div0;
         f.d1 = c.walert_div1 == 0.0 ? 1.0 : c.walert_div1; f.d2 = c.walert_div2 == 0.0 ? 1.0 : c.walert_div2; f.thr = c.walert_threshold;
@@ -412,7 +432,7 @@ int32_t fmq_get_key_state(fmq_handle* h, const uint64_t* keys, size_t n, int32_t
     u64* dk = nullptr; int *df = nullptr, *dc = nullptr; u64* dr = nullptr;
     CU(h, dalloc(&dk, n)); CU(h, dalloc(&df, n)); CU(h, dalloc(&dc, n)); CU(h, dalloc(&dr, n));
     CU(h, cudaMemcpyAsync(dk, keys, n * 8, cudaMemcpyHostToDevice, h->stream));
-    key_state_lookup_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(dk, n, h->d_keys, h->capacity, h->d_kflags, h->d_kmax, df, dc, dr);
+    key_state_lookup_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(dk, n, h->d_keys, h->capacity, h->cfg.key_mode == FMQ_KEYS_DENSE, h->d_kflags, h->d_kmax, df, dc, dr);
     LAUNCHED(h, "key_state_lookup_kernel");
     CU(h, cudaMemcpyAsync(found, df, n * 4, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaMemcpyAsync(consec, dc, n * 4, cudaMemcpyDeviceToHost, h->stream));

@@ -13,14 +13,16 @@ namespace fmq {
 //   kflags[slot] : bit 31 = rolling max present, bits 0..30 = consecutive-breach counter
 //   kmax[slot]   : rolling max value bits
 constexpr u32 KF_HAS_MAX = 0x80000000u;
+constexpr u32 KF_SEEN = 0x40000000u;       // dense-id mode: this id has been seen by a keyed operator
+constexpr u32 KF_COUNT_MASK = 0x3FFFFFFFu;
 
-__global__ void __launch_bounds__(256) resolve_slots_kernel(const u64* __restrict__ key, size_t n, u64* dkeys, u64 dcap,
+__global__ void __launch_bounds__(256) resolve_slots_kernel(const u64* __restrict__ key, size_t n, u64* dkeys, u64 dcap, int dense,
                                                             DevState* st, u32* __restrict__ slot_out, u32* __restrict__ idx_out) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const u64 k = ldg_stream(key + i);
         u32 s = SLOT_INVALID;
-        if (k == KEY_EMPTY) atomicOr(&st->err_flags, ERRB_BAD_INPUT);
-        else s = dir_find_or_insert(dkeys, dcap, k, st);
+        if (k == KEY_EMPTY || (dense && k >= dcap)) atomicOr(&st->err_flags, ERRB_BAD_INPUT);
+        else s = dense ? (u32)k : dir_find_or_insert(dkeys, dcap, k, st);
         slot_out[i] = s; idx_out[i] = (u32)i;
     }
 }
@@ -46,7 +48,7 @@ __global__ void __launch_bounds__(256) keyed_apply_kernel(const __grid_constant_
         if (s == SLOT_INVALID) continue;
         if (t > 0 && a.slot_sorted[t - 1] == s) continue;          // not a run head
         u32 fl = a.kflags[s];
-        bool has = fl & KF_HAS_MAX; int c = (int)(fl & ~KF_HAS_MAX);
+        bool has = fl & KF_HAS_MAX; int c = (int)(fl & KF_COUNT_MASK);
         u64 mbits = a.kmax[s];
         for (size_t j = t; j < a.n && a.slot_sorted[j] == s; ++j) {
             const u32 i = a.idx_sorted[j];
@@ -70,21 +72,21 @@ __global__ void __launch_bounds__(256) keyed_apply_kernel(const __grid_constant_
                 }
             }
         }
-        a.kflags[s] = (has ? KF_HAS_MAX : 0u) | ((u32)c & ~KF_HAS_MAX);
+        a.kflags[s] = (has ? KF_HAS_MAX : 0u) | KF_SEEN | ((u32)c & KF_COUNT_MASK);
         a.kmax[s] = mbits;
     }
     nalert = warp_sum_u64(nalert);
     if ((threadIdx.x & 31) == 0 && nalert) atomicAdd(&a.st->consec_alerts, nalert);
 }
 
-__global__ void key_state_lookup_kernel(const u64* keys, size_t n, const u64* dkeys, u64 dcap, const u32* kflags, const u64* kmax,
+__global__ void key_state_lookup_kernel(const u64* keys, size_t n, const u64* dkeys, u64 dcap, int dense, const u32* kflags, const u64* kmax,
                                         int* found, int* consec, u64* rolling) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const u32 s = dir_find(dkeys, dcap, keys[i]);
-    if (s == SLOT_INVALID) { found[i] = 0; consec[i] = 0; rolling[i] = 0; return; }
+    const u32 s = dense ? (keys[i] < dcap ? (u32)keys[i] : SLOT_INVALID) : dir_find(dkeys, dcap, keys[i]);
+    if (s == SLOT_INVALID || (dense && !(kflags[s] & KF_SEEN))) { found[i] = 0; consec[i] = 0; rolling[i] = 0; return; }
     const u32 fl = kflags[s];
-    found[i] = 1; consec[i] = (int)(fl & ~KF_HAS_MAX); rolling[i] = (fl & KF_HAS_MAX) ? kmax[s] : 0;
+    found[i] = 1; consec[i] = (int)(fl & KF_COUNT_MASK); rolling[i] = (fl & KF_HAS_MAX) ? kmax[s] : 0;
 }
 
 }  // namespace fmq

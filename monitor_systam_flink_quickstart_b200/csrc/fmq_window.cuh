@@ -66,81 +66,200 @@ __device__ __forceinline__ void accumulate_pair(Acc32* __restrict__ acc, bool va
 
 constexpr int INGEST_THREADS = 256;
 constexpr int INGEST_EPT = 4;          // events per thread per tile (one 32 B load per column)
+#ifndef FMQ_INGEST_MIN_BLOCKS
+#define FMQ_INGEST_MIN_BLOCKS 2
+#endif
 
+// Loads the (up to) four consecutive events of this thread.
 template <typename V>
-__global__ void __launch_bounds__(INGEST_THREADS) ingest_kernel(const __grid_constant__ IngestArgs a) {
+__device__ __forceinline__ void load_events(const IngestArgs& a, size_t i, i64 (&ts_)[INGEST_EPT], u64 (&key_)[INGEST_EPT],
+                                            u64 (&vb_)[INGEST_EPT], u32& in_mask) {
+    const V* __restrict__ val = static_cast<const V*>(a.val);
+    if (a.vec32 && i + INGEST_EPT <= a.n) {
+        const ulonglong4 x = ldg_stream_v4(a.ts + i), y = ldg_stream_v4(a.key + i), z = ldg_stream_v4(val + i);
+        ts_[0] = (i64)x.x; ts_[1] = (i64)x.y; ts_[2] = (i64)x.z; ts_[3] = (i64)x.w;
+        key_[0] = y.x; key_[1] = y.y; key_[2] = y.z; key_[3] = y.w;
+        vb_[0] = z.x; vb_[1] = z.y; vb_[2] = z.z; vb_[3] = z.w;
+        in_mask = 0xFu;
+    } else {
+        in_mask = 0;
+#pragma unroll
+        for (int e = 0; e < INGEST_EPT; ++e) {
+            const bool in = i + e < a.n;
+            in_mask |= in ? (1u << e) : 0u;
+            ts_[e] = in ? (i64)ldg_stream(a.ts + i + e) : 0;
+            key_[e] = in ? ldg_stream(a.key + i + e) : 0;
+            vb_[e] = in ? ldg_stream(val + i + e) : 0;
+        }
+    }
+}
+
+// A6-i: per-event threshold filter + compaction (Main.java:31); one reservation per block tile,
+// rows keep arrival order inside the tile.  Called by every thread of the block.
+template <typename V>
+__device__ __forceinline__ u32 filter_events(const IngestArgs& a, DevState* st, const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT],
+                                             const u64 (&vb_)[INGEST_EPT], u32 ok_mask) {
+    u32 hits = 0;
+#pragma unroll
+    for (int e = 0; e < INGEST_EPT; ++e) {
+        V v; memcpy(&v, &vb_[e], 8);
+        hits |= (cmp_op((double)v, a.efilter_op, a.efilter_thr) ? 1u : 0u) << e;
+    }
+    hits &= ok_mask;
+    const u32 nh = __popc(hits);
+    u64 row = block_append<INGEST_THREADS>(nh, &st->n_ealert, a.ea_cap, st);
+    if (row != ~0ull) {
+#pragma unroll
+        for (int e = 0; e < INGEST_EPT; ++e)
+            if (hits & (1u << e)) { a.ea_ts[row] = ts_[e]; a.ea_key[row] = key_[e]; a.ea_val[row] = vb_[e]; ++row; }
+    }
+    return nh;
+}
+
+// Chooses the kernel on the device-resident stream position without a host round trip: the fast
+// kernel is launched first and returns immediately unless its preconditions hold, and vice versa.
+__device__ __forceinline__ bool ingest_fast_ok(const DevState* st, const WindowGeom& g) {
+    return st->anchored && g.slide32 != 0 && (u64)(g.ring_mask + 1) * g.slide32 < 0x100000000ull;
+}
+
+// ---- ingest, fast kernel --------------------------------------------------------------------------
+// Preconditions (checked by the host): the stream is anchored (a watermark exists, so the pane
+// origin is known) and pane_ring * slide < 2^32, so the pane of a record is a 32-bit quotient of
+// (ts - origin).  The hot loop is branch-free per event: late test, pane, home-bucket match and the
+// pair-lane accumulate are all predicated; only events whose key is not in its home bucket leave it.
+template <typename V, bool DENSE>
+__global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_fast_kernel(const __grid_constant__ IngestArgs a) {
     DevState* st = a.st;
+    if (!ingest_fast_ok(st, a.g)) return;                        // the generic kernel handles this batch
+    const i64 origin_ts = st->origin_ts;
+    const u32 origin_ring = (u32)st->origin_pane & a.g.ring_mask;
+    const u32 slide = a.g.slide32;
+    const u32 recip = 0xFFFFFFFFu / slide;                      // floor((2^32-1)/slide): quotient estimate, never too big
+    const u64 span = (u64)(a.g.ring_mask + 1) * slide;           // first d that falls outside the ring (< 2^32)
+    const u64 nbuckets = a.g.capacity >> 2;
+
+    u64 late = 0, nea = 0; i64 dmax = I64_MIN_; u32 pmin = 0xFFFFFFFFu, pmax = 0; u32 err = 0;
+
+    const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
+    const size_t ntiles = (a.n + tile - 1) / tile;
+    for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const size_t i = t * tile + (size_t)threadIdx.x * INGEST_EPT;
+        i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; u32 in_mask;
+        load_events<V>(a, i, ts_, key_, vb_, in_mask);
+        u32 ok_mask = 0;
+#pragma unroll
+        for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
+        if ((ok_mask & in_mask) != in_mask) err |= ERRB_BAD_INPUT;
+        ok_mask &= in_mask;
+        if (a.efilter_enabled) nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
+        if (!a.window_enabled) continue;
+        // ---- per event: A1 max-ts, A3 late test, A2 pane, and (hashed keys) the home-bucket load:
+        //      all four directory loads are in flight before any of them is consumed ----
+        u32 ring_[INGEST_EPT]; u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0;
+#pragma unroll
+        for (int e = 0; e < INGEST_EPT; ++e) {
+            const bool ok = ok_mask & (1u << e);
+            const i64 d = ts_[e] - origin_ts;
+            dmax = (ok && d > dmax) ? d : dmax;                        // A1 (ts = origin + d)
+            const bool is_late = ok && d < 0;                          // A3: every window of this record has fired
+            late += is_late ? 1 : 0;
+            const bool beyond = ok && d >= 0 && (u64)d >= span;        // would alias an older pane of the ring
+            err |= beyond ? ERRB_RING : 0u;
+            const u32 du = (u32)d;
+            u32 q = __umulhi(du, recip);                               // A2: q <= du / slide <= q + 2
+            u32 r = du - q * slide;
+            if (r >= slide) { q++; r -= slide; }
+            if (r >= slide) { q++; }
+            bool act = ok && d >= 0 && !beyond;
+            if (DENSE) {
+                if (act && key_[e] >= a.g.capacity) { err |= ERRB_BAD_INPUT; act = false; }   // id outside the table
+            } else {
+                hb_[e] = dir_home_bucket(key_[e], nbuckets);
+                if (act) kv_[e] = ld_bucket(a.dkeys + hb_[e] * 4);
+            }
+            pmin = (act && q < pmin) ? q : pmin; pmax = (act && q > pmax) ? q : pmax;
+            ring_[e] = (origin_ring + q) & a.g.ring_mask;
+            act_mask |= act ? (1u << e) : 0u;
+        }
+        // ---- A5: slot -> pair-lane accumulate ----
+#pragma unroll
+        for (int e = 0; e < INGEST_EPT; ++e) {
+            bool valid = act_mask & (1u << e);
+            u32 slot = (u32)key_[e];                                   // dense ids index the table directly
+            if (!DENSE) {
+                if (valid) slot = dir_resolve_inline(a.dkeys, nbuckets, key_[e], hb_[e], kv_[e], st);
+                valid = valid && slot != SLOT_INVALID;
+            }
+            const u64 idx = (u64)ring_[e] * a.g.capacity + slot;
+            V v; memcpy(&v, &vb_[e], 8);
+            accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask);
+        }
+    }
+    // ---- per-warp reduction of the batch scalars, one atomic each per warp ----
+    nea = warp_sum_u64(nea);
+    for (int o = 16; o > 0; o >>= 1) err |= __shfl_xor_sync(0xffffffffu, err, o);
+    if (a.window_enabled) {
+        late = warp_sum_u64(late); dmax = warp_max_i64(dmax);
+        pmin = __reduce_min_sync(0xffffffffu, pmin); pmax = __reduce_max_sync(0xffffffffu, pmax);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (nea) atomicAdd(&st->event_alerts, nea);
+        if (err) atomicOr(&st->err_flags, err);
+        if (a.window_enabled) {
+            if (late) atomicAdd(&st->late_dropped, late);
+            if (dmax != I64_MIN_) atomicMax(&st->batch_max_ts, origin_ts + dmax);
+            if (pmin <= pmax) { atomicMin(&st->min_pane, st->origin_pane + (i64)pmin); atomicMax(&st->max_pane, st->origin_pane + (i64)pmax); }
+        }
+    }
+}
+
+// ---- ingest, generic kernel -------------------------------------------------------------------------
+// Used while the stream is not anchored yet (no watermark: nothing can be late and the pane origin
+// is unknown, so pane indices need a 64-bit division) or when the geometry does not fit 32 bits.
+template <typename V, bool DENSE>
+__global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __grid_constant__ IngestArgs a) {
+    DevState* st = a.st;
+    if (ingest_fast_ok(st, a.g)) return;                         // the fast kernel handles this batch
     const int anchored = st->anchored;
     const i64 origin_ts = anchored ? st->origin_ts : (a.g.off - a.g.slide);
     const i64 origin_pane = anchored ? st->origin_pane : -1;
     const u32 R = a.g.ring_mask + 1;
-    const V* __restrict__ val = static_cast<const V*>(a.val);
 
     u64 late = 0, nea = 0; i64 max_ts = I64_MIN_; i64 pmin = I64_MAX_, pmax = I64_MIN_; u32 err = 0;
 
     const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
     const size_t ntiles = (a.n + tile - 1) / tile;
     for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        // each thread owns 4 consecutive events: one 256-bit load per column (3 x 32 B in flight)
         const size_t i = t * tile + (size_t)threadIdx.x * INGEST_EPT;
-        i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; bool in_[INGEST_EPT];
-        if (a.vec32 && i + INGEST_EPT <= a.n) {
-            const ulonglong4 x = ldg_stream_v4(a.ts + i), y = ldg_stream_v4(a.key + i), z = ldg_stream_v4(val + i);
-            ts_[0] = (i64)x.x; ts_[1] = (i64)x.y; ts_[2] = (i64)x.z; ts_[3] = (i64)x.w;
-            key_[0] = y.x; key_[1] = y.y; key_[2] = y.z; key_[3] = y.w;
-            vb_[0] = z.x; vb_[1] = z.y; vb_[2] = z.z; vb_[3] = z.w;
-            in_[0] = in_[1] = in_[2] = in_[3] = true;
-        } else {
+        i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; u32 in_mask;
+        load_events<V>(a, i, ts_, key_, vb_, in_mask);
+        u32 ok_mask = 0;
 #pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e) {
-                in_[e] = i + e < a.n;
-                ts_[e] = in_[e] ? (i64)ldg_stream(a.ts + i + e) : 0;
-                key_[e] = in_[e] ? ldg_stream(a.key + i + e) : 0;
-                vb_[e] = in_[e] ? ldg_stream(val + i + e) : 0;
-            }
-        }
-        // ---- A6-i: per-event threshold filter + compaction (Main.java:31), one reservation per tile;
-        //      rows keep arrival order inside the tile ----
-        if (a.efilter_enabled) {
-            u32 hits = 0;
-#pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e) {
-                V v; memcpy(&v, &vb_[e], 8);
-                const bool ok = in_[e] && ts_[e] >= 0 && key_[e] != KEY_EMPTY;
-                if (ok && cmp_op((double)v, a.efilter_op, a.efilter_thr)) hits |= 1u << e;
-            }
-            const u32 nh = __popc(hits);
-            nea += nh;
-            u64 row = block_append<INGEST_THREADS>(nh, &st->n_ealert, a.ea_cap, st);
-            if (row != ~0ull) {
-#pragma unroll
-                for (int e = 0; e < INGEST_EPT; ++e)
-                    if (hits & (1u << e)) { a.ea_ts[row] = ts_[e]; a.ea_key[row] = key_[e]; a.ea_val[row] = vb_[e]; ++row; }
-            }
-        }
+        for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
+        if ((ok_mask & in_mask) != in_mask) err |= ERRB_BAD_INPUT;
+        ok_mask &= in_mask;
+        if (a.efilter_enabled) nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
+        if (!a.window_enabled) continue;
 #pragma unroll
         for (int e = 0; e < INGEST_EPT; ++e) {
             const i64 ts = ts_[e]; const u64 key = key_[e];
             V v; memcpy(&v, &vb_[e], 8);
-            bool ok = in_[e];
-            if (ok && (ts < 0 || key == KEY_EMPTY)) { err |= ERRB_BAD_INPUT; ok = false; }
-            if (!a.window_enabled) continue;
             bool valid = false; u64 idx = 0;
-            if (ok) {
+            if (ok_mask & (1u << e)) {
                 max_ts = ts > max_ts ? ts : max_ts;                 // A1: currentMaxTimestamp
                 const i64 d = ts - origin_ts;
                 if (d < 0) {
-                    late++;                                          // A3: every window of this record has fired
+                    late++;                                          // A3
                 } else {
-                    // A2: pane index relative to the origin; 32-bit division on the common path
-                    const u64 prel = (a.g.slide32 && (u64)d < 0x100000000ull) ? (u64)((u32)d / a.g.slide32)
-                                                                              : (u64)d / (u64)a.g.slide;
+                    const u64 prel = (u64)d / (u64)a.g.slide;        // A2 (64-bit)
                     if (anchored && prel >= R) {
                         err |= ERRB_RING;
                     } else {
                         const i64 p = origin_pane + (i64)prel;
                         pmin = p < pmin ? p : pmin; pmax = p > pmax ? p : pmax;
-                        const u32 slot = dir_find_or_insert(a.dkeys, a.g.capacity, key, st);
+                        u32 slot;
+                        if (DENSE) { slot = key < a.g.capacity ? (u32)key : SLOT_INVALID; if (slot == SLOT_INVALID) err |= ERRB_BAD_INPUT; }
+                        else slot = dir_find_or_insert(a.dkeys, a.g.capacity, key, st);
                         if (slot != SLOT_INVALID) { valid = true; idx = (u64)((u32)p & a.g.ring_mask) * a.g.capacity + slot; }
                     }
                 }
@@ -148,18 +267,17 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_kernel(const __grid_con
             accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask);  // A5
         }
     }
-    // ---- per-warp reduction of the batch scalars, one atomic each per warp ----
-    if (a.window_enabled) {
-        late = warp_sum_u64(late); max_ts = warp_max_i64(max_ts); pmin = warp_min_i64(pmin); pmax = warp_max_i64(pmax);
-    }
-    for (int o = 16; o > 0; o >>= 1) err |= __shfl_xor_sync(0xffffffffu, err, o);
     nea = warp_sum_u64(nea);
+    for (int o = 16; o > 0; o >>= 1) err |= __shfl_xor_sync(0xffffffffu, err, o);
+    if (a.window_enabled) { late = warp_sum_u64(late); max_ts = warp_max_i64(max_ts); pmin = warp_min_i64(pmin); pmax = warp_max_i64(pmax); }
     if ((threadIdx.x & 31) == 0) {
         if (nea) atomicAdd(&st->event_alerts, nea);
-        if (late) atomicAdd(&st->late_dropped, late);
-        if (max_ts != I64_MIN_) atomicMax(&st->batch_max_ts, max_ts);
-        if (pmin <= pmax) { atomicMin(&st->min_pane, pmin); atomicMax(&st->max_pane, pmax); }
         if (err) atomicOr(&st->err_flags, err);
+        if (a.window_enabled) {
+            if (late) atomicAdd(&st->late_dropped, late);
+            if (max_ts != I64_MIN_) atomicMax(&st->batch_max_ts, max_ts);
+            if (pmin <= pmax) { atomicMin(&st->min_pane, pmin); atomicMax(&st->max_pane, pmax); }
+        }
     }
 }
 
@@ -231,6 +349,7 @@ __global__ void commit_kernel(DevState* st) {
 // ---- fire: thread per key slot; combine panes, emit, evaluate the alert, clear expired panes -----
 struct FireArgs {
     DevState* st; const u64* dkeys; Acc32* acc; WindowGeom g;
+    int dense_keys;             // 1: key == slot, no directory
     int emit_fired; int walert_source, walert_op; double mul, d0, d1, d2, thr;
     u64* f_key; i64* f_wend; i64* f_count; u64* f_sum; u64* f_min; u64* f_max; u64 f_cap;
     u64* wa_key; i64* wa_wend; double* wa_val; u64 wa_cap;
@@ -252,8 +371,8 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
     u64 fired_local = 0, alerts_local = 0;
     const u64 nslots_rounded = (C + FIRE_THREADS - 1) / FIRE_THREADS * FIRE_THREADS;   // block-uniform trip count
     for (u64 slot = (u64)blockIdx.x * blockDim.x + threadIdx.x; slot < nslots_rounded; slot += (u64)gridDim.x * blockDim.x) {
-        const bool live = slot < C && a.dkeys[slot] != KEY_EMPTY;
-        const u64 key = live ? a.dkeys[slot] : 0;
+        const u64 key = slot < C ? (a.dense_keys ? slot : a.dkeys[slot]) : KEY_EMPTY;
+        const bool live = key != KEY_EMPTY;
         for (i64 j = 0; j < nfire; ++j) {
             const i64 wend = first_end + j * slide;
             // panes of [wend - size, wend): absolute indices, clipped to the panes holding data

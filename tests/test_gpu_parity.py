@@ -111,8 +111,13 @@ CONFIGS = {
 
 @pytest.mark.parametrize("name", list(CONFIGS))
 @pytest.mark.parametrize("batch", [1000, 37_001])
-def test_window_parity_seeded(name, batch):
+@pytest.mark.parametrize("key_mode", ["hashed", "dense"])
+def test_window_parity_seeded(name, batch, key_mode):
     kw, spec = CONFIGS[name]
+    if key_mode == "dense":
+        if spec.key_kind != "uniform":
+            pytest.skip("composite (host<<32|metric) keys are not dense ids")
+        kw = dict(kw, key_mode=capi.FMQ_KEYS_DENSE)
     gpu, cpu = pair(**kw, **SMALL)
     total = 150_000
     for s in range(0, total, batch):
@@ -180,9 +185,10 @@ def test_int64_sum_wraps_like_java_long():
 # ---- keyed ValueState operators ------------------------------------------------------------------
 @pytest.mark.parametrize("vt", ["f64", "i64"])
 @pytest.mark.parametrize("reset", [1, 0])
-def test_keyed_state_parity(vt, reset):
+@pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
+def test_keyed_state_parity(vt, reset, key_mode):
     thr = 50.0 if vt == "f64" else 500_000.0
-    kw = dict(value_type=capi.FMQ_VAL_F64 if vt == "f64" else capi.FMQ_VAL_I64, rolling_max_enabled=1,
+    kw = dict(value_type=capi.FMQ_VAL_F64 if vt == "f64" else capi.FMQ_VAL_I64, rolling_max_enabled=1, key_mode=key_mode,
               consec_n=3, consec_threshold=thr, consec_reset_on_fire=reset, **SMALL)
     gpu, cpu = pair(**kw)
     spec = StreamSpec(n_keys=700, events_per_ms=5, value_type=vt)
@@ -238,6 +244,15 @@ def test_error_codes():
     with pytest.raises(capi.FmqError) as ex:
         e.poll_event_alerts()
     assert ex.value.status == 4
+
+
+def test_dense_ids_outside_the_table_are_an_input_error():
+    e = capi.Engine(window_enabled=1, agg_mask=3, window_size_ms=1000, window_slide_ms=1000, key_mode=capi.FMQ_KEYS_DENSE,
+                    table_capacity=64, pane_ring=4, max_batch=1 << 12)
+    e.push_batch(np.array([5, 6], np.int64), np.array([63, 64], np.uint64), np.ones(2))
+    with pytest.raises(capi.FmqError) as ex:
+        e.counters()
+    assert ex.value.status == 6
 
 
 def test_partial_polls_drain_everything():
