@@ -244,7 +244,7 @@ static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* v
         a.efilter_enabled = c.efilter_enabled; a.efilter_op = c.efilter_op; a.efilter_thr = c.efilter_threshold;
         a.ea_ts = h->ea_ts; a.ea_key = h->ea_key; a.ea_val = h->ea_val; a.ea_cap = h->ea_cap;
         const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
-        size_t blocks = (n + tile - 1) / tile; const size_t maxb = (size_t)h->num_sms * 8;
+        size_t blocks = (n + tile - 1) / tile; const size_t maxb = (size_t)h->num_sms * FMQ_INGEST_MIN_BLOCKS;   // persistent: resident blocks only
         if (blocks > maxb) blocks = maxb;
         // The kernels pick themselves on the device-resident stream position (no host round trip):
         // the fast kernel returns at once unless a watermark anchors the pane origin, the generic
@@ -252,8 +252,9 @@ static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* v
         const bool fast_geom = !c.window_enabled || (h->g.slide32 != 0 && (u64)h->ring * h->g.slide32 < 0x100000000ull);
         const bool dense = c.key_mode == FMQ_KEYS_DENSE;
         if (c.window_enabled && fast_geom) {
-            if (dense) ingest_fast_kernel<V, true><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a);
-            else       ingest_fast_kernel<V, false><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a);
+            auto kfn = dense ? ingest_fast_kernel<V, true> : ingest_fast_kernel<V, false>;
+            CU(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, INGEST_SMEM_BYTES));
+            kfn<<<(unsigned)blocks, INGEST_THREADS, INGEST_SMEM_BYTES, h->stream>>>(a);
             LAUNCHED(h, "ingest_fast_kernel");
         }
         if (!c.window_enabled || !fast_geom || !h->anchored_known) {

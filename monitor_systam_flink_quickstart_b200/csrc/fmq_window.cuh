@@ -67,7 +67,7 @@ __device__ __forceinline__ void accumulate_pair(Acc32* __restrict__ acc, bool va
 constexpr int INGEST_THREADS = 256;
 constexpr int INGEST_EPT = 4;          // events per thread per tile (one 32 B load per column)
 #ifndef FMQ_INGEST_MIN_BLOCKS
-#define FMQ_INGEST_MIN_BLOCKS 2
+#define FMQ_INGEST_MIN_BLOCKS 3
 #endif
 
 // Loads the (up to) four consecutive events of this thread.
@@ -123,92 +123,179 @@ __device__ __forceinline__ bool ingest_fast_ok(const DevState* st, const WindowG
 }
 
 // ---- ingest, fast kernel --------------------------------------------------------------------------
-// Preconditions (checked by the host): the stream is anchored (a watermark exists, so the pane
+// Preconditions (checked on the device): the stream is anchored (a watermark exists, so the pane
 // origin is known) and pane_ring * slide < 2^32, so the pane of a record is a 32-bit quotient of
-// (ts - origin).  The hot loop is branch-free per event: late test, pane, home-bucket match and the
-// pair-lane accumulate are all predicated; only events whose key is not in its home bucket leave it.
+// (ts - origin).  Per event the late test, the pane and the accumulate are predicated, not branched.
+//
+// Staging: the three event columns are streamed into shared memory by the TMA engine
+// (cp.async.bulk 1-D copies completing on an mbarrier, L2 evict-first policy) through a ring of
+// INGEST_STAGES tiles per block, issued INGEST_STAGES tiles ahead by one thread.  The compute
+// threads therefore never wait on HBM latency themselves: their only global-memory traffic is the
+// directory bucket load (hashed keys) and the fire-and-forget RED updates.
+constexpr int INGEST_STAGES = 3;
+constexpr int INGEST_TILE = INGEST_THREADS * INGEST_EPT;                       // 1024 events = 3 x 8 KB
+constexpr int INGEST_SMEM_BYTES = INGEST_STAGES * 3 * INGEST_TILE * 8;         // 72 KB of dynamic shared memory
+
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64* bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(u64* bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}"
+        ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (TMA, SASS UBLKCP), byte count signalled on `bar`, L2 evict-first
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, u32 bytes, u64* bar, u64 policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
+}
+
+struct IngestRun {            // per-thread running scalars of one batch
+    u64 late = 0, nea = 0; i64 dmax = I64_MIN_; u32 pmin = 0xFFFFFFFFu, pmax = 0; u32 err = 0;
+};
+struct IngestConst {
+    i64 origin_ts; u32 origin_ring, slide, recip; u64 span, nbuckets;
+};
+
+// One tile of the fast path: the four events held by this thread.  Called by every thread of the block.
+template <typename V, bool DENSE>
+__device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
+                                            const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 in_mask) {
+    u32 ok_mask = 0;
+#pragma unroll
+    for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
+    if ((ok_mask & in_mask) != in_mask) r.err |= ERRB_BAD_INPUT;
+    ok_mask &= in_mask;
+    if (a.efilter_enabled) r.nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
+    if (!a.window_enabled) return;
+    // ---- per event: A1 max-ts, A3 late test, A2 pane, and (hashed keys) the home-bucket load:
+    //      all four directory loads are in flight before any of them is consumed ----
+    u32 ring_[INGEST_EPT]; u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0;
+#pragma unroll
+    for (int e = 0; e < INGEST_EPT; ++e) {
+        const bool ok = ok_mask & (1u << e);
+        const i64 d = ts_[e] - k.origin_ts;
+        r.dmax = (ok && d > r.dmax) ? d : r.dmax;                  // A1 (ts = origin + d)
+        const bool is_late = ok && d < 0;                          // A3: every window of this record has fired
+        r.late += is_late ? 1 : 0;
+        const bool beyond = ok && d >= 0 && (u64)d >= k.span;      // would alias an older pane of the ring
+        r.err |= beyond ? ERRB_RING : 0u;
+        const u32 du = (u32)d;
+        u32 q = __umulhi(du, k.recip);                             // A2: q <= du / slide <= q + 2
+        u32 rem = du - q * k.slide;
+        if (rem >= k.slide) { q++; rem -= k.slide; }
+        if (rem >= k.slide) { q++; }
+        bool act = ok && d >= 0 && !beyond;
+        if (DENSE) {
+            if (act && key_[e] >= a.g.capacity) { r.err |= ERRB_BAD_INPUT; act = false; }   // id outside the table
+        } else {
+            hb_[e] = dir_home_bucket(key_[e], k.nbuckets);
+            if (act) kv_[e] = ld_bucket(a.dkeys + hb_[e] * 4);
+        }
+        r.pmin = (act && q < r.pmin) ? q : r.pmin; r.pmax = (act && q > r.pmax) ? q : r.pmax;
+        ring_[e] = (k.origin_ring + q) & a.g.ring_mask;
+        act_mask |= act ? (1u << e) : 0u;
+    }
+    // ---- A5: slot -> pair-lane accumulate ----
+#pragma unroll
+    for (int e = 0; e < INGEST_EPT; ++e) {
+        bool valid = act_mask & (1u << e);
+        u32 slot = (u32)key_[e];                                   // dense ids index the table directly
+        if (!DENSE) {
+            if (valid) slot = dir_resolve_inline(a.dkeys, k.nbuckets, key_[e], hb_[e], kv_[e], st);
+            valid = valid && slot != SLOT_INVALID;
+        }
+        const u64 idx = (u64)ring_[e] * a.g.capacity + slot;
+        V v; memcpy(&v, &vb_[e], 8);
+        accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask);
+    }
+}
+
 template <typename V, bool DENSE>
 __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_fast_kernel(const __grid_constant__ IngestArgs a) {
+    extern __shared__ __align__(128) unsigned char ingest_smem[];
+    __shared__ __align__(8) u64 bars[INGEST_STAGES];
     DevState* st = a.st;
     if (!ingest_fast_ok(st, a.g)) return;                        // the generic kernel handles this batch
-    const i64 origin_ts = st->origin_ts;
-    const u32 origin_ring = (u32)st->origin_pane & a.g.ring_mask;
-    const u32 slide = a.g.slide32;
-    const u32 recip = 0xFFFFFFFFu / slide;                      // floor((2^32-1)/slide): quotient estimate, never too big
-    const u64 span = (u64)(a.g.ring_mask + 1) * slide;           // first d that falls outside the ring (< 2^32)
-    const u64 nbuckets = a.g.capacity >> 2;
+    IngestConst k;
+    k.origin_ts = st->origin_ts;
+    k.origin_ring = (u32)st->origin_pane & a.g.ring_mask;
+    k.slide = a.g.slide32;
+    k.recip = 0xFFFFFFFFu / k.slide;                             // floor((2^32-1)/slide): quotient estimate, never too big
+    k.span = (u64)(a.g.ring_mask + 1) * k.slide;                 // first d that falls outside the ring (< 2^32)
+    k.nbuckets = a.g.capacity >> 2;
+    IngestRun r;
 
-    u64 late = 0, nea = 0; i64 dmax = I64_MIN_; u32 pmin = 0xFFFFFFFFu, pmax = 0; u32 err = 0;
-
-    const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
-    const size_t ntiles = (a.n + tile - 1) / tile;
-    for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const size_t i = t * tile + (size_t)threadIdx.x * INGEST_EPT;
+    const V* __restrict__ val = static_cast<const V*>(a.val);
+    // bulk copies need 16-byte aligned, whole tiles; the (at most one) ragged tile goes the direct way
+    const size_t full_tiles = a.vec32 ? a.n / INGEST_TILE : 0;
+    u64 policy;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+    auto stage_ptr = [&](int s, int col) { return reinterpret_cast<u64*>(ingest_smem + ((size_t)(s * 3 + col) * INGEST_TILE) * 8); };
+    auto issue = [&](size_t t, int s) {                          // one thread: arm the barrier, start 3 x 8 KB copies
+        mbar_expect_tx(&bars[s], 3u * INGEST_TILE * 8u);
+        tma_load_1d(stage_ptr(s, 0), a.ts + t * INGEST_TILE, INGEST_TILE * 8u, &bars[s], policy);
+        tma_load_1d(stage_ptr(s, 1), a.key + t * INGEST_TILE, INGEST_TILE * 8u, &bars[s], policy);
+        tma_load_1d(stage_ptr(s, 2), val + t * INGEST_TILE, INGEST_TILE * 8u, &bars[s], policy);
+    };
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < INGEST_STAGES; ++s) mbar_init(&bars[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        for (int s = 0; s < INGEST_STAGES; ++s) {
+            const size_t t = blockIdx.x + (size_t)s * gridDim.x;
+            if (t < full_tiles) issue(t, s);
+        }
+    }
+    __syncthreads();
+    size_t it = 0;
+    for (size_t t = blockIdx.x; t < full_tiles; t += gridDim.x, ++it) {
+        const int s = (int)(it % INGEST_STAGES);
+        mbar_wait(&bars[s], (u32)((it / INGEST_STAGES) & 1));
+        // thread x takes events x, x+256, x+512, x+768 of the tile: conflict-free 8-byte shared loads
+        i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT];
+        const u64 *sts = stage_ptr(s, 0), *skey = stage_ptr(s, 1), *sval = stage_ptr(s, 2);
+#pragma unroll
+        for (int e = 0; e < INGEST_EPT; ++e) {
+            ts_[e] = (i64)sts[threadIdx.x + e * INGEST_THREADS]; key_[e] = skey[threadIdx.x + e * INGEST_THREADS]; vb_[e] = sval[threadIdx.x + e * INGEST_THREADS];
+        }
+        __syncthreads();                                         // every thread has its events in registers: the stage is free
+        if (threadIdx.x == 0) {
+            const size_t tn = t + (size_t)INGEST_STAGES * gridDim.x;
+            if (tn < full_tiles) issue(tn, s);
+        }
+        ingest_tile<V, DENSE>(a, st, k, r, ts_, key_, vb_, 0xFu);
+    }
+    // ragged tail (and unaligned columns): direct 8-byte loads
+    const size_t tail_tiles = (a.n - full_tiles * INGEST_TILE + INGEST_TILE - 1) / INGEST_TILE;
+    for (size_t t = blockIdx.x; t < tail_tiles; t += gridDim.x) {
+        const size_t i = (full_tiles + t) * INGEST_TILE + (size_t)threadIdx.x * INGEST_EPT;
         i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; u32 in_mask;
         load_events<V>(a, i, ts_, key_, vb_, in_mask);
-        u32 ok_mask = 0;
-#pragma unroll
-        for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
-        if ((ok_mask & in_mask) != in_mask) err |= ERRB_BAD_INPUT;
-        ok_mask &= in_mask;
-        if (a.efilter_enabled) nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
-        if (!a.window_enabled) continue;
-        // ---- per event: A1 max-ts, A3 late test, A2 pane, and (hashed keys) the home-bucket load:
-        //      all four directory loads are in flight before any of them is consumed ----
-        u32 ring_[INGEST_EPT]; u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0;
-#pragma unroll
-        for (int e = 0; e < INGEST_EPT; ++e) {
-            const bool ok = ok_mask & (1u << e);
-            const i64 d = ts_[e] - origin_ts;
-            dmax = (ok && d > dmax) ? d : dmax;                        // A1 (ts = origin + d)
-            const bool is_late = ok && d < 0;                          // A3: every window of this record has fired
-            late += is_late ? 1 : 0;
-            const bool beyond = ok && d >= 0 && (u64)d >= span;        // would alias an older pane of the ring
-            err |= beyond ? ERRB_RING : 0u;
-            const u32 du = (u32)d;
-            u32 q = __umulhi(du, recip);                               // A2: q <= du / slide <= q + 2
-            u32 r = du - q * slide;
-            if (r >= slide) { q++; r -= slide; }
-            if (r >= slide) { q++; }
-            bool act = ok && d >= 0 && !beyond;
-            if (DENSE) {
-                if (act && key_[e] >= a.g.capacity) { err |= ERRB_BAD_INPUT; act = false; }   // id outside the table
-            } else {
-                hb_[e] = dir_home_bucket(key_[e], nbuckets);
-                if (act) kv_[e] = ld_bucket(a.dkeys + hb_[e] * 4);
-            }
-            pmin = (act && q < pmin) ? q : pmin; pmax = (act && q > pmax) ? q : pmax;
-            ring_[e] = (origin_ring + q) & a.g.ring_mask;
-            act_mask |= act ? (1u << e) : 0u;
-        }
-        // ---- A5: slot -> pair-lane accumulate ----
-#pragma unroll
-        for (int e = 0; e < INGEST_EPT; ++e) {
-            bool valid = act_mask & (1u << e);
-            u32 slot = (u32)key_[e];                                   // dense ids index the table directly
-            if (!DENSE) {
-                if (valid) slot = dir_resolve_inline(a.dkeys, nbuckets, key_[e], hb_[e], kv_[e], st);
-                valid = valid && slot != SLOT_INVALID;
-            }
-            const u64 idx = (u64)ring_[e] * a.g.capacity + slot;
-            V v; memcpy(&v, &vb_[e], 8);
-            accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask);
-        }
+        ingest_tile<V, DENSE>(a, st, k, r, ts_, key_, vb_, in_mask);
     }
     // ---- per-warp reduction of the batch scalars, one atomic each per warp ----
-    nea = warp_sum_u64(nea);
-    for (int o = 16; o > 0; o >>= 1) err |= __shfl_xor_sync(0xffffffffu, err, o);
+    r.nea = warp_sum_u64(r.nea);
+    for (int o = 16; o > 0; o >>= 1) r.err |= __shfl_xor_sync(0xffffffffu, r.err, o);
     if (a.window_enabled) {
-        late = warp_sum_u64(late); dmax = warp_max_i64(dmax);
-        pmin = __reduce_min_sync(0xffffffffu, pmin); pmax = __reduce_max_sync(0xffffffffu, pmax);
+        r.late = warp_sum_u64(r.late); r.dmax = warp_max_i64(r.dmax);
+        r.pmin = __reduce_min_sync(0xffffffffu, r.pmin); r.pmax = __reduce_max_sync(0xffffffffu, r.pmax);
     }
     if ((threadIdx.x & 31) == 0) {
-        if (nea) atomicAdd(&st->event_alerts, nea);
-        if (err) atomicOr(&st->err_flags, err);
+        if (r.nea) atomicAdd(&st->event_alerts, r.nea);
+        if (r.err) atomicOr(&st->err_flags, r.err);
         if (a.window_enabled) {
-            if (late) atomicAdd(&st->late_dropped, late);
-            if (dmax != I64_MIN_) atomicMax(&st->batch_max_ts, origin_ts + dmax);
-            if (pmin <= pmax) { atomicMin(&st->min_pane, st->origin_pane + (i64)pmin); atomicMax(&st->max_pane, st->origin_pane + (i64)pmax); }
+            if (r.late) atomicAdd(&st->late_dropped, r.late);
+            if (r.dmax != I64_MIN_) atomicMax(&st->batch_max_ts, k.origin_ts + r.dmax);
+            if (r.pmin <= r.pmax) { atomicMin(&st->min_pane, st->origin_pane + (i64)r.pmin); atomicMax(&st->max_pane, st->origin_pane + (i64)r.pmax); }
         }
     }
 }
