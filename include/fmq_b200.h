@@ -255,6 +255,32 @@ int32_t fmq_partition_by_owner(fmq_handle* h, const int64_t* ts, const uint64_t*
                                int64_t* ts_out, uint64_t* key_out, void* val_out,
                                uint64_t* counts);
 
+/* Largest batch fmq_partition_by_owner_noalloc accepts (events). */
+#define FMQ_NOALLOC_MAX_EVENTS 4194304
+
+/* No counterpart in the reference.  The same stable owner split as fmq_partition_by_owner, for
+ * callers that may not allocate device memory while they run: an operator thread that shares its
+ * GPU with other subtasks (cudaMalloc / cudaFree synchronise the whole device and would stall
+ * their kernels), or a process that has handed all device memory to its own arena, where a
+ * driver allocation can simply fail.  The call needs no handle and calls no cudaMalloc, cudaFree
+ * or any other allocating routine: the only scratch it uses is a fixed ~2 MB array built into the
+ * library's device image (every GPU that loads the library carries it until the process exits).
+ *   - n may not exceed FMQ_NOALLOC_MAX_EVENTS; larger batches are refused with FMQ_ERR_BAD_ARG
+ *     (message via fmq_last_error(NULL)) — split them, or use fmq_partition_by_owner.
+ *   - ts/key/val and the *_out columns are device pointers owned by the caller; counts[world] is
+ *     host memory.  The work is queued on `stream` (a cudaStream_t, NULL = default stream) of
+ *     `device`, and the call returns after that stream has drained (the counts are read back).
+ *   - The first call on each device looks up the device address of the built-in scratch once.
+ *     Make that first call before starting any stream capture.
+ *   - All calls on one device share the one scratch array, which keeps whatever the previous call
+ *     left in it.  Nothing in it needs clearing (every counter is stored before it is read), but
+ *     two calls whose kernels can overlap on the same GPU — different streams, different
+ *     threads — race on it: run them one after the other. */
+int32_t fmq_partition_by_owner_noalloc(int32_t device, void* stream, const int64_t* ts,
+                                       const uint64_t* key, const void* val, size_t n,
+                                       uint32_t world, int64_t* ts_out, uint64_t* key_out,
+                                       void* val_out, uint64_t* counts);
+
 #ifdef __cplusplus
 }
 #endif

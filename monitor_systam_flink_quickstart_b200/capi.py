@@ -145,6 +145,7 @@ def _declare(lib, p: str, has_mem: bool = True):
         sig("flink_key_group", [i32, i32])
         sig("flink_subtask", [i32, i32, i32])
         sig("partition_by_owner", [vp, vp, vp, vp, sz, C.c_uint32, vp, vp, vp, vp])
+        sig("partition_by_owner_noalloc", [i32, vp, vp, vp, vp, sz, C.c_uint32, vp, vp, vp, vp])
 
 
 def _ptr(a) -> int:

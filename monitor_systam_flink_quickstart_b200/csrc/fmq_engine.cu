@@ -6,6 +6,7 @@
 #include <cstring>
 #include <string>
 #include <new>
+#include <mutex>
 #include "../../include/fmq_b200.h"
 #include "fmq_device.cuh"
 #include "fmq_window.cuh"
@@ -504,3 +505,78 @@ int32_t fmq_partition_by_owner(fmq_handle* h, const int64_t* ts, const uint64_t*
 }
 
 }  // extern "C"
+
+// ---- owner split for callers that must not allocate ------------------------------------------------
+// Same stable multi-split as fmq_partition_by_owner, but its scratch (the per-chunk digit counters
+// and the scan's tile sums) lives in a fixed file-scope device array instead of a handle's
+// cudaMalloc'ed buffers, so the call performs no allocation of any kind.  See include/fmq_b200.h.
+namespace {
+constexpr size_t NOALLOC_MAX_CHUNKS = FMQ_NOALLOC_MAX_EVENTS / RS_CHUNK;                 // 2048
+constexpr size_t NOALLOC_COUNTS = (size_t)RS_DIGITS * NOALLOC_MAX_CHUNKS;                 // 524288 counters
+constexpr size_t NOALLOC_TILES = (NOALLOC_COUNTS + SCAN_TILE - 1) / SCAN_TILE;            // 128 tile sums
+// ~2 MB per GPU that loads this library, held until the process exits.
+static __device__ __align__(256) unsigned int g_noalloc_scratch[NOALLOC_COUNTS + NOALLOC_TILES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+u32* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};   // device address of g_noalloc_scratch, per device
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, never a device address: the
+// address each device gave its copy is asked for once, with that device current.
+int noalloc_scratch_for(int device, u32** out) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            g_create_err = std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e);
+            return FMQ_ERR_CUDA;
+        }
+        g_noalloc_ptr[device] = static_cast<u32*>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return FMQ_OK;
+}
+#define NA_CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { g_create_err = std::string(#call) + ": " + cudaGetErrorString(e_); return FMQ_ERR_CUDA; } } while (0)
+}  // namespace
+
+extern "C" int32_t fmq_partition_by_owner_noalloc(int32_t device, void* stream_, const int64_t* ts, const uint64_t* key, const void* val,
+                                                  size_t n, uint32_t world, int64_t* ts_out, uint64_t* key_out, void* val_out,
+                                                  uint64_t* counts) {
+    if (!counts || world == 0 || world > RS_DIGITS) { g_create_err = "need counts != NULL and 1 <= world <= 256"; return FMQ_ERR_BAD_ARG; }
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) { g_create_err = "device ordinal out of range"; return FMQ_ERR_BAD_ARG; }
+    if (n > FMQ_NOALLOC_MAX_EVENTS) {
+        g_create_err = "fmq_partition_by_owner_noalloc: n exceeds FMQ_NOALLOC_MAX_EVENTS (" FMQ_STR(FMQ_NOALLOC_MAX_EVENTS)
+                       " events, the size of the built-in scratch); split the batch or use fmq_partition_by_owner";
+        return FMQ_ERR_BAD_ARG;
+    }
+    for (uint32_t w = 0; w < world; ++w) counts[w] = 0;
+    if (n == 0) return FMQ_OK;
+    if (!ts || !key || !val || !ts_out || !key_out || !val_out) { g_create_err = "null column pointer"; return FMQ_ERR_BAD_ARG; }
+    NA_CU(cudaSetDevice(device));
+    u32* scratch = nullptr;
+    int st = noalloc_scratch_for(device, &scratch); if (st) return st;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    u32* d_counts = scratch; u32* d_tiles = scratch + NOALLOC_COUNTS;
+    // Nothing in the scratch has to start at zero: the histogram kernel stores (not adds) every one
+    // of the 256 x nchunks counters it owns and the scan stores every tile sum before reading it, so
+    // whatever the previous call left behind is overwritten before it can be read.
+    const u32 nchunks = rs_num_chunks(n);
+    const u32 nblocks = (nchunks + RS_WARPS - 1) / RS_WARPS;
+    const size_t len = (size_t)RS_DIGITS * nchunks;
+    const u32 ntiles = (u32)((len + SCAN_TILE - 1) / SCAN_TILE);
+    OwnerDigit dg{(const u64*)key, world};
+    MoveEvent3 mv{(const u64*)ts, (const u64*)key, (const u64*)val, (u64*)ts_out, (u64*)key_out, (u64*)val_out};
+    rs_hist_kernel<<<nblocks, RS_THREADS, 0, stream>>>(n, nchunks, dg, d_counts);
+    scan_tile_sums<<<ntiles, SCAN_THREADS, 0, stream>>>(d_counts, len, d_tiles);
+    scan_tile_offsets<<<1, SCAN_THREADS, 0, stream>>>(d_tiles, ntiles);
+    scan_apply<<<ntiles, SCAN_THREADS, 0, stream>>>(d_counts, len, d_tiles);
+    rs_scatter_kernel<<<nblocks, RS_THREADS, 0, stream>>>(n, nchunks, dg, mv, d_counts);
+    NA_CU(cudaGetLastError());
+    u32 starts[RS_DIGITS];
+    NA_CU(cudaMemcpy2DAsync(starts, 4, d_counts, (size_t)nchunks * 4, 4, world, cudaMemcpyDeviceToHost, stream));
+    NA_CU(cudaStreamSynchronize(stream));
+    for (uint32_t w = 0; w < world; ++w) counts[w] = (w + 1 < world ? starts[w + 1] : (u32)n) - starts[w];
+    return FMQ_OK;
+}
+
