@@ -144,7 +144,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--keys", type=int, default=N_KEYS, help="experiment: number of distinct hosts")
     ap.add_argument("--load", type=float, default=1.5, help="experiment: directory slots per key")
-    ap.add_argument("--key-mode", default="hashed", choices=["hashed", "dense"],
+    ap.add_argument("--key-mode", default="dense", choices=["hashed", "dense"],
                     help="hashed: arbitrary u64 keys through the hash directory; dense: dictionary ids index the table")
     ap.add_argument("--no-efilter", action="store_true", help="experiment: drop the per-event filter from the workload")
     args = ap.parse_args()

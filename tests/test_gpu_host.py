@@ -1,0 +1,102 @@
+"""GPU tests of the host-side mirrors of the reference's operator interface: the C++ operator
+(compiled against the C ABI only) and the Python operator, both replaying the reference's
+event-time session, and the NCCL-sharded operator on 2 GPUs when the box has them."""
+import json
+import os
+import pickle
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+from monitor_systam_flink_quickstart_b200 import capi
+from monitor_systam_flink_quickstart_b200.operator import GpuWindowAggOperator
+from monitor_systam_flink_quickstart_b200.text import parse_flow_line
+from oracle_lib import OracleEngine, assert_events_equal, assert_fired_equal
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+G = json.load(open(os.path.join(ROOT, "tests", "golden", "readme_sessions.json"), encoding="utf-8"))
+
+
+def test_cpp_operator_mirror_replays_g7():
+    exe = os.path.join(ROOT, "monitor_systam_flink_quickstart_b200", "host", "operator_demo")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", os.path.dirname(exe)])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "(www.163.com,0.0012715657552083333)" in r.stdout and "(www.163.com,0.0012969970703125)" in r.stdout
+    assert "alerts=132 late_dropped=1 OK" in r.stdout
+
+
+def test_python_operator_mirror_replays_g7_on_gpu():
+    out = []
+    op = GpuWindowAggOperator(lambda kind, row: out.append((kind, row)), batch_capacity=64,
+                              value_type=capi.FMQ_VAL_I64, window_enabled=1, agg_mask=3, emit_fired=1,
+                              window_size_ms=300000, window_slide_ms=5000, max_out_of_orderness_ms=60000,
+                              walert_source=capi.FMQ_ALERT_SUM, walert_op=capi.FMQ_CMP_LT, walert_mul=8.0, walert_div0=60.0,
+                              walert_div1=1024.0, walert_div2=1024.0, walert_threshold=100.0, table_capacity=256, pane_ring=128).open()
+    for line in G["G7_event_time"]["input"]:
+        t, ch, flow = parse_flow_line(line)
+        op.process_element(t, ch, flow)
+        op.process_watermark()
+    assert op.metrics()["late_dropped"] == 1
+    printed = [f"({row[0]},{row[2]!r})" for kind, row in out if kind == "window_alert"]
+    assert all(w.split("> ")[1] in printed for w in G["G7_event_time"]["output"]) and len(printed) == 60
+    sums = [row[3] for kind, row in out if kind == "window"]
+    assert sums == [10000] * 12 + [10100] * 12 + [10200] * 36
+    op.close()
+
+
+# ---- 2 GPUs over NCCL ------------------------------------------------------------------------------
+KW = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=5000, max_out_of_orderness_ms=3000,
+          efilter_enabled=1, efilter_threshold=90.0, consec_n=3, consec_threshold=50.0, consec_reset_on_fire=1,
+          table_capacity=1 << 12, pane_ring=64, max_batch=1 << 16)
+NB, B = 5, 20_000
+
+
+def _nccl_worker(rank, world, port, outdir):
+    import torch
+    import torch.distributed as dist
+    from monitor_systam_flink_quickstart_b200.shard import ShardedOperator
+    from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_torch
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
+    eng = capi.Engine(device=rank, **KW)
+    op = ShardedOperator(eng, rank, world, KW["max_out_of_orderness_ms"])
+    for b in range(NB):
+        ts, key, val = generate_torch(spec, (b * world + rank) * B, B, device=f"cuda:{rank}")
+        torch.cuda.synchronize()
+        op.process_batch(ts, key, val)
+    op.flush()
+    res = dict(fired=eng.poll_fired(), ealerts=eng.poll_event_alerts(), calerts=eng.poll_consec_alerts(), counters=eng.counters())
+    pickle.dump(res, open(os.path.join(outdir, f"r{rank}.pkl"), "wb"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_gpu_sharded_equals_oracle():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy
+    world, port = 2, 29600 + os.getpid() % 2000
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_nccl_worker, args=(world, port, d), nprocs=world, join=True)
+        res = [pickle.load(open(os.path.join(d, f"r{r}.pkl"), "rb")) for r in range(world)]
+    spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
+    okw = {k: v for k, v in KW.items()}
+    ref = OracleEngine(**okw)
+    for b in range(NB):
+        parts = [generate_numpy(spec, (b * world + r) * B, B) for r in range(world)]
+        ref.push_batch(*[np.concatenate([p[i] for p in parts]) for i in range(3)])
+    ref.flush()
+    cat = lambda name, cls, fields: cls(*[np.concatenate([getattr(r[name], f) for r in res]) for f in fields])  # noqa: E731
+    assert_fired_equal(cat("fired", capi.Fired, ("key", "window_end", "count", "sum", "min", "max")), ref.poll_fired())
+    assert_events_equal(cat("ealerts", capi.EventRows, ("ts", "key", "val")), ref.poll_event_alerts())
+    assert_events_equal(cat("calerts", capi.EventRows, ("ts", "key", "val")), ref.poll_consec_alerts())
+    assert sum(r["counters"]["late_dropped"] for r in res) == ref.counters()["late_dropped"]
