@@ -55,46 +55,57 @@ def stream_spec(StreamSpec, n_keys=N_KEYS):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons while the timed region runs."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons while the timed region runs, read through NVML in a thread.
+    (An `nvidia-smi -lms` child process was measured to stall every synchronising CUDA call of the
+    sharded step — 27 ms/step instead of 2.1 — so it is only the fallback.)"""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, index):
-        self.rows, self.p = [], None
+    def __init__(self, index, period_s=0.02):
+        self.samples, self.stop_flag, self.index, self.period = [], False, index, period_s
+        self.nvml = None
         try:
-            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
-                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            # CUDA_VISIBLE_DEVICES-relative index -> NVML handle by UUID-free approach: same order unless remapped
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
         except Exception:
-            self.p = None
+            self.nvml = None
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
 
-    def _read(self):
-        for line in self.p.stdout:
-            self.rows.append((time.time(), line.strip()))
+    def _run(self):
+        if self.nvml is None:
+            return
+        n = self.nvml
+        while not self.stop_flag:
+            try:
+                mhz = float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM))
+                try:
+                    rs = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    rs = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.samples.append((time.time(), mhz, rs))
+            except Exception:
+                pass
+            time.sleep(self.period)
 
     def stop(self, t0, t1):
-        if not self.p:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.p.terminate()
-        sm, mx, reasons = [], None, set()
-        for t, line in self.rows:
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 8:
-                continue
-            try:
-                mx = float(f[1])
-                if t0 - 0.05 <= t <= t1 + 0.05:
-                    sm.append(float(f[0]))
-                    for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
-                        if v.lower().startswith("active"):
-                            reasons.add(name)
-            except ValueError:
-                continue
-        if not sm:   # region shorter than the sampling period: take every sample
-            sm = [float(l.split(",")[0]) for _, l in self.rows if l.split(",")[0].strip().replace(".", "").isdigit()]
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+        self.stop_flag = True
+        self.t.join(timeout=1.0)
+        if self.nvml is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable"], "samples": 0}
+        inside = [(m, r) for t, m, r in self.samples if t0 - 0.02 <= t <= t1 + 0.02] or [(m, r) for _, m, r in self.samples]
+        reasons = set()
+        for _, r in inside:
+            for bit, name in self.REASONS.items():
+                if r & bit:
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median([m for m, _ in inside])) if inside else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(reasons), "samples": len(inside), "source": "nvml"}
 
 
 def measured_peak():
@@ -116,6 +127,9 @@ def ncu_traffic():
 
 
 # --------------------------------------------------------------------------------------------------
+os.environ.setdefault("TORCH_NCCL_AVOID_RECORD_STREAMS", "1")
+
+
 def cpu_reference_run(steps, warmup, sample_events, threads, capi, ParallelOracle, StreamSpec, generate_numpy):
     """The CPU restatement on host cores: `steps` timed steps of `sample_events` events each."""
     kw = workload_kwargs(capi, sample_events)
@@ -139,9 +153,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch-log2", type=int, default=24, help="events per micro-batch per GPU (log2)")
-    ap.add_argument("--cpu-sample-log2", type=int, default=21, help="events per step of the CPU baseline")
+    ap.add_argument("--cpu-sample-log2", type=int, default=23, help="events per step of the CPU baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-variants", action="store_true")
+    ap.add_argument("--no-clocks", action="store_true", help="experiment: do not sample nvidia-smi during the timed region")
     ap.add_argument("--keys", type=int, default=N_KEYS, help="experiment: number of distinct hosts")
     ap.add_argument("--load", type=float, default=1.5, help="experiment: directory slots per key")
     ap.add_argument("--key-mode", default="dense", choices=["hashed", "dense"],
@@ -201,7 +217,7 @@ def main():
         kw["efilter_enabled"] = 0
     if args.key_mode == "dense":
         kw["key_mode"] = capi.FMQ_KEYS_DENSE
-        kw["table_capacity"] = args.keys
+        kw["table_capacity"] = (args.keys + world - 1) // world        # rank-local dense ids (id // world)
     # outputs stay in HBM during the timed region (polled after it): size the buffers for K steps.
     # ~1 fired row per 10 events (one report per host per second, 10 s windows), ~10 % event alerts.
     per_rank_events = B * max(K, W)
@@ -210,9 +226,6 @@ def main():
         kw["fired_capacity"] = int(per_rank_events * 0.125 * 4) + 4 * N_KEYS
     kw["walert_capacity"] = kw["fired_capacity"]
     kw["ealert_capacity"] = int(per_rank_events * 0.115) + 65536
-    eng = capi.Engine(**kw)
-    stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local_rank))
-
     # synthetic inputs, resident in HBM before any timing: rank r owns slice r of every global batch
     def dev_batch(step):
         start = (step * world + rank) * B
@@ -221,75 +234,90 @@ def main():
     batches = [dev_batch(s) for s in range(W + K)]
     torch.cuda.synchronize()
 
-    sharded = None
-    if world > 1:
-        from monitor_systam_flink_quickstart_b200.shard import ShardedOperator
-        sharded = ShardedOperator(eng, rank, world, BOUND_MS)
+    def measure(kw, with_clocks):
+        """W warm-up + K timed steps with device-resident inputs; CUDA events on the engine's stream
+        (every kernel, copy and collective of a step is ordered on it)."""
+        eng = capi.Engine(**kw)
+        stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local_rank))
+        sharded = None
+        if world > 1:
+            from monitor_systam_flink_quickstart_b200.shard import ShardedOperator
+            sharded = ShardedOperator(eng, rank, world, BOUND_MS)
 
-    def step(b):
-        if sharded:
-            sharded.process_batch(*batches[b])
-        else:
-            eng.push_batch(*batches[b])
+        def step(b):
+            if sharded:
+                sharded.process_batch(*batches[b])
+            else:
+                eng.push_batch(*batches[b])
 
-    def drain():
+        def drain():
+            eng.synchronize()
+            return len(eng.poll_fired()), len(eng.poll_window_alerts()), len(eng.poll_event_alerts())
+
+        # the sampler thread starts before the warm-up so that the timed region follows the last
+        # warm-up step without an idle gap (an idle gap of 0.25 s was measured to cost the first
+        # NCCL step after it ~250 ms)
+        sampler = ClockSampler(local_rank) if (with_clocks and rank == 0 and not args.no_clocks) else None
+        for b in range(W):
+            step(b)
+        drain()
+        c0 = eng.counters()
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_wall0 = time.time()
+        ev0.record(stream)
+        for b in range(W, W + K):
+            step(b)
+        ev1.record(stream)
         eng.synchronize()
-        f = eng.poll_fired(); a = eng.poll_window_alerts(); e = eng.poll_event_alerts()
-        return len(f), len(a), len(e)
+        torch.cuda.synchronize()
+        t_wall1 = time.time()
+        if dist:
+            dist.barrier()
+        ms = ev0.elapsed_time(ev1)
+        clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+        # per-kernel timing over the timed pushes (CUDA events on the engine stream, recorded by the library)
+        ing = [eng.push_timing(back)["ingest_ms"] for back in range(min(K, 64))]
+        fire = [eng.push_timing(back)["fire_ms"] for back in range(min(K, 64))]
+        c1 = eng.counters()
+        delta = {k: c1[k] - c0[k] for k in ("gpu_launches", "event_alerts", "late_dropped", "windows_fired", "events_in")}
+        drain()
+        eng.close()
+        return ms, float(np.mean(ing)), float(np.mean(fire)), delta, clocks
 
-    for b in range(W):
-        step(b)
-    drain()
-    c0 = eng.counters()
-
-    # -------- timed region: device-resident inputs --------
-    if dist:
-        dist.barrier()
-    torch.cuda.synchronize()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    time.sleep(0.25 if sampler else 0)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t_wall0 = time.time()
-    ev0.record(stream)                    # every kernel, copy and collective of a step is ordered on the engine's stream
-    for b in range(W, W + K):
-        step(b)
-    ev1.record(stream)
-    eng.synchronize()
-    torch.cuda.synchronize()
-    t_wall1 = time.time()
-    if dist:
-        dist.barrier()
-    ms = ev0.elapsed_time(ev1)
-    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
-    # per-kernel timing of the ingest kernel over the timed pushes (CUDA events on the engine stream)
-    ing = [eng.push_timing(back)["ingest_ms"] for back in range(min(K, 64))]
-    fire = [eng.push_timing(back)["fire_ms"] for back in range(min(K, 64))]
-    c1 = eng.counters()
-    launches = c1["gpu_launches"] - c0["gpu_launches"]
+    ms, ing_ms, fire_ms, delta, clocks = measure(kw, True)
+    launches, n_ealert, n_late, n_fired = delta["gpu_launches"], delta["event_alerts"], delta["late_dropped"], delta["windows_fired"]
+    ealert_rank, events_rank = delta["event_alerts"] / K, delta["events_in"] / K
     if dist:
         t = torch.tensor([ms], device=f"cuda:{local_rank}", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-        tot = torch.tensor([launches, c1["event_alerts"] - c0["event_alerts"], c1["late_dropped"] - c0["late_dropped"],
-                            c1["windows_fired"] - c0["windows_fired"]], device=f"cuda:{local_rank}", dtype=torch.int64)
+        tot = torch.tensor([launches, n_ealert, n_late, n_fired], device=f"cuda:{local_rank}", dtype=torch.int64)
         dist.all_reduce(tot)
         launches, n_ealert, n_late, n_fired = [int(x) for x in tot.tolist()]
-    else:
-        n_ealert = c1["event_alerts"] - c0["event_alerts"]; n_late = c1["late_dropped"] - c0["late_dropped"]
-        n_fired = c1["windows_fired"] - c0["windows_fired"]
-    drain()
     value = world * B * K / (ms * 1e-3)
+    sharded = world > 1
+
+    # the other key mode, same stream, same steps (N = 1 only): reported as a variant, not the headline
+    variants = None
+    if world == 1 and not args.no_variants:
+        other = "hashed" if args.key_mode == "dense" else "dense"
+        kw2 = dict(kw)
+        kw2["key_mode"] = capi.FMQ_KEYS_DENSE if other == "dense" else capi.FMQ_KEYS_HASHED
+        kw2["table_capacity"] = args.keys if other == "dense" else int(args.keys * args.load)
+        ms2, ing2, fire2, d2, _ = measure(kw2, False)
+        variants = {f"key_mode={other}": {"value": B * K / (ms2 * 1e-3), "unit": "events/s", "ms_per_step": ms2 / K, "ingest_kernel_ms": ing2,
+                                          "roofline_frac": (24.0 * B + 24.0 * d2["event_alerts"] / K) / (ing2 * 1e-3) / 1e9 / measured_peak()[0]}}
 
     # -------- roofline of the dominant kernel (ingest), this rank --------
     peak, peak_src = measured_peak()
-    ealert_rank = (c1["event_alerts"] - c0["event_alerts"]) / K
-    ing_events = B if not sharded else (c1["events_in"] - c0["events_in"]) / K
-    alg_bytes = 24.0 * ing_events + 24.0 * ealert_rank
-    ing_ms = float(np.mean(ing))
+    alg_bytes = 24.0 * events_rank + 24.0 * ealert_rank
     achieved = alg_bytes / (ing_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "ingest_kernel<double>", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+    roofline = {"bound": "hbm", "kernel": "ingest_fast_kernel<double,%s>" % args.key_mode, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": ncu_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
-                "avg_launch_ms": ing_ms, "fire_chain_ms": float(np.mean(fire)), "share_of_step": ing_ms * K / ms if not sharded else None}
+                "avg_launch_ms": ing_ms, "fire_chain_ms": fire_ms, "share_of_step": ing_ms * K / ms}
 
     # -------- e2e: host columns through the C ABI, outputs read back --------
     e2e = None
@@ -300,6 +328,7 @@ def main():
             ts, key, val = batches[W + s]
             host.append(tuple(t.cpu().pin_memory() for t in (ts, key, val)))
         eng2 = capi.Engine(**kw)
+        eng = eng2
         hw = tuple(t.cpu().pin_memory() for t in batches[0])
         eng2.push_batch(hw[0].numpy(), hw[1].numpy().view(np.uint64), hw[2].numpy())
         eng2.synchronize(); eng2.poll_fired(); eng2.poll_window_alerts(); eng2.poll_event_alerts()
@@ -328,9 +357,9 @@ def main():
         subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
         from oracle_lib import ParallelOracle
         threads = os.cpu_count() or 1
-        v, dt, _ = cpu_reference_run(6, 1, 1 << args.cpu_sample_log2, threads, capi, ParallelOracle, StreamSpec, generate_numpy)
+        v, dt, _ = cpu_reference_run(12, 1, 1 << args.cpu_sample_log2, threads, capi, ParallelOracle, StreamSpec, generate_numpy)
         cpu_baseline = {"value": v, "unit": "events/s", "cores": threads, "kind": "port",
-                        "sample": f"6 steps x 2^{args.cpu_sample_log2} events of the same stream, {dt:.1f} s of CPU work"}
+                        "sample": f"12 steps x 2^{args.cpu_sample_log2} events of the same stream: {dt:.1f} s wall x {threads} threads = {dt * threads:.0f} core-seconds"}
 
     line = {"metric": "events/sec keyed window-agg+alert", "value": value, "unit": "events/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -338,7 +367,7 @@ def main():
                        "events_per_step_per_gpu": B, "keys": args.keys, "key_mode": args.key_mode, "window_ms": WINDOW_MS, "bound_ms": BOUND_MS,
                        "l2": "inputs larger than L2 (each batch = 24 B x 2^%d = %.0f MB, read once)" % (args.batch_log2, 24 * B / 1e6),
                        "parallelism": "1 GPU" if world == 1 else f"keyBy hash-sharded over {world} GPUs, NCCL all-to-all"},
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "variants": variants,
             "step_counts": {"event_alert_rows": int(n_ealert), "late_dropped": int(n_late), "fired_rows": int(n_fired)}}
     print(json.dumps(line))
     if dist:

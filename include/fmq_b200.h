@@ -247,7 +247,9 @@ int32_t  fmq_flink_key_group(int32_t key_hash, int32_t max_parallelism);
 int32_t  fmq_flink_subtask(int32_t key_group, int32_t parallelism, int32_t max_parallelism);
 
 /* Multi-GPU keyBy exchange, device side (A4): stable partition of a device-resident batch into
- * `world` contiguous buckets by fmq_owner_of.  counts[world] is written to HOST memory.
+ * `world` contiguous buckets by owner.  HASHED handles route by fmq_owner_of; DENSE handles route
+ * by id % world and rewrite the key column to the owner's local id (id / world), so that every
+ * rank's table stays dense — the global id of an output row of rank r is local * world + r.  counts[world] is written to HOST memory.
  * All pointers except counts are device pointers; runs on the handle's stream and
  * synchronises before returning (the counts are needed to size the all-to-all). */
 int32_t fmq_partition_by_owner(fmq_handle* h, const int64_t* ts, const uint64_t* key,

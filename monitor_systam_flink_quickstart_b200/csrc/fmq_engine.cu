@@ -492,8 +492,9 @@ int32_t fmq_partition_by_owner(fmq_handle* h, const int64_t* ts, const uint64_t*
     if (n == 0) return FMQ_OK;
     if (!ts || !key || !val || !ts_out || !key_out || !val_out) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
     CU(h, cudaSetDevice(h->device));
-    OwnerDigit dg{(const u64*)key, world};
-    MoveEvent3 mv{(const u64*)ts, (const u64*)key, (const u64*)val, (u64*)ts_out, (u64*)key_out, (u64*)val_out};
+    const u32 dense = h->cfg.key_mode == FMQ_KEYS_DENSE;
+    OwnerDigit dg{(const u64*)key, world, dense};
+    MoveEvent3 mv{(const u64*)ts, (const u64*)key, (const u64*)val, (u64*)ts_out, (u64*)key_out, (u64*)val_out, world, dense};
     int s = multisplit(h, n, dg, mv); if (s) return s;
     // bucket starts = scanned offsets of chunk 0 for each digit
     const u32 nchunks = rs_num_chunks(n);
@@ -565,8 +566,8 @@ extern "C" int32_t fmq_partition_by_owner_noalloc(int32_t device, void* stream_,
     const u32 nblocks = (nchunks + RS_WARPS - 1) / RS_WARPS;
     const size_t len = (size_t)RS_DIGITS * nchunks;
     const u32 ntiles = (u32)((len + SCAN_TILE - 1) / SCAN_TILE);
-    OwnerDigit dg{(const u64*)key, world};
-    MoveEvent3 mv{(const u64*)ts, (const u64*)key, (const u64*)val, (u64*)ts_out, (u64*)key_out, (u64*)val_out};
+    OwnerDigit dg{(const u64*)key, world, 0u};
+    MoveEvent3 mv{(const u64*)ts, (const u64*)key, (const u64*)val, (u64*)ts_out, (u64*)key_out, (u64*)val_out, world, 0u};
     rs_hist_kernel<<<nblocks, RS_THREADS, 0, stream>>>(n, nchunks, dg, d_counts);
     scan_tile_sums<<<ntiles, SCAN_THREADS, 0, stream>>>(d_counts, len, d_tiles);
     scan_tile_offsets<<<1, SCAN_THREADS, 0, stream>>>(d_tiles, ntiles);

@@ -129,13 +129,16 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply(u32* __restrict__ dat
 }
 
 // ---- digit / emit functors -----------------------------------------------------------------------
-struct OwnerDigit {      // keyBy routing on the GPU: owner = mix64(key) % world  (A4)
-    const u64* key; u32 world;
-    __device__ __forceinline__ u32 operator()(size_t i) const { return (u32)(mix64(key[i]) % world); }
+struct OwnerDigit {      // keyBy routing on the GPU (A4): hashed keys -> mix64(key) % world; dense ids -> id % world
+    const u64* key; u32 world; u32 dense;
+    __device__ __forceinline__ u32 operator()(size_t i) const { return (u32)((dense ? key[i] : mix64(key[i])) % world); }
 };
-struct MoveEvent3 {      // moves one 24 B event (three 8 B columns)
-    const u64* ts; const u64* key; const u64* val; u64* ts_o; u64* key_o; u64* val_o;
-    __device__ __forceinline__ void operator()(size_t s, size_t d) const { ts_o[d] = ts[s]; key_o[d] = key[s]; val_o[d] = val[s]; }
+struct MoveEvent3 {      // moves one 24 B event (three 8 B columns); dense ids become the owner's local id (id / world)
+    const u64* ts; const u64* key; const u64* val; u64* ts_o; u64* key_o; u64* val_o; u32 world; u32 dense;
+    __device__ __forceinline__ void operator()(size_t s, size_t d) const {
+        const u64 k = key[s];
+        ts_o[d] = ts[s]; key_o[d] = (dense && k != KEY_EMPTY) ? k / world : k; val_o[d] = val[s];
+    }
 };
 struct SlotDigit {       // one 8-bit digit of the key-directory slot
     const u32* slot; u32 shift;

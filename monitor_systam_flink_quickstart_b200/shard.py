@@ -58,14 +58,34 @@ class ShardedOperator:
         self.cur_max_ts = I64_MIN + bound_ms
         self.wm = I64_MIN
         self.shuffle_bytes_sent = 0
-        self._bufs = None
+        self._send = None
+        self._recv = None
+        cfg = getattr(engine, "cfg", None)
+        self.dense = bool(cfg is not None and cfg.key_mode == capi.FMQ_KEYS_DENSE and partition is None)
+
+    def global_keys(self, local_keys: np.ndarray) -> np.ndarray:
+        """Output rows of a DENSE engine carry the rank-local id; this maps them back."""
+        if not self.dense:
+            return local_keys
+        return local_keys * np.uint64(self.world) + np.uint64(self.rank)
 
     # -- step 1: owner buckets on the GPU ------------------------------------------------------
     def _cuda_partition(self, ts, key, val, world):
         import torch
-        outs = [torch.empty_like(t) for t in (ts, key, val)]
+        n = ts.numel()
+        # persistent bucket buffers: no allocator traffic (and no cross-stream block recycling) per step
+        if self._send is None or self._send[0].numel() < n:
+            self._send = [torch.empty(n, dtype=t.dtype, device=t.device) for t in (ts, key, val)]
+        outs = [b[:n] for b in self._send]
         counts = self.engine.partition_by_owner(ts, key, val, world, *outs)
         return outs[0], outs[1], outs[2], counts.astype(np.int64)
+
+    def _recv_buffers(self, like, n_recv):
+        import torch
+        if self._recv is None or self._recv[0].numel() < n_recv:
+            cap = max(n_recv, int(getattr(self.engine.cfg, "max_batch", 0) or 0)) if hasattr(self.engine, "cfg") else n_recv
+            self._recv = [torch.empty(cap, dtype=t.dtype, device=t.device) for t in like]
+        return [b[:n_recv] for b in self._recv]
 
     def process_batch(self, ts, key, val, watermark_after: Optional[int] = None):
         """ts/key/val: this rank's slice of the micro-batch (torch tensors; int64 bit patterns for
@@ -96,11 +116,9 @@ class ShardedOperator:
         rc = recv_counts.cpu().tolist(); sc = [int(c) for c in counts]
         n_recv = sum(rc)
         # -- step 3: variable-size all-to-all of the three columns --
-        outs = []
-        for col in (ts_b, key_b, val_b):
-            out = torch.empty(n_recv, dtype=col.dtype, device=col.device)
+        outs = self._recv_buffers((ts_b, key_b, val_b), n_recv)
+        for out, col in zip(outs, (ts_b, key_b, val_b)):
             dist.all_to_all_single(out, col, output_split_sizes=rc, input_split_sizes=sc, group=self.group)
-            outs.append(out)
         self.shuffle_bytes_sent += 24 * (n - sc[self.rank])
         # -- step 4: one watermark for the whole job --
         if watermark_after is None:

@@ -56,7 +56,7 @@ KW = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=
 NB, B = 5, 20_000
 
 
-def _nccl_worker(rank, world, port, outdir):
+def _nccl_worker(rank, world, port, outdir, key_mode=0):
     import torch
     import torch.distributed as dist
     from monitor_systam_flink_quickstart_b200.shard import ShardedOperator
@@ -65,7 +65,7 @@ def _nccl_worker(rank, world, port, outdir):
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
-    eng = capi.Engine(device=rank, **KW)
+    eng = capi.Engine(device=rank, key_mode=key_mode, **KW)
     op = ShardedOperator(eng, rank, world, KW["max_out_of_orderness_ms"])
     for b in range(NB):
         ts, key, val = generate_torch(spec, (b * world + rank) * B, B, device=f"cuda:{rank}")
@@ -73,12 +73,15 @@ def _nccl_worker(rank, world, port, outdir):
         op.process_batch(ts, key, val)
     op.flush()
     res = dict(fired=eng.poll_fired(), ealerts=eng.poll_event_alerts(), calerts=eng.poll_consec_alerts(), counters=eng.counters())
+    for name in ("fired", "ealerts", "calerts"):
+        res[name].key = op.global_keys(res[name].key)
     pickle.dump(res, open(os.path.join(outdir, f"r{rank}.pkl"), "wb"))
     dist.barrier()
     dist.destroy_process_group()
 
 
-def test_two_gpu_sharded_equals_oracle():
+@pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
+def test_two_gpu_sharded_equals_oracle(key_mode):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
@@ -86,7 +89,7 @@ def test_two_gpu_sharded_equals_oracle():
     from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy
     world, port = 2, 29600 + os.getpid() % 2000
     with tempfile.TemporaryDirectory() as d:
-        mp.spawn(_nccl_worker, args=(world, port, d), nprocs=world, join=True)
+        mp.spawn(_nccl_worker, args=(world, port + key_mode, d, key_mode), nprocs=world, join=True)
         res = [pickle.load(open(os.path.join(d, f"r{r}.pkl"), "rb")) for r in range(world)]
     spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
     okw = {k: v for k, v in KW.items()}

@@ -1,4 +1,2 @@
-timeout 200 python -m pytest tests -x -q -m gpu 2>&1 | tail -3
-for f in "" "--key-mode dense" "--key-mode dense --no-efilter"; do
-echo "== $f"; timeout 120 python bench.py --steps 6 --warmup 3 --no-cpu-baseline --no-e2e $f 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); r=d['roofline']; print(round(d['value']/1e9,2),'Gev/s ingest_ms',round(r['avg_launch_ms'],3),'fire_ms',round(r['fire_chain_ms'],3))"
-done
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 10 --warmup 3 2> gpurun_out/b2.err | tail -1 > gpurun_out/bench_n2.json; python -c "
+import json; d=json.load(open('gpurun_out/bench_n2.json')); print(d['value']/1e9,'Gev/s', d['ms_per_step'],'ms/step', d['roofline']['avg_launch_ms'], d['clocks'])"
