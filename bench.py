@@ -127,9 +127,6 @@ def ncu_traffic():
 
 
 # --------------------------------------------------------------------------------------------------
-os.environ.setdefault("TORCH_NCCL_AVOID_RECORD_STREAMS", "1")
-
-
 def cpu_reference_run(steps, warmup, sample_events, threads, capi, ParallelOracle, StreamSpec, generate_numpy):
     """The CPU restatement on host cores: `steps` timed steps of `sample_events` events each."""
     kw = workload_kwargs(capi, sample_events)
@@ -156,6 +153,9 @@ def main():
     ap.add_argument("--cpu-sample-log2", type=int, default=23, help="events per step of the CPU baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--multi", default="combiner", choices=["combiner", "alltoall"],
+                    help="N>1: combiner = local accumulate + peer-memory fire (no event shuffle; dense ids); "
+                         "alltoall = owner split + NCCL all-to-all of the events")
     ap.add_argument("--no-variants", action="store_true")
     ap.add_argument("--no-clocks", action="store_true", help="experiment: do not sample nvidia-smi during the timed region")
     ap.add_argument("--keys", type=int, default=N_KEYS, help="experiment: number of distinct hosts")
@@ -217,7 +217,8 @@ def main():
         kw["efilter_enabled"] = 0
     if args.key_mode == "dense":
         kw["key_mode"] = capi.FMQ_KEYS_DENSE
-        kw["table_capacity"] = (args.keys + world - 1) // world        # rank-local dense ids (id // world)
+        # all-to-all route: rank-local dense ids (id // world); combiner route: every rank holds the full id space
+        kw["table_capacity"] = (args.keys + world - 1) // world if (world > 1 and args.multi == "alltoall") else args.keys
     # outputs stay in HBM during the timed region (polled after it): size the buffers for K steps.
     # ~1 fired row per 10 events (one report per host per second, 10 s windows), ~10 % event alerts.
     per_rank_events = B * max(K, W)
@@ -241,8 +242,11 @@ def main():
         stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local_rank))
         sharded = None
         if world > 1:
-            from monitor_systam_flink_quickstart_b200.shard import ShardedOperator
-            sharded = ShardedOperator(eng, rank, world, BOUND_MS)
+            from monitor_systam_flink_quickstart_b200.shard import CombinerOperator, ShardedOperator
+            if args.multi == "combiner" and kw.get("key_mode") == capi.FMQ_KEYS_DENSE:
+                sharded = CombinerOperator(eng, rank, world)
+            else:
+                sharded = ShardedOperator(eng, rank, world, BOUND_MS)
 
         def step(b):
             if sharded:
@@ -366,7 +370,9 @@ def main():
             "config": {"workload": "C3 10s tumbling event-time count/avg/max per host + late drop + avg>limit alert + per-event >90 filter, 1M keys",
                        "events_per_step_per_gpu": B, "keys": args.keys, "key_mode": args.key_mode, "window_ms": WINDOW_MS, "bound_ms": BOUND_MS,
                        "l2": "inputs larger than L2 (each batch = 24 B x 2^%d = %.0f MB, read once)" % (args.batch_log2, 24 * B / 1e6),
-                       "parallelism": "1 GPU" if world == 1 else f"keyBy hash-sharded over {world} GPUs, NCCL all-to-all"},
+                       "parallelism": "1 GPU" if world == 1 else (
+                           f"{world} GPUs, combiner: local accumulate + 32 B all-reduce per batch + fire over NVLink peer memory"
+                           if (args.multi == "combiner" and args.key_mode == "dense") else f"keyBy hash-sharded over {world} GPUs, NCCL all-to-all")},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "variants": variants,
             "step_counts": {"event_alert_rows": int(n_ealert), "late_dropped": int(n_late), "fired_rows": int(n_fired)}}
     print(json.dumps(line))

@@ -257,6 +257,33 @@ int32_t fmq_partition_by_owner(fmq_handle* h, const int64_t* ts, const uint64_t*
                                int64_t* ts_out, uint64_t* key_out, void* val_out,
                                uint64_t* counts);
 
+/* ---- combiner mode: multi-GPU window aggregation without an event shuffle (A4/A5/A5f) -------------
+ * Replaces the keyBy network exchange in front of the WindowOperator
+ * (BandwidthMonitorWithEventTime.java:45) for the commutative window aggregates: every rank folds its
+ * own share of the events into a full-size local table (DENSE ids, so a slot means the same key on
+ * every rank) and a window is fired by the rank that owns the slot range, which reads that range of
+ * every rank's table over NVLink peer memory inside the fire kernel.  Per batch the ranks exchange
+ * 32 bytes (max timestamp and live pane range, one all-reduce(MAX) over fmq_exchange_ptr) instead of
+ * 24 bytes per event.  Order-dependent keyed state (A7) cannot be combined this way and stays on
+ * the all-to-all route (fmq_partition_by_owner).  Call sequence per micro-batch, on every rank:
+ *     fmq_push_local(..)                       ingest own events (device columns)
+ *     all-reduce(MAX) of the 4 int64 at fmq_exchange_ptr(h), on fmq_stream(h)   [also the barrier
+ *                                               "every rank has ingested"]
+ *     fmq_fire_global(h, watermark_after)      same watermark on every rank; fires own slot range
+ *     barrier on fmq_stream(h)                 [every rank has finished reading its peers]
+ *     fmq_retire(h)                            clear expired panes, advance the pane origin
+ * Peer tables are plain device pointers: within one process pass fmq_table_ptr of the other
+ * handles; across processes exchange fmq_ipc_export blobs (64 bytes) and map them with fmq_ipc_open. */
+void*   fmq_table_ptr(fmq_handle* h);
+void*   fmq_exchange_ptr(fmq_handle* h);
+int32_t fmq_ipc_export(fmq_handle* h, void* handle64);
+int32_t fmq_ipc_open(fmq_handle* h, const void* handle64, void** ptr);
+int32_t fmq_attach_peers(fmq_handle* h, int32_t rank, int32_t world, const void* const* peer_tables);
+int32_t fmq_push_local(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val,
+                       size_t n, int32_t mem);
+int32_t fmq_fire_global(fmq_handle* h, int64_t watermark_after);
+int32_t fmq_retire(fmq_handle* h);
+
 /* Largest batch fmq_partition_by_owner_noalloc accepts (events). */
 #define FMQ_NOALLOC_MAX_EVENTS 4194304
 

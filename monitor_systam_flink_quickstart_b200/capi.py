@@ -145,6 +145,14 @@ def _declare(lib, p: str, has_mem: bool = True):
         sig("flink_key_group", [i32, i32])
         sig("flink_subtask", [i32, i32, i32])
         sig("partition_by_owner", [vp, vp, vp, vp, sz, C.c_uint32, vp, vp, vp, vp])
+        sig("table_ptr", [vp], vp)
+        sig("exchange_ptr", [vp], vp)
+        sig("ipc_export", [vp, vp])
+        sig("ipc_open", [vp, vp, C.POINTER(vp)])
+        sig("attach_peers", [vp, i32, i32, C.POINTER(vp)])
+        sig("push_local", [vp, vp, vp, vp, sz, i32])
+        sig("fire_global", [vp, i64])
+        sig("retire", [vp])
         sig("partition_by_owner_noalloc", [i32, vp, vp, vp, vp, sz, C.c_uint32, vp, vp, vp, vp])
 
 
@@ -348,6 +356,38 @@ class Engine(EngineBase):
     @property
     def handle(self):
         return self._h
+
+    # ---- combiner mode (multi-GPU without an event shuffle) -----------------------------------
+    @property
+    def table_ptr(self) -> int:
+        return self._lib.fmq_table_ptr(self._h) or 0
+
+    @property
+    def exchange_ptr(self) -> int:
+        return self._lib.fmq_exchange_ptr(self._h) or 0
+
+    def ipc_export(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        self._check(self._lib.fmq_ipc_export(self._h, buf))
+        return buf.raw
+
+    def ipc_open(self, blob: bytes) -> int:
+        p = C.c_void_p()
+        self._check(self._lib.fmq_ipc_open(self._h, blob, C.byref(p)))
+        return p.value
+
+    def attach_peers(self, rank: int, world: int, tables):
+        arr = (C.c_void_p * world)(*[C.c_void_p(t) for t in tables])
+        self._check(self._lib.fmq_attach_peers(self._h, rank, world, arr))
+
+    def push_local(self, ts, key, val):
+        self._check(self._lib.fmq_push_local(self._h, _ptr(ts), _ptr(key), _ptr(val), len(ts), FMQ_MEM_DEVICE))
+
+    def fire_global(self, watermark_after: int = FMQ_WM_AUTO):
+        self._check(self._lib.fmq_fire_global(self._h, watermark_after))
+
+    def retire(self):
+        self._check(self._lib.fmq_retire(self._h))
 
     def partition_by_owner(self, ts, key, val, world: int, ts_out, key_out, val_out) -> np.ndarray:
         counts = np.zeros(world, np.uint64)

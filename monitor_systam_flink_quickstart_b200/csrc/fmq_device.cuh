@@ -9,6 +9,7 @@ typedef unsigned long long u64;
 typedef long long i64;
 typedef unsigned int u32;
 
+#define FMQ_MAX_PEERS 8
 constexpr u64 KEY_EMPTY = 0xFFFFFFFFFFFFFFFFull;
 constexpr u32 SLOT_INVALID = 0xFFFFFFFFu;
 constexpr i64 I64_MIN_ = (i64)0x8000000000000000ull;

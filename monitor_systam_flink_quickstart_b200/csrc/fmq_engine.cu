@@ -52,6 +52,11 @@ struct fmq_handle {
     u32 *d_slot[2] = {nullptr, nullptr}, *d_idx[2] = {nullptr, nullptr};
     u32* d_counts = nullptr; u32* d_tiles = nullptr; size_t counts_len = 0, tiles_len = 0;
     uint64_t launches = 0;
+    // combiner mode (fmq_attach_peers)
+    int world = 1, rank = 0;
+    const Acc32* peer_acc[FMQ_MAX_PEERS] = {};
+    i64* d_xchg = nullptr;               // 4 x int64 exchange buffer for the all-reduce of the batch scalars
+    size_t pending_n = 0;                // events ingested by fmq_push_local and not yet accounted by fmq_fire_global
 };
 
 #define CU(h, call)                                                                                   \
@@ -82,7 +87,7 @@ static void free_all(fmq_handle* h) {
     void* ptrs[] = {h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
                     h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
-                    h->d_slot[0], h->d_slot[1], h->d_idx[0], h->d_idx[1], h->d_counts, h->d_tiles};
+                    h->d_slot[0], h->d_slot[1], h->d_idx[0], h->d_idx[1], h->d_counts, h->d_tiles, h->d_xchg};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->h_st) cudaFreeHost(h->h_st);
     for (auto& q : h->tev) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
@@ -171,6 +176,8 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     h->counts_len = (size_t)RS_DIGITS * rs_num_chunks(h->max_batch);
     h->tiles_len = (h->counts_len + SCAN_TILE - 1) / SCAN_TILE;
     CUC(dalloc(&h->d_counts, h->counts_len)); CUC(dalloc(&h->d_tiles, h->tiles_len));
+    CUC(dalloc(&h->d_xchg, 4)); CUC(cudaMemset(h->d_xchg, 0, 32));
+    h->peer_acc[0] = h->d_acc;
     CUC(cudaDeviceSynchronize());
 #undef CUC
     *out = h;
@@ -234,8 +241,9 @@ static int sync_state(fmq_handle* h) {
     return status_from_flags(h, h->h_st->err_flags);
 }
 
+// stage 1 of a push: everything that touches only this handle's own events
 template <typename V>
-static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n, int64_t wm_after) {
+static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n) {
     const fmq_config& c = h->cfg;
     cudaEvent_t* tev = h->tev[h->pushes % fmq_handle::TIMING_RING];
     if (n > 0 && (c.window_enabled || c.efilter_enabled)) {
@@ -286,6 +294,14 @@ static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* v
         h->rolling_n = 0;
     }
     CU(h, cudaEventRecord(tev[2], h->stream));
+    return FMQ_OK;
+}
+
+// stage 2 of a push: watermark, fire, cleanup.  In combiner mode (`retire_now` false) the cleanup is
+// a separate step (fmq_retire) because peers may still be reading this rank's table.
+template <typename V>
+static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now) {
+    const fmq_config& c = h->cfg;
     PlanArgs p{h->d_st, h->g, c.max_out_of_orderness_ms, wm_after, (u64)n, c.window_enabled, wm_after == FMQ_WM_AUTO};
     plan_kernel<<<1, 32, 0, h->stream>>>(p); LAUNCHED(h, "plan_kernel");
     if (c.window_enabled && wm_after != FMQ_WM_AUTO && wm_after > INT64_MIN) h->anchored_known = true;
@@ -297,12 +313,24 @@ static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* v
         f.d1 = c.walert_div1 == 0.0 ? 1.0 : c.walert_div1; f.d2 = c.walert_div2 == 0.0 ? 1.0 : c.walert_div2; f.thr = c.walert_threshold;
         f.f_key = h->f_key; f.f_wend = h->f_wend; f.f_count = h->f_count; f.f_sum = h->f_sum; f.f_min = h->f_min; f.f_max = h->f_max; f.f_cap = h->f_cap;
         f.wa_key = h->wa_key; f.wa_wend = h->wa_wend; f.wa_val = h->wa_val; f.wa_cap = h->wa_cap;
-        size_t blocks = (h->capacity + FIRE_THREADS - 1) / FIRE_THREADS; const size_t maxb = (size_t)h->num_sms * 8;
+        f.world = h->world; f.clear_in_fire = retire_now ? 1 : 0;
+        const u64 per = (h->capacity + h->world - 1) / h->world;            // this rank fires a contiguous slot range
+        f.slot_lo = per * h->rank < h->capacity ? per * h->rank : h->capacity;
+        f.slot_hi = f.slot_lo + per < h->capacity ? f.slot_lo + per : h->capacity;
+        for (int r = 0; r < h->world; ++r) f.peer_acc[r] = h->peer_acc[r];
+        size_t blocks = (f.slot_hi - f.slot_lo + FIRE_THREADS - 1) / FIRE_THREADS; const size_t maxb = (size_t)h->num_sms * 8;
         if (blocks > maxb) blocks = maxb;
+        if (blocks == 0) blocks = 1;
         fire_kernel<V><<<(unsigned)blocks, FIRE_THREADS, 0, h->stream>>>(f); LAUNCHED(h, "fire_kernel");
-        commit_kernel<<<1, 32, 0, h->stream>>>(h->d_st); LAUNCHED(h, "commit_kernel");
+        if (retire_now) { commit_kernel<<<1, 32, 0, h->stream>>>(h->d_st); LAUNCHED(h, "commit_kernel"); }
     }
     return FMQ_OK;
+}
+
+template <typename V>
+static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n, int64_t wm_after) {
+    int s = stage_ingest<V>(h, ts, key, val, n); if (s) return s;
+    return stage_fire<V>(h, n, wm_after, true);
 }
 
 extern "C" {
@@ -313,6 +341,7 @@ int32_t fmq_push_batch(fmq_handle* h, const int64_t* ts, const uint64_t* key, co
     if (n > 0 && (!ts || !key || !val)) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
     if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
     if (mem != FMQ_MEM_HOST && mem != FMQ_MEM_DEVICE) return set_err(h, FMQ_ERR_BAD_ARG, "bad mem");
+    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: use fmq_push_local / fmq_fire_global / fmq_retire");
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][0], h->stream));
     const i64* dts = (const i64*)ts; const u64* dkey = (const u64*)key; const void* dval = val;
@@ -339,6 +368,7 @@ int32_t fmq_flush(fmq_handle* h, int64_t watermark) {
     if (!h) return FMQ_ERR_BAD_ARG;
     if (h->sticky) return FMQ_ERR_POISONED;
     if (watermark == FMQ_WM_AUTO) return set_err(h, FMQ_ERR_BAD_ARG, "flush needs an explicit watermark");
+    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: use fmq_fire_global / fmq_retire");
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][0], h->stream));
     int s = (h->cfg.value_type == FMQ_VAL_F64) ? run_chain<double>(h, nullptr, nullptr, nullptr, 0, watermark)
@@ -441,6 +471,79 @@ int32_t fmq_get_key_state(fmq_handle* h, const uint64_t* keys, size_t n, int32_t
     CU(h, cudaMemcpyAsync(rolling, dr, n * 8, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
     cudaFree(dk); cudaFree(df); cudaFree(dc); cudaFree(dr);
+    return FMQ_OK;
+}
+
+// ---- combiner mode: multi-GPU without an event shuffle ------------------------------------------
+void* fmq_table_ptr(fmq_handle* h) { return h ? (void*)h->d_acc : nullptr; }
+void* fmq_exchange_ptr(fmq_handle* h) { return h ? (void*)h->d_xchg : nullptr; }
+
+int32_t fmq_ipc_export(fmq_handle* h, void* handle64) {
+    if (!h || !handle64 || !h->d_acc) return h ? set_err(h, FMQ_ERR_BAD_ARG, "no accumulator table to export") : FMQ_ERR_BAD_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    CU(h, cudaSetDevice(h->device));
+    cudaIpcMemHandle_t ih;
+    CU(h, cudaIpcGetMemHandle(&ih, h->d_acc));
+    memcpy(handle64, &ih, 64);
+    return FMQ_OK;
+}
+int32_t fmq_ipc_open(fmq_handle* h, const void* handle64, void** ptr) {
+    if (!h || !handle64 || !ptr) return FMQ_ERR_BAD_ARG;
+    CU(h, cudaSetDevice(h->device));
+    cudaIpcMemHandle_t ih; memcpy(&ih, handle64, 64);
+    CU(h, cudaIpcOpenMemHandle(ptr, ih, cudaIpcMemLazyEnablePeerAccess));
+    return FMQ_OK;
+}
+int32_t fmq_attach_peers(fmq_handle* h, int32_t rank, int32_t world, const void* const* peer_tables) {
+    if (!h || !peer_tables) return FMQ_ERR_BAD_ARG;
+    if (world < 1 || world > FMQ_MAX_PEERS || rank < 0 || rank >= world) return set_err(h, FMQ_ERR_BAD_ARG, "need 1 <= world <= 8 and 0 <= rank < world");
+    if (!h->cfg.window_enabled) return set_err(h, FMQ_ERR_BAD_ARG, "combiner mode needs window aggregation");
+    if (h->cfg.key_mode != FMQ_KEYS_DENSE) return set_err(h, FMQ_ERR_BAD_ARG, "combiner mode needs FMQ_KEYS_DENSE (slots must mean the same key on every rank)");
+    if (keyed_enabled(h->cfg)) return set_err(h, FMQ_ERR_BAD_ARG, "keyed ValueState operators depend on per-key order: route them through the all-to-all exchange instead");
+    for (int r = 0; r < world; ++r) {
+        if (r != rank && !peer_tables[r]) return set_err(h, FMQ_ERR_BAD_ARG, "null peer table");
+        h->peer_acc[r] = (r == rank) ? h->d_acc : static_cast<const Acc32*>(peer_tables[r]);
+    }
+    h->world = world; h->rank = rank;
+    return FMQ_OK;
+}
+int32_t fmq_push_local(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val, size_t n, int32_t mem) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (n > 0 && (!ts || !key || !val)) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
+    if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
+    if (mem != FMQ_MEM_DEVICE) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_push_local takes device columns");
+    if (n > 0 && (((uintptr_t)ts | (uintptr_t)key | (uintptr_t)val) & 7)) return set_err(h, FMQ_ERR_BAD_ARG, "device columns must be 8-byte aligned");
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][0], h->stream));
+    int s = (h->cfg.value_type == FMQ_VAL_F64) ? stage_ingest<double>(h, (const i64*)ts, (const u64*)key, val, n)
+                                               : stage_ingest<i64>(h, (const i64*)ts, (const u64*)key, val, n);
+    if (s) return s;
+    pack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "pack_scalars_kernel");
+    h->pending_n += n;
+    return FMQ_OK;
+}
+int32_t fmq_fire_global(fmq_handle* h, int64_t watermark_after) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    CU(h, cudaSetDevice(h->device));
+    unpack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "unpack_scalars_kernel");
+    int s = (h->cfg.value_type == FMQ_VAL_F64) ? stage_fire<double>(h, h->pending_n, watermark_after, false)
+                                               : stage_fire<i64>(h, h->pending_n, watermark_after, false);
+    if (s) return s;
+    h->pending_n = 0;
+    return FMQ_OK;
+}
+int32_t fmq_retire(fmq_handle* h) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    CU(h, cudaSetDevice(h->device));
+    retire_kernel<<<(unsigned)h->num_sms * 4, 256, 0, h->stream>>>(h->d_st, h->d_acc, h->capacity, h->g.ring_mask); LAUNCHED(h, "retire_kernel");
+    commit_kernel<<<1, 32, 0, h->stream>>>(h->d_st); LAUNCHED(h, "commit_kernel");
+    // pre-arm the exchange buffer so that a fire with no preceding local push contributes nothing
+    pack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "pack_scalars_kernel");
+    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][3], h->stream));
+    h->pushes++;
     return FMQ_OK;
 }
 

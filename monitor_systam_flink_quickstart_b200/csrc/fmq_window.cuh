@@ -437,6 +437,13 @@ __global__ void commit_kernel(DevState* st) {
 struct FireArgs {
     DevState* st; const u64* dkeys; Acc32* acc; WindowGeom g;
     int dense_keys;             // 1: key == slot, no directory
+    // combiner mode (multi-GPU): every rank accumulates its share of the events into a
+    // full-size local table; a window fires on the rank that owns the slot range [slot_lo, slot_hi)
+    // by reading that range of EVERY rank's table over NVLink peer memory and combining the cells.
+    int world;                  // 1 = single GPU
+    int clear_in_fire;          // 1: the firing thread also clears expired panes (single GPU)
+    u64 slot_lo, slot_hi;
+    const Acc32* peer_acc[FMQ_MAX_PEERS];
     int emit_fired; int walert_source, walert_op; double mul, d0, d1, d2, thr;
     u64* f_key; i64* f_wend; i64* f_count; u64* f_sum; u64* f_min; u64* f_max; u64 f_cap;
     u64* wa_key; i64* wa_wend; double* wa_val; u64 wa_cap;
@@ -444,21 +451,48 @@ struct FireArgs {
 
 constexpr int FIRE_THREADS = 256;
 
+// [batch max ts, -(min pane), max pane, 0]: the three batch scalars every rank must agree on,
+// laid out so that ONE all-reduce(MAX) over int64 makes them global (combiner mode).
+__global__ void pack_scalars_kernel(const DevState* st, i64* x) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    x[0] = st->batch_max_ts;
+    x[1] = (st->min_pane <= st->max_pane) ? -st->min_pane : I64_MIN_;
+    x[2] = (st->min_pane <= st->max_pane) ? st->max_pane : I64_MIN_;
+    x[3] = 0;
+}
+__global__ void unpack_scalars_kernel(DevState* st, const i64* x) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    st->batch_max_ts = x[0];
+    if (x[1] != I64_MIN_) { st->min_pane = -x[1]; st->max_pane = x[2]; }
+}
+// combiner mode: clear the panes whose last window has fired everywhere (runs after the barrier that
+// follows the peer-reading fire), then retire them like commit_kernel does
+__global__ void __launch_bounds__(256) retire_kernel(DevState* st, Acc32* acc, u64 capacity, u32 ring_mask) {
+    const i64 x_lo = st->expire_lo, x_hi = st->expire_hi;
+    if (x_lo > x_hi) return;
+    const ulonglong4 z = make_ulonglong4(0, 0, 0, 0);
+    for (i64 p = x_lo; p <= x_hi; ++p) {
+        ulonglong4* pane = reinterpret_cast<ulonglong4*>(acc + (u64)((u32)p & ring_mask) * capacity);
+        for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < capacity; i += (u64)gridDim.x * blockDim.x) pane[i] = z;
+    }
+}
+
 template <typename V>
 __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constant__ FireArgs a) {
     DevState* st = a.st;
     const i64 nfire = st->fire_count;
     const i64 x_lo = st->expire_lo, x_hi = st->expire_hi;
-    if (nfire == 0 && x_lo > x_hi) return;
+    if (nfire == 0 && (x_lo > x_hi || !a.clear_in_fire)) return;
     const i64 first_end = st->fire_first_end;
     const i64 pmin = st->min_pane, pmax = st->max_pane;
     const i64 size = a.g.size, slide = a.g.slide, off = a.g.off;
     const u64 C = a.g.capacity;
     constexpr bool is_f64 = IsF64<V>::value;
     u64 fired_local = 0, alerts_local = 0;
-    const u64 nslots_rounded = (C + FIRE_THREADS - 1) / FIRE_THREADS * FIRE_THREADS;   // block-uniform trip count
-    for (u64 slot = (u64)blockIdx.x * blockDim.x + threadIdx.x; slot < nslots_rounded; slot += (u64)gridDim.x * blockDim.x) {
-        const u64 key = slot < C ? (a.dense_keys ? slot : a.dkeys[slot]) : KEY_EMPTY;
+    const u64 nslots_rounded = (a.slot_hi - a.slot_lo + FIRE_THREADS - 1) / FIRE_THREADS * FIRE_THREADS;   // block-uniform trip count
+    for (u64 sidx = (u64)blockIdx.x * blockDim.x + threadIdx.x; sidx < nslots_rounded; sidx += (u64)gridDim.x * blockDim.x) {
+        const u64 slot = a.slot_lo + sidx;
+        const u64 key = slot < a.slot_hi ? (a.dense_keys ? slot : a.dkeys[slot]) : KEY_EMPTY;
         const bool live = key != KEY_EMPTY;
         for (i64 j = 0; j < nfire; ++j) {
             const i64 wend = first_end + j * slide;
@@ -469,10 +503,13 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
             u64 cnt_i = 0; double cnt_d = 0.0; u64 sum_i = 0; double sum_d = 0.0; u64 mx = 0, mn = 0;
             if (live) {
                 for (i64 p = p0; p <= p1; ++p) {
-                    const Acc32 c = a.acc[(u64)((u32)p & a.g.ring_mask) * C + slot];
-                    if (is_f64) { cnt_d += __longlong_as_double((i64)c.cnt); sum_d += __longlong_as_double((i64)c.sum); }
-                    else        { cnt_i += c.cnt; sum_i += c.sum; }
-                    mx = c.mx > mx ? c.mx : mx; mn = c.mn > mn ? c.mn : mn;
+                    const u64 cell = (u64)((u32)p & a.g.ring_mask) * C + slot;
+                    for (int r = 0; r < a.world; ++r) {                    // fixed rank order: deterministic double sums
+                        const ulonglong4 q = *reinterpret_cast<const ulonglong4*>(a.peer_acc[r] + cell);
+                        if (is_f64) { cnt_d += __longlong_as_double((i64)q.x); sum_d += __longlong_as_double((i64)q.y); }
+                        else        { cnt_i += q.x; sum_i += q.y; }
+                        mx = q.z > mx ? q.z : mx; mn = q.w > mn ? q.w : mn;
+                    }
                 }
             }
             const i64 count = is_f64 ? (i64)cnt_d : (i64)cnt_i;
@@ -509,7 +546,7 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
             }
         }
         // cleanup: WindowOperator.clearAllState for panes whose last window has fired
-        if (live) {
+        if (live && a.clear_in_fire) {
             const ulonglong4 z = make_ulonglong4(0, 0, 0, 0);
             for (i64 p = x_lo; p <= x_hi; ++p)
                 *reinterpret_cast<ulonglong4*>(&a.acc[(u64)((u32)p & a.g.ring_mask) * C + slot]) = z;

@@ -135,3 +135,62 @@ class ShardedOperator:
 
     def flush(self, wm: int = capi.FMQ_WM_FINAL):
         self.engine.flush(wm)
+
+
+class _DevicePtr:
+    """Lets torch alias a raw device pointer (CUDA array interface): used for the 4 x int64
+    exchange buffer of an engine, so that the all-reduce runs on it in place."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i8", "data": (ptr, False), "version": 2}
+
+
+def exchange_tensor(engine, device):
+    import torch
+    return torch.as_tensor(_DevicePtr(engine.exchange_ptr, 4), device=device)
+
+
+class CombinerOperator:
+    """Multi-GPU window aggregation without an event shuffle (include/fmq_b200.h, "combiner mode").
+
+    Every rank folds its own slice of each micro-batch into a full-size local table; per batch the
+    ranks exchange 32 bytes (one all-reduce(MAX): max timestamp and live pane range) instead of
+    24 bytes per event, and the fire kernel of the rank that owns a slot range reads that range of
+    every rank's table over NVLink peer memory.  Needs dense key ids and only covers the commutative
+    window aggregates + the stateless per-event filter; keyed ValueState goes through
+    :class:`ShardedOperator`.
+    """
+
+    def __init__(self, engine, rank: int, world: int, group=None):
+        import torch
+        import torch.distributed as dist
+        self.dist, self.engine, self.rank, self.world, self.group = dist, engine, rank, world, group
+        dev = torch.device("cuda", torch.cuda.current_device())
+        blobs = [None] * world
+        dist.all_gather_object(blobs, engine.ipc_export(), group=group)
+        tables = [engine.table_ptr if r == rank else engine.ipc_open(blobs[r]) for r in range(world)]
+        engine.attach_peers(rank, world, tables)
+        self._ext = torch.cuda.ExternalStream(engine.stream, device=dev)
+        self._x = exchange_tensor(engine, dev)
+        self._token = torch.zeros(1, dtype=torch.int64, device=dev)
+        dist.barrier(group=group)
+
+    def process_batch(self, ts, key, val, watermark_after: int = capi.FMQ_WM_AUTO):
+        """One micro-batch: everything below is queued on the engine's stream, no host round trip."""
+        import torch
+        dist = self.dist
+        with torch.cuda.stream(self._ext):
+            self.engine.push_local(ts, key, val)
+            dist.all_reduce(self._x, op=dist.ReduceOp.MAX, group=self.group)     # global scalars + "all ingested"
+            self.engine.fire_global(watermark_after)
+            dist.all_reduce(self._token, group=self.group)                         # "all peers done reading"
+            self.engine.retire()
+
+    def flush(self, wm: int = capi.FMQ_WM_FINAL):
+        import torch
+        dist = self.dist
+        with torch.cuda.stream(self._ext):
+            dist.all_reduce(self._x, op=dist.ReduceOp.MAX, group=self.group)
+            self.engine.fire_global(wm)
+            dist.all_reduce(self._token, group=self.group)
+            self.engine.retire()

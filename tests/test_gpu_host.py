@@ -103,3 +103,119 @@ def test_two_gpu_sharded_equals_oracle(key_mode):
     assert_events_equal(cat("ealerts", capi.EventRows, ("ts", "key", "val")), ref.poll_event_alerts())
     assert_events_equal(cat("calerts", capi.EventRows, ("ts", "key", "val")), ref.poll_consec_alerts())
     assert sum(r["counters"]["late_dropped"] for r in res) == ref.counters()["late_dropped"]
+
+
+# ---- combiner mode --------------------------------------------------------------------------------
+CKW = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=5000, max_out_of_orderness_ms=3000,
+           efilter_enabled=1, efilter_threshold=90.0, walert_source=capi.FMQ_ALERT_AVG, walert_op=capi.FMQ_CMP_GT, walert_threshold=52.0,
+           key_mode=capi.FMQ_KEYS_DENSE, table_capacity=1000, pane_ring=64, max_batch=1 << 16)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("vt", ["f64", "i64"])
+def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt):
+    """`world` engines in ONE process on one GPU play the ranks (their tables are attached to each other
+    as plain device pointers); the two collectives are done by hand between synchronised streams.
+    Union of the ranks' outputs == oracle over the whole stream."""
+    import torch
+    from monitor_systam_flink_quickstart_b200.shard import exchange_tensor
+    from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy, generate_torch
+    from oracle_lib import sort_walerts
+    kw = dict(CKW, value_type=capi.FMQ_VAL_F64 if vt == "f64" else capi.FMQ_VAL_I64)
+    if vt == "i64":
+        kw.update(walert_source=capi.FMQ_ALERT_SUM, walert_op=capi.FMQ_CMP_LT, walert_mul=8.0, walert_div0=60.0, walert_div1=1024.0,
+                  walert_div2=1024.0, walert_threshold=0.9)
+    spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000, value_type=vt)
+    engs = [capi.Engine(**kw) for _ in range(world)]
+    for r, e in enumerate(engs):
+        e.attach_peers(r, world, [x.table_ptr for x in engs])
+    xs = [exchange_tensor(e, "cuda:0") for e in engs]
+    ref = OracleEngine(**{k: v for k, v in kw.items()})
+    nb, b = 6, 7001
+
+    def collective_max():
+        for e in engs:
+            e.synchronize()
+        m = torch.stack(xs).max(dim=0).values
+        for x in xs:
+            x.copy_(m)
+        torch.cuda.synchronize()
+
+    def fire(wm):
+        collective_max()
+        for e in engs:
+            e.fire_global(wm)
+        for e in engs:
+            e.synchronize()                       # barrier: everybody finished reading its peers
+        for e in engs:
+            e.retire()
+
+    for i in range(nb):
+        parts = []
+        for r, e in enumerate(engs):
+            start = (i * world + r) * b
+            e.push_local(*generate_torch(spec, start, b, device="cuda:0"))
+            parts.append(generate_numpy(spec, start, b))
+        fire(capi.FMQ_WM_AUTO)
+        ref.push_batch(*[np.concatenate([p[j] for p in parts]) for j in range(3)])
+    fire(capi.FMQ_WM_FINAL)
+    ref.flush()
+    res = [dict(fired=e.poll_fired(), wal=e.poll_window_alerts(), eal=e.poll_event_alerts(), c=e.counters()) for e in engs]
+    cat = lambda name, cls, fields: cls(*[np.concatenate([getattr(r[name], f) for r in res]) for f in fields])  # noqa: E731
+    assert_fired_equal(cat("fired", capi.Fired, ("key", "window_end", "count", "sum", "min", "max")), ref.poll_fired())
+    a, w = sort_walerts(cat("wal", capi.WindowAlerts, ("key", "window_end", "value"))), sort_walerts(ref.poll_window_alerts())
+    np.testing.assert_array_equal(a.key, w.key); np.testing.assert_array_equal(a.window_end, w.window_end)
+    np.testing.assert_allclose(a.value, w.value, rtol=1e-9)
+    assert_events_equal(cat("eal", capi.EventRows, ("ts", "key", "val")), ref.poll_event_alerts())
+    rc = ref.counters()
+    assert sum(r["c"]["late_dropped"] for r in res) == rc["late_dropped"] > 0
+    assert sum(r["c"]["windows_fired"] for r in res) == rc["windows_fired"]
+    assert all(r["c"]["watermark"] == rc["watermark"] for r in res)
+    # every rank fired only its own slot range
+    per = (1000 + world - 1) // world
+    for r, x in enumerate(res):
+        assert len(x["fired"]) > 0 and x["fired"].key.min() >= per * r and x["fired"].key.max() < per * (r + 1)
+
+
+def _combiner_worker(rank, world, port, outdir):
+    import torch
+    import torch.distributed as dist
+    from monitor_systam_flink_quickstart_b200.shard import CombinerOperator
+    from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_torch
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
+    eng = capi.Engine(device=rank, **CKW)
+    op = CombinerOperator(eng, rank, world)
+    for b in range(NB):
+        ts, key, val = generate_torch(spec, (b * world + rank) * B, B, device=f"cuda:{rank}")
+        torch.cuda.synchronize()
+        op.process_batch(ts, key, val)
+    op.flush()
+    res = dict(fired=eng.poll_fired(), ealerts=eng.poll_event_alerts(), counters=eng.counters())
+    pickle.dump(res, open(os.path.join(outdir, f"r{rank}.pkl"), "wb"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_gpu_combiner_over_nvlink_equals_oracle():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy
+    world, port = 2, 29700 + os.getpid() % 2000
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_combiner_worker, args=(world, port, d), nprocs=world, join=True)
+        res = [pickle.load(open(os.path.join(d, f"r{r}.pkl"), "rb")) for r in range(world)]
+    spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
+    ref = OracleEngine(**{k: v for k, v in CKW.items()})
+    for b in range(NB):
+        parts = [generate_numpy(spec, (b * world + r) * B, B) for r in range(world)]
+        ref.push_batch(*[np.concatenate([p[i] for p in parts]) for i in range(3)])
+    ref.flush()
+    cat = lambda name, cls, fields: cls(*[np.concatenate([getattr(r[name], f) for r in res]) for f in fields])  # noqa: E731
+    assert_fired_equal(cat("fired", capi.Fired, ("key", "window_end", "count", "sum", "min", "max")), ref.poll_fired())
+    assert_events_equal(cat("ealerts", capi.EventRows, ("ts", "key", "val")), ref.poll_event_alerts())
+    assert sum(r["counters"]["late_dropped"] for r in res) == ref.counters()["late_dropped"]
