@@ -262,6 +262,33 @@ class EngineBase:
                 break
         return [np.concatenate([p[i] for p in parts]) for i in range(len(parts[0]))]
 
+    # --- zero-allocation polls: the caller supplies (ideally pinned) column buffers ---------------
+    def _poll_into(self, name, cols_cls, arrays, offset_rows=0):
+        """Single poll call into caller-owned arrays (numpy or pinned torch tensors, all of one
+        capacity).  Returns (rows copied, rows left)."""
+        cap = len(arrays[0]) - offset_rows
+        ptrs = [(_ptr(a) + offset_rows * 8) if a is not None else 0 for a in arrays]
+        cols = cols_cls(*ptrs)
+        n_out, n_left = C.c_size_t(0), C.c_size_t(0)
+        args = [self._h, C.byref(cols), cap]
+        if self._has_mem:
+            args.append(FMQ_MEM_DEVICE if _is_device(arrays[0]) else FMQ_MEM_HOST)
+        args += [C.byref(n_out), C.byref(n_left)]
+        self._check(self._f(name)(*args))
+        return n_out.value, n_left.value
+
+    def poll_fired_into(self, key, window_end, count, sum, min, max):
+        return self._poll_into("poll_fired", FmqFiredCols, [key, window_end, count, sum, min, max])
+
+    def poll_window_alerts_into(self, key, window_end, value):
+        return self._poll_into("poll_window_alerts", FmqWAlertCols, [key, window_end, value])
+
+    def poll_event_alerts_into(self, ts, key, val):
+        return self._poll_into("poll_event_alerts", FmqEventCols, [ts, key, val])
+
+    def poll_consec_alerts_into(self, ts, key, val):
+        return self._poll_into("poll_consec_alerts", FmqEventCols, [ts, key, val])
+
     def poll_fired(self, chunk: int = 1 << 20) -> Fired:
         def mk(c):
             arrs = [np.empty(c, np.uint64), np.empty(c, np.int64), np.empty(c, np.int64),
