@@ -213,6 +213,13 @@ def main():
     kw = workload_kwargs(capi, B * (2 if world > 1 else 1), args.keys)
     kw["table_capacity"] = int(args.keys * args.load)
     kw["device"] = local_rank
+    # weak scaling keeps events per GPU per step fixed, so one global step spans world x more event
+    # time: size the pane ring for it (panes per step + bound + late tail), power of two
+    panes_per_step = (B * world // 1000) // WINDOW_MS + 4
+    ring = 16
+    while ring < panes_per_step + 4:
+        ring *= 2
+    kw["pane_ring"] = ring
     if args.no_efilter:
         kw["efilter_enabled"] = 0
     if args.key_mode == "dense":
