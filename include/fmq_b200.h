@@ -220,6 +220,15 @@ int32_t fmq_get_counters(fmq_handle* h, fmq_counters* out);
 int32_t fmq_get_key_state(fmq_handle* h, const uint64_t* keys, size_t n, int32_t* found,
                           int32_t* consec, void* rolling);
 
+/* Replaces: AbstractStreamOperator#snapshotState / #initializeState (the checkpoint hooks the
+ * tutorial's promised-but-unwritten next chapter is about, chapter3/README.md:454-456).  A snapshot is
+ * the operator's keyed state only — key directory, open-pane accumulators, per-key ValueState,
+ * watermark and counters — copied to a host buffer; rows already emitted must be polled first.
+ * fmq_restore loads it into a handle created with the same job geometry. */
+int32_t fmq_snapshot_size(fmq_handle* h, size_t* bytes);
+int32_t fmq_snapshot(fmq_handle* h, void* host_buf, size_t cap, size_t* written);
+int32_t fmq_restore(fmq_handle* h, const void* host_buf, size_t bytes);
+
 /* Blocks until all work queued on the handle has finished. */
 int32_t fmq_synchronize(fmq_handle* h);
 /* Device time in ms of the last fmq_push_batch / fmq_flush kernel chain (CUDA events on the

@@ -145,6 +145,9 @@ def _declare(lib, p: str, has_mem: bool = True):
         sig("flink_key_group", [i32, i32])
         sig("flink_subtask", [i32, i32, i32])
         sig("partition_by_owner", [vp, vp, vp, vp, sz, C.c_uint32, vp, vp, vp, vp])
+        sig("snapshot_size", [vp, psz])
+        sig("snapshot", [vp, vp, sz, psz])
+        sig("restore", [vp, vp, sz])
         sig("table_ptr", [vp], vp)
         sig("exchange_ptr", [vp], vp)
         sig("ipc_export", [vp, vp])
@@ -383,6 +386,19 @@ class Engine(EngineBase):
     @property
     def handle(self):
         return self._h
+
+    # ---- checkpointing (snapshotState / initializeState) ------------------------------------------
+    def snapshot(self) -> np.ndarray:
+        n = C.c_size_t(0)
+        self._check(self._lib.fmq_snapshot_size(self._h, C.byref(n)))
+        buf = np.empty(n.value, np.uint8)
+        w = C.c_size_t(0)
+        self._check(self._lib.fmq_snapshot(self._h, buf.ctypes.data, n.value, C.byref(w)))
+        return buf[: w.value]
+
+    def restore(self, snap: np.ndarray):
+        snap = np.ascontiguousarray(snap, dtype=np.uint8)
+        self._check(self._lib.fmq_restore(self._h, snap.ctypes.data, snap.nbytes))
 
     # ---- combiner mode (multi-GPU without an event shuffle) -----------------------------------
     @property

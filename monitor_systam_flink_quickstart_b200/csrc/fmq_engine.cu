@@ -547,6 +547,83 @@ int32_t fmq_retire(fmq_handle* h) {
     return FMQ_OK;
 }
 
+// ---- snapshot / restore (Flink snapshotState / initializeState) --------------------
+namespace {
+struct SnapHeader {
+    uint64_t magic; uint32_t version; uint32_t header_bytes;
+    fmq_config cfg; uint64_t capacity; uint32_t ring; uint32_t has_window, has_keyed, anchored_known;
+    uint64_t total_bytes;
+};
+constexpr uint64_t SNAP_MAGIC = 0x31504E53514D46ull;   // "FMQSNP1"
+size_t snap_bytes(const fmq_handle* h) {
+    size_t b = sizeof(SnapHeader) + sizeof(DevState) + h->capacity * 8;
+    if (h->cfg.window_enabled) b += (size_t)h->ring * h->capacity * sizeof(Acc32);
+    if (keyed_enabled(h->cfg)) b += h->capacity * 4 + h->capacity * 8;
+    return b;
+}
+bool same_job(const fmq_config& a, const fmq_config& b) {
+    return a.value_type == b.value_type && a.key_mode == b.key_mode && a.window_enabled == b.window_enabled &&
+           a.window_size_ms == b.window_size_ms && a.window_slide_ms == b.window_slide_ms && a.window_offset_ms == b.window_offset_ms &&
+           (a.agg_mask | FMQ_AGG_COUNT) == (b.agg_mask | FMQ_AGG_COUNT) && a.rolling_max_enabled == b.rolling_max_enabled &&
+           (a.consec_n > 0) == (b.consec_n > 0);
+}
+}  // namespace
+
+int32_t fmq_snapshot_size(fmq_handle* h, size_t* bytes) {
+    if (!h || !bytes) return FMQ_ERR_BAD_ARG;
+    *bytes = snap_bytes(h);
+    return FMQ_OK;
+}
+int32_t fmq_snapshot(fmq_handle* h, void* buf, size_t cap, size_t* written) {
+    if (!h || !buf || !written) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "snapshot of a combiner-mode handle is not supported");
+    const size_t need = snap_bytes(h);
+    if (cap < need) return set_err(h, FMQ_ERR_BAD_ARG, "snapshot buffer too small (see fmq_snapshot_size)");
+    int st = sync_state(h); if (st) return st;
+    const DevState& d = *h->h_st;
+    if (d.n_fired || d.n_walert || d.n_ealert || d.n_calert) return set_err(h, FMQ_ERR_BAD_ARG, "poll every output before taking a snapshot: emitted rows are not operator state");
+    char* p = static_cast<char*>(buf);
+    SnapHeader hd{}; hd.magic = SNAP_MAGIC; hd.version = 1; hd.header_bytes = sizeof(SnapHeader); hd.cfg = h->cfg; hd.capacity = h->capacity; hd.ring = h->ring;
+    hd.has_window = h->cfg.window_enabled; hd.has_keyed = keyed_enabled(h->cfg); hd.anchored_known = h->anchored_known; hd.total_bytes = need;
+    memcpy(p, &hd, sizeof(hd)); p += sizeof(hd);
+    memcpy(p, &d, sizeof(DevState)); p += sizeof(DevState);
+    CU(h, cudaMemcpyAsync(p, h->d_keys, h->capacity * 8, cudaMemcpyDeviceToHost, h->stream)); p += h->capacity * 8;
+    if (hd.has_window) { const size_t b = (size_t)h->ring * h->capacity * sizeof(Acc32); CU(h, cudaMemcpyAsync(p, h->d_acc, b, cudaMemcpyDeviceToHost, h->stream)); p += b; }
+    if (hd.has_keyed) {
+        CU(h, cudaMemcpyAsync(p, h->d_kflags, h->capacity * 4, cudaMemcpyDeviceToHost, h->stream)); p += h->capacity * 4;
+        CU(h, cudaMemcpyAsync(p, h->d_kmax, h->capacity * 8, cudaMemcpyDeviceToHost, h->stream)); p += h->capacity * 8;
+    }
+    CU(h, cudaStreamSynchronize(h->stream));
+    *written = need;
+    return FMQ_OK;
+}
+int32_t fmq_restore(fmq_handle* h, const void* buf, size_t bytes) {
+    if (!h || !buf) return FMQ_ERR_BAD_ARG;
+    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "restore into a combiner-mode handle is not supported");
+    if (bytes < sizeof(SnapHeader)) return set_err(h, FMQ_ERR_BAD_ARG, "not a snapshot");
+    SnapHeader hd; memcpy(&hd, buf, sizeof(hd));
+    if (hd.magic != SNAP_MAGIC || hd.version != 1 || hd.header_bytes != sizeof(SnapHeader)) return set_err(h, FMQ_ERR_BAD_ARG, "not a snapshot of this library version");
+    if (hd.capacity != h->capacity || hd.ring != h->ring || !same_job(hd.cfg, h->cfg) || hd.total_bytes != snap_bytes(h) || bytes < hd.total_bytes)
+        return set_err(h, FMQ_ERR_BAD_ARG, "snapshot was taken with a different job geometry (capacity, ring, window, value type, key mode)");
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaStreamSynchronize(h->stream));
+    const char* p = static_cast<const char*>(buf) + sizeof(SnapHeader);
+    DevState d; memcpy(&d, p, sizeof(d)); p += sizeof(d);
+    d.n_fired = d.n_walert = d.n_ealert = d.n_calert = 0; d.err_flags = 0;
+    CU(h, cudaMemcpyAsync(h->d_st, &d, sizeof(d), cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(h->d_keys, p, h->capacity * 8, cudaMemcpyHostToDevice, h->stream)); p += h->capacity * 8;
+    if (hd.has_window) { const size_t b = (size_t)h->ring * h->capacity * sizeof(Acc32); CU(h, cudaMemcpyAsync(h->d_acc, p, b, cudaMemcpyHostToDevice, h->stream)); p += b; }
+    if (hd.has_keyed) {
+        CU(h, cudaMemcpyAsync(h->d_kflags, p, h->capacity * 4, cudaMemcpyHostToDevice, h->stream)); p += h->capacity * 4;
+        CU(h, cudaMemcpyAsync(h->d_kmax, p, h->capacity * 8, cudaMemcpyHostToDevice, h->stream)); p += h->capacity * 8;
+    }
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->cur_fired = h->cur_walert = h->cur_ealert = h->cur_calert = 0; h->rolling_n = 0; h->sticky = 0;
+    h->anchored_known = hd.anchored_known != 0;
+    return FMQ_OK;
+}
+
 int32_t fmq_synchronize(fmq_handle* h) {
     if (!h) return FMQ_ERR_BAD_ARG;
     CU(h, cudaSetDevice(h->device));

@@ -266,6 +266,45 @@ def test_partial_polls_drain_everything():
     assert len(gpu.poll_fired()) == 0
 
 
+# ---- checkpoint / restore ---------------------------------------------------------
+@pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
+def test_snapshot_restore_continues_exactly(key_mode):
+    """Kill the operator mid-stream, restore a fresh handle from the snapshot, finish the stream: the
+    concatenated output equals an uninterrupted run of the oracle."""
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=20_000, window_slide_ms=5000, max_out_of_orderness_ms=4000,
+              walert_source=capi.FMQ_ALERT_AVG, walert_op=capi.FMQ_CMP_GT, walert_threshold=50.0, rolling_max_enabled=1,
+              consec_n=3, consec_threshold=50.0, consec_reset_on_fire=1, key_mode=key_mode, **SMALL)
+    spec = StreamSpec(n_keys=2000, events_per_ms=3, late_frac_ppm=20000)
+    cpu = OracleEngine(**kw)
+    gpu = capi.Engine(**kw)
+    fired, cal, wal = [], [], []
+
+    def collect(e):
+        fired.append(e.poll_fired()); cal.append(e.poll_consec_alerts()); wal.append(e.poll_window_alerts())
+    for b in range(6):
+        ts, key, val = generate_numpy(spec, b * 20_000, 20_000)
+        cpu.push_batch(ts, key, val); gpu.push_batch(ts, key, val)
+        np.testing.assert_array_equal(gpu.poll_rolling_max(20_000).view(np.uint64), cpu.poll_rolling_max(20_000).view(np.uint64))
+        if b == 2:
+            with pytest.raises(capi.FmqError):
+                gpu.snapshot()                       # un-polled output rows are not state
+            collect(gpu)
+            snap = gpu.snapshot()
+            gpu.close()
+            gpu = capi.Engine(**kw)
+            gpu.restore(snap)
+    gpu.flush(); cpu.flush(); collect(gpu)
+    cat = lambda parts, cls, fields: cls(*[np.concatenate([getattr(p, f) for p in parts]) for f in fields])  # noqa: E731
+    assert_fired_equal(cat(fired, capi.Fired, ("key", "window_end", "count", "sum", "min", "max")), cpu.poll_fired())
+    assert_events_equal(cat(cal, capi.EventRows, ("ts", "key", "val")), cpu.poll_consec_alerts())
+    a, w = sort_walerts(cat(wal, capi.WindowAlerts, ("key", "window_end", "value"))), sort_walerts(cpu.poll_window_alerts())
+    np.testing.assert_array_equal(a.key, w.key); np.testing.assert_allclose(a.value, w.value, rtol=1e-9)
+    cg, cc = gpu.counters(), cpu.counters()
+    assert cg["late_dropped"] == cc["late_dropped"] and cg["windows_fired"] == cc["windows_fired"] and cg["events_in"] == cc["events_in"]
+    with pytest.raises(capi.FmqError):
+        capi.Engine(**dict(kw, pane_ring=64)).restore(snap)        # different geometry is refused
+
+
 # ---- keyBy exchange ------------------------------------------------------------------------------
 @pytest.mark.parametrize("world", [1, 2, 8])
 def test_partition_by_owner_is_a_stable_split(world):
