@@ -49,7 +49,7 @@ struct fmq_handle {
     u64* d_rolling = nullptr; size_t rolling_n = 0;
     size_t cur_fired = 0, cur_walert = 0, cur_ealert = 0, cur_calert = 0;   // host read cursors
     // keyed-path / partition scratch
-    u32 *d_slot[2] = {nullptr, nullptr}, *d_idx[2] = {nullptr, nullptr};
+    u64* d_pack[2] = {nullptr, nullptr};   // (slot << 32 | arrival index), ping-pong
     u32* d_counts = nullptr; u32* d_tiles = nullptr; size_t counts_len = 0, tiles_len = 0;
     uint64_t launches = 0;
     // combiner mode (fmq_attach_peers)
@@ -87,7 +87,7 @@ static void free_all(fmq_handle* h) {
     void* ptrs[] = {h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
                     h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
-                    h->d_slot[0], h->d_slot[1], h->d_idx[0], h->d_idx[1], h->d_counts, h->d_tiles, h->d_xchg};
+                    h->d_pack[0], h->d_pack[1], h->d_counts, h->d_tiles, h->d_xchg};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->h_st) cudaFreeHost(h->h_st);
     for (auto& q : h->tev) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
@@ -165,7 +165,7 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     if (keyed_enabled(*cfg)) {
         CUC(dalloc(&h->d_kflags, h->capacity)); CUC(cudaMemset(h->d_kflags, 0, h->capacity * 4));
         CUC(dalloc(&h->d_kmax, h->capacity)); CUC(cudaMemset(h->d_kmax, 0, h->capacity * 8));
-        for (int k = 0; k < 2; ++k) { CUC(dalloc(&h->d_slot[k], h->max_batch)); CUC(dalloc(&h->d_idx[k], h->max_batch)); }
+        for (int k = 0; k < 2; ++k) CUC(dalloc(&h->d_pack[k], h->max_batch));
         if (cfg->rolling_max_enabled) CUC(dalloc(&h->d_rolling, h->max_batch));
         if (cfg->consec_n > 0) {
             h->ca_cap = cfg->calert_capacity ? cfg->calert_capacity : h->max_batch;
@@ -174,6 +174,7 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     }
     // radix counter matrix (keyed path and owner partition)
     h->counts_len = (size_t)RS_DIGITS * rs_num_chunks(h->max_batch);
+    if (keyed_enabled(*cfg)) { const size_t k = (size_t)2048 * ps_num_chunks(h->max_batch); if (k > h->counts_len) h->counts_len = k; }
     h->tiles_len = (h->counts_len + SCAN_TILE - 1) / SCAN_TILE;
     CUC(dalloc(&h->d_counts, h->counts_len)); CUC(dalloc(&h->d_tiles, h->tiles_len));
     CUC(dalloc(&h->d_xchg, 4)); CUC(cudaMemset(h->d_xchg, 0, 32));
@@ -275,20 +276,42 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
     CU(h, cudaEventRecord(tev[1], h->stream));
     if (n > 0 && keyed_enabled(c)) {
         const unsigned gb = (unsigned)((n + 255) / 256 < (size_t)h->num_sms * 8 ? (n + 255) / 256 : (size_t)h->num_sms * 8);
-        resolve_slots_kernel<<<gb, 256, 0, h->stream>>>(key, n, h->d_keys, h->capacity, c.key_mode == FMQ_KEYS_DENSE, h->d_st, h->d_slot[0], h->d_idx[0]); LAUNCHED(h, "resolve_slots_kernel");
+        resolve_pack_kernel<<<gb, 256, 0, h->stream>>>(key, n, h->d_keys, h->capacity, c.key_mode == FMQ_KEYS_DENSE, h->d_st, h->d_pack[0]); LAUNCHED(h, "resolve_pack_kernel");
+        // LSD radix sort by slot: as few passes as 11-bit digits allow, bits spread evenly over them
+        const u32 passes = (h->slot_bits + 10) / 11;
+        u32 bits = (h->slot_bits + passes - 1) / passes; if (bits < 6) bits = 6;
+        const u32 nchunks = ps_num_chunks(n), nblocks = (nchunks + 7) / 8;
         int cur = 0;
-        for (u32 shift = 0; shift < h->slot_bits; shift += 8) {
-            SlotDigit dg{h->d_slot[cur], shift};
-            MovePair mv{h->d_slot[cur], h->d_idx[cur], h->d_slot[cur ^ 1], h->d_idx[cur ^ 1]};
-            int s = multisplit(h, n, dg, mv); if (s) return s;
+        for (u32 pass = 0; pass < passes; ++pass) {
+            const u32 shift = 32 + pass * bits;
+            const size_t smem = (size_t)8 * (1u << bits) * 4;
+            auto launch = [&](auto hist, auto scat) -> int {
+                CU(h, cudaFuncSetAttribute(hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                CU(h, cudaFuncSetAttribute(scat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                hist<<<nblocks, 256, smem, h->stream>>>(h->d_pack[cur], nullptr, n, nchunks, shift, h->d_counts); LAUNCHED(h, "ps_pass_kernel(hist)");
+                int s_ = exclusive_scan_counts(h, (size_t)(1u << bits) * nchunks); if (s_) return s_;
+                scat<<<nblocks, 256, smem, h->stream>>>(h->d_pack[cur], h->d_pack[cur ^ 1], n, nchunks, shift, h->d_counts); LAUNCHED(h, "ps_pass_kernel(scatter)");
+                return FMQ_OK;
+            };
+            int s_ = FMQ_OK;
+            switch (bits) {
+                case 6: s_ = launch(ps_pass_kernel<6, false>, ps_pass_kernel<6, true>); break;
+                case 7: s_ = launch(ps_pass_kernel<7, false>, ps_pass_kernel<7, true>); break;
+                case 8: s_ = launch(ps_pass_kernel<8, false>, ps_pass_kernel<8, true>); break;
+                case 9: s_ = launch(ps_pass_kernel<9, false>, ps_pass_kernel<9, true>); break;
+                case 10: s_ = launch(ps_pass_kernel<10, false>, ps_pass_kernel<10, true>); break;
+                default: s_ = launch(ps_pass_kernel<11, false>, ps_pass_kernel<11, true>); break;
+            }
+            if (s_) return s_;
             cur ^= 1;
         }
         KeyedArgs k{};
-        k.slot_sorted = h->d_slot[cur]; k.idx_sorted = h->d_idx[cur]; k.n = n; k.ts = ts; k.key = key; k.val = val; k.st = h->d_st;
+        k.sorted = h->d_pack[cur]; k.n = n; k.ts = ts; k.key = key; k.val = val; k.st = h->d_st;
         k.kflags = h->d_kflags; k.kmax = h->d_kmax; k.rolling_enabled = c.rolling_max_enabled; k.rolling_out = h->d_rolling;
         k.consec_n = c.consec_n; k.consec_op = c.consec_op; k.consec_reset = c.consec_reset_on_fire; k.consec_thr = c.consec_threshold;
         k.ca_ts = h->ca_ts; k.ca_key = h->ca_key; k.ca_val = h->ca_val; k.ca_cap = h->ca_cap;
-        keyed_apply_kernel<V><<<gb, 256, 0, h->stream>>>(k); LAUNCHED(h, "keyed_apply_kernel");
+        const size_t nwarps = (n + KA_RANGE - 1) / KA_RANGE;
+        keyed_scan_kernel<V><<<(unsigned)((nwarps + 7) / 8), 256, 0, h->stream>>>(k); LAUNCHED(h, "keyed_scan_kernel");
         h->rolling_n = c.rolling_max_enabled ? n : 0;
     } else if (keyed_enabled(c)) {
         h->rolling_n = 0;

@@ -204,6 +204,24 @@ def test_keyed_state_parity(vt, reset, key_mode):
     assert gpu.counters()["consec_alerts"] == cpu.counters()["consec_alerts"] > 0
 
 
+@pytest.mark.parametrize("n_keys,thr", [(3, 50.0), (1, 20.0), (40, 90.0), (100_000, 50.0)])
+def test_keyed_state_long_runs_and_sparse_keys(n_keys, thr):
+    """Heavy-hitter keys (one run spans many warps' ranges and rounds) and very sparse keys."""
+    kw = dict(rolling_max_enabled=1, consec_n=3, consec_threshold=thr, consec_reset_on_fire=1,
+              table_capacity=1 << 18, max_batch=1 << 17)
+    gpu, cpu = pair(**kw)
+    spec = StreamSpec(n_keys=n_keys, events_per_ms=5)
+    for b, n in enumerate([70_001, 100_000, 513]):
+        ts, key, val = generate_numpy(spec, b * 100_000, n)
+        gpu.push_batch(ts, key, val); cpu.push_batch(ts, key, val)
+        np.testing.assert_array_equal(gpu.poll_rolling_max(n).view(np.uint64), cpu.poll_rolling_max(n).view(np.uint64))
+        assert_events_equal(gpu.poll_consec_alerts(), cpu.poll_consec_alerts())
+    keys = np.arange(0, min(n_keys, 5000), dtype=np.uint64)
+    fg, cg, rg = gpu.key_state(keys); fc, cc, rc = cpu.key_state(keys)
+    np.testing.assert_array_equal(fg, fc); np.testing.assert_array_equal(cg, cc)
+    np.testing.assert_array_equal(rg.view(np.uint64), rc.view(np.uint64))
+
+
 def test_consecutive_rule_known_answers():
     """6 consecutive overs -> 2 alerts with reset-on-fire; a dip resets the run."""
     e = capi.Engine(consec_n=3, consec_threshold=90.0, consec_reset_on_fire=1, **SMALL)
