@@ -54,6 +54,13 @@ __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in
         u64 it[PS_AHEAD];
 #pragma unroll
         for (int r = 0; r < PS_AHEAD; ++r) { const size_t i = i0 + r * 32 + lane; it[r] = i < hi ? in[i] : ~0ull; }
+        if (!SCATTER) {
+            // counting needs no order: one shared-memory atomic per item on the warp's private bins
+#pragma unroll
+            for (int r = 0; r < PS_AHEAD; ++r)
+                if (i0 + r * 32 + lane < hi) atomicAdd(&bins[(u32)(it[r] >> shift) & (NB - 1)], 1u);
+            continue;
+        }
 #pragma unroll
         for (int r = 0; r < PS_AHEAD; ++r) {
             const bool act = i0 + r * 32 + lane < hi;
@@ -62,18 +69,15 @@ __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in
                 const u32 d = (u32)(it[r] >> shift) & (NB - 1);
                 const unsigned m = __match_any_sync(am, d);
                 const int leader = __ffs(m) - 1;
-                if (SCATTER) {
-                    u32 base = 0;
-                    if ((int)lane == leader) { base = bins[d]; bins[d] = base + __popc(m); }
-                    base = __shfl_sync(m, base, leader);
-                    out[(size_t)base + __popc(m & ((1u << lane) - 1))] = it[r];
-                } else if ((int)lane == leader) {
-                    bins[d] += __popc(m);
-                }
+                u32 base = 0;
+                if ((int)lane == leader) { base = bins[d]; bins[d] = base + __popc(m); }
+                base = __shfl_sync(m, base, leader);
+                out[(size_t)base + __popc(m & ((1u << lane) - 1))] = it[r];
             }
             __syncwarp();
         }
     }
+    __syncwarp();
     if (!SCATTER) for (u32 d = lane; d < NB; d += 32) counts[(size_t)d * nchunks + chunk] = bins[d];
 }
 
