@@ -154,7 +154,9 @@ def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt):
         parts = []
         for r, e in enumerate(engs):
             start = (i * world + r) * b
-            e.push_local(*generate_torch(spec, start, b, device="cuda:0"))
+            cols = generate_torch(spec, start, b, device="cuda:0")
+            torch.cuda.synchronize()
+            e.push_local(*cols); e.synchronize()
             parts.append(generate_numpy(spec, start, b))
         fire(capi.FMQ_WM_AUTO)
         ref.push_batch(*[np.concatenate([p[j] for p in parts]) for j in range(3)])
@@ -192,6 +194,7 @@ def _combiner_worker(rank, world, port, outdir):
         ts, key, val = generate_torch(spec, (b * world + rank) * B, B, device=f"cuda:{rank}")
         torch.cuda.synchronize()
         op.process_batch(ts, key, val)
+        eng.synchronize()          # the columns are freed at the next iteration: wait until they have been consumed
     op.flush()
     res = dict(fired=eng.poll_fired(), ealerts=eng.poll_event_alerts(), counters=eng.counters())
     pickle.dump(res, open(os.path.join(outdir, f"r{rank}.pkl"), "wb"))
