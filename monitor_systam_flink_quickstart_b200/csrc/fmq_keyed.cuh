@@ -54,13 +54,12 @@ __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in
         u64 it[PS_AHEAD];
 #pragma unroll
         for (int r = 0; r < PS_AHEAD; ++r) { const size_t i = i0 + r * 32 + lane; it[r] = i < hi ? in[i] : ~0ull; }
-        if (!SCATTER) {
+        if constexpr (!SCATTER) {
             // counting needs no order: one shared-memory atomic per item on the warp's private bins
 #pragma unroll
             for (int r = 0; r < PS_AHEAD; ++r)
                 if (i0 + r * 32 + lane < hi) atomicAdd(&bins[(u32)(it[r] >> shift) & (NB - 1)], 1u);
-            continue;
-        }
+        } else {
 #pragma unroll
         for (int r = 0; r < PS_AHEAD; ++r) {
             const bool act = i0 + r * 32 + lane < hi;
@@ -75,6 +74,7 @@ __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in
                 out[(size_t)base + __popc(m & ((1u << lane) - 1))] = it[r];
             }
             __syncwarp();
+        }
         }
     }
     __syncwarp();

@@ -269,6 +269,11 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
         }
         __syncthreads();                                         // every thread has its events in registers: the stage is free
         if (threadIdx.x == 0) {
+            // The stage was just read through the generic proxy (by every thread, ordered by the barrier
+            // above); the bulk copy below overwrites it through the async proxy.  Without this
+            // cross-proxy fence the copy can overtake those reads: measured as a rare wrong value column
+            // (counts conserved, sums not) once blocks reuse a stage (tests/test_gpu_fullsize.py).
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             const size_t tn = t + (size_t)INGEST_STAGES * gridDim.x;
             if (tn < full_tiles) issue(tn, s);
         }
