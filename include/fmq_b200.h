@@ -134,6 +134,7 @@ typedef struct fmq_config {
     uint64_t walert_capacity;        /* window-alert rows buffered between polls                 */
     uint64_t ealert_capacity;        /* per-event filter rows buffered between polls             */
     uint64_t calert_capacity;        /* consecutive-breach alert rows buffered between polls     */
+    uint64_t text_max_bytes;         /* > 0: device buffers for fmq_parse_text / fmq_push_text    */
 } fmq_config;
 
 /* one fired (key, window): 48 B per row */
@@ -219,6 +220,32 @@ int32_t fmq_get_counters(fmq_handle* h, fmq_counters* out);
  * n keys; found[i] = 0/1, consec[i] = breach counter, rolling[i] = rolling max bits. */
 int32_t fmq_get_key_state(fmq_handle* h, const uint64_t* keys, size_t n, int32_t* found,
                           int32_t* consec, void* rolling);
+
+/* Text ingest on the device.  Replaces: the `map` functions in front of every job —
+ * FMQ_TEXT_CPU  "<epoch-s> <host> <cpu> <usage>"     Main.java:21-25, ComputeCpuAvg.java:22-25
+ *               -> ts = epoch-s * 1000, key = fmq_text_key_hash(host), val = (double) usage
+ * FMQ_TEXT_FLOW "<ISO local time> <channel> <flow>"  BandwidthMonitorWithEventTime.java:33-34,39-44
+ *               -> ts = (int) epochSecond(UTC+utc_offset_hours) * 1000 (the reference's 32-bit cast),
+ *                  key = fmq_text_key_hash(channel), val = (int64) flow
+ * Lines are '\n'-separated (a final unterminated line counts); fields are split on single spaces like
+ * String.split(" ").  Doubles are parsed on the device only where that is exact (<= 15 significant
+ * digits, |decimal exponent| <= 22: one correctly rounded IEEE operation, identical to
+ * Double.parseDouble); any other value is flagged FMQ_TEXT_VALUE_ON_HOST for the caller to parse.
+ * fmq_parse_text writes the columns (and a per-line status) to caller buffers of `cap` lines.
+ * fmq_push_text parses and feeds the result straight into the operator chain without leaving the
+ * device; it refuses the batch (FMQ_ERR_BAD_ARG) if any line is not FMQ_TEXT_OK.
+ * Needs fmq_config.text_max_bytes >= bytes and max_batch >= number of lines. */
+#define FMQ_TEXT_CPU 0
+#define FMQ_TEXT_FLOW 1
+#define FMQ_TEXT_OK 0u
+#define FMQ_TEXT_MALFORMED 1u
+#define FMQ_TEXT_VALUE_ON_HOST 2u
+uint64_t fmq_text_key_hash(const char* s, size_t len);
+int32_t fmq_parse_text(fmq_handle* h, const char* text, size_t bytes, int32_t text_mem, int32_t format,
+                       int32_t utc_offset_hours, int64_t* ts_out, uint64_t* key_out, void* val_out,
+                       uint32_t* status_out, size_t cap, int32_t out_mem, size_t* n_lines, size_t* n_bad);
+int32_t fmq_push_text(fmq_handle* h, const char* text, size_t bytes, int32_t text_mem, int32_t format,
+                      int32_t utc_offset_hours, int64_t watermark_after, size_t* n_lines);
 
 /* Replaces: AbstractStreamOperator#snapshotState / #initializeState (the checkpoint hooks the
  * tutorial's promised-but-unwritten next chapter is about, chapter3/README.md:454-456).  A snapshot is

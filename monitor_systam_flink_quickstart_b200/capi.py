@@ -18,6 +18,8 @@ import numpy as np
 FMQ_VAL_F64, FMQ_VAL_I64 = 0, 1
 FMQ_MEM_HOST, FMQ_MEM_DEVICE = 0, 1
 FMQ_KEYS_HASHED, FMQ_KEYS_DENSE = 0, 1
+FMQ_TEXT_CPU, FMQ_TEXT_FLOW = 0, 1
+FMQ_TEXT_OK, FMQ_TEXT_MALFORMED, FMQ_TEXT_VALUE_ON_HOST = 0, 1, 2
 FMQ_CMP_GT, FMQ_CMP_LT, FMQ_CMP_GE, FMQ_CMP_LE = 0, 1, 2, 3
 FMQ_AGG_COUNT, FMQ_AGG_SUM, FMQ_AGG_MIN, FMQ_AGG_MAX = 1, 2, 4, 8
 FMQ_ALERT_NONE, FMQ_ALERT_SUM, FMQ_ALERT_AVG, FMQ_ALERT_MIN, FMQ_ALERT_MAX, FMQ_ALERT_COUNT = range(6)
@@ -44,6 +46,7 @@ class FmqConfig(C.Structure):
         ("table_capacity", C.c_uint64), ("pane_ring", C.c_uint32), ("reserved2", C.c_uint32),
         ("max_batch", C.c_uint64), ("fired_capacity", C.c_uint64), ("walert_capacity", C.c_uint64),
         ("ealert_capacity", C.c_uint64), ("calert_capacity", C.c_uint64),
+        ("text_max_bytes", C.c_uint64),
     ]
 
 
@@ -145,6 +148,9 @@ def _declare(lib, p: str, has_mem: bool = True):
         sig("flink_key_group", [i32, i32])
         sig("flink_subtask", [i32, i32, i32])
         sig("partition_by_owner", [vp, vp, vp, vp, sz, C.c_uint32, vp, vp, vp, vp])
+        sig("text_key_hash", [C.c_char_p, sz], C.c_uint64)
+        sig("parse_text", [vp, vp, sz, i32, i32, i32, vp, vp, vp, vp, sz, i32, psz, psz])
+        sig("push_text", [vp, vp, sz, i32, i32, i32, i64, psz])
         sig("snapshot_size", [vp, psz])
         sig("snapshot", [vp, vp, sz, psz])
         sig("restore", [vp, vp, sz])
@@ -386,6 +392,22 @@ class Engine(EngineBase):
     @property
     def handle(self):
         return self._h
+
+    # ---- text ingest on the device ------------------------------------------------------------------
+    def parse_text(self, text: bytes, fmt: int, utc_offset_hours: int = 8):
+        """-> (ts, key, val, status) numpy arrays, one entry per line."""
+        cap = text.count(b"\n") + 1
+        ts, key, val, st = np.empty(cap, np.int64), np.empty(cap, np.uint64), np.empty(cap, self._vdtype), np.empty(cap, np.uint32)
+        n, bad = C.c_size_t(0), C.c_size_t(0)
+        self._check(self._lib.fmq_parse_text(self._h, text, len(text), FMQ_MEM_HOST, fmt, utc_offset_hours, ts.ctypes.data, key.ctypes.data,
+                                             val.ctypes.data, st.ctypes.data, cap, FMQ_MEM_HOST, C.byref(n), C.byref(bad)))
+        k = n.value
+        return ts[:k], key[:k], val[:k], st[:k]
+
+    def push_text(self, text: bytes, fmt: int, watermark_after: int = FMQ_WM_AUTO, utc_offset_hours: int = 8) -> int:
+        n = C.c_size_t(0)
+        self._check(self._lib.fmq_push_text(self._h, text, len(text), FMQ_MEM_HOST, fmt, utc_offset_hours, watermark_after, C.byref(n)))
+        return n.value
 
     # ---- checkpointing (snapshotState / initializeState) ------------------------------------------
     def snapshot(self) -> np.ndarray:

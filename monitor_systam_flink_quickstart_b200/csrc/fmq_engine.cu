@@ -12,6 +12,7 @@
 #include "fmq_window.cuh"
 #include "fmq_sort.cuh"
 #include "fmq_keyed.cuh"
+#include "fmq_text.cuh"
 
 using namespace fmq;
 
@@ -56,7 +57,9 @@ struct fmq_handle {
     int world = 1, rank = 0;
     const Acc32* peer_acc[FMQ_MAX_PEERS] = {};
     i64* d_xchg = nullptr;               // 4 x int64 exchange buffer for the all-reduce of the batch scalars
-    size_t pending_n = 0;                // events ingested by fmq_push_local and not yet accounted by fmq_fire_global
+    size_t pending_n = 0;
+    // text ingest
+    char* d_text = nullptr; u64* d_line_start = nullptr; u32* d_txt_status = nullptr; unsigned long long* d_txt_bad = nullptr;                // events ingested by fmq_push_local and not yet accounted by fmq_fire_global
 };
 
 #define CU(h, call)                                                                                   \
@@ -87,7 +90,7 @@ static void free_all(fmq_handle* h) {
     void* ptrs[] = {h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
                     h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
-                    h->d_pack[0], h->d_pack[1], h->d_counts, h->d_tiles, h->d_xchg};
+                    h->d_pack[0], h->d_pack[1], h->d_counts, h->d_tiles, h->d_xchg, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->h_st) cudaFreeHost(h->h_st);
     for (auto& q : h->tev) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
@@ -178,6 +181,12 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     h->tiles_len = (h->counts_len + SCAN_TILE - 1) / SCAN_TILE;
     CUC(dalloc(&h->d_counts, h->counts_len)); CUC(dalloc(&h->d_tiles, h->tiles_len));
     CUC(dalloc(&h->d_xchg, 4)); CUC(cudaMemset(h->d_xchg, 0, 32));
+    if (cfg->text_max_bytes > 0) {
+        CUC(dalloc(&h->d_text, cfg->text_max_bytes + 64)); CUC(dalloc(&h->d_line_start, h->max_batch + 2));
+        CUC(dalloc(&h->d_txt_status, h->max_batch)); CUC(dalloc(&h->d_txt_bad, 1));
+        const size_t nb = (cfg->text_max_bytes + TXT_CHUNK - 1) / TXT_CHUNK + 1;
+        if (nb > h->counts_len) return fail(FMQ_ERR_BAD_ARG, "text_max_bytes too large for this max_batch (raise max_batch)");
+    }
     h->peer_acc[0] = h->d_acc;
     CUC(cudaDeviceSynchronize());
 #undef CUC
@@ -568,6 +577,71 @@ int32_t fmq_retire(fmq_handle* h) {
     CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][3], h->stream));
     h->pushes++;
     return FMQ_OK;
+}
+
+// ---- text ingest ------------------------------------------------------------------------------------
+uint64_t fmq_text_key_hash(const char* s, size_t len) {
+    u64 hsh = 0xcbf29ce484222325ull;
+    for (size_t i = 0; i < len; ++i) { hsh ^= (unsigned char)s[i]; hsh *= 0x100000001b3ull; }
+    hsh = mix64(hsh);
+    return hsh == KEY_EMPTY ? 0 : hsh;
+}
+// parses into the handle's staging columns (d_in_ts / d_in_key / d_in_val) and d_txt_status
+static int parse_text_to_staging(fmq_handle* h, const char* text, size_t bytes, int32_t text_mem, int32_t format, int32_t utc, size_t* n_lines, size_t* n_bad) {
+    if (!h->d_text) return set_err(h, FMQ_ERR_BAD_ARG, "text ingest needs fmq_config.text_max_bytes > 0");
+    if (bytes > h->cfg.text_max_bytes) return set_err(h, FMQ_ERR_BAD_ARG, "text larger than fmq_config.text_max_bytes");
+    if (format != FMQ_TEXT_CPU && format != FMQ_TEXT_FLOW) return set_err(h, FMQ_ERR_BAD_ARG, "bad text format");
+    if ((format == FMQ_TEXT_CPU) != (h->cfg.value_type == FMQ_VAL_F64)) return set_err(h, FMQ_ERR_BAD_ARG, "FMQ_TEXT_CPU yields f64 values, FMQ_TEXT_FLOW int64: value_type does not match");
+    *n_lines = 0; *n_bad = 0;
+    if (bytes == 0) return FMQ_OK;
+    if (!text) return set_err(h, FMQ_ERR_BAD_ARG, "null text");
+    CU(h, cudaSetDevice(h->device));
+    const char* d = text;
+    if (text_mem == FMQ_MEM_HOST) { CU(h, cudaMemcpyAsync(h->d_text, text, bytes, cudaMemcpyHostToDevice, h->stream)); d = h->d_text; }
+    const u32 nblocks = (u32)((bytes + TXT_CHUNK - 1) / TXT_CHUNK);
+    txt_count_kernel<<<nblocks, TXT_THREADS, 0, h->stream>>>(d, bytes, h->d_counts); LAUNCHED(h, "txt_count_kernel");
+    CU(h, cudaMemsetAsync(h->d_counts + nblocks, 0, 4, h->stream));
+    int s = exclusive_scan_counts(h, (size_t)nblocks + 1); if (s) return s;
+    u32 newlines = 0; char last = 0;
+    CU(h, cudaMemcpyAsync(&newlines, h->d_counts + nblocks, 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaMemcpyAsync(&last, d + bytes - 1, 1, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    const size_t lines = (size_t)newlines + (last != '\n' ? 1 : 0);
+    if (lines > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "more lines than fmq_config.max_batch");
+    txt_mark_kernel<<<nblocks, TXT_THREADS, 0, h->stream>>>(d, bytes, h->d_counts, h->d_line_start, h->max_batch + 2); LAUNCHED(h, "txt_mark_kernel");
+    if (last != '\n') { const u64 end = bytes; CU(h, cudaMemcpyAsync(h->d_line_start + lines, &end, 8, cudaMemcpyHostToDevice, h->stream)); }
+    CU(h, cudaMemsetAsync(h->d_txt_bad, 0, 8, h->stream));
+    TextArgs a{d, bytes, h->d_line_start, lines, format, utc, h->d_in_ts, h->d_in_key, h->d_in_val, h->d_txt_status, h->d_txt_bad};
+    txt_parse_kernel<<<(unsigned)((lines + 255) / 256), 256, 0, h->stream>>>(a); LAUNCHED(h, "txt_parse_kernel");
+    unsigned long long bad = 0;
+    CU(h, cudaMemcpyAsync(&bad, h->d_txt_bad, 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    *n_lines = lines; *n_bad = (size_t)bad;
+    return FMQ_OK;
+}
+int32_t fmq_parse_text(fmq_handle* h, const char* text, size_t bytes, int32_t text_mem, int32_t format, int32_t utc, int64_t* ts_out, uint64_t* key_out,
+                       void* val_out, uint32_t* status_out, size_t cap, int32_t out_mem, size_t* n_lines, size_t* n_bad) {
+    if (!h || !n_lines || !n_bad) return FMQ_ERR_BAD_ARG;
+    int s = parse_text_to_staging(h, text, bytes, text_mem, format, utc, n_lines, n_bad); if (s) return s;
+    if (*n_lines > cap) return set_err(h, FMQ_ERR_BAD_ARG, "output buffers smaller than the number of lines");
+    const cudaMemcpyKind kind = out_mem == FMQ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    const size_t n = *n_lines;
+    if (n) {
+        if (ts_out) CU(h, cudaMemcpyAsync(ts_out, h->d_in_ts, n * 8, kind, h->stream));
+        if (key_out) CU(h, cudaMemcpyAsync(key_out, h->d_in_key, n * 8, kind, h->stream));
+        if (val_out) CU(h, cudaMemcpyAsync(val_out, h->d_in_val, n * 8, kind, h->stream));
+        if (status_out) CU(h, cudaMemcpyAsync(status_out, h->d_txt_status, n * 4, kind, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+    }
+    return FMQ_OK;
+}
+int32_t fmq_push_text(fmq_handle* h, const char* text, size_t bytes, int32_t text_mem, int32_t format, int32_t utc, int64_t wm_after, size_t* n_lines) {
+    if (!h || !n_lines) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    size_t bad = 0;
+    int s = parse_text_to_staging(h, text, bytes, text_mem, format, utc, n_lines, &bad); if (s) return s;
+    if (bad) { h->err = std::to_string(bad) + " line(s) are malformed or need a host-side value parse: use fmq_parse_text and fix them"; return FMQ_ERR_BAD_ARG; }
+    return fmq_push_batch(h, (const int64_t*)h->d_in_ts, (const uint64_t*)h->d_in_key, h->d_in_val, *n_lines, wm_after, FMQ_MEM_DEVICE);
 }
 
 // ---- snapshot / restore (Flink snapshotState / initializeState) --------------------

@@ -61,3 +61,17 @@ def parse_flow_line(line: str) -> Tuple[int, str, int]:
     """-> (event time ms, channel, flow bytes).  BandwidthMonitorWithEventTime.java:33-44."""
     items = line.split(" ")
     return iso_local_to_epoch_ms(items[0]), items[1], int(items[2])
+
+
+def text_key_hash(name: str) -> int:
+    """Host restatement of ``fmq_text_key_hash`` (FNV-1a over the UTF-8 bytes, finished with mix64):
+    the key id the device text parser assigns to a host / channel string."""
+    m = (1 << 64) - 1
+    h = 0xCBF29CE484222325
+    for b in name.encode("utf-8"):
+        h ^= b
+        h = (h * 0x100000001B3) & m
+    h ^= h >> 30; h = (h * 0xBF58476D1CE4E5B9) & m
+    h ^= h >> 27; h = (h * 0x94D049BB133111EB) & m
+    h ^= h >> 31
+    return 0 if h == m else h

@@ -131,6 +131,24 @@ def test_window_parity_seeded(name, batch, key_mode):
     assert cpu.counters()["windows_fired"] > 0
 
 
+@pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
+def test_window_parity_when_blocks_reuse_their_staging_ring(key_mode):
+    """2.2 M events per batch = ~5 tiles per resident block: every shared-memory stage of the TMA ring is
+    refilled while the kernel runs (the small tests above never get that far).  Against the oracle."""
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=5000, max_out_of_orderness_ms=3000,
+              efilter_enabled=1, efilter_threshold=97.0, key_mode=key_mode, table_capacity=60_000, pane_ring=64, max_batch=1 << 22,
+              fired_capacity=1 << 21, ealert_capacity=1 << 20)
+    spec = StreamSpec(n_keys=40_000, events_per_ms=200, jitter_ms=3000, late_frac_ppm=2000, late_extra_ms=20_000)
+    gpu, cpu = pair(**kw)
+    n = 2_200_000
+    for b in range(3):
+        ts, key, val = generate_numpy(spec, b * n, n)
+        gpu.push_batch(ts, key, val); cpu.push_batch(ts, key, val)
+    gpu.flush(); cpu.flush()
+    compare_all(gpu, cpu)
+    assert cpu.counters()["late_dropped"] > 0
+
+
 def test_explicit_watermarks_and_empty_batches():
     kw = dict(window_enabled=1, agg_mask=15, window_size_ms=5000, window_slide_ms=5000, **SMALL)
     gpu, cpu = pair(**kw)
