@@ -135,6 +135,10 @@ typedef struct fmq_config {
     uint64_t ealert_capacity;        /* per-event filter rows buffered between polls             */
     uint64_t calert_capacity;        /* consecutive-breach alert rows buffered between polls     */
     uint64_t text_max_bytes;         /* > 0: device buffers for fmq_parse_text / fmq_push_text    */
+    uint64_t median_log_capacity;    /* > 0: also compute the per-(key, window) median
+                                        (ComputeCpuMiddle.java:34-47); this many accepted records
+                                        can be buffered while their windows are open (f64 only)   */
+    uint64_t median_capacity;        /* median rows buffered between polls                        */
 } fmq_config;
 
 /* one fired (key, window): 48 B per row */
@@ -203,6 +207,11 @@ int32_t fmq_poll_fired(fmq_handle* h, const fmq_fired_cols* out, size_t cap, int
 /* Replaces: the chained map + filter after the window (BandwidthMonitorWithEventTime.java:48-55). */
 int32_t fmq_poll_window_alerts(fmq_handle* h, const fmq_walert_cols* out, size_t cap, int32_t mem,
                                size_t* n_out, size_t* n_left);
+/* Replaces: the ProcessWindowFunction output of ComputeCpuMiddle.java:36-47: one row
+ * (key, window_end, median) per fired (key, window); `value` is the middle element of the window's
+ * sorted values, or the mean of the two middle ones.  Needs fmq_config.median_log_capacity > 0. */
+int32_t fmq_poll_medians(fmq_handle* h, const fmq_walert_cols* out, size_t cap, int32_t mem,
+                         size_t* n_out, size_t* n_left);
 /* Replaces: StreamFilter output of Main.java:27-32 (row order unspecified, compare as sets). */
 int32_t fmq_poll_event_alerts(fmq_handle* h, const fmq_event_cols* out, size_t cap, int32_t mem,
                               size_t* n_out, size_t* n_left);

@@ -46,7 +46,7 @@ class FmqConfig(C.Structure):
         ("table_capacity", C.c_uint64), ("pane_ring", C.c_uint32), ("reserved2", C.c_uint32),
         ("max_batch", C.c_uint64), ("fired_capacity", C.c_uint64), ("walert_capacity", C.c_uint64),
         ("ealert_capacity", C.c_uint64), ("calert_capacity", C.c_uint64),
-        ("text_max_bytes", C.c_uint64),
+        ("text_max_bytes", C.c_uint64), ("median_log_capacity", C.c_uint64), ("median_capacity", C.c_uint64),
     ]
 
 
@@ -129,6 +129,8 @@ def _declare(lib, p: str, has_mem: bool = True):
     sig("poll_fired", [vp, C.POINTER(FmqFiredCols), sz] + mem + [psz, psz])
     sig("poll_window_alerts", [vp, C.POINTER(FmqWAlertCols), sz] + mem + [psz, psz])
     sig("poll_event_alerts", [vp, C.POINTER(FmqEventCols), sz] + mem + [psz, psz])
+    if has_mem or p == "orc_":
+        sig("poll_medians", [vp, C.POINTER(FmqWAlertCols), sz] + mem + [psz, psz])
     sig("poll_consec_alerts", [vp, C.POINTER(FmqEventCols), sz] + mem + [psz, psz])
     sig("poll_rolling_max", [vp, vp, sz] + mem + [psz])
     sig("get_counters", [vp, C.POINTER(FmqCounters)])
@@ -310,6 +312,13 @@ class EngineBase:
             arrs = [np.empty(c, np.uint64), np.empty(c, np.int64), np.empty(c, np.float64)]
             return FmqWAlertCols(*[a.ctypes.data for a in arrs]), arrs
         return WindowAlerts(*self._poll_loop("poll_window_alerts", mk, chunk))
+
+    def poll_medians(self, chunk: int = 1 << 20) -> WindowAlerts:
+        """(key, window_end, median) rows of ComputeCpuMiddle's window function."""
+        def mk(c):
+            arrs = [np.empty(c, np.uint64), np.empty(c, np.int64), np.empty(c, np.float64)]
+            return FmqWAlertCols(*[a.ctypes.data for a in arrs]), arrs
+        return WindowAlerts(*self._poll_loop("poll_medians", mk, chunk))
 
     def _poll_events(self, name, chunk) -> EventRows:
         def mk(c):

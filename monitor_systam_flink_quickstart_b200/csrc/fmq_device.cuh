@@ -51,6 +51,7 @@ struct DevState {
     u64 events_in, late_dropped, windows_fired, window_alerts, event_alerts, consec_alerts, keys;
     // output cursors (rows appended since the last full drain)
     u64 n_fired, n_walert, n_ealert, n_calert;
+    u64 n_mlog, n_mwork, n_median;   // median path: logged records, records selected for the window being fired, emitted rows
     u32 err_flags;
     u32 pad1;
 };

@@ -13,6 +13,7 @@
 #include "fmq_sort.cuh"
 #include "fmq_keyed.cuh"
 #include "fmq_text.cuh"
+#include "fmq_median.cuh"
 
 using namespace fmq;
 
@@ -58,6 +59,10 @@ struct fmq_handle {
     const Acc32* peer_acc[FMQ_MAX_PEERS] = {};
     i64* d_xchg = nullptr;               // 4 x int64 exchange buffer for the all-reduce of the batch scalars
     size_t pending_n = 0;
+    // median path (N3)
+    i64* ml_pane[2] = {nullptr, nullptr}; u32* ml_slot[2] = {nullptr, nullptr}; u64* ml_val[2] = {nullptr, nullptr}; int ml_cur = 0; u64 ml_cap = 0;
+    u64* mw_items[2] = {nullptr, nullptr}; u64* mw_vals = nullptr;
+    u64* md_key = nullptr; i64* md_wend = nullptr; double* md_val = nullptr; u64 md_cap = 0; size_t cur_median = 0;
     // text ingest
     char* d_text = nullptr; u64* d_line_start = nullptr; u32* d_txt_status = nullptr; unsigned long long* d_txt_bad = nullptr;                // events ingested by fmq_push_local and not yet accounted by fmq_fire_global
 };
@@ -90,7 +95,9 @@ static void free_all(fmq_handle* h) {
     void* ptrs[] = {h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
                     h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
-                    h->d_pack[0], h->d_pack[1], h->d_counts, h->d_tiles, h->d_xchg, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad};
+                    h->d_pack[0], h->d_pack[1], h->d_counts, h->d_tiles, h->d_xchg, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad,
+                    h->ml_pane[0], h->ml_pane[1], h->ml_slot[0], h->ml_slot[1], h->ml_val[0], h->ml_val[1], h->mw_items[0], h->mw_items[1], h->mw_vals,
+                    h->md_key, h->md_wend, h->md_val};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->h_st) cudaFreeHost(h->h_st);
     for (auto& q : h->tev) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
@@ -178,9 +185,19 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     // radix counter matrix (keyed path and owner partition)
     h->counts_len = (size_t)RS_DIGITS * rs_num_chunks(h->max_batch);
     if (keyed_enabled(*cfg)) { const size_t k = (size_t)2048 * ps_num_chunks(h->max_batch); if (k > h->counts_len) h->counts_len = k; }
+    if (cfg->median_log_capacity > 0) { const size_t k = (size_t)2048 * ps_num_chunks(cfg->median_log_capacity); if (k > h->counts_len) h->counts_len = k; }
     h->tiles_len = (h->counts_len + SCAN_TILE - 1) / SCAN_TILE;
     CUC(dalloc(&h->d_counts, h->counts_len)); CUC(dalloc(&h->d_tiles, h->tiles_len));
     CUC(dalloc(&h->d_xchg, 4)); CUC(cudaMemset(h->d_xchg, 0, 32));
+    if (cfg->median_log_capacity > 0) {
+        if (!cfg->window_enabled || cfg->value_type != FMQ_VAL_F64) return fail(FMQ_ERR_BAD_ARG, "the window median needs window_enabled and f64 values");
+        if (cfg->median_log_capacity >= 0xFFFFFFF0ull) return fail(FMQ_ERR_BAD_ARG, "median_log_capacity must be < 2^32");
+        h->ml_cap = cfg->median_log_capacity;
+        for (int k = 0; k < 2; ++k) { CUC(dalloc(&h->ml_pane[k], h->ml_cap)); CUC(dalloc(&h->ml_slot[k], h->ml_cap)); CUC(dalloc(&h->ml_val[k], h->ml_cap)); CUC(dalloc(&h->mw_items[k], h->ml_cap)); }
+        CUC(dalloc(&h->mw_vals, h->ml_cap));
+        h->md_cap = cfg->median_capacity ? cfg->median_capacity : (2 * h->capacity > (1u << 20) ? 2 * h->capacity : (1u << 20));
+        CUC(dalloc(&h->md_key, h->md_cap)); CUC(dalloc(&h->md_wend, h->md_cap)); CUC(dalloc(&h->md_val, h->md_cap));
+    }
     if (cfg->text_max_bytes > 0) {
         CUC(dalloc(&h->d_text, cfg->text_max_bytes + 64)); CUC(dalloc(&h->d_line_start, h->max_batch + 2));
         CUC(dalloc(&h->d_txt_status, h->max_batch)); CUC(dalloc(&h->d_txt_bad, 1));
@@ -251,6 +268,40 @@ static int sync_state(fmq_handle* h) {
     return status_from_flags(h, h->h_st->err_flags);
 }
 
+// Stable LSD radix sort of 8-byte items between buf[0] and buf[1] by the low `key_bits` of keyfn(item):
+// as few passes as 11-bit digits allow, bits spread evenly over them.  *cur = index of the sorted buffer.
+template <typename KeyFn>
+static int sort_items(fmq_handle* h, u64* const* buf, size_t n, u32 key_bits, KeyFn keyfn, int* cur) {
+    const u32 passes = (key_bits + 10) / 11;
+    u32 bits = (key_bits + passes - 1) / passes; if (bits < 6) bits = 6;
+    const u32 nchunks = ps_num_chunks(n), nblocks = (nchunks + 7) / 8;
+    if ((size_t)(1u << bits) * nchunks > h->counts_len) return set_err(h, FMQ_ERR_BAD_ARG, "internal: radix counter matrix too small");
+    for (u32 pass = 0; pass < passes; ++pass) {
+        const u32 shift = pass * bits;
+        const size_t smem = (size_t)8 * (1u << bits) * 4;
+        auto launch = [&](auto hist, auto scat) -> int {
+            CU(h, cudaFuncSetAttribute(hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            CU(h, cudaFuncSetAttribute(scat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            hist<<<nblocks, 256, smem, h->stream>>>(buf[*cur], nullptr, n, nchunks, shift, h->d_counts, keyfn); LAUNCHED(h, "ps_pass_kernel(hist)");
+            int s_ = exclusive_scan_counts(h, (size_t)(1u << bits) * nchunks); if (s_) return s_;
+            scat<<<nblocks, 256, smem, h->stream>>>(buf[*cur], buf[*cur ^ 1], n, nchunks, shift, h->d_counts, keyfn); LAUNCHED(h, "ps_pass_kernel(scatter)");
+            return FMQ_OK;
+        };
+        int s_ = FMQ_OK;
+        switch (bits) {
+            case 6: s_ = launch(ps_pass_kernel<6, false, KeyFn>, ps_pass_kernel<6, true, KeyFn>); break;
+            case 7: s_ = launch(ps_pass_kernel<7, false, KeyFn>, ps_pass_kernel<7, true, KeyFn>); break;
+            case 8: s_ = launch(ps_pass_kernel<8, false, KeyFn>, ps_pass_kernel<8, true, KeyFn>); break;
+            case 9: s_ = launch(ps_pass_kernel<9, false, KeyFn>, ps_pass_kernel<9, true, KeyFn>); break;
+            case 10: s_ = launch(ps_pass_kernel<10, false, KeyFn>, ps_pass_kernel<10, true, KeyFn>); break;
+            default: s_ = launch(ps_pass_kernel<11, false, KeyFn>, ps_pass_kernel<11, true, KeyFn>); break;
+        }
+        if (s_) return s_;
+        *cur ^= 1;
+    }
+    return FMQ_OK;
+}
+
 // stage 1 of a push: everything that touches only this handle's own events
 template <typename V>
 static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n) {
@@ -262,6 +313,7 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         a.window_enabled = c.window_enabled; a.vec32 = ((((uintptr_t)ts | (uintptr_t)key | (uintptr_t)val) & 31) == 0);
         a.efilter_enabled = c.efilter_enabled; a.efilter_op = c.efilter_op; a.efilter_thr = c.efilter_threshold;
         a.ea_ts = h->ea_ts; a.ea_key = h->ea_key; a.ea_val = h->ea_val; a.ea_cap = h->ea_cap;
+        a.mlog_enabled = h->ml_cap > 0; a.ml_pane = h->ml_pane[h->ml_cur]; a.ml_slot = h->ml_slot[h->ml_cur]; a.ml_val = h->ml_val[h->ml_cur]; a.ml_cap = h->ml_cap;
         const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
         size_t blocks = (n + tile - 1) / tile; const size_t maxb = (size_t)h->num_sms * FMQ_INGEST_MIN_BLOCKS;   // persistent: resident blocks only
         if (blocks > maxb) blocks = maxb;
@@ -286,34 +338,8 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
     if (n > 0 && keyed_enabled(c)) {
         const unsigned gb = (unsigned)((n + 255) / 256 < (size_t)h->num_sms * 8 ? (n + 255) / 256 : (size_t)h->num_sms * 8);
         resolve_pack_kernel<<<gb, 256, 0, h->stream>>>(key, n, h->d_keys, h->capacity, c.key_mode == FMQ_KEYS_DENSE, h->d_st, h->d_pack[0]); LAUNCHED(h, "resolve_pack_kernel");
-        // LSD radix sort by slot: as few passes as 11-bit digits allow, bits spread evenly over them
-        const u32 passes = (h->slot_bits + 10) / 11;
-        u32 bits = (h->slot_bits + passes - 1) / passes; if (bits < 6) bits = 6;
-        const u32 nchunks = ps_num_chunks(n), nblocks = (nchunks + 7) / 8;
         int cur = 0;
-        for (u32 pass = 0; pass < passes; ++pass) {
-            const u32 shift = 32 + pass * bits;
-            const size_t smem = (size_t)8 * (1u << bits) * 4;
-            auto launch = [&](auto hist, auto scat) -> int {
-                CU(h, cudaFuncSetAttribute(hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                CU(h, cudaFuncSetAttribute(scat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                hist<<<nblocks, 256, smem, h->stream>>>(h->d_pack[cur], nullptr, n, nchunks, shift, h->d_counts); LAUNCHED(h, "ps_pass_kernel(hist)");
-                int s_ = exclusive_scan_counts(h, (size_t)(1u << bits) * nchunks); if (s_) return s_;
-                scat<<<nblocks, 256, smem, h->stream>>>(h->d_pack[cur], h->d_pack[cur ^ 1], n, nchunks, shift, h->d_counts); LAUNCHED(h, "ps_pass_kernel(scatter)");
-                return FMQ_OK;
-            };
-            int s_ = FMQ_OK;
-            switch (bits) {
-                case 6: s_ = launch(ps_pass_kernel<6, false>, ps_pass_kernel<6, true>); break;
-                case 7: s_ = launch(ps_pass_kernel<7, false>, ps_pass_kernel<7, true>); break;
-                case 8: s_ = launch(ps_pass_kernel<8, false>, ps_pass_kernel<8, true>); break;
-                case 9: s_ = launch(ps_pass_kernel<9, false>, ps_pass_kernel<9, true>); break;
-                case 10: s_ = launch(ps_pass_kernel<10, false>, ps_pass_kernel<10, true>); break;
-                default: s_ = launch(ps_pass_kernel<11, false>, ps_pass_kernel<11, true>); break;
-            }
-            if (s_) return s_;
-            cur ^= 1;
-        }
+        { int s_ = sort_items(h, h->d_pack, n, h->slot_bits, SlotKey{}, &cur); if (s_) return s_; }
         KeyedArgs k{};
         k.sorted = h->d_pack[cur]; k.n = n; k.ts = ts; k.key = key; k.val = val; k.st = h->d_st;
         k.kflags = h->d_kflags; k.kmax = h->d_kmax; k.rolling_enabled = c.rolling_max_enabled; k.rolling_out = h->d_rolling;
@@ -329,6 +355,44 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
     return FMQ_OK;
 }
 
+__global__ void set_mlog_kernel(DevState* st) { st->n_mlog = st->n_mwork; }
+
+// N3: for every window the plan says is firing, select its records from the value log, sort them by
+// (slot, value) and emit one median per key; then drop the records of expired panes from the log.
+// The sizes of these steps are data-dependent, so this (slow by nature) path reads the plan back.
+static int sync_state(fmq_handle* h);
+static int fire_medians(fmq_handle* h) {
+    int s = sync_state(h); if (s) return s;
+    const DevState d = *h->h_st;
+    const i64 size = h->g.size, slide = h->g.slide, off = h->g.off;
+    const size_t off_mwork = offsetof(DevState, n_mwork);
+    const unsigned grid = (unsigned)h->num_sms * 4;
+    for (i64 j = 0; j < d.fire_count && d.n_mlog > 0; ++j) {
+        const i64 wend = d.fire_first_end + j * slide;
+        const i64 p0 = (wend - size - off) / slide, p1 = (wend - off) / slide - 1;
+        CU(h, cudaMemsetAsync((char*)h->d_st + off_mwork, 0, 8, h->stream));
+        median_select_kernel<<<grid, MED_THREADS, 0, h->stream>>>(h->ml_pane[h->ml_cur], h->ml_slot[h->ml_cur], h->ml_val[h->ml_cur], h->d_st, p0, p1,
+                                                                 h->mw_items[0], h->mw_vals, h->ml_cap); LAUNCHED(h, "median_select_kernel");
+        s = sync_state(h); if (s) return s;
+        const size_t nsel = (size_t)h->h_st->n_mwork;
+        if (nsel == 0) continue;
+        int cur = 0;
+        s = sort_items(h, h->mw_items, nsel, 64, F64ValueKey{h->mw_vals}, &cur); if (s) return s;      // Collections.sort order
+        s = sort_items(h, h->mw_items, nsel, h->slot_bits, SlotKey{}, &cur); if (s) return s;           // stable: groups by key
+        MedianEmitArgs m{h->mw_items[cur], h->mw_vals, nsel, h->d_keys, h->cfg.key_mode == FMQ_KEYS_DENSE, wend, h->d_st, h->md_key, h->md_wend, h->md_val, h->md_cap};
+        median_emit_kernel<<<grid, MED_THREADS, 0, h->stream>>>(m); LAUNCHED(h, "median_emit_kernel");
+    }
+    if (d.expire_lo <= d.expire_hi && d.n_mlog > 0) {
+        CU(h, cudaMemsetAsync((char*)h->d_st + off_mwork, 0, 8, h->stream));
+        const int c = h->ml_cur;
+        median_compact_kernel<<<grid, MED_THREADS, 0, h->stream>>>(h->ml_pane[c], h->ml_slot[c], h->ml_val[c], d.n_mlog, h->d_st, d.expire_hi,
+                                                                  h->ml_pane[c ^ 1], h->ml_slot[c ^ 1], h->ml_val[c ^ 1], h->ml_cap); LAUNCHED(h, "median_compact_kernel");
+        set_mlog_kernel<<<1, 1, 0, h->stream>>>(h->d_st); LAUNCHED(h, "set_mlog_kernel");
+        h->ml_cur = c ^ 1;
+    }
+    return FMQ_OK;
+}
+
 // stage 2 of a push: watermark, fire, cleanup.  In combiner mode (`retire_now` false) the cleanup is
 // a separate step (fmq_retire) because peers may still be reading this rank's table.
 template <typename V>
@@ -337,6 +401,7 @@ static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now
     PlanArgs p{h->d_st, h->g, c.max_out_of_orderness_ms, wm_after, (u64)n, c.window_enabled, wm_after == FMQ_WM_AUTO};
     plan_kernel<<<1, 32, 0, h->stream>>>(p); LAUNCHED(h, "plan_kernel");
     if (c.window_enabled && wm_after != FMQ_WM_AUTO && wm_after > INT64_MIN) h->anchored_known = true;
+    if (c.window_enabled && h->ml_cap > 0) { int s_ = fire_medians(h); if (s_) return s_; }
     if (c.window_enabled) {
         FireArgs f{};
         f.st = h->d_st; f.dkeys = h->d_keys; f.acc = h->d_acc; f.g = h->g; f.dense_keys = c.key_mode == FMQ_KEYS_DENSE; f.emit_fired = c.emit_fired;
@@ -452,6 +517,13 @@ int32_t fmq_poll_window_alerts(fmq_handle* h, const fmq_walert_cols* o, size_t c
     void* c[3] = {o->key, o->window_end, o->value};
     return drain_cols(h, d, c, 3, &DevState::n_walert, &h->cur_walert, cap, mem, n_out, n_left);
 }
+int32_t fmq_poll_medians(fmq_handle* h, const fmq_walert_cols* o, size_t cap, int32_t mem, size_t* n_out, size_t* n_left) {
+    if (!h || !o) return FMQ_ERR_BAD_ARG;
+    if (!h->ml_cap) return set_err(h, FMQ_ERR_BAD_ARG, "the window median is not enabled (fmq_config.median_log_capacity)");
+    void* d[3] = {h->md_key, h->md_wend, h->md_val};
+    void* c[3] = {o->key, o->window_end, o->value};
+    return drain_cols(h, d, c, 3, &DevState::n_median, &h->cur_median, cap, mem, n_out, n_left);
+}
 int32_t fmq_poll_event_alerts(fmq_handle* h, const fmq_event_cols* o, size_t cap, int32_t mem, size_t* n_out, size_t* n_left) {
     if (!h || !o) return FMQ_ERR_BAD_ARG;
     void* d[3] = {h->ea_ts, h->ea_key, h->ea_val};
@@ -531,6 +603,7 @@ int32_t fmq_attach_peers(fmq_handle* h, int32_t rank, int32_t world, const void*
     if (world < 1 || world > FMQ_MAX_PEERS || rank < 0 || rank >= world) return set_err(h, FMQ_ERR_BAD_ARG, "need 1 <= world <= 8 and 0 <= rank < world");
     if (!h->cfg.window_enabled) return set_err(h, FMQ_ERR_BAD_ARG, "combiner mode needs window aggregation");
     if (h->cfg.key_mode != FMQ_KEYS_DENSE) return set_err(h, FMQ_ERR_BAD_ARG, "combiner mode needs FMQ_KEYS_DENSE (slots must mean the same key on every rank)");
+    if (h->ml_cap) return set_err(h, FMQ_ERR_BAD_ARG, "the window median needs every value of a key on one rank: route it through the all-to-all exchange instead");
     if (keyed_enabled(h->cfg)) return set_err(h, FMQ_ERR_BAD_ARG, "keyed ValueState operators depend on per-key order: route them through the all-to-all exchange instead");
     for (int r = 0; r < world; ++r) {
         if (r != rank && !peer_tables[r]) return set_err(h, FMQ_ERR_BAD_ARG, "null peer table");
@@ -675,11 +748,12 @@ int32_t fmq_snapshot(fmq_handle* h, void* buf, size_t cap, size_t* written) {
     if (!h || !buf || !written) return FMQ_ERR_BAD_ARG;
     if (h->sticky) return FMQ_ERR_POISONED;
     if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "snapshot of a combiner-mode handle is not supported");
+    if (h->ml_cap) return set_err(h, FMQ_ERR_BAD_ARG, "snapshot of a handle with the window median enabled is not supported yet");
     const size_t need = snap_bytes(h);
     if (cap < need) return set_err(h, FMQ_ERR_BAD_ARG, "snapshot buffer too small (see fmq_snapshot_size)");
     int st = sync_state(h); if (st) return st;
     const DevState& d = *h->h_st;
-    if (d.n_fired || d.n_walert || d.n_ealert || d.n_calert) return set_err(h, FMQ_ERR_BAD_ARG, "poll every output before taking a snapshot: emitted rows are not operator state");
+    if (d.n_fired || d.n_walert || d.n_ealert || d.n_calert || d.n_median) return set_err(h, FMQ_ERR_BAD_ARG, "poll every output before taking a snapshot: emitted rows are not operator state");
     char* p = static_cast<char*>(buf);
     SnapHeader hd{}; hd.magic = SNAP_MAGIC; hd.version = 1; hd.header_bytes = sizeof(SnapHeader); hd.cfg = h->cfg; hd.capacity = h->capacity; hd.ring = h->ring;
     hd.has_window = h->cfg.window_enabled; hd.has_keyed = keyed_enabled(h->cfg); hd.anchored_known = h->anchored_known; hd.total_bytes = need;

@@ -37,9 +37,18 @@ constexpr u32 PS_CHUNK = 4096;
 constexpr int PS_AHEAD = 4;
 __host__ __device__ inline u32 ps_num_chunks(size_t n) { return (u32)((n + PS_CHUNK - 1) / PS_CHUNK); }
 
-template <int BITS, bool SCATTER>
+// KeyFn: u64 operator()(u64 item) -> the sort key of an item; a pass ranks by (key >> shift) & (2^BITS - 1)
+struct SlotKey {            // item = (slot << 32 | index): sort by slot
+    __device__ __forceinline__ u64 operator()(u64 item) const { return item >> 32; }
+};
+struct F64ValueKey {        // item = (slot << 32 | index into vals): sort by vals[index] in Double.compareTo order
+    const u64* vals;
+    __device__ __forceinline__ u64 operator()(u64 item) const { return Codec<double>::cmp_key(__longlong_as_double((i64)vals[(u32)item])); }
+};
+
+template <int BITS, bool SCATTER, typename KeyFn>
 __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t n, u32 nchunks, u32 shift,
-                                                      u32* __restrict__ counts /* hist: written; scatter: scanned offsets */) {
+                                                      u32* __restrict__ counts /* hist: written; scatter: scanned offsets */, KeyFn keyfn) {
     extern __shared__ u32 ps_smem[];
     constexpr u32 NB = 1u << BITS;
     const u32 wl = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -58,14 +67,14 @@ __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in
             // counting needs no order: one shared-memory atomic per item on the warp's private bins
 #pragma unroll
             for (int r = 0; r < PS_AHEAD; ++r)
-                if (i0 + r * 32 + lane < hi) atomicAdd(&bins[(u32)(it[r] >> shift) & (NB - 1)], 1u);
+                if (i0 + r * 32 + lane < hi) atomicAdd(&bins[(u32)(keyfn(it[r]) >> shift) & (NB - 1)], 1u);
         } else {
 #pragma unroll
         for (int r = 0; r < PS_AHEAD; ++r) {
             const bool act = i0 + r * 32 + lane < hi;
             const unsigned am = __ballot_sync(0xffffffffu, act);
             if (act) {
-                const u32 d = (u32)(it[r] >> shift) & (NB - 1);
+                const u32 d = (u32)(keyfn(it[r]) >> shift) & (NB - 1);
                 const unsigned m = __match_any_sync(am, d);
                 const int leader = __ffs(m) - 1;
                 u32 base = 0;

@@ -25,6 +25,8 @@ struct IngestArgs {
     int vec32;                  // all three columns are 32-byte aligned
     int efilter_enabled, efilter_op; double efilter_thr;
     i64* ea_ts; u64* ea_key; u64* ea_val; u64 ea_cap;
+    // median path (N3): every accepted record is also appended to a value log (pane, slot, value)
+    int mlog_enabled; i64* ml_pane; u32* ml_slot; u64* ml_val; u64 ml_cap;
 };
 
 // Two adjacent lanes share one event per round: the even lane updates the first 8 B of a pair,
@@ -163,7 +165,7 @@ struct IngestRun {            // per-thread running scalars of one batch
     u64 late = 0, nea = 0; i64 dmax = I64_MIN_; u32 pmin = 0xFFFFFFFFu, pmax = 0; u32 err = 0;
 };
 struct IngestConst {
-    i64 origin_ts; u32 origin_ring, slide, recip; u64 span, nbuckets;
+    i64 origin_ts, origin_pane; u32 origin_ring, slide, recip; u64 span, nbuckets;
 };
 
 // One tile of the fast path: the four events held by this thread.  Called by every thread of the block.
@@ -179,7 +181,7 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
     if (!a.window_enabled) return;
     // ---- per event: A1 max-ts, A3 late test, A2 pane, and (hashed keys) the home-bucket load:
     //      all four directory loads are in flight before any of them is consumed ----
-    u32 ring_[INGEST_EPT]; u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0;
+    u32 ring_[INGEST_EPT]; u32 q_[INGEST_EPT]; u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0;
 #pragma unroll
     for (int e = 0; e < INGEST_EPT; ++e) {
         const bool ok = ok_mask & (1u << e);
@@ -202,10 +204,12 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
             if (act) kv_[e] = ld_bucket(a.dkeys + hb_[e] * 4);
         }
         r.pmin = (act && q < r.pmin) ? q : r.pmin; r.pmax = (act && q > r.pmax) ? q : r.pmax;
+        q_[e] = q;
         ring_[e] = (k.origin_ring + q) & a.g.ring_mask;
         act_mask |= act ? (1u << e) : 0u;
     }
     // ---- A5: slot -> pair-lane accumulate ----
+    u32 slot_[INGEST_EPT]; u32 vmask = 0;
 #pragma unroll
     for (int e = 0; e < INGEST_EPT; ++e) {
         bool valid = act_mask & (1u << e);
@@ -217,6 +221,16 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
         const u64 idx = (u64)ring_[e] * a.g.capacity + slot;
         V v; memcpy(&v, &vb_[e], 8);
         accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask);
+        slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
+    }
+    // ---- N3: non-incremental window functions keep every value (ComputeCpuMiddle.java:36-38) ----
+    if (a.mlog_enabled) {
+        u64 row = block_append<INGEST_THREADS>(__popc(vmask), &st->n_mlog, a.ml_cap, st);
+        if (row != ~0ull) {
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e)
+                if (vmask & (1u << e)) { a.ml_pane[row] = k.origin_pane + (i64)q_[e]; a.ml_slot[row] = slot_[e]; a.ml_val[row] = vb_[e]; ++row; }
+        }
     }
 }
 
@@ -228,6 +242,7 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
     if (!ingest_fast_ok(st, a.g)) return;                        // the generic kernel handles this batch
     IngestConst k;
     k.origin_ts = st->origin_ts;
+    k.origin_pane = st->origin_pane;
     k.origin_ring = (u32)st->origin_pane & a.g.ring_mask;
     k.slide = a.g.slide32;
     k.recip = 0xFFFFFFFFu / k.slide;                             // floor((2^32-1)/slide): quotient estimate, never too big
@@ -332,11 +347,12 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
         ok_mask &= in_mask;
         if (a.efilter_enabled) nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
         if (!a.window_enabled) continue;
+        i64 gp_[INGEST_EPT]; u32 gs_[INGEST_EPT]; u32 gmask = 0;
 #pragma unroll
         for (int e = 0; e < INGEST_EPT; ++e) {
             const i64 ts = ts_[e]; const u64 key = key_[e];
             V v; memcpy(&v, &vb_[e], 8);
-            bool valid = false; u64 idx = 0;
+            bool valid = false; u64 idx = 0; i64 gpane = 0;
             if (ok_mask & (1u << e)) {
                 max_ts = ts > max_ts ? ts : max_ts;                 // A1: currentMaxTimestamp
                 const i64 d = ts - origin_ts;
@@ -349,6 +365,7 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
                     } else {
                         const i64 p = origin_pane + (i64)prel;
                         pmin = p < pmin ? p : pmin; pmax = p > pmax ? p : pmax;
+                        gpane = p;
                         u32 slot;
                         if (DENSE) { slot = key < a.g.capacity ? (u32)key : SLOT_INVALID; if (slot == SLOT_INVALID) err |= ERRB_BAD_INPUT; }
                         else slot = dir_find_or_insert(a.dkeys, a.g.capacity, key, st);
@@ -357,6 +374,15 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
                 }
             }
             accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask);  // A5
+            gp_[e] = valid ? gpane : 0; gs_[e] = valid ? (u32)(idx % a.g.capacity) : 0; gmask |= valid ? (1u << e) : 0u;
+        }
+        if (a.mlog_enabled) {
+            u64 row = block_append<INGEST_THREADS>(__popc(gmask), &st->n_mlog, a.ml_cap, st);
+            if (row != ~0ull) {
+#pragma unroll
+                for (int e = 0; e < INGEST_EPT; ++e)
+                    if (gmask & (1u << e)) { a.ml_pane[row] = gp_[e]; a.ml_slot[row] = gs_[e]; a.ml_val[row] = vb_[e]; ++row; }
+            }
         }
     }
     nea = warp_sum_u64(nea);

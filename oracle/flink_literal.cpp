@@ -78,7 +78,7 @@ struct OracleBase {
     virtual ~OracleBase() {}
     virtual int push(const int64_t* ts, const uint64_t* key, const void* val, size_t n, int64_t wm_after) = 0;
     virtual int flush(int64_t wm) = 0;
-    std::vector<FiredRow> fired; std::vector<WAlert> walerts; std::vector<EvRow> ealerts, calerts;
+    std::vector<FiredRow> fired; std::vector<WAlert> walerts, medians; std::vector<EvRow> ealerts, calerts;
     std::vector<uint64_t> rolling;   // rolling max output of the last batch
     fmq_counters ctr{};
     virtual int key_state(uint64_t key, int32_t* consec, uint64_t* rolling_bits) = 0;
@@ -88,6 +88,7 @@ template <typename V>
 struct Oracle : OracleBase {
     using WKey = std::pair<uint64_t, int64_t>;                 // (key, window start) = (key, namespace)
     std::map<WKey, Acc<V>> wstate;                             // Heap{Reducing,Aggregating}State
+    std::map<WKey, std::vector<V>> wlist;                      // HeapListState: ComputeCpuMiddle.java:34 (process(...))
     std::set<std::tuple<int64_t, uint64_t, int64_t>> timers;   // (timestamp, key, window start)
     int64_t current_wm = INT64_MIN;                            // InternalTimerServiceImpl.currentWatermark
     // BoundedOutOfOrdernessTimestampExtractor (chapter3/README.md:342-397)
@@ -143,6 +144,7 @@ struct Oracle : OracleBase {
                 a.count += 1; a.sum = a.sum + val;               // arrival order; long wraps (two's complement)
                 a.mn = java_min(a.mn, val); a.mx = java_max(a.mx, val);
             }
+            if (cfg.median_log_capacity > 0) wlist[{key, s}].push_back(val);
             timers.insert({max_ts, key, s});                     // EventTimeTrigger.onElement (+ cleanup timer, same ts)
         }
         if (skipped && ts + 0 <= current_wm) ctr.late_dropped++; // numLateRecordsDropped
@@ -178,6 +180,15 @@ struct Oracle : OracleBase {
             if (cfg.walert_source != FMQ_ALERT_NONE) {
                 double v = alert_value(a);
                 if (cmp(v, cfg.walert_op, cfg.walert_threshold)) { walerts.push_back({key, wend, v}); ctr.window_alerts++; }
+            }
+            if (cfg.median_log_capacity > 0) {
+                // ComputeCpuMiddle.java:36-47: copy, Collections.sort (Double.compareTo), middle element(s)
+                std::vector<V>& vals = wlist[{key, s}];
+                std::sort(vals.begin(), vals.end(), [](V x, V y) { return java_compare(x, y) < 0; });
+                const size_t n = vals.size();
+                double med = n == 0 ? 0.0 : (n % 2 != 0 ? (double)vals[n / 2] : ((double)vals[n / 2] + (double)vals[n / 2 - 1]) / 2);
+                medians.push_back({key, wend, med});
+                wlist.erase({key, s});
             }
             wstate.erase(it);                                    // clearAllState at cleanup time
         }
@@ -246,6 +257,12 @@ int32_t orc_poll_window_alerts(void* h, const fmq_walert_cols* o, size_t cap, si
     auto* b = static_cast<OracleBase*>(h);
     *n_out = drain(b->walerts, cap, [&](size_t i, const WAlert& r) { o->key[i] = r.key; o->window_end[i] = r.wend; o->value[i] = r.value; });
     if (n_left) *n_left = b->walerts.size();
+    return FMQ_OK;
+}
+int32_t orc_poll_medians(void* h, const fmq_walert_cols* o, size_t cap, size_t* n_out, size_t* n_left) {
+    auto* b = static_cast<OracleBase*>(h);
+    *n_out = drain(b->medians, cap, [&](size_t i, const WAlert& r) { o->key[i] = r.key; o->window_end[i] = r.wend; o->value[i] = r.value; });
+    if (n_left) *n_left = b->medians.size();
     return FMQ_OK;
 }
 static int32_t poll_ev(std::vector<EvRow>& v, const fmq_event_cols* o, size_t cap, size_t* n_out, size_t* n_left) {

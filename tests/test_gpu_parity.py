@@ -302,6 +302,39 @@ def test_partial_polls_drain_everything():
     assert len(gpu.poll_fired()) == 0
 
 
+# ---- non-incremental window function: median --------------------------------------
+def test_g5_median_gpu():
+    """chapter2/README.md:236-248: medians 80.5 and 20.2 (ComputeCpuMiddle.java:41-47)."""
+    d = KeyDictionary()
+    e = capi.Engine(window_enabled=1, agg_mask=1, window_size_ms=60000, window_slide_ms=60000, median_log_capacity=1024, **SMALL)
+    rows = [parse_cpu_line(l) for l in G["G5_median"]["input"]]
+    e.push_batch(1563452040000 + np.arange(4, dtype=np.int64) * 1000, np.array([d.encode(r[1]) for r in rows], np.uint64), np.array([r[3] for r in rows]), 0)
+    e.flush()
+    m = e.poll_medians()
+    assert {d.decode(k): v for k, v in zip(m.key, m.value)} == {"10.8.22.1": 80.5, "10.8.22.2": 20.2}
+
+
+@pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
+@pytest.mark.parametrize("slide", [10_000, 5_000])
+def test_window_median_parity(key_mode, slide):
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=slide, max_out_of_orderness_ms=3000,
+              median_log_capacity=400_000, key_mode=key_mode, **SMALL)
+    gpu, cpu = pair(**kw)
+    spec = StreamSpec(n_keys=37, events_per_ms=2, jitter_ms=3000, late_frac_ppm=20000, late_extra_ms=20000)   # even and odd counts, long runs
+    spec2 = StreamSpec(n_keys=3000, events_per_ms=3, late_frac_ppm=20000)
+    for b in range(6):
+        ts, key, val = generate_numpy(spec if b % 2 == 0 else spec2, b * 30_000, 30_000)
+        val = np.round(val, 1)                                  # many ties; -0.0 and 0.0 both present
+        val[::97] = -0.0
+        gpu.push_batch(ts, key, val); cpu.push_batch(ts, key, val)
+    gpu.flush(); cpu.flush()
+    a, w = sort_walerts(gpu.poll_medians()), sort_walerts(cpu.poll_medians())
+    assert len(w) == cpu.counters()["windows_fired"] > 1000
+    np.testing.assert_array_equal(a.key, w.key); np.testing.assert_array_equal(a.window_end, w.window_end)
+    np.testing.assert_array_equal(a.value.view(np.uint64), w.value.view(np.uint64))          # medians are order statistics: bit-exact
+    assert_fired_equal(gpu.poll_fired(), cpu.poll_fired())
+
+
 # ---- checkpoint / restore (SURVEY §8f N4) ---------------------------------------------------------
 @pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
 def test_snapshot_restore_continues_exactly(key_mode):

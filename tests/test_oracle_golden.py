@@ -194,6 +194,17 @@ def test_g2_passthrough_uses_four_subtasks():
     assert p == [3, 4, 1] and all(((p[i] - 1 + 1) % 4) + 1 == p[i + 1] for i in range(2))
 
 
+def test_g5_median_oracle():
+    """chapter2/README.md:236-248 through the oracle's ListState restatement (ComputeCpuMiddle.java:36-47)."""
+    d = KeyDictionary()
+    e = OracleEngine(window_enabled=1, agg_mask=1, window_size_ms=60000, window_slide_ms=60000, median_log_capacity=1)
+    _, key, val = _cpu_cols(G["G5_median"]["input"], d)
+    e.push_batch(1563452040000 + np.arange(4, dtype=np.int64) * 1000, key, val, 0)
+    e.flush()
+    m = e.poll_medians()
+    assert {d.decode(k): v for k, v in zip(m.key, m.value)} == {"10.8.22.1": 80.5, "10.8.22.2": 20.2}
+
+
 def test_g5_median_is_out_of_scope_value_check():
     """chapter2/README.md:236-248 (ComputeCpuMiddle.java:41-47): median 80.5 / 20.2 — SURVEY §8f N3,
     restated here only so the fixture is exercised."""
