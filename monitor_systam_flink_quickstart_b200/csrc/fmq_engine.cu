@@ -52,6 +52,7 @@ struct fmq_handle {
     size_t cur_fired = 0, cur_walert = 0, cur_ealert = 0, cur_calert = 0;   // host read cursors
     // keyed-path / partition scratch
     u64* d_pack[2] = {nullptr, nullptr};   // (slot << 32 | arrival index), ping-pong
+    u32 *kr_lead = nullptr, *kr_k = nullptr, *kr_fl = nullptr, *kr_in_c = nullptr; u64 *kr_mk = nullptr, *kr_mb = nullptr, *kr_in_mk = nullptr, *kr_in_mb = nullptr;
     u32* d_counts = nullptr; u32* d_tiles = nullptr; size_t counts_len = 0, tiles_len = 0;
     uint64_t launches = 0;
     // combiner mode (fmq_attach_peers)
@@ -95,7 +96,7 @@ static void free_all(fmq_handle* h) {
     void* ptrs[] = {h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
                     h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
-                    h->d_pack[0], h->d_pack[1], h->d_counts, h->d_tiles, h->d_xchg, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad,
+                    h->d_pack[0], h->d_pack[1], h->kr_lead, h->kr_k, h->kr_fl, h->kr_in_c, h->kr_mk, h->kr_mb, h->kr_in_mk, h->kr_in_mb, h->d_counts, h->d_tiles, h->d_xchg, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad,
                     h->ml_pane[0], h->ml_pane[1], h->ml_slot[0], h->ml_slot[1], h->ml_val[0], h->ml_val[1], h->mw_items[0], h->mw_items[1], h->mw_vals,
                     h->md_key, h->md_wend, h->md_val};
     for (void* p : ptrs) if (p) cudaFree(p);
@@ -176,6 +177,9 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
         CUC(dalloc(&h->d_kflags, h->capacity)); CUC(cudaMemset(h->d_kflags, 0, h->capacity * 4));
         CUC(dalloc(&h->d_kmax, h->capacity)); CUC(cudaMemset(h->d_kmax, 0, h->capacity * 8));
         for (int k = 0; k < 2; ++k) CUC(dalloc(&h->d_pack[k], h->max_batch));
+        const size_t nr = (h->max_batch + KA_RANGE - 1) / KA_RANGE + 1;
+        CUC(dalloc(&h->kr_lead, nr)); CUC(dalloc(&h->kr_k, nr)); CUC(dalloc(&h->kr_fl, nr)); CUC(dalloc(&h->kr_in_c, nr));
+        CUC(dalloc(&h->kr_mk, nr)); CUC(dalloc(&h->kr_mb, nr)); CUC(dalloc(&h->kr_in_mk, nr)); CUC(dalloc(&h->kr_in_mb, nr));
         if (cfg->rolling_max_enabled) CUC(dalloc(&h->d_rolling, h->max_batch));
         if (cfg->consec_n > 0) {
             h->ca_cap = cfg->calert_capacity ? cfg->calert_capacity : h->max_batch;
@@ -345,8 +349,12 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         k.kflags = h->d_kflags; k.kmax = h->d_kmax; k.rolling_enabled = c.rolling_max_enabled; k.rolling_out = h->d_rolling;
         k.consec_n = c.consec_n; k.consec_op = c.consec_op; k.consec_reset = c.consec_reset_on_fire; k.consec_thr = c.consec_threshold;
         k.ca_ts = h->ca_ts; k.ca_key = h->ca_key; k.ca_val = h->ca_val; k.ca_cap = h->ca_cap;
-        const size_t nwarps = (n + KA_RANGE - 1) / KA_RANGE;
-        keyed_scan_kernel<V><<<(unsigned)((nwarps + 7) / 8), 256, 0, h->stream>>>(k); LAUNCHED(h, "keyed_scan_kernel");
+        k.r_lead = h->kr_lead; k.r_fn_k = h->kr_k; k.r_fn_flags = h->kr_fl; k.r_fn_mkey = h->kr_mk; k.r_fn_mbits = h->kr_mb;
+        k.r_in_c = h->kr_in_c; k.r_in_mkey = h->kr_in_mk; k.r_in_mbits = h->kr_in_mb;
+        const size_t nranges = (n + KA_RANGE - 1) / KA_RANGE;
+        keyed_scan_kernel<V><<<(unsigned)((nranges + 7) / 8), 256, 0, h->stream>>>(k); LAUNCHED(h, "keyed_scan_kernel");
+        keyed_carry_kernel<<<1, 1024, 0, h->stream>>>(k, (u32)nranges, (u32)c.consec_n, c.consec_reset_on_fire); LAUNCHED(h, "keyed_carry_kernel");
+        keyed_lead_kernel<V><<<(unsigned)((nranges + 7) / 8), 256, 0, h->stream>>>(k); LAUNCHED(h, "keyed_lead_kernel");
         h->rolling_n = c.rolling_max_enabled ? n : 0;
     } else if (keyed_enabled(c)) {
         h->rolling_n = 0;

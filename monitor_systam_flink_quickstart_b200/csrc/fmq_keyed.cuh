@@ -91,6 +91,23 @@ __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in
 }
 
 // ---- step 3: apply the operators along every key's run, in arrival order ---------------------------
+// The sorted array is cut into ranges of KA_RANGE positions, one warp each.  A record's new state is a
+// FUNCTION of the key's state before it:
+//   consecutive-breach counter:  over -> c+1 (alert when it reaches N, then 0 if reset-on-fire), else -> 0
+//       composite of a sub-run = (hr, k):  c -> hr ? k : c + k            (taken mod N at the end in reset mode)
+//   rolling max (ComparableAggregator: keep cur iff cur.compareTo(v) > 0, else take v)
+//       composite = (mc, m):  cur -> mc ? m : max(cur, m), ties to the later record
+// and composition is associative, so a run is scanned in parallel: 32 positions per round with a
+// segmented warp scan, rounds chained through a carried function.  Three kernels:
+//   A  keyed_scan_kernel   every range: runs whose head lies inside the range are seeded from the key's
+//                          stored state and finished (outputs, alerts, state write-back at the tail);
+//                          the leading part of a range that continues a run from an earlier range is
+//                          only summarised.  Each range also records its end function E (a constant if
+//                          its last run has its head inside, the composite of the whole range otherwise).
+//   B  keyed_carry_kernel  one block: exclusive scan of the E's = state entering every range.
+//   C  keyed_lead_kernel   ranges that start inside a run: redo that leading part with the carried state.
+// A heavy-hitter key (Zipf: one key = 18 % of a batch, a run of 3 M records) is thereby spread over
+// thousands of warps instead of being one warp's job (measured 215 ms -> see profiles/).
 struct KeyedArgs {
     const u64* sorted; size_t n;                    // (slot << 32 | arrival index), sorted by slot, stable
     const i64* ts; const u64* key; const void* val;
@@ -98,74 +115,47 @@ struct KeyedArgs {
     int rolling_enabled; u64* rolling_out;          // [n], input order
     int consec_n, consec_op, consec_reset; double consec_thr;
     i64* ca_ts; u64* ca_key; u64* ca_val; u64 ca_cap;
+    // per-range summaries / carries
+    u32* r_lead; u32* r_fn_k; u32* r_fn_flags; u64* r_fn_mkey; u64* r_fn_mbits;     // E: flags bit0 = hr, bit1 = mc, bit2 = has max
+    u32* r_in_c; u64* r_in_mkey; u64* r_in_mbits;                                     // state entering the range
 };
 
-constexpr u32 KA_RANGE = 512;                       // nominal sorted positions per warp
+constexpr u32 KA_RANGE = 2048;                      // sorted positions per warp
+constexpr u32 KFN_HR = 1u, KFN_MC = 2u, KFN_HASM = 4u;
 
-// A run (= all records of one key in this batch) belongs to the warp whose nominal range contains
-// its first position; the warp follows its last run past the end of the range, so no state ever
-// crosses warps.  Inside a warp 32 consecutive positions are handled per round: the per-record
-// transition functions are composed with a segmented warp scan, seeded from the key's stored state
-// at run heads and from the previous round otherwise.
-//   consecutive-breach counter:  over -> c+1 (alert when it reaches N, then 0 if reset-on-fire), else -> 0;
-//     composite of a sub-run = (has_reset, k): c -> has_reset ? k : c + k
-//   rolling max (ComparableAggregator): keep cur iff cur.compareTo(v) > 0, else take v = max-scan
-//     on the compareTo order with ties going to the later record
+struct KCarry { bool hr; u32 k; bool mc; bool hasm; u64 mkey, mbits; };
+
+// Scans sorted positions [lo, hi) with one warp.  `c` = function carried into the first position (identity
+// for kernel A, the constant entering state for kernel C).  Outputs are produced for the positions whose
+// state is fully known (c.hr && c.mc or a run head at/before them).  Returns the carried function after
+// `hi` and the number of positions before the first run head (`lead`).
 template <typename V>
-__global__ void __launch_bounds__(256) keyed_scan_kernel(const __grid_constant__ KeyedArgs a) {
+__device__ __forceinline__ void keyed_scan_range(const KeyedArgs& a, size_t lo, size_t hi, KCarry& c, u32& lead, u64& nalert) {
     const V* __restrict__ val = static_cast<const V*>(a.val);
     const u32 lane = threadIdx.x & 31;
-    const size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const size_t r_lo = warp * KA_RANGE;
-    if (r_lo >= a.n) return;
-    const size_t r_hi = (r_lo + KA_RANGE < a.n) ? r_lo + KA_RANGE : a.n;
     const u32 N = (u32)a.consec_n;
-    // ---- find the first run head at or after r_lo ----
-    size_t pos = r_lo;
-    {
-        bool found = false;
-        while (pos < r_hi) {
-            const size_t p = pos + lane;
-            bool head = false;
-            if (p < r_hi) { const u32 s = (u32)(a.sorted[p] >> 32); head = (p == 0) || ((u32)(a.sorted[p - 1] >> 32) != s); }
-            const unsigned hm = __ballot_sync(0xffffffffu, head);
-            if (hm) { pos += __ffs(hm) - 1; found = true; break; }
-            pos += 32;
-        }
-        if (!found) return;                            // the whole range continues a run owned by an earlier warp
-    }
-    // carried from the previous round (lane-uniform)
-    u32 c_state = 0; u64 c_mkey = 0, c_mbits = 0; bool c_hasmax = false; u32 c_slot = SLOT_INVALID;
-    u64 nalert = 0;
-    bool done = false;
-    while (!done && pos < a.n) {
+    u32 c_slot = lo > 0 ? (u32)(a.sorted[lo - 1] >> 32) : SLOT_INVALID;
+    bool seen_head = false; lead = (u32)(hi - lo);
+    for (size_t pos = lo; pos < hi; pos += 32) {
         const size_t p = pos + lane;
-        const bool in = p < a.n;
+        const bool in = p < hi;
         const u64 item = in ? a.sorted[p] : ~0ull;
         const u32 slot = (u32)(item >> 32), idx = (u32)item;
         const u32 prev_slot = __shfl_up_sync(0xffffffffu, slot, 1);
-        bool head = in && (lane == 0 ? (slot != c_slot) : (slot != prev_slot));
-        // the warp stops at the first head at or beyond the end of its nominal range
-        const unsigned stopm = __ballot_sync(0xffffffffu, in && head && p >= r_hi);
-        const u32 nact = stopm ? (u32)(__ffs(stopm) - 1) : 32u;
-        const bool act = in && lane < nact && slot != SLOT_INVALID;
-        // warp-uniform exit: a later run head past the range, the end of the array, or the invalid slots (sorted last)
-        if (stopm || __ballot_sync(0xffffffffu, !in || slot == SLOT_INVALID)) done = true;
-        if (!act) head = false;
+        const bool act = in && slot != SLOT_INVALID;
+        const bool head = act && (lane == 0 ? (slot != c_slot || p == 0) : (slot != prev_slot));
+        const unsigned hm = __ballot_sync(0xffffffffu, head);
+        if (hm && !seen_head) { seen_head = true; lead = (u32)(pos - lo) + (u32)(__ffs(hm) - 1); }
         // gathers: value of this record, stored state at run heads
         V v = act ? val[idx] : V(0);
         u64 vb; memcpy(&vb, &v, 8);
         u32 fl = 0; u64 smax = 0;
         if (head) { fl = a.kflags[slot]; smax = a.kmax[slot]; }
-        // ---- consecutive-breach: element (hr = result independent of what precedes, k) ----
+        const bool over = act && N > 0 && cmp_op((double)v, a.consec_op, a.consec_thr);
+        // ---- elements ----
         bool hr = false; u32 k = 0;
-        if (N > 0 && act) {
-            const bool over = cmp_op((double)v, a.consec_op, a.consec_thr);
-            hr = !over; k = over ? 1u : 0u;
-            if (head) { const u32 seed = fl & KF_COUNT_MASK; k = over ? seed + 1 : 0; hr = true; }
-        }
-        // ---- rolling max: element (mkey, mbits, has) ----
-        u64 mkey = act ? Codec<V>::cmp_key(v) : 0, mbits = vb; bool seg = head;     // seg = "a head lies at or before me in this round"
+        if (N > 0 && act) { hr = !over; k = over ? 1u : 0u; if (head) { k = over ? (fl & KF_COUNT_MASK) + 1 : 0; hr = true; } }
+        u64 mkey = act ? Codec<V>::cmp_key(v) : 0, mbits = vb; bool seg = head;        // seg = "a head lies at or before me in this round"
         if (a.rolling_enabled && head && (fl & KF_HAS_MAX)) {
             const u64 sk = Codec<V>::cmp_key(Codec<V>::from_bits(smax));
             if (sk > mkey) { mkey = sk; mbits = smax; }
@@ -181,44 +171,111 @@ __global__ void __launch_bounds__(256) keyed_scan_kernel(const __grid_constant__
                 seg = seg_p;
             }
         }
-        // prepend the carry of the previous round for lanes whose run began before this round
+        // prepend the function carried from the previous round for lanes whose run began before this round
+        bool known_c = seg, known_m = seg;                          // is my state a known value (not a function of an unknown)?
         if (act && !seg) {
-            if (!hr) k += c_state;
-            if (c_hasmax && c_mkey > mkey) { mkey = c_mkey; mbits = c_mbits; }
+            if (!hr) { k += c.k; hr = c.hr; }
+            if (c.hasm && c.mkey > mkey) { mkey = c.mkey; mbits = c.mbits; }
+            known_c = hr; known_m = c.mc;
         }
+        // Outputs are produced only for runs whose head this warp has seen (or, in kernel C, whose entering
+        // state was handed in): known_m.  known_c may hold earlier (an under-threshold record resets the
+        // counter whatever preceded it) and is what the carried function needs.
         u32 state = k; bool alert = false;
-        if (N > 0 && act) {
-            if (a.consec_reset) {
-                state = k % N;
-                alert = cmp_op((double)v, a.consec_op, a.consec_thr) && state == 0;     // the counter just reached N (and went back to 0)
-            } else {
-                if (state > KF_COUNT_MASK) state = KF_COUNT_MASK;
-                alert = state >= N;
-            }
+        if (N > 0 && act && known_c) {
+            if (a.consec_reset) { state = k % N; alert = over && state == 0; }         // the counter just reached N (and went back to 0)
+            else { if (state > KF_COUNT_MASK) state = KF_COUNT_MASK; alert = state >= N; }
         }
+        const bool emit = act && known_m;
         if (N > 0) {
-            const u64 row = warp_append(alert, &a.st->n_calert, a.ca_cap, a.st);         // one reservation per warp round
+            const u64 row = warp_append(alert && emit, &a.st->n_calert, a.ca_cap, a.st);   // one reservation per warp round
             if (row != ~0ull) { a.ca_ts[row] = a.ts[idx]; a.ca_key[row] = a.key[idx]; a.ca_val[row] = vb; }
-            nalert += alert ? 1 : 0;
+            nalert += (alert && emit) ? 1 : 0;
         }
-        if (a.rolling_enabled && act) a.rolling_out[idx] = mbits;
+        if (a.rolling_enabled && emit) a.rolling_out[idx] = mbits;
         // run tails write the key's state back
         const u32 next_slot = __shfl_down_sync(0xffffffffu, slot, 1);
         const u64 peek = (p + 1 < a.n) ? a.sorted[p + 1] : ~0ull;
-        const bool tail = act && ((lane == 31 || lane + 1 >= nact) ? ((u32)(peek >> 32) != slot) : (next_slot != slot));
+        const bool tail = emit && ((lane == 31 || p + 1 >= hi) ? ((u32)(peek >> 32) != slot) : (next_slot != slot));
         if (tail) {
             a.kflags[slot] = (a.rolling_enabled ? KF_HAS_MAX : 0u) | KF_SEEN | (state & KF_COUNT_MASK);
             if (a.rolling_enabled) a.kmax[slot] = mbits;
         }
-        // carry = last active lane
-        const int last = (int)(nact < 32 ? nact : 32) - 1;
-        if (last >= 0) {
-            c_state = __shfl_sync(0xffffffffu, state, last); c_mkey = __shfl_sync(0xffffffffu, mkey, last);
-            c_mbits = __shfl_sync(0xffffffffu, mbits, last); c_slot = __shfl_sync(0xffffffffu, slot, last);
-            c_hasmax = a.rolling_enabled != 0;
+        // carry = function/state after the last active lane of this round
+        const unsigned am = __ballot_sync(0xffffffffu, act);
+        if (am) {
+            const int last = 31 - __clz(am);
+            const bool l_seg = __shfl_sync(0xffffffffu, (int)seg, last) != 0;
+            c.hr = __shfl_sync(0xffffffffu, (int)(hr), last) != 0 || l_seg;
+            c.k = __shfl_sync(0xffffffffu, known_c ? state : k, last);
+            c.mc = l_seg || c.mc; c.hasm = a.rolling_enabled != 0;
+            c.mkey = __shfl_sync(0xffffffffu, mkey, last); c.mbits = __shfl_sync(0xffffffffu, mbits, last);
+            c_slot = __shfl_sync(0xffffffffu, slot, last);
         }
-        pos += 32;
     }
+}
+
+template <typename V>
+__global__ void __launch_bounds__(256) keyed_scan_kernel(const __grid_constant__ KeyedArgs a) {
+    const u32 lane = threadIdx.x & 31;
+    const size_t range = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const size_t lo = range * KA_RANGE;
+    if (lo >= a.n) return;
+    const size_t hi = (lo + KA_RANGE < a.n) ? lo + KA_RANGE : a.n;
+    KCarry c{false, 0u, false, false, 0ull, 0ull};                 // identity: nothing known about what precedes
+    u32 lead; u64 nalert = 0;
+    keyed_scan_range<V>(a, lo, hi, c, lead, nalert);
+    if (lane == 0) {
+        a.r_lead[range] = lead;
+        a.r_fn_k[range] = c.k; a.r_fn_flags[range] = (c.hr ? KFN_HR : 0u) | (c.mc ? KFN_MC : 0u) | (c.hasm ? KFN_HASM : 0u);
+        a.r_fn_mkey[range] = c.mkey; a.r_fn_mbits[range] = c.mbits;
+    }
+    nalert = warp_sum_u64(nalert);
+    if (lane == 0 && nalert) atomicAdd(&a.st->consec_alerts, nalert);
+}
+
+// state entering range r = E[r-1] o ... o E[0]; one block, each thread owns a contiguous chunk of ranges
+__global__ void __launch_bounds__(1024) keyed_carry_kernel(const KeyedArgs a, u32 nranges, u32 N, int reset) {
+    __shared__ u32 s_k[1024], s_fl[1024]; __shared__ u64 s_mk[1024], s_mb[1024];
+    const u32 t = threadIdx.x;
+    const u32 per = (nranges + 1023) / 1024;
+    const u32 r0 = t * per, r1 = (r0 + per < nranges) ? r0 + per : nranges;
+    auto compose = [&](u32& fk, u32& ffl, u64& fmk, u64& fmb, u32 gk, u32 gfl, u64 gmk, u64 gmb) {   // f then g -> f
+        if (gfl & KFN_HR) { fk = gk; ffl |= KFN_HR; } else { fk += gk; if (reset && N) fk %= N; }
+        if (gfl & KFN_MC) { fmk = gmk; fmb = gmb; ffl |= KFN_MC | KFN_HASM; }
+        else if (gfl & KFN_HASM) { if (!(ffl & KFN_HASM) || !(fmk > gmk)) { fmk = gmk; fmb = gmb; } ffl |= KFN_HASM; }
+    };
+    u32 k = 0, fl = 0; u64 mk = 0, mb = 0;                          // identity
+    for (u32 r = r0; r < r1; ++r) compose(k, fl, mk, mb, a.r_fn_k[r], a.r_fn_flags[r], a.r_fn_mkey[r], a.r_fn_mbits[r]);
+    s_k[t] = k; s_fl[t] = fl; s_mk[t] = mk; s_mb[t] = mb;
+    __syncthreads();
+    if (t == 0) {                                                   // exclusive scan of the 1024 chunk functions
+        u32 ck = 0, cfl = 0; u64 cmk = 0, cmb = 0;
+        for (u32 i = 0; i < 1024; ++i) {
+            const u32 tk = s_k[i], tfl = s_fl[i]; const u64 tmk = s_mk[i], tmb = s_mb[i];
+            s_k[i] = ck; s_fl[i] = cfl; s_mk[i] = cmk; s_mb[i] = cmb;
+            compose(ck, cfl, cmk, cmb, tk, tfl, tmk, tmb);
+        }
+    }
+    __syncthreads();
+    k = s_k[t]; fl = s_fl[t]; mk = s_mk[t]; mb = s_mb[t];
+    for (u32 r = r0; r < r1; ++r) {
+        a.r_in_c[r] = k; a.r_in_mkey[r] = mk; a.r_in_mbits[r] = mb;
+        compose(k, fl, mk, mb, a.r_fn_k[r], a.r_fn_flags[r], a.r_fn_mkey[r], a.r_fn_mbits[r]);
+    }
+}
+
+template <typename V>
+__global__ void __launch_bounds__(256) keyed_lead_kernel(const __grid_constant__ KeyedArgs a) {
+    const u32 lane = threadIdx.x & 31;
+    const size_t range = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const size_t lo = range * KA_RANGE;
+    if (lo >= a.n) return;
+    const u32 lead_len = a.r_lead[range];
+    if (lead_len == 0) return;
+    KCarry c{true, a.r_in_c[range], true, a.rolling_enabled != 0, a.r_in_mkey[range], a.r_in_mbits[range]};   // the entering state is a constant
+    u32 lead; u64 nalert = 0;
+    keyed_scan_range<V>(a, lo, lo + lead_len, c, lead, nalert);
     nalert = warp_sum_u64(nalert);
     if (lane == 0 && nalert) atomicAdd(&a.st->consec_alerts, nalert);
 }
