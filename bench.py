@@ -48,9 +48,11 @@ def workload_kwargs(capi, batch, n_keys=N_KEYS):
                 emit_fired=1, table_capacity=int(n_keys * 1.5), pane_ring=16, max_batch=batch)
 
 
-def stream_spec(StreamSpec, n_keys=N_KEYS):
-    # 1000 events/ms over 1 M hosts = one report per host per second; jitter <= bound, 0.1 % late tail
-    return StreamSpec(n_keys=n_keys, events_per_ms=1000, jitter_ms=BOUND_MS, late_frac_ppm=1000, late_extra_ms=25_000,
+def stream_spec(StreamSpec, n_keys=N_KEYS, world=1):
+    # 1000 events/ms per GPU over 1 M hosts = one report per host per second per GPU; jitter <= bound, 0.1 % late tail.
+    # Weak scaling: a streaming job adds GPUs to keep up with a higher event RATE, so the global stream carries
+    # world x 1000 events/ms (same hosts reporting world x as often) and one step still spans ~16.8 s of event time.
+    return StreamSpec(n_keys=n_keys, events_per_ms=1000 * world, jitter_ms=BOUND_MS, late_frac_ppm=1000, late_extra_ms=25_000,
                       value_type="f64", key_kind="uniform", seed=42)
 
 
@@ -209,13 +211,12 @@ def main():
 
     B = 1 << args.batch_log2
     K, W = args.steps, args.warmup
-    spec = stream_spec(StreamSpec, args.keys)
+    spec = stream_spec(StreamSpec, args.keys, world)
     kw = workload_kwargs(capi, B * (2 if world > 1 else 1), args.keys)
     kw["table_capacity"] = int(args.keys * args.load)
     kw["device"] = local_rank
-    # weak scaling keeps events per GPU per step fixed, so one global step spans world x more event
-    # time: size the pane ring for it (panes per step + bound + late tail), power of two
-    panes_per_step = (B * world // 1000) // WINDOW_MS + 4
+    # size the pane ring for the event time one global step spans (panes per step + bound + late tail), power of two
+    panes_per_step = (B * world // spec.events_per_ms) // WINDOW_MS + 4
     ring = 16
     while ring < panes_per_step + 4:
         ring *= 2
@@ -385,7 +386,7 @@ def main():
     line = {"metric": "events/sec keyed window-agg+alert", "value": value, "unit": "events/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C3 10s tumbling event-time count/avg/max per host + late drop + avg>limit alert + per-event >90 filter, 1M keys",
-                       "events_per_step_per_gpu": B, "keys": args.keys, "key_mode": args.key_mode, "window_ms": WINDOW_MS, "bound_ms": BOUND_MS,
+                       "events_per_step_per_gpu": B, "global_events_per_ms": spec.events_per_ms, "keys": args.keys, "key_mode": args.key_mode, "window_ms": WINDOW_MS, "bound_ms": BOUND_MS,
                        "l2": "inputs larger than L2 (each batch = 24 B x 2^%d = %.0f MB, read once)" % (args.batch_log2, 24 * B / 1e6),
                        "parallelism": "1 GPU" if world == 1 else (
                            f"{world} GPUs, combiner: local accumulate + 32 B all-reduce per batch + fire over NVLink peer memory"
