@@ -139,6 +139,8 @@ typedef struct fmq_config {
                                         (ComputeCpuMiddle.java:34-47); this many accepted records
                                         can be buffered while their windows are open (f64 only)   */
     uint64_t median_capacity;        /* median rows buffered between polls                        */
+    uint64_t late_capacity;          /* > 0: dropped late records are kept as a side output
+                                        (sideOutputLateData), this many rows between polls        */
 } fmq_config;
 
 /* one fired (key, window): 48 B per row */
@@ -207,6 +209,12 @@ int32_t fmq_poll_fired(fmq_handle* h, const fmq_fired_cols* out, size_t cap, int
 /* Replaces: the chained map + filter after the window (BandwidthMonitorWithEventTime.java:48-55). */
 int32_t fmq_poll_window_alerts(fmq_handle* h, const fmq_walert_cols* out, size_t cap, int32_t mem,
                                size_t* n_out, size_t* n_left);
+/* Replaces: DataStream#getSideOutput(lateOutputTag) after .sideOutputLateData(tag) — option 3 of the
+ * lateness handling the tutorial lists (chapter3/README.md:209-228): the records the window operator
+ * drops as late (every window they belong to has fired), as (ts, key, val) rows.  Needs
+ * fmq_config.late_capacity > 0.  late_dropped counts them either way. */
+int32_t fmq_poll_late(fmq_handle* h, const fmq_event_cols* out, size_t cap, int32_t mem,
+                      size_t* n_out, size_t* n_left);
 /* Replaces: the ProcessWindowFunction output of ComputeCpuMiddle.java:36-47: one row
  * (key, window_end, median) per fired (key, window); `value` is the middle element of the window's
  * sorted values, or the mean of the two middle ones.  Needs fmq_config.median_log_capacity > 0. */

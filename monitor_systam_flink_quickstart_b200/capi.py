@@ -47,6 +47,7 @@ class FmqConfig(C.Structure):
         ("max_batch", C.c_uint64), ("fired_capacity", C.c_uint64), ("walert_capacity", C.c_uint64),
         ("ealert_capacity", C.c_uint64), ("calert_capacity", C.c_uint64),
         ("text_max_bytes", C.c_uint64), ("median_log_capacity", C.c_uint64), ("median_capacity", C.c_uint64),
+        ("late_capacity", C.c_uint64),
     ]
 
 
@@ -130,6 +131,7 @@ def _declare(lib, p: str, has_mem: bool = True):
     sig("poll_window_alerts", [vp, C.POINTER(FmqWAlertCols), sz] + mem + [psz, psz])
     sig("poll_event_alerts", [vp, C.POINTER(FmqEventCols), sz] + mem + [psz, psz])
     if has_mem or p == "orc_":
+        sig("poll_late", [vp, C.POINTER(FmqEventCols), sz] + mem + [psz, psz])
         sig("poll_medians", [vp, C.POINTER(FmqWAlertCols), sz] + mem + [psz, psz])
     sig("poll_consec_alerts", [vp, C.POINTER(FmqEventCols), sz] + mem + [psz, psz])
     sig("poll_rolling_max", [vp, vp, sz] + mem + [psz])
@@ -328,6 +330,10 @@ class EngineBase:
 
     def poll_event_alerts(self, chunk: int = 1 << 20) -> EventRows:
         return self._poll_events("poll_event_alerts", chunk)
+
+    def poll_late(self, chunk: int = 1 << 20) -> EventRows:
+        """The late side output (sideOutputLateData)."""
+        return self._poll_events("poll_late", chunk)
 
     def poll_consec_alerts(self, chunk: int = 1 << 20) -> EventRows:
         return self._poll_events("poll_consec_alerts", chunk)

@@ -54,6 +54,7 @@ struct DevState {
     // skew adaptation: one warp per block samples how many lanes of a warp hit the same cell; the plan
     // kernel turns warp-level pre-aggregation on for the next batch when that is common
     u64 dup_sampled, dup_found; u32 combine_dups; u32 pad2;
+    u64 n_late;                      // rows in the late side output
     u64 n_mlog, n_mwork, n_median;   // median path: logged records, records selected for the window being fired, emitted rows
     u32 err_flags;
     u32 pad1;

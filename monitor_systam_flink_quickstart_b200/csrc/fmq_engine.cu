@@ -60,6 +60,7 @@ struct fmq_handle {
     const Acc32* peer_acc[FMQ_MAX_PEERS] = {};
     i64* d_xchg = nullptr;               // 4 x int64 exchange buffer for the all-reduce of the batch scalars
     size_t pending_n = 0;
+    i64* lt_ts = nullptr; u64 *lt_key = nullptr, *lt_val = nullptr; u64 lt_cap = 0; size_t cur_late = 0;
     // median path (N3)
     i64* ml_pane[2] = {nullptr, nullptr}; u32* ml_slot[2] = {nullptr, nullptr}; u64* ml_val[2] = {nullptr, nullptr}; int ml_cur = 0; u64 ml_cap = 0;
     u64* mw_items[2] = {nullptr, nullptr}; u64* mw_vals = nullptr;
@@ -98,7 +99,7 @@ static void free_all(fmq_handle* h) {
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
                     h->d_pack[0], h->d_pack[1], h->kr_lead, h->kr_k, h->kr_fl, h->kr_in_c, h->kr_mk, h->kr_mb, h->kr_in_mk, h->kr_in_mb, h->d_counts, h->d_tiles, h->d_xchg, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad,
                     h->ml_pane[0], h->ml_pane[1], h->ml_slot[0], h->ml_slot[1], h->ml_val[0], h->ml_val[1], h->mw_items[0], h->mw_items[1], h->mw_vals,
-                    h->md_key, h->md_wend, h->md_val};
+                    h->md_key, h->md_wend, h->md_val, h->lt_ts, h->lt_key, h->lt_val};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->h_st) cudaFreeHost(h->h_st);
     for (auto& q : h->tev) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
@@ -193,6 +194,10 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     h->tiles_len = (h->counts_len + SCAN_TILE - 1) / SCAN_TILE;
     CUC(dalloc(&h->d_counts, h->counts_len)); CUC(dalloc(&h->d_tiles, h->tiles_len));
     CUC(dalloc(&h->d_xchg, 4)); CUC(cudaMemset(h->d_xchg, 0, 32));
+    if (cfg->late_capacity > 0 && cfg->window_enabled) {
+        h->lt_cap = cfg->late_capacity;
+        CUC(dalloc(&h->lt_ts, h->lt_cap)); CUC(dalloc(&h->lt_key, h->lt_cap)); CUC(dalloc(&h->lt_val, h->lt_cap));
+    }
     if (cfg->median_log_capacity > 0) {
         if (!cfg->window_enabled || cfg->value_type != FMQ_VAL_F64) return fail(FMQ_ERR_BAD_ARG, "the window median needs window_enabled and f64 values");
         if (cfg->median_log_capacity >= 0xFFFFFFF0ull) return fail(FMQ_ERR_BAD_ARG, "median_log_capacity must be < 2^32");
@@ -317,6 +322,7 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         a.window_enabled = c.window_enabled; a.vec32 = ((((uintptr_t)ts | (uintptr_t)key | (uintptr_t)val) & 31) == 0);
         a.efilter_enabled = c.efilter_enabled; a.efilter_op = c.efilter_op; a.efilter_thr = c.efilter_threshold;
         a.ea_ts = h->ea_ts; a.ea_key = h->ea_key; a.ea_val = h->ea_val; a.ea_cap = h->ea_cap;
+        a.lt_ts = h->lt_ts; a.lt_key = h->lt_key; a.lt_val = h->lt_val; a.lt_cap = h->lt_cap;
         a.mlog_enabled = h->ml_cap > 0; a.ml_pane = h->ml_pane[h->ml_cur]; a.ml_slot = h->ml_slot[h->ml_cur]; a.ml_val = h->ml_val[h->ml_cur]; a.ml_cap = h->ml_cap;
         const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
         size_t blocks = (n + tile - 1) / tile; const size_t maxb = (size_t)h->num_sms * FMQ_INGEST_MIN_BLOCKS;   // persistent: resident blocks only
@@ -524,6 +530,13 @@ int32_t fmq_poll_window_alerts(fmq_handle* h, const fmq_walert_cols* o, size_t c
     void* d[3] = {h->wa_key, h->wa_wend, h->wa_val};
     void* c[3] = {o->key, o->window_end, o->value};
     return drain_cols(h, d, c, 3, &DevState::n_walert, &h->cur_walert, cap, mem, n_out, n_left);
+}
+int32_t fmq_poll_late(fmq_handle* h, const fmq_event_cols* o, size_t cap, int32_t mem, size_t* n_out, size_t* n_left) {
+    if (!h || !o) return FMQ_ERR_BAD_ARG;
+    if (!h->lt_cap) return set_err(h, FMQ_ERR_BAD_ARG, "the late side output is not enabled (fmq_config.late_capacity)");
+    void* d[3] = {h->lt_ts, h->lt_key, h->lt_val};
+    void* c[3] = {o->ts, o->key, o->val};
+    return drain_cols(h, d, c, 3, &DevState::n_late, &h->cur_late, cap, mem, n_out, n_left);
 }
 int32_t fmq_poll_medians(fmq_handle* h, const fmq_walert_cols* o, size_t cap, int32_t mem, size_t* n_out, size_t* n_left) {
     if (!h || !o) return FMQ_ERR_BAD_ARG;
@@ -761,7 +774,7 @@ int32_t fmq_snapshot(fmq_handle* h, void* buf, size_t cap, size_t* written) {
     if (cap < need) return set_err(h, FMQ_ERR_BAD_ARG, "snapshot buffer too small (see fmq_snapshot_size)");
     int st = sync_state(h); if (st) return st;
     const DevState& d = *h->h_st;
-    if (d.n_fired || d.n_walert || d.n_ealert || d.n_calert || d.n_median) return set_err(h, FMQ_ERR_BAD_ARG, "poll every output before taking a snapshot: emitted rows are not operator state");
+    if (d.n_fired || d.n_walert || d.n_ealert || d.n_calert || d.n_median || d.n_late) return set_err(h, FMQ_ERR_BAD_ARG, "poll every output before taking a snapshot: emitted rows are not operator state");
     char* p = static_cast<char*>(buf);
     SnapHeader hd{}; hd.magic = SNAP_MAGIC; hd.version = 1; hd.header_bytes = sizeof(SnapHeader); hd.cfg = h->cfg; hd.capacity = h->capacity; hd.ring = h->ring;
     hd.has_window = h->cfg.window_enabled; hd.has_keyed = keyed_enabled(h->cfg); hd.anchored_known = h->anchored_known; hd.total_bytes = need;
@@ -789,7 +802,7 @@ int32_t fmq_restore(fmq_handle* h, const void* buf, size_t bytes) {
     CU(h, cudaStreamSynchronize(h->stream));
     const char* p = static_cast<const char*>(buf) + sizeof(SnapHeader);
     DevState d; memcpy(&d, p, sizeof(d)); p += sizeof(d);
-    d.n_fired = d.n_walert = d.n_ealert = d.n_calert = 0; d.err_flags = 0;
+    d.n_fired = d.n_walert = d.n_ealert = d.n_calert = 0; d.n_late = 0; d.err_flags = 0;
     CU(h, cudaMemcpyAsync(h->d_st, &d, sizeof(d), cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaMemcpyAsync(h->d_keys, p, h->capacity * 8, cudaMemcpyHostToDevice, h->stream)); p += h->capacity * 8;
     if (hd.has_window) { const size_t b = (size_t)h->ring * h->capacity * sizeof(Acc32); CU(h, cudaMemcpyAsync(h->d_acc, p, b, cudaMemcpyHostToDevice, h->stream)); p += b; }

@@ -25,6 +25,8 @@ struct IngestArgs {
     int vec32;                  // all three columns are 32-byte aligned
     int efilter_enabled, efilter_op; double efilter_thr;
     i64* ea_ts; u64* ea_key; u64* ea_val; u64 ea_cap;
+    // late side output (sideOutputLateData): dropped records are also copied here
+    i64* lt_ts; u64* lt_key; u64* lt_val; u64 lt_cap;
     // median path (N3): every accepted record is also appended to a value log (pane, slot, value)
     int mlog_enabled; i64* ml_pane; u32* ml_slot; u64* ml_val; u64 ml_cap;
 };
@@ -234,7 +236,7 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
     if (!a.window_enabled) return;
     // ---- per event: A1 max-ts, A3 late test, A2 pane, and (hashed keys) the home-bucket load:
     //      all four directory loads are in flight before any of them is consumed ----
-    u32 ring_[INGEST_EPT]; u32 q_[INGEST_EPT]; u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0;
+    u32 ring_[INGEST_EPT]; u32 q_[INGEST_EPT]; u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0, late_mask = 0;
 #pragma unroll
     for (int e = 0; e < INGEST_EPT; ++e) {
         const bool ok = ok_mask & (1u << e);
@@ -242,6 +244,7 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
         r.dmax = (ok && d > r.dmax) ? d : r.dmax;                  // A1 (ts = origin + d)
         const bool is_late = ok && d < 0;                          // A3: every window of this record has fired
         r.late += is_late ? 1 : 0;
+        late_mask |= is_late ? (1u << e) : 0u;
         const bool beyond = ok && d >= 0 && (u64)d >= k.span;      // would alias an older pane of the ring
         r.err |= beyond ? ERRB_RING : 0u;
         const u32 du = (u32)d;
@@ -275,6 +278,15 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
         V v; memcpy(&v, &vb_[e], 8);
         accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask, k.combine, e == 0 && threadIdx.x < 32, r.dup);
         slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
+    }
+    // ---- late side output (chapter3/README.md:213-228, option 3: "a separate stream of the late data") ----
+    if (a.lt_cap) {
+        u64 row = block_append<INGEST_THREADS>(__popc(late_mask), &st->n_late, a.lt_cap, st);
+        if (row != ~0ull) {
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e)
+                if (late_mask & (1u << e)) { a.lt_ts[row] = ts_[e]; a.lt_key[row] = key_[e]; a.lt_val[row] = vb_[e]; ++row; }
+        }
     }
     // ---- N3: non-incremental window functions keep every value (ComputeCpuMiddle.java:36-38) ----
     if (a.mlog_enabled) {
@@ -402,7 +414,7 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
         ok_mask &= in_mask;
         if (a.efilter_enabled) nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
         if (!a.window_enabled) continue;
-        i64 gp_[INGEST_EPT]; u32 gs_[INGEST_EPT]; u32 gmask = 0;
+        i64 gp_[INGEST_EPT]; u32 gs_[INGEST_EPT]; u32 gmask = 0, glate = 0;
 #pragma unroll
         for (int e = 0; e < INGEST_EPT; ++e) {
             const i64 ts = ts_[e]; const u64 key = key_[e];
@@ -413,6 +425,7 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
                 const i64 d = ts - origin_ts;
                 if (d < 0) {
                     late++;                                          // A3
+                    glate |= 1u << e;
                 } else {
                     const u64 prel = (u64)d / (u64)a.g.slide;        // A2 (64-bit)
                     if (anchored && prel >= R) {
@@ -430,6 +443,14 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
             }
             accumulate_pair_lean<V>(a.acc, valid, idx, v, a.g.agg_mask);  // A5
             gp_[e] = valid ? gpane : 0; gs_[e] = valid ? (u32)(idx % a.g.capacity) : 0; gmask |= valid ? (1u << e) : 0u;
+        }
+        if (a.lt_cap) {
+            u64 row = block_append<INGEST_THREADS>(__popc(glate), &st->n_late, a.lt_cap, st);
+            if (row != ~0ull) {
+#pragma unroll
+                for (int e = 0; e < INGEST_EPT; ++e)
+                    if (glate & (1u << e)) { a.lt_ts[row] = ts_[e]; a.lt_key[row] = key_[e]; a.lt_val[row] = vb_[e]; ++row; }
+            }
         }
         if (a.mlog_enabled) {
             u64 row = block_append<INGEST_THREADS>(__popc(gmask), &st->n_mlog, a.ml_cap, st);

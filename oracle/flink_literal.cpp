@@ -78,7 +78,7 @@ struct OracleBase {
     virtual ~OracleBase() {}
     virtual int push(const int64_t* ts, const uint64_t* key, const void* val, size_t n, int64_t wm_after) = 0;
     virtual int flush(int64_t wm) = 0;
-    std::vector<FiredRow> fired; std::vector<WAlert> walerts, medians; std::vector<EvRow> ealerts, calerts;
+    std::vector<FiredRow> fired; std::vector<WAlert> walerts, medians; std::vector<EvRow> ealerts, calerts, late;
     std::vector<uint64_t> rolling;   // rolling max output of the last batch
     fmq_counters ctr{};
     virtual int key_state(uint64_t key, int32_t* consec, uint64_t* rolling_bits) = 0;
@@ -147,7 +147,10 @@ struct Oracle : OracleBase {
             if (cfg.median_log_capacity > 0) wlist[{key, s}].push_back(val);
             timers.insert({max_ts, key, s});                     // EventTimeTrigger.onElement (+ cleanup timer, same ts)
         }
-        if (skipped && ts + 0 <= current_wm) ctr.late_dropped++; // numLateRecordsDropped
+        if (skipped && ts + 0 <= current_wm) {                   // numLateRecordsDropped / sideOutput(lateDataOutputTag, element)
+            ctr.late_dropped++;
+            if (cfg.late_capacity > 0) late.push_back({ts, key, bits_of(val)});
+        }
     }
 
     double alert_value(const Acc<V>& a) const {
@@ -272,6 +275,9 @@ static int32_t poll_ev(std::vector<EvRow>& v, const fmq_event_cols* o, size_t ca
 }
 int32_t orc_poll_event_alerts(void* h, const fmq_event_cols* o, size_t cap, size_t* n_out, size_t* n_left) {
     return poll_ev(static_cast<OracleBase*>(h)->ealerts, o, cap, n_out, n_left);
+}
+int32_t orc_poll_late(void* h, const fmq_event_cols* o, size_t cap, size_t* n_out, size_t* n_left) {
+    return poll_ev(static_cast<OracleBase*>(h)->late, o, cap, n_out, n_left);
 }
 int32_t orc_poll_consec_alerts(void* h, const fmq_event_cols* o, size_t cap, size_t* n_out, size_t* n_left) {
     return poll_ev(static_cast<OracleBase*>(h)->calerts, o, cap, n_out, n_left);

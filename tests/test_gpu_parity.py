@@ -23,6 +23,8 @@ def pair(**kw):
 
 
 def compare_all(gpu, cpu, agg_mask=15, rtol=1e-9):
+    if gpu.cfg.late_capacity:
+        assert_events_equal(gpu.poll_late(), cpu.poll_late())
     assert_fired_equal(gpu.poll_fired(), cpu.poll_fired(), f64_sum_rtol=rtol, agg_mask=agg_mask)
     if gpu.cfg.walert_source:
         a, b = sort_walerts(gpu.poll_window_alerts()), sort_walerts(cpu.poll_window_alerts())
@@ -96,7 +98,7 @@ def test_g6_g7_bandwidth_gpu():
 
 # ---- seeded streams ------------------------------------------------------------------------------
 CONFIGS = {
-    "c3_tumbling_f64": (dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=10_000, max_out_of_orderness_ms=5000,
+    "c3_tumbling_f64": (dict(late_capacity=1 << 16, window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=10_000, max_out_of_orderness_ms=5000,
                              walert_source=capi.FMQ_ALERT_AVG, walert_op=capi.FMQ_CMP_GT, walert_threshold=50.0,
                              efilter_enabled=1, efilter_threshold=90.0),
                         StreamSpec(n_keys=3000, events_per_ms=3, late_frac_ppm=20000)),
@@ -135,7 +137,7 @@ def test_window_parity_seeded(name, batch, key_mode):
 def test_window_parity_when_blocks_reuse_their_staging_ring(key_mode):
     """2.2 M events per batch = ~5 tiles per resident block: every shared-memory stage of the TMA ring is
     refilled while the kernel runs (the small tests above never get that far).  Against the oracle."""
-    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=5000, max_out_of_orderness_ms=3000,
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=5000, max_out_of_orderness_ms=3000, late_capacity=1 << 16,
               efilter_enabled=1, efilter_threshold=97.0, key_mode=key_mode, table_capacity=60_000, pane_ring=64, max_batch=1 << 22,
               fired_capacity=1 << 21, ealert_capacity=1 << 20)
     spec = StreamSpec(n_keys=40_000, events_per_ms=200, jitter_ms=3000, late_frac_ppm=2000, late_extra_ms=20_000)
