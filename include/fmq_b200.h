@@ -141,6 +141,8 @@ typedef struct fmq_config {
     uint64_t median_capacity;        /* median rows buffered between polls                        */
     uint64_t late_capacity;          /* > 0: dropped late records are kept as a side output
                                         (sideOutputLateData), this many rows between polls        */
+    int32_t  overlapped_polls;       /* 1: second set of output columns for fmq_poll_all_begin/end */
+    int32_t  reserved3;
 } fmq_config;
 
 /* one fired (key, window): 48 B per row */
@@ -209,6 +211,16 @@ int32_t fmq_poll_fired(fmq_handle* h, const fmq_fired_cols* out, size_t cap, int
 /* Replaces: the chained map + filter after the window (BandwidthMonitorWithEventTime.java:48-55). */
 int32_t fmq_poll_window_alerts(fmq_handle* h, const fmq_walert_cols* out, size_t cap, int32_t mem,
                                size_t* n_out, size_t* n_left);
+/* Replaces: Output#collect of everything a micro-batch produced (fired rows, window alerts, per-event
+ * filter rows), for shims that overlap PCIe directions: fmq_poll_all_begin waits for the kernels,
+ * returns the three row counts, queues the device->host copies on a second stream and returns;
+ * the caller may push the next micro-batch (host->device) while they run, and calls
+ * fmq_poll_all_end before reading the buffers.  Host buffers (pinned) only; every buffer must hold
+ * all waiting rows.  Needs fmq_config.overlapped_polls = 1. */
+int32_t fmq_poll_all_begin(fmq_handle* h, const fmq_fired_cols* fired, size_t fired_cap,
+                           const fmq_walert_cols* walerts, size_t walert_cap,
+                           const fmq_event_cols* ealerts, size_t ealert_cap, size_t* counts3);
+int32_t fmq_poll_all_end(fmq_handle* h);
 /* Replaces: DataStream#getSideOutput(lateOutputTag) after .sideOutputLateData(tag) — option 3 of the
  * lateness handling the tutorial lists (chapter3/README.md:209-228): the records the window operator
  * drops as late (every window they belong to has fired), as (ts, key, val) rows.  Needs

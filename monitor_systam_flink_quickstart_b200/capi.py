@@ -47,7 +47,7 @@ class FmqConfig(C.Structure):
         ("max_batch", C.c_uint64), ("fired_capacity", C.c_uint64), ("walert_capacity", C.c_uint64),
         ("ealert_capacity", C.c_uint64), ("calert_capacity", C.c_uint64),
         ("text_max_bytes", C.c_uint64), ("median_log_capacity", C.c_uint64), ("median_capacity", C.c_uint64),
-        ("late_capacity", C.c_uint64),
+        ("late_capacity", C.c_uint64), ("overlapped_polls", C.c_int32), ("reserved3", C.c_int32),
     ]
 
 
@@ -155,6 +155,8 @@ def _declare(lib, p: str, has_mem: bool = True):
         sig("text_key_hash", [C.c_char_p, sz], C.c_uint64)
         sig("parse_text", [vp, vp, sz, i32, i32, i32, vp, vp, vp, vp, sz, i32, psz, psz])
         sig("push_text", [vp, vp, sz, i32, i32, i32, i64, psz])
+        sig("poll_all_begin", [vp, C.POINTER(FmqFiredCols), sz, C.POINTER(FmqWAlertCols), sz, C.POINTER(FmqEventCols), sz, psz])
+        sig("poll_all_end", [vp])
         sig("snapshot_size", [vp, psz])
         sig("snapshot", [vp, vp, sz, psz])
         sig("restore", [vp, vp, sz])
@@ -289,6 +291,21 @@ class EngineBase:
         args += [C.byref(n_out), C.byref(n_left)]
         self._check(self._f(name)(*args))
         return n_out.value, n_left.value
+
+    def poll_all_begin(self, fired6, walert3, ealert3):
+        """Overlapped poll: queues the D2H copies of all three outputs into the given (pinned) column
+        lists and returns (n_fired, n_walert, n_ealert) at once; call poll_all_end() before reading."""
+        f = FmqFiredCols(*[_ptr(a) for a in fired6]) if fired6 else None
+        w = FmqWAlertCols(*[_ptr(a) for a in walert3]) if walert3 else None
+        e = FmqEventCols(*[_ptr(a) for a in ealert3]) if ealert3 else None
+        counts = (C.c_size_t * 3)()
+        self._check(self._lib.fmq_poll_all_begin(self._h, C.byref(f) if f else None, len(fired6[0]) if fired6 else 0,
+                                                 C.byref(w) if w else None, len(walert3[0]) if walert3 else 0,
+                                                 C.byref(e) if e else None, len(ealert3[0]) if ealert3 else 0, counts))
+        return tuple(counts)
+
+    def poll_all_end(self):
+        self._check(self._lib.fmq_poll_all_end(self._h))
 
     def poll_fired_into(self, key, window_end, count, sum, min, max):
         return self._poll_into("poll_fired", FmqFiredCols, [key, window_end, count, sum, min, max])

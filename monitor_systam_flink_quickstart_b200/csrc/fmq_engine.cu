@@ -60,6 +60,8 @@ struct fmq_handle {
     const Acc32* peer_acc[FMQ_MAX_PEERS] = {};
     i64* d_xchg = nullptr;               // 4 x int64 exchange buffer for the all-reduce of the batch scalars
     size_t pending_n = 0;
+    // second set of fired / window-alert / event-alert columns + a copy-out stream, for overlapped polls
+    void* alt_out[12] = {}; cudaStream_t out_stream = nullptr; cudaEvent_t ev_out = nullptr; bool out_pending = false;
     i64* lt_ts = nullptr; u64 *lt_key = nullptr, *lt_val = nullptr; u64 lt_cap = 0; size_t cur_late = 0;
     // median path (N3)
     i64* ml_pane[2] = {nullptr, nullptr}; u32* ml_slot[2] = {nullptr, nullptr}; u64* ml_val[2] = {nullptr, nullptr}; int ml_cur = 0; u64 ml_cap = 0;
@@ -101,6 +103,9 @@ static void free_all(fmq_handle* h) {
                     h->ml_pane[0], h->ml_pane[1], h->ml_slot[0], h->ml_slot[1], h->ml_val[0], h->ml_val[1], h->mw_items[0], h->mw_items[1], h->mw_vals,
                     h->md_key, h->md_wend, h->md_val, h->lt_ts, h->lt_key, h->lt_val};
     for (void* p : ptrs) if (p) cudaFree(p);
+    for (void* p : h->alt_out) if (p) cudaFree(p);
+    if (h->out_stream) cudaStreamDestroy(h->out_stream);
+    if (h->ev_out) cudaEventDestroy(h->ev_out);
     if (h->h_st) cudaFreeHost(h->h_st);
     for (auto& q : h->tev) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
     if (h->ev_copy) cudaEventDestroy(h->ev_copy);
@@ -194,6 +199,11 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     h->tiles_len = (h->counts_len + SCAN_TILE - 1) / SCAN_TILE;
     CUC(dalloc(&h->d_counts, h->counts_len)); CUC(dalloc(&h->d_tiles, h->tiles_len));
     CUC(dalloc(&h->d_xchg, 4)); CUC(cudaMemset(h->d_xchg, 0, 32));
+    if (cfg->overlapped_polls) {
+        CUC(cudaStreamCreateWithFlags(&h->out_stream, cudaStreamNonBlocking)); CUC(cudaEventCreateWithFlags(&h->ev_out, cudaEventDisableTiming));
+        const size_t caps[12] = {h->f_cap, h->f_cap, h->f_cap, h->f_cap, h->f_cap, h->f_cap, h->wa_cap, h->wa_cap, h->wa_cap, h->ea_cap, h->ea_cap, h->ea_cap};
+        for (int i = 0; i < 12; ++i) if (caps[i]) CUC(cudaMalloc(&h->alt_out[i], caps[i] * 8));
+    }
     if (cfg->late_capacity > 0 && cfg->window_enabled) {
         h->lt_cap = cfg->late_capacity;
         CUC(dalloc(&h->lt_ts, h->lt_cap)); CUC(dalloc(&h->lt_key, h->lt_cap)); CUC(dalloc(&h->lt_val, h->lt_cap));
@@ -531,6 +541,50 @@ int32_t fmq_poll_window_alerts(fmq_handle* h, const fmq_walert_cols* o, size_t c
     void* c[3] = {o->key, o->window_end, o->value};
     return drain_cols(h, d, c, 3, &DevState::n_walert, &h->cur_walert, cap, mem, n_out, n_left);
 }
+// ---- overlapped polls --------------------------------------------------------------------------------
+// fmq_poll_all_begin waits for the handle's kernels, reads the row counts, queues the device->host
+// copies of the fired / window-alert / event-alert columns on a second stream and switches the
+// kernels to a second set of output columns, so the caller can already push the next micro-batch
+// (its host->device copy runs on the other PCIe direction at the same time).  fmq_poll_all_end waits
+// for the copies.  Host buffers should be pinned.
+int32_t fmq_poll_all_begin(fmq_handle* h, const fmq_fired_cols* f, size_t f_cap, const fmq_walert_cols* wa, size_t wa_cap,
+                           const fmq_event_cols* ea, size_t ea_cap, size_t* counts3) {
+    if (!h || !counts3) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (!h->out_stream) return set_err(h, FMQ_ERR_BAD_ARG, "overlapped polls need fmq_config.overlapped_polls = 1");
+    if (h->out_pending) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_poll_all_end has not been called for the previous fmq_poll_all_begin");
+    if (h->cur_fired || h->cur_walert || h->cur_ealert) return set_err(h, FMQ_ERR_BAD_ARG, "finish the partial fmq_poll_* first");
+    int s = sync_state(h); if (s) return s;
+    const DevState& d = *h->h_st;
+    const size_t nf = d.n_fired, nw = d.n_walert, ne = d.n_ealert;
+    if ((nf && (!f || nf > f_cap)) || (nw && (!wa || nw > wa_cap)) || (ne && (!ea || ne > ea_cap))) return set_err(h, FMQ_ERR_BAD_ARG, "caller buffers smaller than the rows waiting");
+    CU(h, cudaEventRecord(h->ev_out, h->stream));
+    CU(h, cudaStreamWaitEvent(h->out_stream, h->ev_out, 0));
+    void* cur[12] = {h->f_key, h->f_wend, h->f_count, h->f_sum, h->f_min, h->f_max, h->wa_key, h->wa_wend, h->wa_val, h->ea_ts, h->ea_key, h->ea_val};
+    void* dst[12] = {f ? f->key : nullptr, f ? f->window_end : nullptr, f ? f->count : nullptr, f ? f->sum : nullptr, f ? f->min : nullptr, f ? f->max : nullptr,
+                     wa ? wa->key : nullptr, wa ? wa->window_end : nullptr, wa ? wa->value : nullptr, ea ? ea->ts : nullptr, ea ? ea->key : nullptr, ea ? ea->val : nullptr};
+    const size_t cnt[12] = {nf, nf, nf, nf, nf, nf, nw, nw, nw, ne, ne, ne};
+    for (int i = 0; i < 12; ++i) if (cnt[i] && dst[i] && cur[i]) CU(h, cudaMemcpyAsync(dst[i], cur[i], cnt[i] * 8, cudaMemcpyDeviceToHost, h->out_stream));
+    // the kernels of the next push append into the other set, from row 0
+    CU(h, cudaMemsetAsync((char*)h->d_st + offsetof(DevState, n_fired), 0, 8, h->stream));
+    CU(h, cudaMemsetAsync((char*)h->d_st + offsetof(DevState, n_walert), 0, 8, h->stream));
+    CU(h, cudaMemsetAsync((char*)h->d_st + offsetof(DevState, n_ealert), 0, 8, h->stream));
+    void** slots[12] = {(void**)&h->f_key, (void**)&h->f_wend, (void**)&h->f_count, (void**)&h->f_sum, (void**)&h->f_min, (void**)&h->f_max,
+                        (void**)&h->wa_key, (void**)&h->wa_wend, (void**)&h->wa_val, (void**)&h->ea_ts, (void**)&h->ea_key, (void**)&h->ea_val};
+    for (int i = 0; i < 12; ++i) { void* t = *slots[i]; *slots[i] = h->alt_out[i]; h->alt_out[i] = t; }
+    counts3[0] = nf; counts3[1] = nw; counts3[2] = ne;
+    h->out_pending = true;
+    return FMQ_OK;
+}
+int32_t fmq_poll_all_end(fmq_handle* h) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (!h->out_pending) return FMQ_OK;
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaStreamSynchronize(h->out_stream));
+    h->out_pending = false;
+    return FMQ_OK;
+}
+
 int32_t fmq_poll_late(fmq_handle* h, const fmq_event_cols* o, size_t cap, int32_t mem, size_t* n_out, size_t* n_left) {
     if (!h || !o) return FMQ_ERR_BAD_ARG;
     if (!h->lt_cap) return set_err(h, FMQ_ERR_BAD_ARG, "the late side output is not enabled (fmq_config.late_capacity)");

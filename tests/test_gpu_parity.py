@@ -393,6 +393,46 @@ def test_snapshot_restore_continues_exactly(key_mode):
         capi.Engine(**dict(kw, pane_ring=64)).restore(snap)        # different geometry is refused
 
 
+def test_overlapped_polls_return_the_same_rows():
+    """fmq_poll_all_begin/end (copy-out on a second stream while the next batch is pushed) against the
+    oracle, batch by batch."""
+    import torch
+    kw, spec = CONFIGS["c3_tumbling_f64"]
+    kw = {k: v for k, v in kw.items() if k != "late_capacity"}
+    gpu = capi.Engine(overlapped_polls=1, **kw, **SMALL)
+    cpu = OracleEngine(**kw)
+    cap = 1 << 16
+    sets = [([torch.empty(cap, dtype=torch.int64).pin_memory() for _ in range(3)] + [torch.empty(cap, dtype=torch.float64).pin_memory() for _ in range(3)],
+             [torch.empty(cap, dtype=torch.int64).pin_memory(), torch.empty(cap, dtype=torch.int64).pin_memory(), torch.empty(cap, dtype=torch.float64).pin_memory()],
+             [torch.empty(cap, dtype=torch.int64).pin_memory(), torch.empty(cap, dtype=torch.int64).pin_memory(), torch.empty(cap, dtype=torch.float64).pin_memory()])
+            for _ in range(2)]
+    fired, eal = [], []
+    pending = None
+
+    def harvest():
+        nonlocal pending
+        if pending is None:
+            return
+        gpu.poll_all_end()
+        (f, w, e), (nf, nw, ne) = pending
+        fired.append(capi.Fired(f[0][:nf].numpy().view(np.uint64).copy(), f[1][:nf].numpy().copy(), f[2][:nf].numpy().copy(),
+                                f[3][:nf].numpy().copy(), f[4][:nf].numpy().copy(), f[5][:nf].numpy().copy()))
+        eal.append(capi.EventRows(e[0][:ne].numpy().copy(), e[1][:ne].numpy().view(np.uint64).copy(), e[2][:ne].numpy().copy()))
+        pending = None
+    for b in range(8):
+        ts, key, val = generate_numpy(spec, b * 20_000, 20_000)
+        gpu.push_batch(ts, key, val); cpu.push_batch(ts, key, val)      # the D2H of the previous batch is still in flight here
+        harvest()
+        bufs = sets[b % 2]
+        pending = (bufs, gpu.poll_all_begin(*bufs))
+    harvest()
+    gpu.flush(); cpu.flush()
+    fired.append(gpu.poll_fired()); eal.append(gpu.poll_event_alerts())
+    cat = lambda parts, cls, fields: cls(*[np.concatenate([getattr(p, f) for p in parts]) for f in fields])  # noqa: E731
+    assert_fired_equal(cat(fired, capi.Fired, ("key", "window_end", "count", "sum", "min", "max")), cpu.poll_fired())
+    assert_events_equal(cat(eal, capi.EventRows, ("ts", "key", "val")), cpu.poll_event_alerts())
+
+
 # ---- keyBy exchange ------------------------------------------------------------------------------
 @pytest.mark.parametrize("world", [1, 2, 8])
 def test_partition_by_owner_is_a_stable_split(world):
