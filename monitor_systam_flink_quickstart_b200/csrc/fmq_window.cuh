@@ -226,13 +226,14 @@ struct IngestConst {
 // One tile of the fast path: the four events held by this thread.  Called by every thread of the block.
 template <typename V, bool DENSE>
 __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
-                                            const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 in_mask) {
+                                            const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 in_mask,
+                                            bool do_filter = true) {
     u32 ok_mask = 0;
 #pragma unroll
     for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
     if ((ok_mask & in_mask) != in_mask) r.err |= ERRB_BAD_INPUT;
     ok_mask &= in_mask;
-    if (a.efilter_enabled) r.nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
+    if (a.efilter_enabled && do_filter) r.nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
     if (!a.window_enabled) return;
     // ---- per event: A1 max-ts, A3 late test, A2 pane, and (hashed keys) the home-bucket load:
     //      all four directory loads are in flight before any of them is consumed ----
@@ -303,6 +304,8 @@ template <typename V, bool DENSE>
 __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_fast_kernel(const __grid_constant__ IngestArgs a) {
     extern __shared__ __align__(128) unsigned char ingest_smem[];
     __shared__ __align__(8) u64 bars[INGEST_STAGES];
+    __shared__ u32 f_wsum[INGEST_THREADS / 32];
+    __shared__ u64 f_base;
     DevState* st = a.st;
     if (!ingest_fast_ok(st, a.g)) return;                        // the generic kernel handles this batch
     IngestConst k;
@@ -348,6 +351,21 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
         for (int e = 0; e < INGEST_EPT; ++e) {
             ts_[e] = (i64)sts[threadIdx.x + e * INGEST_THREADS]; key_[e] = skey[threadIdx.x + e * INGEST_THREADS]; vb_[e] = sval[threadIdx.x + e * INGEST_THREADS];
         }
+        // A6-i, first half: hit mask and the warp-level prefix, BEFORE the barrier that frees the stage, so that
+        // this one barrier also publishes the per-warp totals (saves a block barrier per tile)
+        u32 hits = 0, inc = 0;
+        if (a.efilter_enabled) {
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e) {
+                V v; memcpy(&v, &vb_[e], 8);
+                hits |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY && cmp_op((double)v, a.efilter_op, a.efilter_thr)) ? 1u : 0u) << e;
+            }
+            inc = __popc(hits);
+            const u32 lane = threadIdx.x & 31;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, inc, o); if ((int)lane >= o) inc += x; }
+            if (lane == 31) f_wsum[threadIdx.x >> 5] = inc;
+        }
         __syncthreads();                                         // every thread has its events in registers: the stage is free
         if (threadIdx.x == 0) {
             // The stage was just read through the generic proxy (by every thread, ordered by the barrier
@@ -358,7 +376,24 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
             const size_t tn = t + (size_t)INGEST_STAGES * gridDim.x;
             if (tn < full_tiles) issue(tn, s);
         }
-        ingest_tile<V, DENSE>(a, st, k, r, ts_, key_, vb_, 0xFu);
+        if (a.efilter_enabled) {                                 // second half: one reservation per tile, rows in thread order
+            u32 wbase = 0, total = 0;
+#pragma unroll
+            for (int i = 0; i < INGEST_THREADS / 32; ++i) { const u32 x = f_wsum[i]; if (i < (int)(threadIdx.x >> 5)) wbase += x; total += x; }
+            if (threadIdx.x == 0) f_base = total ? atomicAdd(&st->n_ealert, (u64)total) : 0;
+            __syncthreads();
+            if (total) {
+                u64 row = f_base + wbase + (inc - __popc(hits));
+                if (f_base + total > a.ea_cap) { if (threadIdx.x == 0) r.err |= ERRB_OUTPUT; }
+                else {
+#pragma unroll
+                    for (int e = 0; e < INGEST_EPT; ++e)
+                        if (hits & (1u << e)) { a.ea_ts[row] = ts_[e]; a.ea_key[row] = key_[e]; a.ea_val[row] = vb_[e]; ++row; }
+                }
+            }
+            r.nea += __popc(hits);
+        }
+        ingest_tile<V, DENSE>(a, st, k, r, ts_, key_, vb_, 0xFu, false);
     }
     // ragged tail (and unaligned columns): direct 8-byte loads
     const size_t tail_tiles = (a.n - full_tiles * INGEST_TILE + INGEST_TILE - 1) / INGEST_TILE;
@@ -626,34 +661,33 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
             const bool fired = live && count > 0;
             const u64 sum_bits = is_f64 ? (u64)__double_as_longlong(sum_d) : sum_i;
             if (fired) fired_local++;
-            if (a.emit_fired) {
-                const u64 row = block_append<FIRE_THREADS>(fired ? 1u : 0u, &st->n_fired, a.f_cap, st);
-                if (fired && row != ~0ull) {
-                    a.f_key[row] = key; a.f_wend[row] = wend; a.f_count[row] = count; a.f_sum[row] = sum_bits;
-                    a.f_min[row] = (a.g.agg_mask & 4u) ? Codec<V>::dec_min(mn) : 0;
-                    a.f_max[row] = (a.g.agg_mask & 8u) ? Codec<V>::dec_max(mx) : 0;
+            // A6-ii/iii: ((double)sum * 8.0 / 60 / 1024 / 1024) < 100, evaluated left to right
+            double v = 0.0; bool hit = false;
+            if (a.walert_source != 0 && fired) {
+                if (a.walert_source == 2) {
+                    v = Codec<V>::as_double(sum_bits) / (double)count;            // ComputeCpuAvg.java:49
+                } else {
+                    double src;
+                    if (a.walert_source == 1) src = Codec<V>::as_double(sum_bits);
+                    else if (a.walert_source == 3) src = Codec<V>::as_double(Codec<V>::dec_min(mn));
+                    else if (a.walert_source == 4) src = Codec<V>::as_double(Codec<V>::dec_max(mx));
+                    else src = (double)count;
+                    v = src * a.mul / a.d0 / a.d1 / a.d2;
                 }
+                hit = cmp_op(v, a.walert_op, a.thr);
             }
-            if (a.walert_source != 0) {
-                // A6-ii/iii: ((double)sum * 8.0 / 60 / 1024 / 1024) < 100, evaluated left to right
-                double v = 0.0; bool hit = false;
-                if (fired) {
-                    if (a.walert_source == 2) {
-                        v = Codec<V>::as_double(sum_bits) / (double)count;            // ComputeCpuAvg.java:49
-                    } else {
-                        double src;
-                        if (a.walert_source == 1) src = Codec<V>::as_double(sum_bits);
-                        else if (a.walert_source == 3) src = Codec<V>::as_double(Codec<V>::dec_min(mn));
-                        else if (a.walert_source == 4) src = Codec<V>::as_double(Codec<V>::dec_max(mx));
-                        else src = (double)count;
-                        v = src * a.mul / a.d0 / a.d1 / a.d2;
-                    }
-                    hit = cmp_op(v, a.walert_op, a.thr);
-                }
-                if (hit) alerts_local++;
-                const u64 row = block_append<FIRE_THREADS>(hit ? 1u : 0u, &st->n_walert, a.wa_cap, st);
-                if (hit && row != ~0ull) { a.wa_key[row] = key; a.wa_wend[row] = wend; a.wa_val[row] = v; }
+            if (hit) alerts_local++;
+            // A5f: compaction of the fired row and of the alert row behind one pair of block barriers
+            u64 row_f = ~0ull, row_a = ~0ull;
+            if (a.emit_fired && a.walert_source != 0) block_append2<FIRE_THREADS>(fired, hit, &st->n_fired, a.f_cap, &st->n_walert, a.wa_cap, st, row_f, row_a);
+            else if (a.emit_fired) { const u64 r_ = block_append<FIRE_THREADS>(fired ? 1u : 0u, &st->n_fired, a.f_cap, st); if (fired) row_f = r_; }
+            else if (a.walert_source != 0) { const u64 r_ = block_append<FIRE_THREADS>(hit ? 1u : 0u, &st->n_walert, a.wa_cap, st); if (hit) row_a = r_; }
+            if (row_f != ~0ull) {
+                a.f_key[row_f] = key; a.f_wend[row_f] = wend; a.f_count[row_f] = count; a.f_sum[row_f] = sum_bits;
+                a.f_min[row_f] = (a.g.agg_mask & 4u) ? Codec<V>::dec_min(mn) : 0;
+                a.f_max[row_f] = (a.g.agg_mask & 8u) ? Codec<V>::dec_max(mx) : 0;
             }
+            if (row_a != ~0ull) { a.wa_key[row_a] = key; a.wa_wend[row_a] = wend; a.wa_val[row_a] = v; }
         }
         // cleanup: WindowOperator.clearAllState for panes whose last window has fired
         if (live && a.clear_in_fire) {
