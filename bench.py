@@ -155,7 +155,7 @@ def main():
     ap.add_argument("--cpu-sample-log2", type=int, default=23, help="events per step of the CPU baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--multi", default="combiner", choices=["combiner", "alltoall"],
+    ap.add_argument("--multi", default="combiner", choices=["combiner", "alltoall", "peerpull"],
                     help="N>1: combiner = local accumulate + peer-memory fire (no event shuffle; dense ids); "
                          "alltoall = owner split + NCCL all-to-all of the events")
     ap.add_argument("--no-variants", action="store_true")
@@ -226,7 +226,7 @@ def main():
     if args.key_mode == "dense":
         kw["key_mode"] = capi.FMQ_KEYS_DENSE
         # all-to-all route: rank-local dense ids (id // world); combiner route: every rank holds the full id space
-        kw["table_capacity"] = (args.keys + world - 1) // world if (world > 1 and args.multi == "alltoall") else args.keys
+        kw["table_capacity"] = (args.keys + world - 1) // world if (world > 1 and args.multi != "combiner") else args.keys
     # outputs stay in HBM during the timed region (polled after it): size the buffers for K steps.
     # ~1 fired row per 10 events (one report per host per second, 10 s windows), ~10 % event alerts.
     per_rank_events = B * max(K, W)
@@ -250,9 +250,11 @@ def main():
         stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local_rank))
         sharded = None
         if world > 1:
-            from monitor_systam_flink_quickstart_b200.shard import CombinerOperator, ShardedOperator
+            from monitor_systam_flink_quickstart_b200.shard import CombinerOperator, PeerPullOperator, ShardedOperator
             if args.multi == "combiner" and kw.get("key_mode") == capi.FMQ_KEYS_DENSE:
                 sharded = CombinerOperator(eng, rank, world)
+            elif args.multi == "peerpull":
+                sharded = PeerPullOperator(eng, rank, world, BOUND_MS)
             else:
                 sharded = ShardedOperator(eng, rank, world, BOUND_MS)
 
@@ -396,7 +398,9 @@ def main():
                        "l2": "inputs larger than L2 (each batch = 24 B x 2^%d = %.0f MB, read once)" % (args.batch_log2, 24 * B / 1e6),
                        "parallelism": "1 GPU" if world == 1 else (
                            f"{world} GPUs, combiner: local accumulate + 32 B all-reduce per batch + fire over NVLink peer memory"
-                           if (args.multi == "combiner" and args.key_mode == "dense") else f"keyBy hash-sharded over {world} GPUs, NCCL all-to-all")},
+                           if (args.multi == "combiner" and args.key_mode == "dense") else (
+                               f"keyBy sharded over {world} GPUs, buckets pulled from peer memory over NVLink" if args.multi == "peerpull"
+                               else f"keyBy hash-sharded over {world} GPUs, NCCL all-to-all"))},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "variants": variants,
             "step_counts": {"event_alert_rows": int(n_ealert), "late_dropped": int(n_late), "fired_rows": int(n_fired)}}
     print(json.dumps(line))

@@ -349,6 +349,24 @@ int32_t fmq_push_local(fmq_handle* h, const int64_t* ts, const uint64_t* key, co
 int32_t fmq_fire_global(fmq_handle* h, int64_t watermark_after);
 int32_t fmq_retire(fmq_handle* h);
 
+/* ---- keyBy exchange over NVLink peer memory ("peer pull", A4) --------------------------------------
+ * Replaces: the keyBy network exchange (KeyGroupStreamPartitioner + Netty/local channels behind
+ * BandwidthMonitorWithEventTime.java:45) for ranks on one NVSwitch node.  Per micro-batch, on every rank:
+ *     fmq_exchange_split(h, ts, key, val, n, parity, counts)    owner buckets into a buffer all peers map
+ *     all-gather the `world` counts of every rank into matrix[src * world + dst]   (caller, e.g. NCCL)
+ *     fmq_exchange_pull_push(h, parity, matrix, watermark_after, &n)   pull own buckets out of every
+ *                       peer's buffer (source-rank order) and run the operator chain on them
+ * parity alternates 0/1 per micro-batch.  Works for every operator (per-key arrival order survives) and
+ * both key modes.  Set-up: fmq_exchange_alloc (returns a 64-byte CUDA IPC blob to hand to the peers),
+ * fmq_ipc_open on the peers' blobs, fmq_exchange_attach (within one process: fmq_exchange_base). */
+int32_t fmq_exchange_alloc(fmq_handle* h, void* handle64);
+void*   fmq_exchange_base(fmq_handle* h);
+int32_t fmq_exchange_attach(fmq_handle* h, int32_t rank, int32_t world, const void* const* peer_bases);
+int32_t fmq_exchange_split(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val,
+                           size_t n, int32_t parity, uint64_t* counts);
+int32_t fmq_exchange_pull_push(fmq_handle* h, int32_t parity, const uint64_t* matrix,
+                               int64_t watermark_after, size_t* n_received);
+
 /* Largest batch fmq_partition_by_owner_noalloc accepts (events). */
 #define FMQ_NOALLOC_MAX_EVENTS 4194304
 

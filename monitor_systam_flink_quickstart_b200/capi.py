@@ -160,6 +160,11 @@ def _declare(lib, p: str, has_mem: bool = True):
         sig("snapshot_size", [vp, psz])
         sig("snapshot", [vp, vp, sz, psz])
         sig("restore", [vp, vp, sz])
+        sig("exchange_alloc", [vp, vp])
+        sig("exchange_base", [vp], vp)
+        sig("exchange_attach", [vp, i32, i32, C.POINTER(vp)])
+        sig("exchange_split", [vp, vp, vp, vp, sz, i32, vp])
+        sig("exchange_pull_push", [vp, i32, vp, i64, psz])
         sig("table_ptr", [vp], vp)
         sig("exchange_ptr", [vp], vp)
         sig("ipc_export", [vp, vp])
@@ -485,6 +490,31 @@ class Engine(EngineBase):
 
     def retire(self):
         self._check(self._lib.fmq_retire(self._h))
+
+    # ---- peer-pull keyBy exchange ---------------------------------------------------------------
+    def exchange_alloc(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        self._check(self._lib.fmq_exchange_alloc(self._h, buf))
+        return buf.raw
+
+    @property
+    def exchange_base(self) -> int:
+        return self._lib.fmq_exchange_base(self._h) or 0
+
+    def exchange_attach(self, rank: int, world: int, bases):
+        arr = (C.c_void_p * world)(*[C.c_void_p(b) for b in bases])
+        self._check(self._lib.fmq_exchange_attach(self._h, rank, world, arr))
+
+    def exchange_split(self, ts, key, val, parity: int, world: int) -> np.ndarray:
+        counts = np.zeros(world, np.uint64)
+        self._check(self._lib.fmq_exchange_split(self._h, _ptr(ts), _ptr(key), _ptr(val), len(ts), parity, counts.ctypes.data))
+        return counts
+
+    def exchange_pull_push(self, parity: int, matrix: np.ndarray, watermark_after: int = FMQ_WM_AUTO) -> int:
+        m = np.ascontiguousarray(matrix, dtype=np.uint64)
+        n = C.c_size_t(0)
+        self._check(self._lib.fmq_exchange_pull_push(self._h, parity, m.ctypes.data, watermark_after, C.byref(n)))
+        return n.value
 
     def partition_by_owner(self, ts, key, val, world: int, ts_out, key_out, val_out) -> np.ndarray:
         counts = np.zeros(world, np.uint64)

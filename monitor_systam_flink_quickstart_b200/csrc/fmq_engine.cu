@@ -60,6 +60,8 @@ struct fmq_handle {
     const Acc32* peer_acc[FMQ_MAX_PEERS] = {};
     i64* d_xchg = nullptr;               // 4 x int64 exchange buffer for the all-reduce of the batch scalars
     size_t pending_n = 0;
+    // peer-pull keyBy exchange: two parities x three columns of owner-bucketed events, mapped by every peer
+    char* d_xsend = nullptr; const char* peer_xsend[FMQ_MAX_PEERS] = {}; int x_world = 0, x_rank = 0;
     // second set of fired / window-alert / event-alert columns + a copy-out stream, for overlapped polls
     void* alt_out[12] = {}; cudaStream_t out_stream = nullptr; cudaEvent_t ev_out = nullptr; bool out_pending = false;
     i64* lt_ts = nullptr; u64 *lt_key = nullptr, *lt_val = nullptr; u64 lt_cap = 0; size_t cur_late = 0;
@@ -99,7 +101,7 @@ static void free_all(fmq_handle* h) {
     void* ptrs[] = {h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
                     h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
-                    h->d_pack[0], h->d_pack[1], h->kr_lead, h->kr_k, h->kr_fl, h->kr_in_c, h->kr_mk, h->kr_mb, h->kr_in_mk, h->kr_in_mb, h->d_counts, h->d_tiles, h->d_xchg, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad,
+                    h->d_pack[0], h->d_pack[1], h->kr_lead, h->kr_k, h->kr_fl, h->kr_in_c, h->kr_mk, h->kr_mb, h->kr_in_mk, h->kr_in_mb, h->d_counts, h->d_tiles, h->d_xchg, h->d_xsend, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad,
                     h->ml_pane[0], h->ml_pane[1], h->ml_slot[0], h->ml_slot[1], h->ml_val[0], h->ml_val[1], h->mw_items[0], h->mw_items[1], h->mw_vals,
                     h->md_key, h->md_wend, h->md_val, h->lt_ts, h->lt_key, h->lt_val};
     for (void* p : ptrs) if (p) cudaFree(p);
@@ -933,6 +935,68 @@ int32_t fmq_partition_by_owner(fmq_handle* h, const int64_t* ts, const uint64_t*
 
 }  // extern "C"
 
+// ---- keyBy exchange over NVLink peer memory ("peer pull") ----------------------------------------
+// The all-to-all of the reference's keyBy (BandwidthMonitorWithEventTime.java:45) without a send side:
+// every rank splits its slice into owner buckets inside a buffer all peers have mapped (CUDA IPC), the
+// ranks exchange the world x world bucket-size matrix, and each rank then PULLS its buckets straight
+// out of the peers' buffers into its own staging columns (device-to-device copies over NVLink, in
+// source-rank order so that per-key arrival order survives) and runs the operator chain on them.
+// Two parities of send buffers: a peer may already split batch b+1 while this rank still reads batch b.
+extern "C" {
+static size_t xsend_col_bytes(const fmq_handle* h) { return h->max_batch * 8; }
+int32_t fmq_exchange_alloc(fmq_handle* h, void* handle64) {
+    if (!h || !handle64) return FMQ_ERR_BAD_ARG;
+    CU(h, cudaSetDevice(h->device));
+    if (!h->d_xsend) CU(h, cudaMalloc((void**)&h->d_xsend, 6 * xsend_col_bytes(h)));
+    cudaIpcMemHandle_t ih;
+    CU(h, cudaIpcGetMemHandle(&ih, h->d_xsend));
+    memcpy(handle64, &ih, 64);
+    return FMQ_OK;
+}
+void* fmq_exchange_base(fmq_handle* h) { return h ? (void*)h->d_xsend : nullptr; }
+int32_t fmq_exchange_attach(fmq_handle* h, int32_t rank, int32_t world, const void* const* peer_bases) {
+    if (!h || !peer_bases) return FMQ_ERR_BAD_ARG;
+    if (world < 1 || world > FMQ_MAX_PEERS || rank < 0 || rank >= world) return set_err(h, FMQ_ERR_BAD_ARG, "need 1 <= world <= 8 and 0 <= rank < world");
+    if (!h->d_xsend) return set_err(h, FMQ_ERR_BAD_ARG, "call fmq_exchange_alloc first");
+    for (int r = 0; r < world; ++r) {
+        if (r != rank && !peer_bases[r]) return set_err(h, FMQ_ERR_BAD_ARG, "null peer buffer");
+        h->peer_xsend[r] = (r == rank) ? h->d_xsend : static_cast<const char*>(peer_bases[r]);
+    }
+    h->x_world = world; h->x_rank = rank;
+    return FMQ_OK;
+}
+int32_t fmq_exchange_split(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val, size_t n, int32_t parity, uint64_t* counts) {
+    if (!h || !counts) return FMQ_ERR_BAD_ARG;
+    if (h->x_world < 1) return set_err(h, FMQ_ERR_BAD_ARG, "call fmq_exchange_attach first");
+    char* base = h->d_xsend + (size_t)(parity & 1) * 3 * xsend_col_bytes(h);
+    return fmq_partition_by_owner(h, ts, key, val, n, (uint32_t)h->x_world, (int64_t*)base, (uint64_t*)(base + xsend_col_bytes(h)),
+                                  (void*)(base + 2 * xsend_col_bytes(h)), counts);
+}
+int32_t fmq_exchange_pull_push(fmq_handle* h, int32_t parity, const uint64_t* matrix, int64_t watermark_after, size_t* n_received) {
+    if (!h || !matrix) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (h->x_world < 1) return set_err(h, FMQ_ERR_BAD_ARG, "call fmq_exchange_attach first");
+    const int W = h->x_world, me = h->x_rank;
+    size_t n_recv = 0;
+    for (int s_ = 0; s_ < W; ++s_) n_recv += matrix[(size_t)s_ * W + me];
+    if (n_recv > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "received more events than fmq_config.max_batch");
+    CU(h, cudaSetDevice(h->device));
+    const size_t col = xsend_col_bytes(h), poff = (size_t)(parity & 1) * 3 * col;
+    void* dst_cols[3] = {h->d_in_ts, h->d_in_key, h->d_in_val};
+    size_t dst_off = 0;
+    for (int src = 0; src < W; ++src) {                                   // source-rank order = arrival order per key
+        const size_t cnt = matrix[(size_t)src * W + me];
+        size_t start = 0;
+        for (int d = 0; d < me; ++d) start += matrix[(size_t)src * W + d];    // buckets are laid out by destination
+        if (cnt) for (int c = 0; c < 3; ++c)
+            CU(h, cudaMemcpyAsync((char*)dst_cols[c] + dst_off * 8, h->peer_xsend[src] + poff + c * col + start * 8, cnt * 8, cudaMemcpyDefault, h->stream));
+        dst_off += cnt;
+    }
+    if (n_received) *n_received = n_recv;
+    return fmq_push_batch(h, (const int64_t*)h->d_in_ts, (const uint64_t*)h->d_in_key, h->d_in_val, n_recv, watermark_after, FMQ_MEM_DEVICE);
+}
+}  // extern "C"
+
 // ---- owner split for callers that must not allocate ------------------------------------------------
 // Same stable multi-split as fmq_partition_by_owner, but its scratch (the per-chunk digit counters
 // and the scan's tile sums) lives in a fixed file-scope device array instead of a handle's
@@ -1006,4 +1070,3 @@ extern "C" int32_t fmq_partition_by_owner_noalloc(int32_t device, void* stream_,
     for (uint32_t w = 0; w < world; ++w) counts[w] = (w + 1 < world ? starts[w + 1] : (u32)n) - starts[w];
     return FMQ_OK;
 }
-

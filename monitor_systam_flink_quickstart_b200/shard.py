@@ -194,3 +194,55 @@ class CombinerOperator:
             self.engine.fire_global(wm)
             dist.all_reduce(self._token, group=self.group)
             self.engine.retire()
+
+
+class PeerPullOperator:
+    """keyBy exchange over NVLink peer memory (include/fmq_b200.h, "peer pull"): same semantics as
+    :class:`ShardedOperator` (every operator, both key modes, per-key arrival order), but the events are
+    never sent: each rank splits into a buffer its peers have mapped through CUDA IPC, ONE collective
+    carries the bucket sizes and the max timestamp, and every rank copies its own buckets straight out
+    of the peers' memory before running its operator chain."""
+
+    def __init__(self, engine, rank: int, world: int, bound_ms: int, group=None):
+        import torch
+        import torch.distributed as dist
+        self.dist, self.engine, self.rank, self.world, self.group, self.bound = dist, engine, rank, world, group, bound_ms
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        blobs = [None] * world
+        dist.all_gather_object(blobs, engine.exchange_alloc(), group=group)
+        bases = [engine.exchange_base if r == rank else engine.ipc_open(blobs[r]) for r in range(world)]
+        engine.exchange_attach(rank, world, bases)
+        self._ext = torch.cuda.ExternalStream(engine.stream, device=self.dev)
+        self._mine = torch.zeros(world + 1, dtype=torch.int64, device=self.dev)
+        self._all = torch.zeros(world * (world + 1), dtype=torch.int64, device=self.dev)
+        self.parity = 0
+        self.cur_max_ts = I64_MIN + bound_ms
+        self.wm = I64_MIN
+        self.dense = engine.cfg.key_mode == capi.FMQ_KEYS_DENSE
+        dist.barrier(group=group)
+
+    def global_keys(self, local_keys: np.ndarray) -> np.ndarray:
+        return local_keys * np.uint64(self.world) + np.uint64(self.rank) if self.dense else local_keys
+
+    def process_batch(self, ts, key, val, watermark_after: Optional[int] = None) -> int:
+        import torch
+        dist, W = self.dist, self.world
+        with torch.cuda.stream(self._ext):
+            counts = self.engine.exchange_split(ts, key, val, self.parity, W)          # synchronises the engine stream
+            local_max = int(ts.max().item()) if ts.numel() else I64_MIN
+            self._mine.copy_(torch.as_tensor(np.append(counts.astype(np.int64), local_max)), non_blocking=False)
+            dist.all_gather_into_tensor(self._all, self._mine, group=self.group)        # sizes + max ts; also "all splits done"
+            allv = self._all.cpu().numpy().reshape(W, W + 1)
+            matrix = allv[:, :W].astype(np.uint64)
+            if watermark_after is None:
+                self.cur_max_ts = max(self.cur_max_ts, int(allv[:, W].max()))
+                pot = self.cur_max_ts - self.bound
+                if pot >= self.wm:
+                    self.wm = pot
+                watermark_after = self.wm
+            n = self.engine.exchange_pull_push(self.parity, matrix, watermark_after)
+        self.parity ^= 1
+        return n
+
+    def flush(self, wm: int = capi.FMQ_WM_FINAL):
+        self.engine.flush(wm)

@@ -222,3 +222,102 @@ def test_two_gpu_combiner_over_nvlink_equals_oracle():
     assert_fired_equal(cat("fired", capi.Fired, ("key", "window_end", "count", "sum", "min", "max")), ref.poll_fired())
     assert_events_equal(cat("ealerts", capi.EventRows, ("ts", "key", "val")), ref.poll_event_alerts())
     assert sum(r["counters"]["late_dropped"] for r in res) == ref.counters()["late_dropped"]
+
+
+# ---- peer-pull keyBy exchange -------------------------------------------------------------------------
+@pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
+def test_peer_pull_exchange_emulated_ranks_on_one_gpu(key_mode):
+    """3 engines in one process play the ranks; their send buffers are attached to each other as plain
+    device pointers and the size matrix is assembled by hand.  Every operator runs behind the exchange
+    (windows, filter, keyed ValueState, median); union of the ranks' outputs == oracle."""
+    import torch
+    from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy, generate_torch
+    from oracle_lib import sort_walerts
+    world = 3
+    kw = dict(KW, key_mode=key_mode, rolling_max_enabled=0, median_log_capacity=1 << 18)
+    engs = [capi.Engine(**kw) for _ in range(world)]
+    for e in engs:
+        e.exchange_alloc()
+    for r, e in enumerate(engs):
+        e.exchange_attach(r, world, [x.exchange_base for x in engs])
+    spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
+    ref = OracleEngine(**{k: v for k, v in kw.items()})
+    cur_max, wm, bound, b = -(2 ** 63) + KW["max_out_of_orderness_ms"], -(2 ** 63), KW["max_out_of_orderness_ms"], 9001
+    for i in range(5):
+        cols = [generate_torch(spec, (i * world + r) * b, b, device="cuda:0") for r in range(world)]
+        torch.cuda.synchronize()
+        matrix = np.stack([e.exchange_split(*cols[r], i & 1, world) for r, e in enumerate(engs)])
+        cur_max = max(cur_max, max(int(c[0].max()) for c in cols))
+        wm = max(wm, cur_max - bound)
+        got = [e.exchange_pull_push(i & 1, matrix, wm) for e in engs]
+        assert sum(got) == world * b and got == matrix.sum(axis=0).tolist()
+        for e in engs:
+            e.synchronize()
+        parts = [generate_numpy(spec, (i * world + r) * b, b) for r in range(world)]
+        ref.push_batch(*[np.concatenate([p[j] for p in parts]) for j in range(3)])
+    for e in engs:
+        e.flush()
+    ref.flush()
+
+    def gk(r, keys):
+        return keys * np.uint64(world) + np.uint64(r) if key_mode == capi.FMQ_KEYS_DENSE else keys
+    fired, cal, med = [], [], []
+    for r, e in enumerate(engs):
+        f = e.poll_fired(); f.key = gk(r, f.key); fired.append(f)
+        c = e.poll_consec_alerts(); c.key = gk(r, c.key); cal.append(c)
+        m = e.poll_medians(); m.key = gk(r, m.key); med.append(m)
+    cat = lambda parts, cls, fields: cls(*[np.concatenate([getattr(p, f) for p in parts]) for f in fields])  # noqa: E731
+    assert_fired_equal(cat(fired, capi.Fired, ("key", "window_end", "count", "sum", "min", "max")), ref.poll_fired())
+    assert_events_equal(cat(cal, capi.EventRows, ("ts", "key", "val")), ref.poll_consec_alerts())
+    a, w = sort_walerts(cat(med, capi.WindowAlerts, ("key", "window_end", "value"))), sort_walerts(ref.poll_medians())
+    np.testing.assert_array_equal(a.key, w.key); np.testing.assert_array_equal(a.value.view(np.uint64), w.value.view(np.uint64))
+    assert sum(e.counters()["late_dropped"] for e in engs) == ref.counters()["late_dropped"] > 0
+
+
+def _peer_pull_worker(rank, world, port, outdir, key_mode):
+    import torch
+    import torch.distributed as dist
+    from monitor_systam_flink_quickstart_b200.shard import PeerPullOperator
+    from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_torch
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
+    eng = capi.Engine(device=rank, key_mode=key_mode, **KW)
+    op = PeerPullOperator(eng, rank, world, KW["max_out_of_orderness_ms"])
+    for b in range(NB):
+        ts, key, val = generate_torch(spec, (b * world + rank) * B, B, device=f"cuda:{rank}")
+        torch.cuda.synchronize()
+        op.process_batch(ts, key, val)
+        eng.synchronize()
+    op.flush()
+    res = dict(fired=eng.poll_fired(), ealerts=eng.poll_event_alerts(), calerts=eng.poll_consec_alerts(), counters=eng.counters())
+    for name in ("fired", "ealerts", "calerts"):
+        res[name].key = op.global_keys(res[name].key)
+    pickle.dump(res, open(os.path.join(outdir, f"r{rank}.pkl"), "wb"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
+def test_two_gpu_peer_pull_equals_oracle(key_mode):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy
+    world, port = 2, 29800 + os.getpid() % 2000 + key_mode
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_peer_pull_worker, args=(world, port, d, key_mode), nprocs=world, join=True)
+        res = [pickle.load(open(os.path.join(d, f"r{r}.pkl"), "rb")) for r in range(world)]
+    spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
+    ref = OracleEngine(**{k: v for k, v in KW.items()})
+    for b in range(NB):
+        parts = [generate_numpy(spec, (b * world + r) * B, B) for r in range(world)]
+        ref.push_batch(*[np.concatenate([p[i] for p in parts]) for i in range(3)])
+    ref.flush()
+    cat = lambda name, cls, fields: cls(*[np.concatenate([getattr(r[name], f) for r in res]) for f in fields])  # noqa: E731
+    assert_fired_equal(cat("fired", capi.Fired, ("key", "window_end", "count", "sum", "min", "max")), ref.poll_fired())
+    assert_events_equal(cat("ealerts", capi.EventRows, ("ts", "key", "val")), ref.poll_event_alerts())
+    assert_events_equal(cat("calerts", capi.EventRows, ("ts", "key", "val")), ref.poll_consec_alerts())
+    assert sum(r["counters"]["late_dropped"] for r in res) == ref.counters()["late_dropped"]
