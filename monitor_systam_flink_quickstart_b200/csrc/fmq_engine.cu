@@ -345,7 +345,9 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         const bool fast_geom = !c.window_enabled || (h->g.slide32 != 0 && (u64)h->ring * h->g.slide32 < 0x100000000ull);
         const bool dense = c.key_mode == FMQ_KEYS_DENSE;
         if (c.window_enabled && fast_geom) {
-            auto kfn = dense ? ingest_fast_kernel<V, true> : ingest_fast_kernel<V, false>;
+            const bool extras = h->ml_cap > 0 || h->lt_cap > 0;
+            auto kfn = dense ? (extras ? ingest_fast_kernel<V, true, true> : ingest_fast_kernel<V, true, false>)
+                             : (extras ? ingest_fast_kernel<V, false, true> : ingest_fast_kernel<V, false, false>);
             CU(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, INGEST_SMEM_BYTES));
             kfn<<<(unsigned)blocks, INGEST_THREADS, INGEST_SMEM_BYTES, h->stream>>>(a);
             LAUNCHED(h, "ingest_fast_kernel");

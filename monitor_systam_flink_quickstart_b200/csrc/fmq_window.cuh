@@ -224,7 +224,7 @@ struct IngestConst {
 };
 
 // One tile of the fast path: the four events held by this thread.  Called by every thread of the block.
-template <typename V, bool DENSE>
+template <typename V, bool DENSE, bool EXTRAS>      // EXTRAS: late side output and/or the median value log are enabled
 __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
                                             const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 in_mask,
                                             bool do_filter = true) {
@@ -281,7 +281,7 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
         slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
     }
     // ---- late side output (chapter3/README.md:213-228, option 3: "a separate stream of the late data") ----
-    if (a.lt_cap) {
+    if (EXTRAS && a.lt_cap) {
         u64 row = block_append<INGEST_THREADS>(__popc(late_mask), &st->n_late, a.lt_cap, st);
         if (row != ~0ull) {
 #pragma unroll
@@ -290,7 +290,7 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
         }
     }
     // ---- N3: non-incremental window functions keep every value (ComputeCpuMiddle.java:36-38) ----
-    if (a.mlog_enabled) {
+    if (EXTRAS && a.mlog_enabled) {
         u64 row = block_append<INGEST_THREADS>(__popc(vmask), &st->n_mlog, a.ml_cap, st);
         if (row != ~0ull) {
 #pragma unroll
@@ -300,7 +300,7 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
     }
 }
 
-template <typename V, bool DENSE>
+template <typename V, bool DENSE, bool EXTRAS>
 __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_fast_kernel(const __grid_constant__ IngestArgs a) {
     extern __shared__ __align__(128) unsigned char ingest_smem[];
     __shared__ __align__(8) u64 bars[INGEST_STAGES];
@@ -393,7 +393,7 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
             }
             r.nea += __popc(hits);
         }
-        ingest_tile<V, DENSE>(a, st, k, r, ts_, key_, vb_, 0xFu, false);
+        ingest_tile<V, DENSE, EXTRAS>(a, st, k, r, ts_, key_, vb_, 0xFu, false);
     }
     // ragged tail (and unaligned columns): direct 8-byte loads
     const size_t tail_tiles = (a.n - full_tiles * INGEST_TILE + INGEST_TILE - 1) / INGEST_TILE;
@@ -401,7 +401,7 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
         const size_t i = (full_tiles + t) * INGEST_TILE + (size_t)threadIdx.x * INGEST_EPT;
         i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; u32 in_mask;
         load_events<V>(a, i, ts_, key_, vb_, in_mask);
-        ingest_tile<V, DENSE>(a, st, k, r, ts_, key_, vb_, in_mask);
+        ingest_tile<V, DENSE, EXTRAS>(a, st, k, r, ts_, key_, vb_, in_mask);
     }
     // ---- per-warp reduction of the batch scalars, one atomic each per warp ----
     r.nea = warp_sum_u64(r.nea);
