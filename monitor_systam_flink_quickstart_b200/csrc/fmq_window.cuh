@@ -90,6 +90,48 @@ __device__ __forceinline__ void accumulate_pair_lean(Acc32* __restrict__ acc, bo
     }
 }
 
+// Per-block cache of heavy-hitter cells (skewed keys): groups of >= HOT_GROUP lanes of one warp that hit
+// the same cell are accumulated in shared memory and written to the global table ONCE per block, at
+// the end of the kernel, instead of once per warp round.
+constexpr int HOT_SLOTS = 64;
+constexpr int HOT_GROUP = 3;
+struct HotTable { u64 idx[HOT_SLOTS]; u64 cnt[HOT_SLOTS], sum[HOT_SLOTS], mx[HOT_SLOTS], mn[HOT_SLOTS]; };
+
+__device__ __forceinline__ void hot_init(HotTable* t) {
+    for (int i = threadIdx.x; i < HOT_SLOTS; i += blockDim.x) { t->idx[i] = ~0ull; t->cnt[i] = 0; t->sum[i] = 0; t->mx[i] = 0; t->mn[i] = 0; }
+}
+// true if the contribution was absorbed by the block's table
+template <typename V>
+__device__ __forceinline__ bool hot_absorb(HotTable* t, u64 idx, u64 cntb, u64 sumb, u64 mx, u64 mn) {
+    u32 hsh = (u32)((idx * 0x9E3779B97F4A7C15ull) >> 58);
+    for (int probe = 0; probe < 4; ++probe, hsh = (hsh + 1) & (HOT_SLOTS - 1)) {
+        u64 k = t->idx[hsh];
+        if (k == ~0ull) k = atomicCAS(&t->idx[hsh], ~0ull, idx), k = (k == ~0ull) ? idx : k;
+        if (k != idx) continue;
+        if constexpr (IsF64<V>::value) {
+            atomicAdd(reinterpret_cast<double*>(&t->cnt[hsh]), __longlong_as_double((i64)cntb));
+            atomicAdd(reinterpret_cast<double*>(&t->sum[hsh]), __longlong_as_double((i64)sumb));
+        } else { atomicAdd(&t->cnt[hsh], cntb); atomicAdd(&t->sum[hsh], sumb); }
+        atomicMax(&t->mx[hsh], mx); atomicMax(&t->mn[hsh], mn);
+        return true;
+    }
+    return false;
+}
+template <typename V>
+__device__ __forceinline__ void hot_flush(const HotTable* t, Acc32* __restrict__ acc, u32 agg_mask) {
+    for (int i = threadIdx.x; i < HOT_SLOTS; i += blockDim.x) {
+        const u64 idx = t->idx[i];
+        if (idx == ~0ull) continue;
+        Acc32* a = acc + idx;
+        if constexpr (IsF64<V>::value) {
+            atomicAdd(reinterpret_cast<double*>(&a->cnt), __longlong_as_double((i64)t->cnt[i]));
+            atomicAdd(reinterpret_cast<double*>(&a->sum), __longlong_as_double((i64)t->sum[i]));
+        } else { atomicAdd(&a->cnt, t->cnt[i]); atomicAdd(&a->sum, t->sum[i]); }
+        if (agg_mask & 8u) atomicMax(&a->mx, t->mx[i]);
+        if (agg_mask & 4u) atomicMax(&a->mn, t->mn[i]);
+    }
+}
+
 // A5 for one event per lane.
 // combine = true: lanes of a warp that hit the SAME cell are combined first (the group's lowest lane
 // carries the whole group's contribution).  With skewed keys (Zipf(1.2): one key gets 18 % of the
@@ -98,7 +140,8 @@ __device__ __forceinline__ void accumulate_pair_lean(Acc32* __restrict__ acc, bo
 // exchange cost +25 %, so the mode is chosen per batch from a sample (`sample` = this warp measures):
 // dup[0] += lanes looked at, dup[1] += lanes that share their cell with another lane.
 template <typename V>
-__device__ __forceinline__ void accumulate_pair(Acc32* __restrict__ acc, bool valid, u64 idx, V val, u32 agg_mask, bool combine, bool sample, u32 (&dup)[2]) {
+__device__ __forceinline__ void accumulate_pair(Acc32* __restrict__ acc, bool valid, u64 idx, V val, u32 agg_mask, bool combine, bool sample, u32 (&dup)[2],
+                                                HotTable* hot) {
     if (!combine && !sample) { accumulate_pair_lean<V>(acc, valid, idx, val, agg_mask); return; }
     const unsigned lane = threadIdx.x & 31;
     const unsigned m = __match_any_sync(0xffffffffu, valid ? idx : (0xFFFF000000000000ull | lane));
@@ -109,15 +152,24 @@ __device__ __forceinline__ void accumulate_pair(Acc32* __restrict__ acc, bool va
     u64 cntb, sumb = vbits, mx = Codec<V>::enc_max(val), mn = Codec<V>::enc_min(val);
     const int leader = __ffs(m) - 1;
     u64 c_acc = 0, s_acc = 0, mx_acc = 0, mn_acc = 0; double cd = 0.0, sd = 0.0;
-    for (int i = 0; i < 32; ++i) {
-        const u64 s_i = __shfl_sync(0xffffffffu, sumb, i), mx_i = __shfl_sync(0xffffffffu, mx, i), mn_i = __shfl_sync(0xffffffffu, mn, i);
-        if ((m >> i) & 1u) {
+    // every lane walks the members of ITS group (lowest lane first: fixed order, deterministic double sums);
+    // the trip count is the largest group of the warp, not 32
+    const int gmax = __reduce_max_sync(0xffffffffu, __popc(m));
+    unsigned rem = m;
+    for (int it = 0; it < gmax; ++it) {
+        const bool use = rem != 0;
+        const int src = use ? __ffs(rem) - 1 : (int)lane;
+        rem &= rem - 1;
+        const u64 s_i = __shfl_sync(0xffffffffu, sumb, src), mx_i = __shfl_sync(0xffffffffu, mx, src), mn_i = __shfl_sync(0xffffffffu, mn, src);
+        if (use) {
             if constexpr (IsF64<V>::value) { cd += 1.0; sd += __longlong_as_double((i64)s_i); } else { c_acc += 1; s_acc += s_i; }
             mx_acc = mx_i > mx_acc ? mx_i : mx_acc; mn_acc = mn_i > mn_acc ? mn_i : mn_acc;
         }
     }
     if constexpr (IsF64<V>::value) { cntb = (u64)__double_as_longlong(cd); sumb = (u64)__double_as_longlong(sd); } else { cntb = c_acc; sumb = s_acc; }
-    accumulate_pair_raw<V>(acc, valid && (int)lane == leader, idx, cntb, sumb, mx_acc, mn_acc, agg_mask);
+    bool mine = valid && (int)lane == leader;
+    if (mine && __popc(m) >= HOT_GROUP && hot_absorb<V>(hot, idx, cntb, sumb, mx_acc, mn_acc)) mine = false;   // heavy hitter: once per block
+    accumulate_pair_raw<V>(acc, mine, idx, cntb, sumb, mx_acc, mn_acc, agg_mask);
 }
 
 constexpr int INGEST_THREADS = 256;
@@ -227,7 +279,7 @@ struct IngestConst {
 template <typename V, bool DENSE, bool EXTRAS>      // EXTRAS: late side output and/or the median value log are enabled
 __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
                                             const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 in_mask,
-                                            bool do_filter = true) {
+                                            HotTable* hot, bool do_filter = true) {
     u32 ok_mask = 0;
 #pragma unroll
     for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
@@ -277,7 +329,7 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
         }
         const u64 idx = (u64)ring_[e] * a.g.capacity + slot;
         V v; memcpy(&v, &vb_[e], 8);
-        accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask, k.combine, e == 0 && threadIdx.x < 32, r.dup);
+        accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask, k.combine, e == 0 && threadIdx.x < 32, r.dup, hot);
         slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
     }
     // ---- late side output (chapter3/README.md:213-228, option 3: "a separate stream of the late data") ----
@@ -306,6 +358,7 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
     __shared__ __align__(8) u64 bars[INGEST_STAGES];
     __shared__ u32 f_wsum[INGEST_THREADS / 32];
     __shared__ u64 f_base;
+    __shared__ HotTable hot_tab;
     DevState* st = a.st;
     if (!ingest_fast_ok(st, a.g)) return;                        // the generic kernel handles this batch
     IngestConst k;
@@ -318,6 +371,7 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
     k.span = (u64)(a.g.ring_mask + 1) * k.slide;                 // first d that falls outside the ring (< 2^32)
     k.nbuckets = a.g.capacity >> 2;
     IngestRun r;
+    if (k.combine) hot_init(&hot_tab);                           // ordered before its first use by the barrier after the prologue
 
     const V* __restrict__ val = static_cast<const V*>(a.val);
     // bulk copies need 16-byte aligned, whole tiles; the (at most one) ragged tile goes the direct way
@@ -393,7 +447,7 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
             }
             r.nea += __popc(hits);
         }
-        ingest_tile<V, DENSE, EXTRAS>(a, st, k, r, ts_, key_, vb_, 0xFu, false);
+        ingest_tile<V, DENSE, EXTRAS>(a, st, k, r, ts_, key_, vb_, 0xFu, &hot_tab, false);
     }
     // ragged tail (and unaligned columns): direct 8-byte loads
     const size_t tail_tiles = (a.n - full_tiles * INGEST_TILE + INGEST_TILE - 1) / INGEST_TILE;
@@ -401,8 +455,9 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
         const size_t i = (full_tiles + t) * INGEST_TILE + (size_t)threadIdx.x * INGEST_EPT;
         i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; u32 in_mask;
         load_events<V>(a, i, ts_, key_, vb_, in_mask);
-        ingest_tile<V, DENSE, EXTRAS>(a, st, k, r, ts_, key_, vb_, in_mask);
+        ingest_tile<V, DENSE, EXTRAS>(a, st, k, r, ts_, key_, vb_, in_mask, &hot_tab);
     }
+    if (k.combine && a.window_enabled) { __syncthreads(); hot_flush<V>(&hot_tab, a.acc, a.g.agg_mask); }
     // ---- per-warp reduction of the batch scalars, one atomic each per warp ----
     r.nea = warp_sum_u64(r.nea);
     for (int o = 16; o > 0; o >>= 1) r.err |= __shfl_xor_sync(0xffffffffu, r.err, o);
