@@ -302,20 +302,21 @@ static int sort_items(fmq_handle* h, u64* const* buf, size_t n, u32 key_bits, Ke
         const size_t smem = (size_t)8 * (1u << bits) * 4;
         auto launch = [&](auto hist, auto scat) -> int {
             CU(h, cudaFuncSetAttribute(hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            CU(h, cudaFuncSetAttribute(scat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             hist<<<nblocks, 256, smem, h->stream>>>(buf[*cur], nullptr, n, nchunks, shift, h->d_counts, keyfn); LAUNCHED(h, "ps_pass_kernel(hist)");
             int s_ = exclusive_scan_counts(h, (size_t)(1u << bits) * nchunks); if (s_) return s_;
-            scat<<<nblocks, 256, smem, h->stream>>>(buf[*cur], buf[*cur ^ 1], n, nchunks, shift, h->d_counts, keyfn); LAUNCHED(h, "ps_pass_kernel(scatter)");
+            const size_t tsmem = (size_t)PS_CHUNK * 8 + (size_t)(1u << bits) * 8 + (size_t)8 * (1u << bits) * 2 + (size_t)PS_CHUNK * 2;
+            CU(h, cudaFuncSetAttribute(scat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
+            scat<<<nchunks, 256, tsmem, h->stream>>>(buf[*cur], buf[*cur ^ 1], n, nchunks, shift, h->d_counts, keyfn); LAUNCHED(h, "ps_scatter_tile_kernel");
             return FMQ_OK;
         };
         int s_ = FMQ_OK;
         switch (bits) {
-            case 6: s_ = launch(ps_pass_kernel<6, false, KeyFn>, ps_pass_kernel<6, true, KeyFn>); break;
-            case 7: s_ = launch(ps_pass_kernel<7, false, KeyFn>, ps_pass_kernel<7, true, KeyFn>); break;
-            case 8: s_ = launch(ps_pass_kernel<8, false, KeyFn>, ps_pass_kernel<8, true, KeyFn>); break;
-            case 9: s_ = launch(ps_pass_kernel<9, false, KeyFn>, ps_pass_kernel<9, true, KeyFn>); break;
-            case 10: s_ = launch(ps_pass_kernel<10, false, KeyFn>, ps_pass_kernel<10, true, KeyFn>); break;
-            default: s_ = launch(ps_pass_kernel<11, false, KeyFn>, ps_pass_kernel<11, true, KeyFn>); break;
+            case 6: s_ = launch(ps_pass_kernel<6, false, KeyFn>, ps_scatter_tile_kernel<6, KeyFn>); break;
+            case 7: s_ = launch(ps_pass_kernel<7, false, KeyFn>, ps_scatter_tile_kernel<7, KeyFn>); break;
+            case 8: s_ = launch(ps_pass_kernel<8, false, KeyFn>, ps_scatter_tile_kernel<8, KeyFn>); break;
+            case 9: s_ = launch(ps_pass_kernel<9, false, KeyFn>, ps_scatter_tile_kernel<9, KeyFn>); break;
+            case 10: s_ = launch(ps_pass_kernel<10, false, KeyFn>, ps_scatter_tile_kernel<10, KeyFn>); break;
+            default: s_ = launch(ps_pass_kernel<11, false, KeyFn>, ps_scatter_tile_kernel<11, KeyFn>); break;
         }
         if (s_) return s_;
         *cur ^= 1;

@@ -90,6 +90,102 @@ __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in
     if (!SCATTER) for (u32 d = lane; d < NB; d += 32) counts[(size_t)d * nchunks + chunk] = bins[d];
 }
 
+// Scatter half of a radix pass, one BLOCK per chunk of PS_CHUNK items: the chunk is sorted by digit in
+// shared memory first (stable: warp w ranks its 512 consecutive items round by round, a cross-warp
+// scan per digit orders the warps) and then copied out position by position, so consecutive threads
+// write consecutive addresses of a digit's run.  The per-warp-chunk version above writes every item as
+// a lone 8-byte store; ncu showed those partial-sector writes congesting the memory system
+// (782 MB of DRAM traffic for 268 MB of payload, 455 us per pass of 2^24 items).
+constexpr int PS_IPT = PS_CHUNK / 256;          // items per thread
+
+// Lanes of `am` holding the same BITS-bit digit, from BITS ballots.  MATCH.ANY does this in one
+// instruction but was measured at ~150 cycles per warp instruction per SM on B200 (it bounded both
+// scatter kernels at ~0.3 ms per pass of 2^24 items); votes are cheap.
+template <int BITS>
+__device__ __forceinline__ unsigned match_digit(unsigned am, u32 d) {
+    unsigned m = am;
+#pragma unroll
+    for (int b = 0; b < BITS; ++b) {
+        const unsigned v = __ballot_sync(am, (d >> b) & 1u);
+        m &= ((d >> b) & 1u) ? v : ~v;
+    }
+    return m;
+}
+template <int BITS, typename KeyFn>
+__global__ void __launch_bounds__(256) ps_scatter_tile_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t n, u32 nchunks, u32 shift,
+                                                              const u32* __restrict__ offsets, KeyFn keyfn) {
+    constexpr u32 NB = 1u << BITS;
+    extern __shared__ __align__(16) unsigned char ps_tile_smem[];
+    u64* items_s = reinterpret_cast<u64*>(ps_tile_smem);                         // [PS_CHUNK]
+    u32* goff = reinterpret_cast<u32*>(items_s + PS_CHUNK);                      // [NB] global offset of (digit, this chunk)
+    u32* dbase = goff + NB;                                                      // [NB] start of the digit inside the sorted chunk
+    unsigned short* wcnt = reinterpret_cast<unsigned short*>(dbase + NB);        // [8][NB] per-warp counts, then exclusive prefixes
+    unsigned short* dig_s = wcnt + 8 * NB;                                       // [PS_CHUNK] digit of every sorted position
+    __shared__ u32 scan_ws[8];
+    const u32 tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+    const u32 chunk = blockIdx.x;
+    const size_t lo = (size_t)chunk * PS_CHUNK;
+    const size_t hi = (lo + PS_CHUNK < n) ? lo + PS_CHUNK : n;
+    for (u32 i = tid; i < 8 * NB; i += 256) wcnt[i] = 0;
+    for (u32 d = tid; d < NB; d += 256) goff[d] = offsets[(size_t)d * nchunks + chunk];
+    __syncthreads();
+    // phase 1: rank inside the warp's 512 consecutive items, in order
+    u64 it[PS_IPT]; unsigned short dg[PS_IPT], rk[PS_IPT];
+#pragma unroll
+    for (int r = 0; r < PS_IPT; ++r) { const size_t i = lo + (size_t)w * (PS_CHUNK / 8) + r * 32 + lane; it[r] = i < hi ? in[i] : ~0ull; }
+#pragma unroll
+    for (int r = 0; r < PS_IPT; ++r) {
+        const bool act = lo + (size_t)w * (PS_CHUNK / 8) + r * 32 + lane < hi;
+        const unsigned am = __ballot_sync(0xffffffffu, act);
+        dg[r] = 0; rk[r] = 0;
+        if (act) {
+            const u32 d = (u32)(keyfn(it[r]) >> shift) & (NB - 1);
+            const unsigned m = match_digit<BITS>(am, d);
+            const int leader = __ffs(m) - 1;
+            u32 base = 0;
+            if ((int)lane == leader) { base = wcnt[w * NB + d]; wcnt[w * NB + d] = (unsigned short)(base + __popc(m)); }
+            base = __shfl_sync(m, base, leader);
+            dg[r] = (unsigned short)d; rk[r] = (unsigned short)(base + __popc(m & ((1u << lane) - 1)));
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    // phase 2: per digit, exclusive prefix over the 8 warps; then exclusive prefix over the digits
+    u32 tot_local = 0;
+    constexpr u32 DPT = NB / 256 ? NB / 256 : 1;                                 // digits per thread (contiguous)
+    u32 dtot[DPT];
+#pragma unroll
+    for (u32 q = 0; q < DPT; ++q) {
+        const u32 d = tid * DPT + q;
+        u32 run = 0;
+        if (d < NB) for (int ww = 0; ww < 8; ++ww) { const u32 c = wcnt[ww * NB + d]; wcnt[ww * NB + d] = (unsigned short)run; run += c; }
+        dtot[q] = run; tot_local += run;
+    }
+    u32 inc = tot_local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, inc, o); if ((int)lane >= o) inc += x; }
+    if (lane == 31) scan_ws[w] = inc;
+    __syncthreads();
+    u32 wb = 0;
+    for (u32 i = 0; i < w; ++i) wb += scan_ws[i];
+    u32 run = wb + inc - tot_local;
+#pragma unroll
+    for (u32 q = 0; q < DPT; ++q) { const u32 d = tid * DPT + q; if (d < NB) dbase[d] = run; run += dtot[q]; }
+    __syncthreads();
+    // phase 3: place every item at its sorted position
+#pragma unroll
+    for (int r = 0; r < PS_IPT; ++r) {
+        if (lo + (size_t)w * (PS_CHUNK / 8) + r * 32 + lane < hi) {
+            const u32 pos = dbase[dg[r]] + wcnt[w * NB + dg[r]] + rk[r];
+            items_s[pos] = it[r]; dig_s[pos] = dg[r];
+        }
+    }
+    __syncthreads();
+    // phase 4: copy out; consecutive threads -> consecutive positions -> consecutive addresses inside a run
+    const u32 cnt = (u32)(hi - lo);
+    for (u32 pos = tid; pos < cnt; pos += 256) { const u32 d = dig_s[pos]; out[(size_t)goff[d] + (pos - dbase[d])] = items_s[pos]; }
+}
+
 // ---- step 3: apply the operators along every key's run, in arrival order ---------------------------
 // The sorted array is cut into ranges of KA_RANGE positions, one warp each.  A record's new state is a
 // FUNCTION of the key's state before it:
