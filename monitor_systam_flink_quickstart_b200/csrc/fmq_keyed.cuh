@@ -232,21 +232,39 @@ __device__ __forceinline__ void keyed_scan_range(const KeyedArgs& a, size_t lo, 
     const u32 N = (u32)a.consec_n;
     u32 c_slot = lo > 0 ? (u32)(a.sorted[lo - 1] >> 32) : SLOT_INVALID;
     bool seen_head = false; lead = (u32)(hi - lo);
-    for (size_t pos = lo; pos < hi; pos += 32) {
+    // Software pipeline: the item, its value (random gather) and the stored state at run heads (another
+    // gather) of round r+1 are requested before round r is computed, so a warp is not three dependent
+    // memory round trips per 32 records.
+    struct Stage { u64 item; V v; bool act, head; u32 fl; u64 smax; };
+    auto fetch = [&](size_t pos, u32 prev_last_slot) {
+        Stage s;
         const size_t p = pos + lane;
         const bool in = p < hi;
-        const u64 item = in ? a.sorted[p] : ~0ull;
-        const u32 slot = (u32)(item >> 32), idx = (u32)item;
+        s.item = in ? a.sorted[p] : ~0ull;
+        const u32 slot = (u32)(s.item >> 32);
+        s.act = in && slot != SLOT_INVALID;
         const u32 prev_slot = __shfl_up_sync(0xffffffffu, slot, 1);
-        const bool act = in && slot != SLOT_INVALID;
-        const bool head = act && (lane == 0 ? (slot != c_slot || p == 0) : (slot != prev_slot));
+        s.head = s.act && (lane == 0 ? (slot != prev_last_slot || p == 0) : (slot != prev_slot));
+        s.v = s.act ? val[(u32)s.item] : V(0);
+        s.fl = 0; s.smax = 0;
+        if (s.head) { s.fl = a.kflags[slot]; s.smax = a.kmax[slot]; }
+        return s;
+    };
+    Stage nxt = fetch(lo, c_slot);
+    for (size_t pos = lo; pos < hi; pos += 32) {
+        const Stage cur = nxt;
+        const size_t p = pos + lane;
+        const u64 item = cur.item;
+        const u32 slot = (u32)(item >> 32), idx = (u32)item;
+        const bool act = cur.act, head = cur.head;
+        const unsigned am0 = __ballot_sync(0xffffffffu, act);
+        const u32 last_slot = am0 ? __shfl_sync(0xffffffffu, slot, 31 - __clz(am0)) : c_slot;
+        if (pos + 32 < hi) nxt = fetch(pos + 32, last_slot);          // requests of the next round are in flight from here on
         const unsigned hm = __ballot_sync(0xffffffffu, head);
         if (hm && !seen_head) { seen_head = true; lead = (u32)(pos - lo) + (u32)(__ffs(hm) - 1); }
-        // gathers: value of this record, stored state at run heads
-        V v = act ? val[idx] : V(0);
+        const V v = cur.v;
         u64 vb; memcpy(&vb, &v, 8);
-        u32 fl = 0; u64 smax = 0;
-        if (head) { fl = a.kflags[slot]; smax = a.kmax[slot]; }
+        const u32 fl = cur.fl; const u64 smax = cur.smax;
         const bool over = act && N > 0 && cmp_op((double)v, a.consec_op, a.consec_thr);
         // ---- elements ----
         bool hr = false; u32 k = 0;
