@@ -184,6 +184,26 @@ def test_explicit_watermarks_and_empty_batches():
     compare_all(gpu, cpu)
 
 
+@pytest.mark.parametrize("t0", [0, 7, (1 << 55) + 123])
+def test_timestamps_at_the_epoch_and_far_in_the_future(t0):
+    """Windows that start before time 0 (negative window starts, pane -1) and timestamps near 2^55."""
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=5000, window_offset_ms=1234, max_out_of_orderness_ms=2000,
+              late_capacity=1 << 12, **SMALL)
+    gpu, cpu = pair(**kw)
+    spec = StreamSpec(n_keys=40, events_per_ms=1, jitter_ms=2500, late_frac_ppm=30000, late_extra_ms=9000, t0=t0)
+    for b in range(5):
+        ts, key, val = generate_numpy(spec, b * 7000, 7000)
+        gpu.push_batch(ts, key, val); cpu.push_batch(ts, key, val)
+        if b == 2:
+            for e in (gpu, cpu):
+                e.push_batch(ts[:0], key[:0], val[:0])           # an empty batch in between
+                e.flush(int(ts.max()) - 20_000)                   # a watermark that does not advance
+    gpu.flush(); cpu.flush()
+    compare_all(gpu, cpu)
+    f = cpu.poll_fired()
+    assert cpu.counters()["windows_fired"] > 0
+
+
 def test_device_resident_and_misaligned_inputs():
     import torch
     kw, spec = CONFIGS["c3_tumbling_f64"]
