@@ -1,6 +1,6 @@
 """Developer probe: device time of the chapter1 filter path and the keyed ValueState path."""
 import os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, ROOT)
 import numpy as np, torch
 from monitor_systam_flink_quickstart_b200 import capi
 from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_torch

@@ -1,6 +1,6 @@
 """Developer probe: wall-clock phases of ShardedOperator.process_batch on N GPUs (torchrun)."""
 import os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, ROOT)
 import numpy as np, torch, torch.distributed as dist
 from monitor_systam_flink_quickstart_b200 import capi
 from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_torch

@@ -1,6 +1,6 @@
 """Developer probe: host wall-clock per phase of ShardedOperator (no added syncs)."""
 import os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, ROOT)
 import numpy as np, torch, torch.distributed as dist
 from monitor_systam_flink_quickstart_b200 import capi, shard
 from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_torch
