@@ -124,7 +124,8 @@ typedef struct fmq_config {
     int32_t  consec_reset_on_fire;   /* 1: counter returns to 0 after an alert                   */
     double   consec_threshold;
 
-    /* --- capacities (all device memory is allocated once, in fmq_create) --- */
+    /* --- capacities (device memory is allocated once, in fmq_create; only the two staging sets
+     *     for host-resident input columns wait for the first host push) --- */
     uint64_t table_capacity;         /* key slots (any size; ~1.5x the key count when HASHED,
                                         max id + 1 when DENSE)                                   */
     uint32_t pane_ring;              /* open panes kept per key; rounded up to a power of two    */
@@ -198,6 +199,38 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out);
  * Asynchronous on the handle's stream; results become visible through the poll functions. */
 int32_t fmq_push_batch(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val,
                        size_t n, int64_t watermark_after, int32_t mem);
+
+/* Same call as fmq_push_batch with a narrower wire format for the columns, for shims whose batches
+ * come from host memory: the host path is bound by PCIe (24 B per event at ~50 GB/s), so a shim that
+ * already maps host names to small ids and whose micro-batch spans less than 49 days can send
+ * 4-byte offsets and ids.  The columns are widened on the device (exactly: zero/sign extension and
+ * one integer add) before the same kernels run; results are identical to fmq_push_batch on the
+ * widened columns.  The record fields it carries are the reference's (timestamp, key, value) tuple
+ * (chapter3/.../BandwidthMonitorWithEventTime.java:39-44); the encoding itself has no reference
+ * counterpart. */
+typedef struct fmq_packed_columns {
+    uint32_t    struct_size;         /* = sizeof(fmq_packed_columns)                             */
+    uint32_t    ts_width;            /* 8: int64 epoch ms;  4: uint32 ms offset from ts_base     */
+    uint32_t    key_width;           /* 8: uint64 key id;   4: uint32 key id, zero-extended      */
+    uint32_t    val_width;           /* 8: double / int64 (fmq_config.value_type);
+                                        4: int32, sign-extended — FMQ_VAL_I64 handles only       */
+    int64_t     ts_base;             /* added to every 4-byte timestamp offset                   */
+    const void* ts;
+    const void* key;
+    const void* val;
+} fmq_packed_columns;
+int32_t fmq_push_packed(fmq_handle* h, const fmq_packed_columns* cols, size_t n,
+                        int64_t watermark_after, int32_t mem);
+
+/* Starts the host->device copy of the NEXT micro-batch and returns at once, so that the copy runs
+ * while the kernels of the batch just pushed finish and its results are polled (a shim that fills
+ * buffer k+1 while buffer k is in flight calls this as soon as k+1 is full).  `cols` describes host
+ * columns (pinned memory for a truly asynchronous copy; all widths 8 = the fmq_push_batch format).
+ * The columns must stay untouched until the consuming call returns: the next fmq_push_batch /
+ * fmq_push_packed with FMQ_MEM_HOST must pass the same pointers, widths, ts_base and n, and finds
+ * them staged.  At most one batch is staged ahead.  Network-buffer hand-over in Flink
+ * (RecordWriter -> InputGate) is the nearest reference notion; it has no direct counterpart. */
+int32_t fmq_stage_host(fmq_handle* h, const fmq_packed_columns* cols, size_t n);
 
 /* Replaces: processWatermark(wm) with no records (and Watermark(Long.MAX_VALUE) at end of a
  * finite source when wm == FMQ_WM_FINAL). */

@@ -64,6 +64,11 @@ class FmqEventCols(C.Structure):
     _fields_ = [("ts", C.c_void_p), ("key", C.c_void_p), ("val", C.c_void_p)]
 
 
+class FmqPackedColumns(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("ts_width", C.c_uint32), ("key_width", C.c_uint32), ("val_width", C.c_uint32),
+                ("ts_base", C.c_int64), ("ts", C.c_void_p), ("key", C.c_void_p), ("val", C.c_void_p)]
+
+
 class FmqCounters(C.Structure):
     _fields_ = [("events_in", C.c_uint64), ("late_dropped", C.c_uint64), ("windows_fired", C.c_uint64),
                 ("window_alerts", C.c_uint64), ("event_alerts", C.c_uint64), ("consec_alerts", C.c_uint64),
@@ -173,6 +178,8 @@ def _declare(lib, p: str, has_mem: bool = True):
         sig("push_local", [vp, vp, vp, vp, sz, i32])
         sig("fire_global", [vp, i64])
         sig("retire", [vp])
+        sig("push_packed", [vp, C.POINTER(FmqPackedColumns), sz, i64, i32])
+        sig("stage_host", [vp, C.POINTER(FmqPackedColumns), sz])
         sig("partition_by_owner_noalloc", [i32, vp, vp, vp, vp, sz, C.c_uint32, vp, vp, vp, vp])
 
 
@@ -262,6 +269,28 @@ class EngineBase:
         if self._has_mem:
             args.append(FMQ_MEM_DEVICE if dev else FMQ_MEM_HOST)
         self._check(self._f("push_batch")(*args))
+
+    @staticmethod
+    def _packed(ts, key, val, ts_base):
+        n = len(ts)
+        assert len(key) == n and len(val) == n
+        dev = _is_device(ts)
+        cols = [a if dev else np.ascontiguousarray(a) for a in (ts, key, val)]
+        w = [a.element_size() if dev else a.dtype.itemsize for a in cols]
+        return FmqPackedColumns(C.sizeof(FmqPackedColumns), w[0], w[1], w[2], ts_base, _ptr(cols[0]), _ptr(cols[1]), _ptr(cols[2])), n, dev, cols
+
+    def push_packed(self, ts, key, val, watermark_after: int = FMQ_WM_AUTO, ts_base: int = 0):
+        """fmq_push_packed: the element size of each column picks the wire format (uint32 ts offsets
+        from `ts_base`, uint32 key ids, int32 values are widened on the device)."""
+        pc, n, dev, _keep = self._packed(ts, key, val, ts_base)
+        self._check(self._f("push_packed")(self._h, C.byref(pc), n, watermark_after, FMQ_MEM_DEVICE if dev else FMQ_MEM_HOST))
+
+    def stage_host(self, ts, key, val, ts_base: int = 0):
+        """fmq_stage_host: start copying the NEXT host batch in; the caller keeps the arrays alive and
+        untouched and passes the very same ones to the next push_batch / push_packed."""
+        pc, n, dev, cols = self._packed(ts, key, val, ts_base)
+        assert not dev and all(c is a for c, a in zip(cols, (ts, key, val))), "stage_host needs contiguous host arrays (no hidden copies)"
+        self._check(self._f("stage_host")(self._h, C.byref(pc), n))
 
     def flush(self, watermark: int = FMQ_WM_FINAL):
         self._check(self._f("flush")(self._h, watermark))

@@ -22,11 +22,13 @@ using namespace fmq;
 
 static thread_local std::string g_create_err;
 
+// the columns of one micro-batch as the caller hands them over
+struct InCols { const void* ts; const void* key; const void* val; int ts_w, key_w, val_w; i64 ts_base; };
+
 struct fmq_handle {
     fmq_config cfg;
     int device = 0, num_sms = 148;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev_copy = nullptr;
     // per-push stage timing: ring of event quadruples {start, after ingest, after keyed, end}
     static constexpr int TIMING_RING = 64;
     cudaEvent_t tev[TIMING_RING][4] = {};
@@ -43,6 +45,12 @@ struct fmq_handle {
     u64* d_keys = nullptr; Acc32* d_acc = nullptr; u32* d_kflags = nullptr; u64* d_kmax = nullptr;
     // staging for host-resident inputs
     i64* d_in_ts = nullptr; u64* d_in_key = nullptr; u64* d_in_val = nullptr;
+    // host pushes: two staging sets filled on a copy stream, so that the copy-in of batch k+1 runs
+    // while the kernels of batch k do (allocated by the first host push)
+    i64* hs_ts[2] = {nullptr, nullptr}; u64* hs_key[2] = {nullptr, nullptr}; u64* hs_val[2] = {nullptr, nullptr};
+    u32* hs_narrow[2] = {nullptr, nullptr};      // 3 x max_batch 4-byte columns of fmq_push_packed
+    cudaStream_t copy_stream = nullptr; cudaEvent_t ev_free[2] = {nullptr, nullptr}, ev_piece[2][4] = {}; uint64_t host_pushes = 0;
+    struct Staged { bool valid = false; InCols c{}; size_t n = 0, chunk = 0; int set = 0, pieces = 0; } staged;   // fmq_stage_host
     // outputs
     u64 *f_key = nullptr, *f_sum = nullptr, *f_min = nullptr, *f_max = nullptr; i64 *f_wend = nullptr, *f_count = nullptr; u64 f_cap = 0;
     u64* wa_key = nullptr; i64* wa_wend = nullptr; double* wa_val = nullptr; u64 wa_cap = 0;
@@ -106,11 +114,18 @@ static void free_all(fmq_handle* h) {
                     h->md_key, h->md_wend, h->md_val, h->lt_ts, h->lt_key, h->lt_val};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : h->alt_out) if (p) cudaFree(p);
+    for (int i = 0; i < 2; ++i) {
+        void* q[] = {h->hs_ts[i], h->hs_key[i], h->hs_val[i], h->hs_narrow[i]};
+        for (void* p : q) if (p) cudaFree(p);
+        if (h->ev_free[i]) cudaEventDestroy(h->ev_free[i]);
+    }
+    if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
+    for (auto& q : h->ev_piece) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->out_stream) cudaStreamDestroy(h->out_stream);
     if (h->ev_out) cudaEventDestroy(h->ev_out);
     if (h->h_st) cudaFreeHost(h->h_st);
     for (auto& q : h->tev) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
-    if (h->ev_copy) cudaEventDestroy(h->ev_copy);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -143,7 +158,6 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
 #define CUC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(FMQ_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
     CUC(cudaSetDevice(h->device));
     CUC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-    CUC(cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming));
     for (auto& q : h->tev) for (cudaEvent_t& e : q) CUC(cudaEventCreate(&e));
 
     h->capacity = cfg->table_capacity ? cfg->table_capacity : (1u << 20);
@@ -459,35 +473,169 @@ static int run_chain(fmq_handle* h, const i64* ts, const u64* key, const void* v
     return stage_fire<V>(h, n, wm_after, true);
 }
 
+// ---- the columns of one micro-batch as the caller hands them over -----------------------------------
+
+// widens the 4-byte columns of fmq_push_packed; a null source leaves that column alone
+__global__ void __launch_bounds__(256) widen_columns_kernel(const u32* __restrict__ ts32, i64 ts_base, const u32* __restrict__ key32, const int* __restrict__ val32,
+                                                            i64* __restrict__ ts, u64* __restrict__ key, u64* __restrict__ val, size_t n) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        if (ts32) ts[i] = ts_base + (i64)ts32[i];
+        if (key32) key[i] = (u64)key32[i];
+        if (val32) val[i] = (u64)(i64)val32[i];
+    }
+}
+
+static int ensure_host_staging(fmq_handle* h, bool narrow) {
+    if (!h->copy_stream) {
+        CU(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) CU(h, cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming));
+        for (auto& q : h->ev_piece) for (cudaEvent_t& e : q) CU(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    const size_t mb = h->max_batch ? h->max_batch : 1;
+    for (int i = 0; i < 2; ++i) {
+        if (!h->hs_ts[i]) { CU(h, dalloc(&h->hs_ts[i], mb)); CU(h, dalloc(&h->hs_key[i], mb)); CU(h, dalloc(&h->hs_val[i], mb)); }
+        if (narrow && !h->hs_narrow[i]) CU(h, dalloc(&h->hs_narrow[i], 3 * mb));
+    }
+    return FMQ_OK;
+}
+
+// Host columns are copied in on the copy stream in up to HOST_CHUNKS pieces; the ingest of a piece
+// runs while the next one is in flight, so that only the last piece's kernels and the fire chain are
+// left when the copy ends.  Ingest does not depend on how a micro-batch is cut (the pane origin and
+// the watermark move in the plan / commit kernels only).
+constexpr int HOST_CHUNKS = 4;
+constexpr size_t HOST_CHUNK_MIN = 1u << 18;
+
+// queues the copy-in of one host batch on the copy stream, into the staging set whose turn it is
+static int queue_host_copy(fmq_handle* h, const InCols& c, size_t n) {
+    const bool narrow = c.ts_w == 4 || c.key_w == 4 || c.val_w == 4;
+    int s_ = ensure_host_staging(h, narrow); if (s_) return s_;
+    fmq_handle::Staged& g = h->staged;
+    g.c = c; g.n = n; g.set = (int)(h->host_pushes++ & 1); g.pieces = 0;
+    const size_t mb = h->max_batch;
+    u32* nar = h->hs_narrow[g.set];
+    size_t chunk = (n + HOST_CHUNKS - 1) / HOST_CHUNKS;
+    if (chunk < HOST_CHUNK_MIN) chunk = HOST_CHUNK_MIN;
+    if (h->cfg.rolling_max_enabled) chunk = n;                          // its output column is indexed by position in the push
+    g.chunk = (chunk + 3) & ~(size_t)3;                                 // keeps every piece 32-byte aligned
+    // the kernels of the push before last read this set: wait for them, on the copy stream only
+    CU(h, cudaStreamWaitEvent(h->copy_stream, h->ev_free[g.set], 0));
+    for (size_t off = 0; off < n; off += g.chunk, ++g.pieces) {
+        const size_t m = n - off < g.chunk ? n - off : g.chunk;
+        CU(h, cudaMemcpyAsync(c.ts_w == 8 ? (void*)(h->hs_ts[g.set] + off) : (void*)(nar + off), (const char*)c.ts + off * c.ts_w, m * c.ts_w, cudaMemcpyHostToDevice, h->copy_stream));
+        CU(h, cudaMemcpyAsync(c.key_w == 8 ? (void*)(h->hs_key[g.set] + off) : (void*)(nar + mb + off), (const char*)c.key + off * c.key_w, m * c.key_w, cudaMemcpyHostToDevice, h->copy_stream));
+        CU(h, cudaMemcpyAsync(c.val_w == 8 ? (void*)(h->hs_val[g.set] + off) : (void*)(nar + 2 * mb + off), (const char*)c.val + off * c.val_w, m * c.val_w, cudaMemcpyHostToDevice, h->copy_stream));
+        CU(h, cudaEventRecord(h->ev_piece[g.set][g.pieces], h->copy_stream));
+    }
+    g.valid = true;
+    return FMQ_OK;
+}
+
+static bool same_cols(const InCols& a, const InCols& b) {
+    return a.ts == b.ts && a.key == b.key && a.val == b.val && a.ts_w == b.ts_w && a.key_w == b.key_w && a.val_w == b.val_w && a.ts_base == b.ts_base;
+}
+
+template <typename V>
+static int push_cols_t(fmq_handle* h, const InCols& c, size_t n, int64_t wm_after, int32_t mem) {
+    const bool narrow = c.ts_w == 4 || c.key_w == 4 || c.val_w == 4;
+    cudaEvent_t* tev = h->tev[h->pushes % fmq_handle::TIMING_RING];
+    CU(h, cudaEventRecord(tev[0], h->stream));
+    const bool host = mem == FMQ_MEM_HOST && n > 0;
+    const unsigned wgrid = (unsigned)h->num_sms * 8;
+    if (host) {
+        fmq_handle::Staged& g = h->staged;
+        if (g.valid && !(g.n == n && same_cols(g.c, c))) return set_err(h, FMQ_ERR_BAD_ARG, "a batch was staged with fmq_stage_host: the next host push must pass the same columns and n");
+        if (!g.valid) { int s_ = queue_host_copy(h, c, n); if (s_) return s_; }
+        g.valid = false;
+        const size_t mb = h->max_batch;
+        const u32* nar = h->hs_narrow[g.set];
+        i64* sts = h->hs_ts[g.set]; u64* skey = h->hs_key[g.set]; u64* sval = h->hs_val[g.set];
+        int piece = 0;
+        for (size_t off = 0; off < n; off += g.chunk, ++piece) {
+            const size_t m = n - off < g.chunk ? n - off : g.chunk;
+            CU(h, cudaStreamWaitEvent(h->stream, h->ev_piece[g.set][piece], 0));
+            if (narrow) {
+                widen_columns_kernel<<<wgrid, 256, 0, h->stream>>>(c.ts_w == 4 ? nar + off : nullptr, c.ts_base, c.key_w == 4 ? nar + mb + off : nullptr,
+                                                                   c.val_w == 4 ? (const int*)(nar + 2 * mb + off) : nullptr, sts + off, skey + off, sval + off, m);
+                LAUNCHED(h, "widen_columns_kernel");
+            }
+            int s_ = stage_ingest<V>(h, sts + off, skey + off, sval + off, m); if (s_) return s_;
+        }
+        int s_ = stage_fire<V>(h, n, wm_after, true); if (s_) return s_;
+        CU(h, cudaEventRecord(tev[3], h->stream));
+        h->pushes++;
+        CU(h, cudaEventRecord(h->ev_free[g.set], h->stream));
+        // the caller owns host columns only until this call returns: wait for the last copy
+        CU(h, cudaEventSynchronize(h->ev_piece[g.set][piece - 1]));
+        return FMQ_OK;
+    }
+    const i64* dts = (const i64*)c.ts; const u64* dkey = (const u64*)c.key; const void* dval = c.val;
+    if (narrow && n > 0) {
+        // device-resident narrow columns: widen into the handle's staging columns on its own stream
+        widen_columns_kernel<<<wgrid, 256, 0, h->stream>>>(c.ts_w == 4 ? (const u32*)c.ts : nullptr, c.ts_base, c.key_w == 4 ? (const u32*)c.key : nullptr,
+                                                           c.val_w == 4 ? (const int*)c.val : nullptr, h->d_in_ts, h->d_in_key, h->d_in_val, n);
+        LAUNCHED(h, "widen_columns_kernel");
+        if (c.ts_w == 4) dts = h->d_in_ts;
+        if (c.key_w == 4) dkey = h->d_in_key;
+        if (c.val_w == 4) dval = h->d_in_val;
+    }
+    int s = run_chain<V>(h, dts, dkey, dval, n, wm_after); if (s) return s;
+    CU(h, cudaEventRecord(tev[3], h->stream));
+    h->pushes++;
+    return FMQ_OK;
+}
+
+static int push_cols(fmq_handle* h, const InCols& c, size_t n, int64_t wm_after, int32_t mem) {
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (n > 0 && (!c.ts || !c.key || !c.val)) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
+    if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
+    if (mem != FMQ_MEM_HOST && mem != FMQ_MEM_DEVICE) return set_err(h, FMQ_ERR_BAD_ARG, "bad mem");
+    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: use fmq_push_local / fmq_fire_global / fmq_retire");
+    if (mem == FMQ_MEM_DEVICE && n > 0) {
+        const uintptr_t wide = (c.ts_w == 8 ? (uintptr_t)c.ts : 0) | (c.key_w == 8 ? (uintptr_t)c.key : 0) | (c.val_w == 8 ? (uintptr_t)c.val : 0);
+        const uintptr_t thin = (c.ts_w == 4 ? (uintptr_t)c.ts : 0) | (c.key_w == 4 ? (uintptr_t)c.key : 0) | (c.val_w == 4 ? (uintptr_t)c.val : 0);
+        if ((wide & 7) || (thin & 3)) return set_err(h, FMQ_ERR_BAD_ARG, "device columns must be aligned to their element size (32-byte alignment of 8-byte columns enables 256-bit loads)");
+    }
+    CU(h, cudaSetDevice(h->device));
+    return h->cfg.value_type == FMQ_VAL_F64 ? push_cols_t<double>(h, c, n, wm_after, mem) : push_cols_t<i64>(h, c, n, wm_after, mem);
+}
+
 extern "C" {
 
 int32_t fmq_push_batch(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val, size_t n, int64_t wm_after, int32_t mem) {
     if (!h) return FMQ_ERR_BAD_ARG;
-    if (h->sticky) return FMQ_ERR_POISONED;
-    if (n > 0 && (!ts || !key || !val)) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
-    if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
-    if (mem != FMQ_MEM_HOST && mem != FMQ_MEM_DEVICE) return set_err(h, FMQ_ERR_BAD_ARG, "bad mem");
-    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: use fmq_push_local / fmq_fire_global / fmq_retire");
-    CU(h, cudaSetDevice(h->device));
-    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][0], h->stream));
-    const i64* dts = (const i64*)ts; const u64* dkey = (const u64*)key; const void* dval = val;
-    if (mem == FMQ_MEM_HOST && n > 0) {
-        CU(h, cudaMemcpyAsync(h->d_in_ts, ts, n * 8, cudaMemcpyHostToDevice, h->stream));
-        CU(h, cudaMemcpyAsync(h->d_in_key, key, n * 8, cudaMemcpyHostToDevice, h->stream));
-        CU(h, cudaMemcpyAsync(h->d_in_val, val, n * 8, cudaMemcpyHostToDevice, h->stream));
-        CU(h, cudaEventRecord(h->ev_copy, h->stream));
-        dts = h->d_in_ts; dkey = h->d_in_key; dval = h->d_in_val;
-    } else if (n > 0 && (((uintptr_t)ts | (uintptr_t)key | (uintptr_t)val) & 7)) {
-        return set_err(h, FMQ_ERR_BAD_ARG, "device columns must be 8-byte aligned (32-byte alignment enables 256-bit loads)");
-    }
-    int s = (h->cfg.value_type == FMQ_VAL_F64) ? run_chain<double>(h, dts, dkey, dval, n, wm_after)
-                                               : run_chain<i64>(h, dts, dkey, dval, n, wm_after);
-    if (s) return s;
-    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][3], h->stream));
-    h->pushes++;
-    // the caller owns host columns only for the duration of this call: wait for the H2D copies
-    if (mem == FMQ_MEM_HOST && n > 0) CU(h, cudaEventSynchronize(h->ev_copy));
+    const InCols c{ts, key, val, 8, 8, 8, 0};
+    return push_cols(h, c, n, wm_after, mem);
+}
+
+static int check_packed(fmq_handle* h, const fmq_packed_columns* p) {
+    if (!p || p->struct_size != sizeof(fmq_packed_columns)) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_packed_columns.struct_size mismatch");
+    if ((p->ts_width != 4 && p->ts_width != 8) || (p->key_width != 4 && p->key_width != 8) || (p->val_width != 4 && p->val_width != 8))
+        return set_err(h, FMQ_ERR_BAD_ARG, "column widths must be 4 or 8");
+    if (p->val_width == 4 && h->cfg.value_type != FMQ_VAL_I64) return set_err(h, FMQ_ERR_BAD_ARG, "4-byte values are int32 and need an FMQ_VAL_I64 handle");
+    if (p->ts_width == 4 && p->ts_base > INT64_MAX - 0xFFFFFFFFll) return set_err(h, FMQ_ERR_BAD_ARG, "ts_base + 2^32 overflows int64");
     return FMQ_OK;
+}
+
+int32_t fmq_stage_host(fmq_handle* h, const fmq_packed_columns* p, size_t n) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    int s = check_packed(h, p); if (s) return s;
+    if (n == 0 || !p->ts || !p->key || !p->val) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_stage_host needs a non-empty batch");
+    if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
+    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: host staging belongs to fmq_push_batch / fmq_push_packed");
+    if (h->staged.valid) return set_err(h, FMQ_ERR_BAD_ARG, "one batch is already staged: push it first");
+    CU(h, cudaSetDevice(h->device));
+    const InCols c{p->ts, p->key, p->val, (int)p->ts_width, (int)p->key_width, (int)p->val_width, p->ts_width == 4 ? p->ts_base : 0};
+    return queue_host_copy(h, c, n);
+}
+
+int32_t fmq_push_packed(fmq_handle* h, const fmq_packed_columns* p, size_t n, int64_t wm_after, int32_t mem) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    int s = check_packed(h, p); if (s) return s;
+    const InCols c{p->ts, p->key, p->val, (int)p->ts_width, (int)p->key_width, (int)p->val_width, p->ts_width == 4 ? p->ts_base : 0};
+    return push_cols(h, c, n, wm_after, mem);
 }
 
 int32_t fmq_flush(fmq_handle* h, int64_t watermark) {

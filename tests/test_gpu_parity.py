@@ -474,3 +474,107 @@ def test_partition_by_owner_is_a_stable_split(world):
     np.testing.assert_array_equal(o[0].cpu().numpy(), ts[order])
     np.testing.assert_array_equal(o[1].cpu().numpy().view(np.uint64), key[order])
     np.testing.assert_array_equal(o[2].cpu().numpy(), val[order])
+
+
+# ---- narrow wire format (fmq_push_packed) ----------------------------------------------------------
+@pytest.mark.parametrize("name", ["c3_tumbling_f64", "c4_sliding_i64"])
+@pytest.mark.parametrize("where", ["host", "device"])
+def test_packed_columns_give_the_results_of_wide_columns(name, where):
+    """uint32 timestamp offsets / uint32 key ids / int32 values are widened on the device: same rows
+    as the oracle fed the wide columns.  Seven host pushes in a row cycle both staging sets."""
+    import torch
+    kw, spec = CONFIGS[name]
+    keyed = dict(consec_n=3, consec_threshold=60.0, consec_reset_on_fire=1) if name == "c3_tumbling_f64" else {}
+    gpu, cpu = pair(**kw, **keyed, **SMALL)
+    batch, total = 23_456, 7 * 23_456
+    for s in range(0, total, batch):
+        ts, key, val = generate_numpy(spec, s, batch)
+        base = int(ts.min()) - 17
+        cols = [(ts - base).astype(np.uint32), key, val]
+        if key.max() < (1 << 32):
+            cols[1] = key.astype(np.uint32)
+        if val.dtype == np.int64 and np.abs(val).max() < (1 << 31):
+            cols[2] = val.astype(np.int32)
+        if s // batch == 3:
+            cols[0], base = ts, 0                               # a wide timestamp column among narrow ones
+        assert any(c.dtype.itemsize == 4 for c in cols)
+        if where == "device":
+            cols = [torch.from_numpy(c.view(np.int32) if c.dtype == np.uint32 else (c.view(np.int64) if c.dtype == np.uint64 else c)).cuda() for c in cols]
+        gpu.push_packed(cols[0], cols[1], cols[2], ts_base=base)
+        gpu.synchronize()
+        cpu.push_batch(ts, key, val)
+        if (s // batch) % 3 == 2:
+            compare_all(gpu, cpu, agg_mask=kw["agg_mask"])
+    gpu.flush(); cpu.flush()
+    compare_all(gpu, cpu, agg_mask=kw["agg_mask"])
+    assert cpu.counters()["windows_fired"] > 0
+
+
+def test_packed_columns_bad_arguments():
+    gpu = capi.Engine(window_enabled=1, window_size_ms=1000, window_slide_ms=1000, **SMALL)       # an f64 handle
+    ts = np.arange(10, dtype=np.uint32); key = np.arange(10, dtype=np.uint32)
+    with pytest.raises(capi.FmqError) as e:
+        gpu.push_packed(ts, key, np.arange(10, dtype=np.int32))
+    assert e.value.status == 1 and "int32" in str(e.value)                          # FMQ_ERR_BAD_ARG
+    with pytest.raises(capi.FmqError):
+        gpu.push_packed(ts, key, np.zeros(10), ts_base=(1 << 63) - 5)
+    with pytest.raises(capi.FmqError):
+        gpu.push_packed(ts, key.astype(np.uint16), np.zeros(10))
+    gpu.push_packed(ts, key, np.ones(10), ts_base=5_000)                                           # and a good one still works
+    gpu.flush()
+    assert gpu.poll_fired().count.sum() == 10
+
+
+@pytest.mark.parametrize("keyed", [0, 1])
+def test_large_host_pushes_are_copied_in_pieces(keyed):
+    """Host batches above 2^18 events go over in up to four pieces whose ingest overlaps the next copy;
+    cutting a micro-batch must not change a single row (wide and packed columns, odd sizes)."""
+    kw, spec = CONFIGS["c3_tumbling_f64"]
+    extra = dict(consec_n=3, consec_threshold=60.0, consec_reset_on_fire=1) if keyed else {}
+    big = dict(table_capacity=1 << 12, pane_ring=1024, max_batch=1 << 21, fired_capacity=1 << 21, walert_capacity=1 << 21, ealert_capacity=1 << 21)
+    if keyed:
+        big["calert_capacity"] = 1 << 21
+    gpu, cpu = pair(**dict(kw, **extra), **big)
+    s = 0
+    for i, n in enumerate([1_000_003, 300_001, 1 << 21, 777_777]):
+        ts, key, val = generate_numpy(spec, s, n); s += n
+        if i % 2 == 0:
+            gpu.push_batch(ts, key, val)
+        else:
+            base = int(ts.min())
+            gpu.push_packed((ts - base).astype(np.uint32), key.astype(np.uint32), val, ts_base=base)
+        cpu.push_batch(ts, key, val)
+        compare_all(gpu, cpu)
+    gpu.flush(); cpu.flush()
+    compare_all(gpu, cpu)
+
+
+def test_staging_the_next_host_batch_ahead():
+    """fmq_stage_host starts the copy-in of batch k+1 before batch k's results are polled; rows are
+    those of plain pushes; a push of other columns while one batch is staged is refused."""
+    kw, spec = CONFIGS["c3_tumbling_f64"]
+    gpu, cpu = pair(**kw, **SMALL)
+    n = 30_011
+    batches = [generate_numpy(spec, s * n, n) for s in range(6)]
+    packed = []
+    for i, (ts, key, val) in enumerate(batches):
+        if i % 2:
+            base = int(ts.min())
+            packed.append(((ts - base).astype(np.uint32), key.astype(np.uint32), val, base))
+        else:
+            packed.append((ts, key, val, 0))
+    gpu.stage_host(*packed[0][:3], ts_base=packed[0][3])
+    for i, cols in enumerate(packed):
+        if i == 2:
+            with pytest.raises(capi.FmqError) as e:
+                gpu.push_batch(*batches[0])                     # not the staged columns
+            assert e.value.status == 1 and "staged" in str(e.value)
+            with pytest.raises(capi.FmqError):
+                gpu.stage_host(*packed[3][:3], ts_base=packed[3][3])    # only one batch ahead
+        gpu.push_packed(*cols[:3], ts_base=cols[3])
+        if i + 1 < len(packed):
+            gpu.stage_host(*packed[i + 1][:3], ts_base=packed[i + 1][3])
+        cpu.push_batch(*batches[i])
+        compare_all(gpu, cpu)
+    gpu.flush(); cpu.flush()
+    compare_all(gpu, cpu)
