@@ -339,7 +339,8 @@ def main():
     # inside the timed region; host wall clock with a full synchronise at both ends.
     e2e = None
     e2e_wide = None
-    if not args.no_e2e and not sharded:
+    combiner = sharded and args.multi == "combiner" and args.key_mode == "dense"
+    if not args.no_e2e and (not sharded or combiner):
         e2e_steps = min(K, 8)
         cap_rows = int(B * 0.14) + 2 * N_KEYS
 
@@ -362,6 +363,10 @@ def main():
             host = [to_host(batches[W + s], packed) for s in range(e2e_steps)]
             warm = [to_host(batches[s], packed) for s in range(W)]
             eng2 = capi.Engine(overlapped_polls=1, **kw)
+            op2 = None
+            if combiner:
+                from monitor_systam_flink_quickstart_b200.shard import CombinerOperator
+                op2 = CombinerOperator(eng2, rank, world)
             # two sets of pinned output columns: the copy-out of step s runs while step s+1 is copied in
             out_sets = [([pinned(cap_rows, torch.int64) for _ in range(3)] + [pinned(cap_rows, torch.float64) for _ in range(3)],
                          [pinned(cap_rows, torch.int64), pinned(cap_rows, torch.int64), pinned(cap_rows, torch.float64)],
@@ -376,7 +381,10 @@ def main():
 
             def e2e_step(cols, nxt):
                 ts, key, val, base = cols
-                eng2.push_packed(ts, key, val, ts_base=base)                               # H2D (already under way); returns when the copy is done
+                if op2:                                                                     # own events in, 2 x all-reduce, fire over NVLink
+                    op2.process_batch(ts, key, val, ts_base=base)
+                else:
+                    eng2.push_packed(ts, key, val, ts_base=base)                           # H2D (already under way); returns when the copy is done
                 if nxt is not None:
                     eng2.stage_host(*nxt[:3], ts_base=nxt[3])                              # next batch's H2D runs under this step's kernels and polls
                 eng2.poll_all_end()                                                         # previous step's rows are now on the host
@@ -389,17 +397,26 @@ def main():
             eng2.poll_all_end()
             d2h = 0
             torch.cuda.synchronize()
+            if dist:
+                dist.barrier()
             t0 = time.perf_counter()
             for s in range(e2e_steps):
                 d2h += e2e_step(seq[W + s], seq[W + s + 1] if s + 1 < e2e_steps else None)
             eng2.poll_all_end()
             eng2.synchronize()
             dt = time.perf_counter() - t0
+            if dist:                                                                        # whole job: slowest rank's time, every rank's rows
+                t = torch.tensor([dt, -dt], device=f"cuda:{local_rank}", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dt = float(t[0].item())
+                tot = torch.tensor([d2h], device=f"cuda:{local_rank}", dtype=torch.int64)
+                dist.all_reduce(tot)
+                d2h = int(tot.item())
             eng2.close()
             per_event = sum(c.element_size() for c in host[0][:3])
-            return {"value": e2e_steps * B / dt, "unit": "events/s", "h2d_bytes_per_step": per_event * B, "d2h_bytes_per_step": d2h // e2e_steps,
+            return {"value": e2e_steps * B * world / dt, "unit": "events/s", "h2d_bytes_per_step": per_event * B * world, "d2h_bytes_per_step": d2h // e2e_steps,
                     "steps": e2e_steps, "ms_per_step": dt / e2e_steps * 1e3,
-                    "entry_point": "fmq_push_packed + fmq_stage_host, " + ("uint32 ts offset + uint32 host id + double" if packed else "int64 ts + uint64 key + double (the fmq_push_batch format)"),
+                    "entry_point": ("CombinerOperator: fmq_push_local_packed + fmq_stage_host + 2 all-reduces + fmq_fire_global/fmq_retire, " if combiner else "fmq_push_packed + fmq_stage_host, ") + ("uint32 ts offset + uint32 host id + double" if packed else "int64 ts + uint64 key + double (the fmq_push_batch format)"),
                     "timing": "host wall clock around K x [push of pinned host columns + fmq_poll_all_begin/end into pinned host buffers]; "
                               "the D2H of step s overlaps the H2D of step s+1; every row is on the host when the clock stops"}
         # What a JVM shim would do per micro-batch: hand over three pinned host columns (direct
@@ -407,7 +424,7 @@ def main():
         # inside the timed region; host wall clock with a full synchronise at both ends.  The host path
         # is PCIe-bound, so the headline uses the 16 B/event wire format; the 24 B one is beside it.
         e2e = run_e2e(True)
-        e2e_wide = run_e2e(False)
+        e2e_wide = run_e2e(False) if world == 1 else None
 
     if rank != 0:
         if dist:

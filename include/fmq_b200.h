@@ -364,7 +364,9 @@ int32_t fmq_partition_by_owner(fmq_handle* h, const int64_t* ts, const uint64_t*
  * 32 bytes (max timestamp and live pane range, one all-reduce(MAX) over fmq_exchange_ptr) instead of
  * 24 bytes per event.  Order-dependent keyed state (A7) cannot be combined this way and stays on
  * the all-to-all route (fmq_partition_by_owner).  Call sequence per micro-batch, on every rank:
- *     fmq_push_local(..)                       ingest own events (device columns)
+ *     fmq_push_local(..) / fmq_push_local_packed(..)
+ *                                              ingest own events (host or device columns; host
+ *                                              columns may have been staged with fmq_stage_host)
  *     all-reduce(MAX) of the 4 int64 at fmq_exchange_ptr(h), on fmq_stream(h)   [also the barrier
  *                                               "every rank has ingested"]
  *     fmq_fire_global(h, watermark_after)      same watermark on every rank; fires own slot range
@@ -379,6 +381,7 @@ int32_t fmq_ipc_open(fmq_handle* h, const void* handle64, void** ptr);
 int32_t fmq_attach_peers(fmq_handle* h, int32_t rank, int32_t world, const void* const* peer_tables);
 int32_t fmq_push_local(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val,
                        size_t n, int32_t mem);
+int32_t fmq_push_local_packed(fmq_handle* h, const fmq_packed_columns* cols, size_t n, int32_t mem);
 int32_t fmq_fire_global(fmq_handle* h, int64_t watermark_after);
 int32_t fmq_retire(fmq_handle* h);
 

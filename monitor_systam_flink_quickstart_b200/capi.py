@@ -180,6 +180,7 @@ def _declare(lib, p: str, has_mem: bool = True):
         sig("retire", [vp])
         sig("push_packed", [vp, C.POINTER(FmqPackedColumns), sz, i64, i32])
         sig("stage_host", [vp, C.POINTER(FmqPackedColumns), sz])
+        sig("push_local_packed", [vp, C.POINTER(FmqPackedColumns), sz, i32])
         sig("partition_by_owner_noalloc", [i32, vp, vp, vp, vp, sz, C.c_uint32, vp, vp, vp, vp])
 
 
@@ -511,8 +512,10 @@ class Engine(EngineBase):
         arr = (C.c_void_p * world)(*[C.c_void_p(t) for t in tables])
         self._check(self._lib.fmq_attach_peers(self._h, rank, world, arr))
 
-    def push_local(self, ts, key, val):
-        self._check(self._lib.fmq_push_local(self._h, _ptr(ts), _ptr(key), _ptr(val), len(ts), FMQ_MEM_DEVICE))
+    def push_local(self, ts, key, val, ts_base: int = 0):
+        """Combiner mode, stage 1: host or device columns; narrow element sizes pick the packed format."""
+        pc, n, dev, _keep = self._packed(ts, key, val, ts_base)
+        self._check(self._lib.fmq_push_local_packed(self._h, C.byref(pc), n, FMQ_MEM_DEVICE if dev else FMQ_MEM_HOST))
 
     def fire_global(self, watermark_after: int = FMQ_WM_AUTO):
         self._check(self._lib.fmq_fire_global(self._h, watermark_after))

@@ -536,14 +536,14 @@ static bool same_cols(const InCols& a, const InCols& b) {
     return a.ts == b.ts && a.key == b.key && a.val == b.val && a.ts_w == b.ts_w && a.key_w == b.key_w && a.val_w == b.val_w && a.ts_base == b.ts_base;
 }
 
+// Stage 1 for columns as the caller hands them over: copy-in (host), widening (narrow columns) and
+// ingest, all queued without waiting.  *wait_copy = the event after which host columns are free again.
 template <typename V>
-static int push_cols_t(fmq_handle* h, const InCols& c, size_t n, int64_t wm_after, int32_t mem) {
+static int ingest_cols(fmq_handle* h, const InCols& c, size_t n, int32_t mem, cudaEvent_t* wait_copy) {
     const bool narrow = c.ts_w == 4 || c.key_w == 4 || c.val_w == 4;
-    cudaEvent_t* tev = h->tev[h->pushes % fmq_handle::TIMING_RING];
-    CU(h, cudaEventRecord(tev[0], h->stream));
-    const bool host = mem == FMQ_MEM_HOST && n > 0;
     const unsigned wgrid = (unsigned)h->num_sms * 8;
-    if (host) {
+    *wait_copy = nullptr;
+    if (mem == FMQ_MEM_HOST && n > 0) {
         fmq_handle::Staged& g = h->staged;
         if (g.valid && !(g.n == n && same_cols(g.c, c))) return set_err(h, FMQ_ERR_BAD_ARG, "a batch was staged with fmq_stage_host: the next host push must pass the same columns and n");
         if (!g.valid) { int s_ = queue_host_copy(h, c, n); if (s_) return s_; }
@@ -562,12 +562,8 @@ static int push_cols_t(fmq_handle* h, const InCols& c, size_t n, int64_t wm_afte
             }
             int s_ = stage_ingest<V>(h, sts + off, skey + off, sval + off, m); if (s_) return s_;
         }
-        int s_ = stage_fire<V>(h, n, wm_after, true); if (s_) return s_;
-        CU(h, cudaEventRecord(tev[3], h->stream));
-        h->pushes++;
-        CU(h, cudaEventRecord(h->ev_free[g.set], h->stream));
-        // the caller owns host columns only until this call returns: wait for the last copy
-        CU(h, cudaEventSynchronize(h->ev_piece[g.set][piece - 1]));
+        CU(h, cudaEventRecord(h->ev_free[g.set], h->stream));              // nothing after ingest reads the staging set
+        *wait_copy = h->ev_piece[g.set][piece - 1];
         return FMQ_OK;
     }
     const i64* dts = (const i64*)c.ts; const u64* dkey = (const u64*)c.key; const void* dval = c.val;
@@ -580,25 +576,56 @@ static int push_cols_t(fmq_handle* h, const InCols& c, size_t n, int64_t wm_afte
         if (c.key_w == 4) dkey = h->d_in_key;
         if (c.val_w == 4) dval = h->d_in_val;
     }
-    int s = run_chain<V>(h, dts, dkey, dval, n, wm_after); if (s) return s;
+    return stage_ingest<V>(h, dts, dkey, dval, n);
+}
+
+template <typename V>
+static int push_cols_t(fmq_handle* h, const InCols& c, size_t n, int64_t wm_after, int32_t mem) {
+    cudaEvent_t* tev = h->tev[h->pushes % fmq_handle::TIMING_RING];
+    CU(h, cudaEventRecord(tev[0], h->stream));
+    cudaEvent_t wait_copy = nullptr;
+    int s = ingest_cols<V>(h, c, n, mem, &wait_copy); if (s) return s;
+    s = stage_fire<V>(h, n, wm_after, true); if (s) return s;
     CU(h, cudaEventRecord(tev[3], h->stream));
     h->pushes++;
+    // the caller owns host columns only until this call returns: wait for the last copy
+    if (wait_copy) CU(h, cudaEventSynchronize(wait_copy));
     return FMQ_OK;
 }
 
-static int push_cols(fmq_handle* h, const InCols& c, size_t n, int64_t wm_after, int32_t mem) {
+// argument checks shared by every call that takes input columns
+static int check_cols(fmq_handle* h, const InCols& c, size_t n, int32_t mem) {
     if (h->sticky) return FMQ_ERR_POISONED;
     if (n > 0 && (!c.ts || !c.key || !c.val)) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
     if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
     if (mem != FMQ_MEM_HOST && mem != FMQ_MEM_DEVICE) return set_err(h, FMQ_ERR_BAD_ARG, "bad mem");
-    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: use fmq_push_local / fmq_fire_global / fmq_retire");
     if (mem == FMQ_MEM_DEVICE && n > 0) {
         const uintptr_t wide = (c.ts_w == 8 ? (uintptr_t)c.ts : 0) | (c.key_w == 8 ? (uintptr_t)c.key : 0) | (c.val_w == 8 ? (uintptr_t)c.val : 0);
         const uintptr_t thin = (c.ts_w == 4 ? (uintptr_t)c.ts : 0) | (c.key_w == 4 ? (uintptr_t)c.key : 0) | (c.val_w == 4 ? (uintptr_t)c.val : 0);
         if ((wide & 7) || (thin & 3)) return set_err(h, FMQ_ERR_BAD_ARG, "device columns must be aligned to their element size (32-byte alignment of 8-byte columns enables 256-bit loads)");
     }
+    return FMQ_OK;
+}
+
+static int push_cols(fmq_handle* h, const InCols& c, size_t n, int64_t wm_after, int32_t mem) {
+    int s = check_cols(h, c, n, mem); if (s) return s;
+    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: use fmq_push_local / fmq_fire_global / fmq_retire");
     CU(h, cudaSetDevice(h->device));
     return h->cfg.value_type == FMQ_VAL_F64 ? push_cols_t<double>(h, c, n, wm_after, mem) : push_cols_t<i64>(h, c, n, wm_after, mem);
+}
+
+// combiner mode, stage 1 (fmq_push_local / fmq_push_local_packed)
+static int push_local_cols(fmq_handle* h, const InCols& c, size_t n, int32_t mem) {
+    int s = check_cols(h, c, n, mem); if (s) return s;
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][0], h->stream));
+    cudaEvent_t wait_copy = nullptr;
+    s = h->cfg.value_type == FMQ_VAL_F64 ? ingest_cols<double>(h, c, n, mem, &wait_copy) : ingest_cols<i64>(h, c, n, mem, &wait_copy);
+    if (s) return s;
+    pack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "pack_scalars_kernel");
+    h->pending_n += n;
+    if (wait_copy) CU(h, cudaEventSynchronize(wait_copy));
+    return FMQ_OK;
 }
 
 extern "C" {
@@ -624,7 +651,6 @@ int32_t fmq_stage_host(fmq_handle* h, const fmq_packed_columns* p, size_t n) {
     int s = check_packed(h, p); if (s) return s;
     if (n == 0 || !p->ts || !p->key || !p->val) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_stage_host needs a non-empty batch");
     if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
-    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: host staging belongs to fmq_push_batch / fmq_push_packed");
     if (h->staged.valid) return set_err(h, FMQ_ERR_BAD_ARG, "one batch is already staged: push it first");
     CU(h, cudaSetDevice(h->device));
     const InCols c{p->ts, p->key, p->val, (int)p->ts_width, (int)p->key_width, (int)p->val_width, p->ts_width == 4 ? p->ts_base : 0};
@@ -842,19 +868,14 @@ int32_t fmq_attach_peers(fmq_handle* h, int32_t rank, int32_t world, const void*
 }
 int32_t fmq_push_local(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val, size_t n, int32_t mem) {
     if (!h) return FMQ_ERR_BAD_ARG;
-    if (h->sticky) return FMQ_ERR_POISONED;
-    if (n > 0 && (!ts || !key || !val)) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
-    if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
-    if (mem != FMQ_MEM_DEVICE) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_push_local takes device columns");
-    if (n > 0 && (((uintptr_t)ts | (uintptr_t)key | (uintptr_t)val) & 7)) return set_err(h, FMQ_ERR_BAD_ARG, "device columns must be 8-byte aligned");
-    CU(h, cudaSetDevice(h->device));
-    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][0], h->stream));
-    int s = (h->cfg.value_type == FMQ_VAL_F64) ? stage_ingest<double>(h, (const i64*)ts, (const u64*)key, val, n)
-                                               : stage_ingest<i64>(h, (const i64*)ts, (const u64*)key, val, n);
-    if (s) return s;
-    pack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "pack_scalars_kernel");
-    h->pending_n += n;
-    return FMQ_OK;
+    const InCols c{ts, key, val, 8, 8, 8, 0};
+    return push_local_cols(h, c, n, mem);
+}
+int32_t fmq_push_local_packed(fmq_handle* h, const fmq_packed_columns* p, size_t n, int32_t mem) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    int s = check_packed(h, p); if (s) return s;
+    const InCols c{p->ts, p->key, p->val, (int)p->ts_width, (int)p->key_width, (int)p->val_width, p->ts_width == 4 ? p->ts_base : 0};
+    return push_local_cols(h, c, n, mem);
 }
 int32_t fmq_fire_global(fmq_handle* h, int64_t watermark_after) {
     if (!h) return FMQ_ERR_BAD_ARG;

@@ -175,12 +175,13 @@ class CombinerOperator:
         self._token = torch.zeros(1, dtype=torch.int64, device=dev)
         dist.barrier(group=group)
 
-    def process_batch(self, ts, key, val, watermark_after: int = capi.FMQ_WM_AUTO):
-        """One micro-batch: everything below is queued on the engine's stream, no host round trip."""
+    def process_batch(self, ts, key, val, watermark_after: int = capi.FMQ_WM_AUTO, ts_base: int = 0):
+        """One micro-batch: everything below is queued on the engine's stream, no host round trip
+        (host columns: the call returns once they are copied in)."""
         import torch
         dist = self.dist
         with torch.cuda.stream(self._ext):
-            self.engine.push_local(ts, key, val)
+            self.engine.push_local(ts, key, val, ts_base)
             dist.all_reduce(self._x, op=dist.ReduceOp.MAX, group=self.group)     # global scalars + "all ingested"
             self.engine.fire_global(watermark_after)
             dist.all_reduce(self._token, group=self.group)                         # "all peers done reading"

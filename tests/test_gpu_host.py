@@ -154,10 +154,18 @@ def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt):
         parts = []
         for r, e in enumerate(engs):
             start = (i * world + r) * b
-            cols = generate_torch(spec, start, b, device="cuda:0")
-            torch.cuda.synchronize()
-            e.push_local(*cols); e.synchronize()
             parts.append(generate_numpy(spec, start, b))
+            if i % 3 == 0:                                        # device columns
+                cols = generate_torch(spec, start, b, device="cuda:0")
+                torch.cuda.synchronize()
+                e.push_local(*cols)
+            elif i % 3 == 1:                                      # host columns, narrow wire format
+                ts_n, key_n, val_n = parts[-1]
+                base = int(ts_n.min())
+                e.push_local((ts_n - base).astype(np.uint32), key_n.astype(np.uint32), val_n, base)
+            else:                                                 # host columns as they are
+                e.push_local(*parts[-1])
+            e.synchronize()
         fire(capi.FMQ_WM_AUTO)
         ref.push_batch(*[np.concatenate([p[j] for p in parts]) for j in range(3)])
     fire(capi.FMQ_WM_FINAL)
