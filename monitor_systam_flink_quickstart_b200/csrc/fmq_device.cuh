@@ -117,6 +117,23 @@ __device__ __forceinline__ u64 ldg_stream(const void* p) {
     return r;
 }
 
+// ---- accumulator updates: REDs that ask the L2 to keep their sector -------------------------------
+// The table is what should stay in the L2 while 400 MB of events stream through it per micro-batch:
+// evict_last on the REDs (and on the directory buckets) beside evict_first on the stream took the dense
+// ingest kernel from 0.290 to 0.272 ms per 2^24 events (A/B on the GPU, profiles/r01_notes.md).
+__device__ __forceinline__ u64 l2_keep_policy() {
+    u64 p; asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p)); return p;
+}
+__device__ __forceinline__ void red_add_keep(double* p, double v) {
+    asm volatile("red.global.add.L2::cache_hint.f64 [%0], %1, %2;" :: "l"(p), "d"(v), "l"(l2_keep_policy()) : "memory");
+}
+__device__ __forceinline__ void red_add_keep(u64* p, u64 v) {
+    asm volatile("red.global.add.L2::cache_hint.u64 [%0], %1, %2;" :: "l"(p), "l"(v), "l"(l2_keep_policy()) : "memory");
+}
+__device__ __forceinline__ void red_max_keep(u64* p, u64 v) {
+    asm volatile("red.global.max.L2::cache_hint.u64 [%0], %1, %2;" :: "l"(p), "l"(v), "l"(l2_keep_policy()) : "memory");
+}
+
 // ---- key directory: bucketized open addressing, keys are never removed ---------------------------
 // The directory is an array of 32-byte buckets of 4 keys; slot = 4 * bucket + position.  One
 // 256-bit load fetches a whole bucket in a single L2 sector request, so a lookup is normally ONE
@@ -128,7 +145,7 @@ __device__ __forceinline__ u64 ldg_stream(const void* p) {
 // inserters of one key walk the same sequence, so a key can never be entered twice.
 __device__ __forceinline__ ulonglong4 ld_bucket(const u64* bucket) {
     ulonglong4 r;
-    asm volatile("ld.global.L1::no_allocate.v4.b64 {%0, %1, %2, %3}, [%4];"
+    asm volatile("ld.global.L1::no_allocate.L2::evict_last.v4.b64 {%0, %1, %2, %3}, [%4];"
                  : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w) : "l"(bucket) : "memory");
     return r;
 }
