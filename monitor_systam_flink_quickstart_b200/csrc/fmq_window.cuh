@@ -705,12 +705,7 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
                 for (i64 p = p0; p <= p1; ++p) {
                     const u64 cell = (u64)((u32)p & a.g.ring_mask) * C + slot;
                     for (int r = 0; r < a.world; ++r) {                    // fixed rank order: deterministic double sums
-#ifdef FMQ_FIRE_STREAM
-                        ulonglong4 q;
-                        asm volatile("ld.global.L1::no_allocate.L2::evict_first.v4.b64 {%0, %1, %2, %3}, [%4];" : "=l"(q.x), "=l"(q.y), "=l"(q.z), "=l"(q.w) : "l"(a.peer_acc[r] + cell) : "memory");
-#else
                         const ulonglong4 q = *reinterpret_cast<const ulonglong4*>(a.peer_acc[r] + cell);
-#endif
                         if (is_f64) { cnt_d += __longlong_as_double((i64)q.x); sum_d += __longlong_as_double((i64)q.y); }
                         else        { cnt_i += q.x; sum_i += q.y; }
                         mx = q.z > mx ? q.z : mx; mn = q.w > mn ? q.w : mn;
@@ -742,33 +737,18 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
             if (a.emit_fired && a.walert_source != 0) block_append2<FIRE_THREADS>(fired, hit, &st->n_fired, a.f_cap, &st->n_walert, a.wa_cap, st, row_f, row_a);
             else if (a.emit_fired) { const u64 r_ = block_append<FIRE_THREADS>(fired ? 1u : 0u, &st->n_fired, a.f_cap, st); if (fired) row_f = r_; }
             else if (a.walert_source != 0) { const u64 r_ = block_append<FIRE_THREADS>(hit ? 1u : 0u, &st->n_walert, a.wa_cap, st); if (hit) row_a = r_; }
-#ifdef FMQ_FIRE_STREAM
-            if (row_f != ~0ull) {
-                __stcs((unsigned long long*)&a.f_key[row_f], (unsigned long long)key); __stcs((long long*)&a.f_wend[row_f], (long long)wend);
-                __stcs((long long*)&a.f_count[row_f], (long long)count); __stcs((unsigned long long*)&a.f_sum[row_f], (unsigned long long)sum_bits);
-                __stcs((unsigned long long*)&a.f_min[row_f], (unsigned long long)((a.g.agg_mask & 4u) ? Codec<V>::dec_min(mn) : 0));
-                __stcs((unsigned long long*)&a.f_max[row_f], (unsigned long long)((a.g.agg_mask & 8u) ? Codec<V>::dec_max(mx) : 0));
-            }
-#else
             if (row_f != ~0ull) {
                 a.f_key[row_f] = key; a.f_wend[row_f] = wend; a.f_count[row_f] = count; a.f_sum[row_f] = sum_bits;
                 a.f_min[row_f] = (a.g.agg_mask & 4u) ? Codec<V>::dec_min(mn) : 0;
                 a.f_max[row_f] = (a.g.agg_mask & 8u) ? Codec<V>::dec_max(mx) : 0;
             }
-#endif
             if (row_a != ~0ull) { a.wa_key[row_a] = key; a.wa_wend[row_a] = wend; a.wa_val[row_a] = v; }
         }
         // cleanup: WindowOperator.clearAllState for panes whose last window has fired
         if (live && a.clear_in_fire) {
             const ulonglong4 z = make_ulonglong4(0, 0, 0, 0);
-            for (i64 p = x_lo; p <= x_hi; ++p) {
-#ifdef FMQ_FIRE_STREAM
-                u64 pol; asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-                asm volatile("st.global.L2::cache_hint.v4.b64 [%0], {%1, %1, %1, %1}, %2;" :: "l"(&a.acc[(u64)((u32)p & a.g.ring_mask) * C + slot]), "l"(0ull), "l"(pol) : "memory");
-#else
+            for (i64 p = x_lo; p <= x_hi; ++p)
                 *reinterpret_cast<ulonglong4*>(&a.acc[(u64)((u32)p & a.g.ring_mask) * C + slot]) = z;
-#endif
-            }
         }
     }
     fired_local = warp_sum_u64(fired_local); alerts_local = warp_sum_u64(alerts_local);
