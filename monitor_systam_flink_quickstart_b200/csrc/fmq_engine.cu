@@ -168,6 +168,7 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     h->slot_bits = 1; while ((1ull << h->slot_bits) < h->capacity) h->slot_bits++;
     h->max_batch = cfg->max_batch ? (size_t)cfg->max_batch : ((size_t)1 << 22);
     if (h->max_batch >= 0xFFFFFFF0ull) return fail(FMQ_ERR_BAD_ARG, "max_batch must be < 2^32");
+    if (cfg->consec_n > 0 && h->max_batch > 0x80000000ull) return fail(FMQ_ERR_BAD_ARG, "max_batch must be <= 2^31 with the consecutive-readings rule");
     h->g.size = cfg->window_size_ms; h->g.slide = cfg->window_slide_ms; h->g.off = cfg->window_offset_ms;
     h->g.ring_mask = h->ring - 1; h->g.agg_mask = cfg->agg_mask | FMQ_AGG_COUNT; h->g.capacity = h->capacity;
     h->g.slide32 = (cfg->window_slide_ms > 0 && cfg->window_slide_ms < 0x100000000ll) ? (u32)cfg->window_slide_ms : 0;
@@ -376,7 +377,10 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
     CU(h, cudaEventRecord(tev[1], h->stream));
     if (n > 0 && keyed_enabled(c)) {
         const unsigned gb = (unsigned)((n + 255) / 256 < (size_t)h->num_sms * 8 ? (n + 255) / 256 : (size_t)h->num_sms * 8);
-        resolve_pack_kernel<<<gb, 256, 0, h->stream>>>(key, n, h->d_keys, h->capacity, c.key_mode == FMQ_KEYS_DENSE, h->d_st, h->d_pack[0]); LAUNCHED(h, "resolve_pack_kernel");
+        // consecutive rule alone: the over-threshold bit travels inside the sorted items, no value gathers
+        const bool pack_over = c.consec_n > 0 && !c.rolling_max_enabled;
+        resolve_pack_kernel<V><<<gb, 256, 0, h->stream>>>(key, static_cast<const V*>(val), n, h->d_keys, h->capacity, c.key_mode == FMQ_KEYS_DENSE,
+                                                          pack_over, c.consec_op, c.consec_threshold, h->d_st, h->d_pack[0]); LAUNCHED(h, "resolve_pack_kernel");
         int cur = 0;
         { int s_ = sort_items(h, h->d_pack, n, h->slot_bits, SlotKey{}, &cur); if (s_) return s_; }
         KeyedArgs k{};
@@ -387,9 +391,12 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         k.r_lead = h->kr_lead; k.r_fn_k = h->kr_k; k.r_fn_flags = h->kr_fl; k.r_fn_mkey = h->kr_mk; k.r_fn_mbits = h->kr_mb;
         k.r_in_c = h->kr_in_c; k.r_in_mkey = h->kr_in_mk; k.r_in_mbits = h->kr_in_mb;
         const size_t nranges = (n + KA_RANGE - 1) / KA_RANGE;
-        keyed_scan_kernel<V><<<(unsigned)((nranges + 7) / 8), 256, 0, h->stream>>>(k); LAUNCHED(h, "keyed_scan_kernel");
+        const unsigned sgrid = (unsigned)((nranges + 7) / 8);
+        if (pack_over) keyed_scan_kernel<V, false><<<sgrid, 256, 0, h->stream>>>(k); else keyed_scan_kernel<V, true><<<sgrid, 256, 0, h->stream>>>(k);
+        LAUNCHED(h, "keyed_scan_kernel");
         keyed_carry_kernel<<<1, 1024, 0, h->stream>>>(k, (u32)nranges, (u32)c.consec_n, c.consec_reset_on_fire); LAUNCHED(h, "keyed_carry_kernel");
-        keyed_lead_kernel<V><<<(unsigned)((nranges + 7) / 8), 256, 0, h->stream>>>(k); LAUNCHED(h, "keyed_lead_kernel");
+        if (pack_over) keyed_lead_kernel<V, false><<<sgrid, 256, 0, h->stream>>>(k); else keyed_lead_kernel<V, true><<<sgrid, 256, 0, h->stream>>>(k);
+        LAUNCHED(h, "keyed_lead_kernel");
         h->rolling_n = c.rolling_max_enabled ? n : 0;
     } else if (keyed_enabled(c)) {
         h->rolling_n = 0;

@@ -17,14 +17,25 @@ constexpr u32 KF_SEEN = 0x40000000u;       // dense-id mode: this id has been se
 constexpr u32 KF_COUNT_MASK = 0x3FFFFFFFu;
 
 // ---- step 1: key -> (slot << 32 | arrival index), one packed 8-byte item per event ----------------
-__global__ void __launch_bounds__(256) resolve_pack_kernel(const u64* __restrict__ key, size_t n, u64* dkeys, u64 dcap, int dense,
-                                                           DevState* st, u64* __restrict__ packed) {
+// When only the consecutive-readings rule runs (no rolling max), the one thing the rule needs from a
+// record, "is the value over the threshold", rides along as bit 31 of the item (KI_OVER): the scan then
+// streams the sorted items and never gathers values (ncu: the gathers were 1.15 GB of DRAM traffic per
+// 2^24 records, 0.31 ms; profiles/r01_ncu_keyed_chain_summary.txt).  max_batch <= 2^31 in that mode.
+constexpr u32 KI_OVER = 0x80000000u;
+template <typename V>
+__global__ void __launch_bounds__(256) resolve_pack_kernel(const u64* __restrict__ key, const V* __restrict__ val, size_t n, u64* dkeys, u64 dcap, int dense,
+                                                           int pack_over, int op, double thr, DevState* st, u64* __restrict__ packed) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const u64 k = ldg_stream(key + i);
         u32 s = SLOT_INVALID;
         if (k == KEY_EMPTY || (dense && k >= dcap)) atomicOr(&st->err_flags, ERRB_BAD_INPUT);
         else s = dense ? (u32)k : dir_find_or_insert(dkeys, dcap, k, st);
-        packed[i] = ((u64)s << 32) | (u32)i;
+        u32 low = (u32)i;
+        if (pack_over) {
+            const u64 vb = ldg_stream(val + i); V v; memcpy(&v, &vb, 8);
+            if (cmp_op((double)v, op, thr)) low |= KI_OVER;
+        }
+        packed[i] = ((u64)s << 32) | low;
     }
 }
 
@@ -227,6 +238,7 @@ struct KCarry { bool hr; u32 k; bool mc; bool hasm; u64 mkey, mbits; };
 // `hi` and the number of positions before the first run head (`lead`).
 template <typename V>
 __device__ __forceinline__ void keyed_scan_range(const KeyedArgs& a, size_t lo, size_t hi, KCarry& c, u32& lead, u64& nalert) {
+    const bool rolling = a.rolling_enabled;
     const V* __restrict__ val = static_cast<const V*>(a.val);
     const u32 lane = threadIdx.x & 31;
     const u32 N = (u32)a.consec_n;
@@ -270,7 +282,7 @@ __device__ __forceinline__ void keyed_scan_range(const KeyedArgs& a, size_t lo, 
         bool hr = false; u32 k = 0;
         if (N > 0 && act) { hr = !over; k = over ? 1u : 0u; if (head) { k = over ? (fl & KF_COUNT_MASK) + 1 : 0; hr = true; } }
         u64 mkey = act ? Codec<V>::cmp_key(v) : 0, mbits = vb; bool seg = head;        // seg = "a head lies at or before me in this round"
-        if (a.rolling_enabled && head && (fl & KF_HAS_MAX)) {
+        if (rolling && head && (fl & KF_HAS_MAX)) {
             const u64 sk = Codec<V>::cmp_key(Codec<V>::from_bits(smax));
             if (sk > mkey) { mkey = sk; mbits = smax; }
         }
@@ -306,14 +318,14 @@ __device__ __forceinline__ void keyed_scan_range(const KeyedArgs& a, size_t lo, 
             if (row != ~0ull) { a.ca_ts[row] = a.ts[idx]; a.ca_key[row] = a.key[idx]; a.ca_val[row] = vb; }
             nalert += (alert && emit) ? 1 : 0;
         }
-        if (a.rolling_enabled && emit) a.rolling_out[idx] = mbits;
+        if (rolling && emit) a.rolling_out[idx] = mbits;
         // run tails write the key's state back
         const u32 next_slot = __shfl_down_sync(0xffffffffu, slot, 1);
         const u64 peek = (p + 1 < a.n) ? a.sorted[p + 1] : ~0ull;
         const bool tail = emit && ((lane == 31 || p + 1 >= hi) ? ((u32)(peek >> 32) != slot) : (next_slot != slot));
         if (tail) {
-            a.kflags[slot] = (a.rolling_enabled ? KF_HAS_MAX : 0u) | KF_SEEN | (state & KF_COUNT_MASK);
-            if (a.rolling_enabled) a.kmax[slot] = mbits;
+            a.kflags[slot] = (rolling ? KF_HAS_MAX : 0u) | KF_SEEN | (state & KF_COUNT_MASK);
+            if (rolling) a.kmax[slot] = mbits;
         }
         // carry = function/state after the last active lane of this round
         const unsigned am = __ballot_sync(0xffffffffu, act);
@@ -322,14 +334,91 @@ __device__ __forceinline__ void keyed_scan_range(const KeyedArgs& a, size_t lo, 
             const bool l_seg = __shfl_sync(0xffffffffu, (int)seg, last) != 0;
             c.hr = __shfl_sync(0xffffffffu, (int)(hr), last) != 0 || l_seg;
             c.k = __shfl_sync(0xffffffffu, known_c ? state : k, last);
-            c.mc = l_seg || c.mc; c.hasm = a.rolling_enabled != 0;
+            c.mc = l_seg || c.mc; c.hasm = rolling;
             c.mkey = __shfl_sync(0xffffffffu, mkey, last); c.mbits = __shfl_sync(0xffffffffu, mbits, last);
             c_slot = __shfl_sync(0xffffffffu, slot, last);
         }
     }
 }
 
+
+// The consecutive-readings rule alone (items carry KI_OVER): the same contract as keyed_scan_range, but a
+// round of 32 records needs no scan at all.  With Z = lanes whose reading is NOT over the threshold and
+// H = run heads (both as ballots), lane i's counter is
+//     i - z                      if the last not-over lane z <= i lies at or after the last head h <= i
+//     stored(h) + (i - h + 1)    if the last head lies after it (lanes h..i are all over)
+//     carried + (i + 1)          if the round has neither up to lane i
+// i.e. two ballots, two count-leading-zeros and one shuffle instead of five scan steps, and no value is
+// read except for the rare alert rows.
 template <typename V>
+__device__ __forceinline__ void consec_scan_range(const KeyedArgs& a, size_t lo, size_t hi, KCarry& c, u32& lead, u64& nalert) {
+    const V* __restrict__ val = static_cast<const V*>(a.val);
+    const u32 lane = threadIdx.x & 31;
+    const u32 N = (u32)a.consec_n;
+    const u32 le = 0xFFFFFFFFu >> (31 - lane);                        // lanes <= me
+    u32 c_slot = lo > 0 ? (u32)(a.sorted[lo - 1] >> 32) : SLOT_INVALID;
+    bool seen_head = false; lead = (u32)(hi - lo);
+    // Software pipeline, two deep: items are requested two rounds ahead, the stored state of run heads
+    // (a gather that needs the item) one round ahead.  Items are read up to a.n, not hi: the first item
+    // after the range tells the last lane whether its run ends here.
+    auto load_item = [&](size_t pos) { const size_t p = pos + lane; return p < a.n ? a.sorted[p] : ~0ull; };
+    auto classify = [&](u64 item, size_t pos, u32 prev_last_slot, bool& act, bool& head, u32& fl) {
+        const size_t p = pos + lane;
+        const u32 slot = (u32)(item >> 32);
+        act = p < hi && slot != SLOT_INVALID;
+        const u32 prev_slot = __shfl_up_sync(0xffffffffu, slot, 1);
+        head = act && (lane == 0 ? (slot != prev_last_slot || p == 0) : (slot != prev_slot));
+        fl = head ? a.kflags[slot] : 0u;
+    };
+    u64 it_cur = load_item(lo), it_nxt = load_item(lo + 32);
+    bool act, head; u32 fl;
+    classify(it_cur, lo, c_slot, act, head, fl);
+    for (size_t pos = lo; pos < hi; pos += 32) {
+        const u64 it_nn = load_item(pos + 64);                       // in flight for two rounds
+        const u32 slot = (u32)(it_cur >> 32), idx = (u32)it_cur & ~KI_OVER;
+        const bool over = act && ((u32)it_cur & KI_OVER);
+        const unsigned am = __ballot_sync(0xffffffffu, act);         // a prefix of the lanes: invalid items sort last
+        const u32 last_slot = am ? __shfl_sync(0xffffffffu, slot, 31 - __clz(am)) : c_slot;
+        bool act_n, head_n; u32 fl_n;
+        classify(it_nxt, pos + 32, last_slot, act_n, head_n, fl_n);  // its state gather is in flight for one round
+        const unsigned hm = __ballot_sync(0xffffffffu, head);
+        const unsigned zm = __ballot_sync(0xffffffffu, act && !over);
+        if (hm && !seen_head) { seen_head = true; lead = (u32)(pos - lo) + (u32)(__ffs(hm) - 1); }
+        const int z = 31 - __clz((int)(zm & le)), h = 31 - __clz((int)(hm & le));          // -1 if none
+        const u32 stored = __shfl_sync(0xffffffffu, fl & KF_COUNT_MASK, h < 0 ? 0 : h);
+        u32 k; bool known_c;
+        if (z >= 0 && z >= h) { k = lane - (u32)z; known_c = true; }
+        else if (h >= 0)      { k = stored + (lane - (u32)h + 1); known_c = true; }
+        else                  { k = c.k + lane + 1; known_c = c.hr; }
+        const bool known_m = h >= 0 || c.mc;                          // a head of my run has been seen by this warp (or its state was handed in)
+        u32 state = k; bool alert = false;
+        if (act && known_c) {
+            if (a.consec_reset) { state = k % N; alert = over && state == 0; }             // the counter just reached N (and went back to 0)
+            else { if (state > KF_COUNT_MASK) state = KF_COUNT_MASK; alert = state >= N; }
+        }
+        const bool emit = act && known_m;
+        const u64 row = warp_append(alert && emit, &a.st->n_calert, a.ca_cap, a.st);       // one reservation per warp round
+        if (row != ~0ull) { a.ca_ts[row] = a.ts[idx]; a.ca_key[row] = a.key[idx]; memcpy(&a.ca_val[row], &val[idx], 8); }
+        nalert += (alert && emit) ? 1 : 0;
+        // run tails write the key's state back
+        const u32 down_slot = __shfl_down_sync(0xffffffffu, slot, 1);
+        const u32 first_nxt = __shfl_sync(0xffffffffu, (u32)(it_nxt >> 32), 0);
+        const bool tail = emit && (lane == 31 ? first_nxt : down_slot) != slot;
+        if (tail) a.kflags[slot] = KF_SEEN | (state & KF_COUNT_MASK);
+        // carry = function/state after the last active lane of this round
+        if (am) {
+            const int last = 31 - __clz(am);
+            c.hr = __shfl_sync(0xffffffffu, (int)known_c, last) != 0;
+            c.k = __shfl_sync(0xffffffffu, known_c ? state : k, last);
+            c.mc = c.mc || (hm & (0xFFFFFFFFu >> (31 - last))) != 0;
+            c_slot = __shfl_sync(0xffffffffu, slot, last);
+        }
+        it_cur = it_nxt; it_nxt = it_nn; act = act_n; head = head_n; fl = fl_n;
+    }
+    c.hasm = false; c.mkey = 0; c.mbits = 0;
+}
+
+template <typename V, bool GATHER>
 __global__ void __launch_bounds__(256) keyed_scan_kernel(const __grid_constant__ KeyedArgs a) {
     const u32 lane = threadIdx.x & 31;
     const size_t range = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -338,7 +427,7 @@ __global__ void __launch_bounds__(256) keyed_scan_kernel(const __grid_constant__
     const size_t hi = (lo + KA_RANGE < a.n) ? lo + KA_RANGE : a.n;
     KCarry c{false, 0u, false, false, 0ull, 0ull};                 // identity: nothing known about what precedes
     u32 lead; u64 nalert = 0;
-    keyed_scan_range<V>(a, lo, hi, c, lead, nalert);
+    if constexpr (GATHER) keyed_scan_range<V>(a, lo, hi, c, lead, nalert); else consec_scan_range<V>(a, lo, hi, c, lead, nalert);
     if (lane == 0) {
         a.r_lead[range] = lead;
         a.r_fn_k[range] = c.k; a.r_fn_flags[range] = (c.hr ? KFN_HR : 0u) | (c.mc ? KFN_MC : 0u) | (c.hasm ? KFN_HASM : 0u);
@@ -379,7 +468,7 @@ __global__ void __launch_bounds__(1024) keyed_carry_kernel(const KeyedArgs a, u3
     }
 }
 
-template <typename V>
+template <typename V, bool GATHER>
 __global__ void __launch_bounds__(256) keyed_lead_kernel(const __grid_constant__ KeyedArgs a) {
     const u32 lane = threadIdx.x & 31;
     const size_t range = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -389,7 +478,7 @@ __global__ void __launch_bounds__(256) keyed_lead_kernel(const __grid_constant__
     if (lead_len == 0) return;
     KCarry c{true, a.r_in_c[range], true, a.rolling_enabled != 0, a.r_in_mkey[range], a.r_in_mbits[range]};   // the entering state is a constant
     u32 lead; u64 nalert = 0;
-    keyed_scan_range<V>(a, lo, lo + lead_len, c, lead, nalert);
+    if constexpr (GATHER) keyed_scan_range<V>(a, lo, lo + lead_len, c, lead, nalert); else consec_scan_range<V>(a, lo, lo + lead_len, c, lead, nalert);
     nalert = warp_sum_u64(nalert);
     if (lane == 0 && nalert) atomicAdd(&a.st->consec_alerts, nalert);
 }

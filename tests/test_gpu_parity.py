@@ -243,16 +243,18 @@ def test_int64_sum_wraps_like_java_long():
 @pytest.mark.parametrize("vt", ["f64", "i64"])
 @pytest.mark.parametrize("reset", [1, 0])
 @pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
-def test_keyed_state_parity(vt, reset, key_mode):
+@pytest.mark.parametrize("rolling", [1, 0])          # 0: the over-threshold bit rides in the sorted items, no value gathers
+def test_keyed_state_parity(vt, reset, key_mode, rolling):
     thr = 50.0 if vt == "f64" else 500_000.0
-    kw = dict(value_type=capi.FMQ_VAL_F64 if vt == "f64" else capi.FMQ_VAL_I64, rolling_max_enabled=1, key_mode=key_mode,
+    kw = dict(value_type=capi.FMQ_VAL_F64 if vt == "f64" else capi.FMQ_VAL_I64, rolling_max_enabled=rolling, key_mode=key_mode,
               consec_n=3, consec_threshold=thr, consec_reset_on_fire=reset, **SMALL)
     gpu, cpu = pair(**kw)
     spec = StreamSpec(n_keys=700, events_per_ms=5, value_type=vt)
     for b, n in enumerate([1, 5000, 33, 60_000, 0, 4097]):
         ts, key, val = generate_numpy(spec, b * 70_000, n)
         gpu.push_batch(ts, key, val); cpu.push_batch(ts, key, val)
-        np.testing.assert_array_equal(gpu.poll_rolling_max(n).view(np.uint64), cpu.poll_rolling_max(n).view(np.uint64))
+        if rolling:
+            np.testing.assert_array_equal(gpu.poll_rolling_max(n).view(np.uint64), cpu.poll_rolling_max(n).view(np.uint64))
     assert_events_equal(gpu.poll_consec_alerts(), cpu.poll_consec_alerts())
     keys = np.arange(0, 800, dtype=np.uint64)
     fg, cg, rg = gpu.key_state(keys); fc, cc, rc = cpu.key_state(keys)
@@ -262,16 +264,18 @@ def test_keyed_state_parity(vt, reset, key_mode):
 
 
 @pytest.mark.parametrize("n_keys,thr", [(3, 50.0), (1, 20.0), (40, 90.0), (100_000, 50.0)])
-def test_keyed_state_long_runs_and_sparse_keys(n_keys, thr):
+@pytest.mark.parametrize("rolling", [1, 0])
+def test_keyed_state_long_runs_and_sparse_keys(n_keys, thr, rolling):
     """Heavy-hitter keys (one run spans many warps' ranges and rounds) and very sparse keys."""
-    kw = dict(rolling_max_enabled=1, consec_n=3, consec_threshold=thr, consec_reset_on_fire=1,
+    kw = dict(rolling_max_enabled=rolling, consec_n=3, consec_threshold=thr, consec_reset_on_fire=1,
               table_capacity=1 << 18, max_batch=1 << 17)
     gpu, cpu = pair(**kw)
     spec = StreamSpec(n_keys=n_keys, events_per_ms=5)
     for b, n in enumerate([70_001, 100_000, 513]):
         ts, key, val = generate_numpy(spec, b * 100_000, n)
         gpu.push_batch(ts, key, val); cpu.push_batch(ts, key, val)
-        np.testing.assert_array_equal(gpu.poll_rolling_max(n).view(np.uint64), cpu.poll_rolling_max(n).view(np.uint64))
+        if rolling:
+            np.testing.assert_array_equal(gpu.poll_rolling_max(n).view(np.uint64), cpu.poll_rolling_max(n).view(np.uint64))
         assert_events_equal(gpu.poll_consec_alerts(), cpu.poll_consec_alerts())
     keys = np.arange(0, min(n_keys, 5000), dtype=np.uint64)
     fg, cg, rg = gpu.key_state(keys); fc, cc, rc = cpu.key_state(keys)

@@ -1,0 +1,14 @@
+"""A few pushes of BASELINE.json configs[1] (3 consecutive readings > 90 per host, 100 K hosts, dense ids), for ncu captures
+of the keyed chain.  usage: python tools/run_keyed_once.py [pushes]"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+import torch
+from monitor_systam_flink_quickstart_b200 import capi
+from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_torch
+B = 1 << 24
+eng = capi.Engine(max_batch=B, consec_n=3, consec_threshold=90.0, consec_reset_on_fire=1, table_capacity=100_000, key_mode=1, calert_capacity=B // 8)
+spec = StreamSpec(n_keys=100_000)
+for i in range(int(sys.argv[1]) if len(sys.argv) > 1 else 4):
+    cols = generate_torch(spec, i * B, B); torch.cuda.synchronize()
+    eng.push_batch(*cols); eng.synchronize()
+    print(i, eng.push_timing(0), len(eng.poll_consec_alerts(chunk=1 << 24)), flush=True)
