@@ -108,6 +108,11 @@ __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in
 // a lone 8-byte store; ncu showed those partial-sector writes congesting the memory system
 // (782 MB of DRAM traffic for 268 MB of payload, 455 us per pass of 2^24 items).
 constexpr int PS_IPT = PS_CHUNK / 256;          // items per thread
+// 3 resident blocks (<= 85 registers) measured best: 2 (123 registers, no spills) 0.19 ms per pass of 2^24
+// items, 3 -> 0.165 ms; re-reading the items in phase 3 to free 32 more registers gained nothing.
+#ifndef FMQ_PS_MINB
+#define FMQ_PS_MINB 3
+#endif
 
 // Lanes of `am` holding the same BITS-bit digit, from BITS ballots.  MATCH.ANY does this in one
 // instruction but was measured at ~150 cycles per warp instruction per SM on B200 (it bounded both
@@ -123,7 +128,7 @@ __device__ __forceinline__ unsigned match_digit(unsigned am, u32 d) {
     return m;
 }
 template <int BITS, typename KeyFn>
-__global__ void __launch_bounds__(256) ps_scatter_tile_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t n, u32 nchunks, u32 shift,
+__global__ void __launch_bounds__(256, FMQ_PS_MINB) ps_scatter_tile_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t n, u32 nchunks, u32 shift,
                                                               const u32* __restrict__ offsets, KeyFn keyfn) {
     constexpr u32 NB = 1u << BITS;
     extern __shared__ __align__(16) unsigned char ps_tile_smem[];
