@@ -22,23 +22,6 @@ constexpr u32 KF_COUNT_MASK = 0x3FFFFFFFu;
 // streams the sorted items and never gathers values (ncu: the gathers were 1.15 GB of DRAM traffic per
 // 2^24 records, 0.31 ms; profiles/r01_ncu_keyed_chain_summary.txt).  max_batch <= 2^31 in that mode.
 constexpr u32 KI_OVER = 0x80000000u;
-template <typename V>
-__global__ void __launch_bounds__(256) resolve_pack_kernel(const u64* __restrict__ key, const V* __restrict__ val, size_t n, u64* dkeys, u64 dcap, int dense,
-                                                           int pack_over, int op, double thr, DevState* st, u64* __restrict__ packed) {
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const u64 k = ldg_stream(key + i);
-        u32 s = SLOT_INVALID;
-        if (k == KEY_EMPTY || (dense && k >= dcap)) atomicOr(&st->err_flags, ERRB_BAD_INPUT);
-        else s = dense ? (u32)k : dir_find_or_insert(dkeys, dcap, k, st);
-        u32 low = (u32)i;
-        if (pack_over) {
-            const u64 vb = ldg_stream(val + i); V v; memcpy(&v, &vb, 8);
-            if (cmp_op((double)v, op, thr)) low |= KI_OVER;
-        }
-        packed[i] = ((u64)s << 32) | low;
-    }
-}
-
 // ---- step 2: stable LSD radix sort of the packed items by slot, BITS (<= 11) bits per pass -------
 // Same scheme as the owner split (a warp owns a contiguous chunk, counts[digit][chunk] scanned
 // digit-major), tuned for this job: 8-byte items, up to 2048 bins so that 22 slot bits need two
@@ -47,6 +30,8 @@ __global__ void __launch_bounds__(256) resolve_pack_kernel(const u64* __restrict
 constexpr u32 PS_CHUNK = 4096;
 constexpr int PS_AHEAD = 4;
 __host__ __device__ inline u32 ps_num_chunks(size_t n) { return (u32)((n + PS_CHUNK - 1) / PS_CHUNK); }
+// digit width of a sort over `key_bits` bits: as few passes as 11-bit digits allow, bits spread evenly
+__host__ __device__ inline u32 ps_pass_bits(u32 key_bits) { const u32 passes = (key_bits + 10) / 11; const u32 b = (key_bits + passes - 1) / passes; return b < 6 ? 6 : b; }
 
 // KeyFn: u64 operator()(u64 item) -> the sort key of an item; a pass ranks by (key >> shift) & (2^BITS - 1)
 struct SlotKey {            // item = (slot << 32 | index): sort by slot
@@ -99,6 +84,46 @@ __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in
     }
     __syncwarp();
     if (!SCATTER) for (u32 d = lane; d < NB; d += 32) counts[(size_t)d * nchunks + chunk] = bins[d];
+}
+
+// Step 1, fused with the counting half of the first radix pass: the warp that resolves a chunk of keys also
+// counts the first digit of the items it writes (saves one read of the packed items: 35 us per 2^24).
+template <typename V, int BITS>
+__global__ void __launch_bounds__(256) resolve_hist_kernel(const u64* __restrict__ key, const V* __restrict__ val, size_t n, u32 nchunks, u64* dkeys, u64 dcap, int dense,
+                                                           int pack_over, int op, double thr, DevState* st, u64* __restrict__ packed, u32* __restrict__ counts) {
+    extern __shared__ u32 ps_smem[];
+    constexpr u32 NB = 1u << BITS;
+    const u32 wl = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    u32* bins = ps_smem + wl * NB;
+    const u32 chunk = blockIdx.x * 8 + wl;
+    if (chunk >= nchunks) return;
+    for (u32 d = lane; d < NB; d += 32) bins[d] = 0u;
+    __syncwarp();
+    const size_t lo = (size_t)chunk * PS_CHUNK;
+    const size_t hi = (lo + PS_CHUNK < n) ? lo + PS_CHUNK : n;
+    for (size_t i0 = lo; i0 < hi; i0 += 32 * PS_AHEAD) {
+        u64 kk[PS_AHEAD], vv[PS_AHEAD];
+#pragma unroll
+        for (int r = 0; r < PS_AHEAD; ++r) {
+            const size_t i = i0 + r * 32 + lane;
+            kk[r] = i < hi ? ldg_stream(key + i) : 0; vv[r] = (pack_over && i < hi) ? ldg_stream(val + i) : 0;
+        }
+#pragma unroll
+        for (int r = 0; r < PS_AHEAD; ++r) {
+            const size_t i = i0 + r * 32 + lane;
+            if (i >= hi) continue;
+            const u64 k = kk[r];
+            u32 s = SLOT_INVALID;
+            if (k == KEY_EMPTY || (dense && k >= dcap)) atomicOr(&st->err_flags, ERRB_BAD_INPUT);
+            else s = dense ? (u32)k : dir_find_or_insert(dkeys, dcap, k, st);
+            u32 low = (u32)i;
+            if (pack_over) { V v; memcpy(&v, &vv[r], 8); if (cmp_op((double)v, op, thr)) low |= KI_OVER; }
+            packed[i] = ((u64)s << 32) | low;
+            atomicAdd(&bins[s & (NB - 1)], 1u);
+        }
+    }
+    __syncwarp();
+    for (u32 d = lane; d < NB; d += 32) counts[(size_t)d * nchunks + chunk] = bins[d];
 }
 
 // Scatter half of a radix pass, one BLOCK per chunk of PS_CHUNK items: the chunk is sorted by digit in
@@ -249,34 +274,34 @@ __device__ __forceinline__ void keyed_scan_range(const KeyedArgs& a, size_t lo, 
     const u32 N = (u32)a.consec_n;
     u32 c_slot = lo > 0 ? (u32)(a.sorted[lo - 1] >> 32) : SLOT_INVALID;
     bool seen_head = false; lead = (u32)(hi - lo);
-    // Software pipeline: the item, its value (random gather) and the stored state at run heads (another
-    // gather) of round r+1 are requested before round r is computed, so a warp is not three dependent
-    // memory round trips per 32 records.
-    struct Stage { u64 item; V v; bool act, head; u32 fl; u64 smax; };
-    auto fetch = [&](size_t pos, u32 prev_last_slot) {
+    // Software pipeline, two deep: items are requested two rounds ahead; the value (random gather) and the
+    // stored state at run heads (another gather), which need the item, one round ahead.  Items are read up
+    // to a.n, not hi: the first item after the range tells the last lane whether its run ends here.
+    struct Stage { V v; bool act, head; u32 fl; u64 smax; };
+    auto load_item = [&](size_t pos) { const size_t p = pos + lane; return p < a.n ? a.sorted[p] : ~0ull; };
+    auto classify = [&](u64 item, size_t pos, u32 prev_last_slot) {
         Stage s;
         const size_t p = pos + lane;
-        const bool in = p < hi;
-        s.item = in ? a.sorted[p] : ~0ull;
-        const u32 slot = (u32)(s.item >> 32);
-        s.act = in && slot != SLOT_INVALID;
+        const u32 slot = (u32)(item >> 32);
+        s.act = p < hi && slot != SLOT_INVALID;
         const u32 prev_slot = __shfl_up_sync(0xffffffffu, slot, 1);
         s.head = s.act && (lane == 0 ? (slot != prev_last_slot || p == 0) : (slot != prev_slot));
-        s.v = s.act ? val[(u32)s.item] : V(0);
+        s.v = s.act ? val[(u32)item] : V(0);
         s.fl = 0; s.smax = 0;
         if (s.head) { s.fl = a.kflags[slot]; s.smax = a.kmax[slot]; }
         return s;
     };
-    Stage nxt = fetch(lo, c_slot);
+    u64 it_cur = load_item(lo), it_nxt = load_item(lo + 32);
+    Stage cur = classify(it_cur, lo, c_slot);
     for (size_t pos = lo; pos < hi; pos += 32) {
-        const Stage cur = nxt;
-        const size_t p = pos + lane;
-        const u64 item = cur.item;
+        const u64 it_nn = load_item(pos + 64);                       // in flight for two rounds
+        const u64 item = it_cur;
         const u32 slot = (u32)(item >> 32), idx = (u32)item;
         const bool act = cur.act, head = cur.head;
         const unsigned am0 = __ballot_sync(0xffffffffu, act);
         const u32 last_slot = am0 ? __shfl_sync(0xffffffffu, slot, 31 - __clz(am0)) : c_slot;
-        if (pos + 32 < hi) nxt = fetch(pos + 32, last_slot);          // requests of the next round are in flight from here on
+        const Stage nxt = classify(it_nxt, pos + 32, last_slot);      // its gathers are in flight for one round
+        const u32 first_nxt = __shfl_sync(0xffffffffu, (u32)(it_nxt >> 32), 0);
         const unsigned hm = __ballot_sync(0xffffffffu, head);
         if (hm && !seen_head) { seen_head = true; lead = (u32)(pos - lo) + (u32)(__ffs(hm) - 1); }
         const V v = cur.v;
@@ -326,8 +351,7 @@ __device__ __forceinline__ void keyed_scan_range(const KeyedArgs& a, size_t lo, 
         if (rolling && emit) a.rolling_out[idx] = mbits;
         // run tails write the key's state back
         const u32 next_slot = __shfl_down_sync(0xffffffffu, slot, 1);
-        const u64 peek = (p + 1 < a.n) ? a.sorted[p + 1] : ~0ull;
-        const bool tail = emit && ((lane == 31 || p + 1 >= hi) ? ((u32)(peek >> 32) != slot) : (next_slot != slot));
+        const bool tail = emit && (lane == 31 ? first_nxt : next_slot) != slot;
         if (tail) {
             a.kflags[slot] = (rolling ? KF_HAS_MAX : 0u) | KF_SEEN | (state & KF_COUNT_MASK);
             if (rolling) a.kmax[slot] = mbits;
@@ -343,9 +367,9 @@ __device__ __forceinline__ void keyed_scan_range(const KeyedArgs& a, size_t lo, 
             c.mkey = __shfl_sync(0xffffffffu, mkey, last); c.mbits = __shfl_sync(0xffffffffu, mbits, last);
             c_slot = __shfl_sync(0xffffffffu, slot, last);
         }
+        it_cur = it_nxt; it_nxt = it_nn; cur = nxt;
     }
 }
-
 
 // The consecutive-readings rule alone (items carry KI_OVER): the same contract as keyed_scan_range, but a
 // round of 32 records needs no scan at all.  With Z = lanes whose reading is NOT over the threshold and
@@ -442,34 +466,54 @@ __global__ void __launch_bounds__(256) keyed_scan_kernel(const __grid_constant__
     if (lane == 0 && nalert) atomicAdd(&a.st->consec_alerts, nalert);
 }
 
-// state entering range r = E[r-1] o ... o E[0]; one block, each thread owns a contiguous chunk of ranges
+// state entering range r = E[r-1] o ... o E[0]; one block, each thread owns a contiguous chunk of ranges.
+// Composition of the range functions is associative: the 1024 chunk functions are scanned with warp
+// shuffles (a first version let thread 0 walk them: 65 us per 8192 ranges, 9 % of the whole keyed chain).
+struct KFn { u32 k, fl; u64 mk, mb; };
+__device__ __forceinline__ void kfn_then(KFn& f, const KFn& g, u32 N, int reset) {                       // f := "f, then g"
+    if (g.fl & KFN_HR) { f.k = g.k; f.fl |= KFN_HR; } else { f.k += g.k; if (reset && N) f.k %= N; }
+    if (g.fl & KFN_MC) { f.mk = g.mk; f.mb = g.mb; f.fl |= KFN_MC | KFN_HASM; }
+    else if (g.fl & KFN_HASM) { if (!(f.fl & KFN_HASM) || !(f.mk > g.mk)) { f.mk = g.mk; f.mb = g.mb; } f.fl |= KFN_HASM; }
+}
+__device__ __forceinline__ KFn kfn_shfl_up(const KFn& f, int o) {
+    KFn r; r.k = __shfl_up_sync(0xffffffffu, f.k, o); r.fl = __shfl_up_sync(0xffffffffu, f.fl, o);
+    r.mk = __shfl_up_sync(0xffffffffu, f.mk, o); r.mb = __shfl_up_sync(0xffffffffu, f.mb, o);
+    return r;
+}
 __global__ void __launch_bounds__(1024) keyed_carry_kernel(const KeyedArgs a, u32 nranges, u32 N, int reset) {
-    __shared__ u32 s_k[1024], s_fl[1024]; __shared__ u64 s_mk[1024], s_mb[1024];
-    const u32 t = threadIdx.x;
+    __shared__ KFn s_w[32];
+    const u32 t = threadIdx.x, lane = t & 31, w = t >> 5;
     const u32 per = (nranges + 1023) / 1024;
-    const u32 r0 = t * per, r1 = (r0 + per < nranges) ? r0 + per : nranges;
-    auto compose = [&](u32& fk, u32& ffl, u64& fmk, u64& fmb, u32 gk, u32 gfl, u64 gmk, u64 gmb) {   // f then g -> f
-        if (gfl & KFN_HR) { fk = gk; ffl |= KFN_HR; } else { fk += gk; if (reset && N) fk %= N; }
-        if (gfl & KFN_MC) { fmk = gmk; fmb = gmb; ffl |= KFN_MC | KFN_HASM; }
-        else if (gfl & KFN_HASM) { if (!(ffl & KFN_HASM) || !(fmk > gmk)) { fmk = gmk; fmb = gmb; } ffl |= KFN_HASM; }
-    };
-    u32 k = 0, fl = 0; u64 mk = 0, mb = 0;                          // identity
-    for (u32 r = r0; r < r1; ++r) compose(k, fl, mk, mb, a.r_fn_k[r], a.r_fn_flags[r], a.r_fn_mkey[r], a.r_fn_mbits[r]);
-    s_k[t] = k; s_fl[t] = fl; s_mk[t] = mk; s_mb[t] = mb;
+    const u32 r0 = t * per < nranges ? t * per : nranges, r1 = (r0 + per < nranges) ? r0 + per : nranges;
+    KFn mine{0, 0, 0, 0};                                           // identity
+    for (u32 r = r0; r < r1; ++r) kfn_then(mine, KFn{a.r_fn_k[r], a.r_fn_flags[r], a.r_fn_mkey[r], a.r_fn_mbits[r]}, N, reset);
+    // inclusive scan inside the warp
+    KFn inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        KFn left = kfn_shfl_up(inc, o);
+        if ((int)lane >= o) { kfn_then(left, inc, N, reset); inc = left; }
+    }
+    if (lane == 31) s_w[w] = inc;
     __syncthreads();
-    if (t == 0) {                                                   // exclusive scan of the 1024 chunk functions
-        u32 ck = 0, cfl = 0; u64 cmk = 0, cmb = 0;
-        for (u32 i = 0; i < 1024; ++i) {
-            const u32 tk = s_k[i], tfl = s_fl[i]; const u64 tmk = s_mk[i], tmb = s_mb[i];
-            s_k[i] = ck; s_fl[i] = cfl; s_mk[i] = cmk; s_mb[i] = cmb;
-            compose(ck, cfl, cmk, cmb, tk, tfl, tmk, tmb);
+    if (w == 0) {                                                   // exclusive scan of the 32 warp totals
+        KFn tot = s_w[lane], x = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            KFn left = kfn_shfl_up(x, o);
+            if ((int)lane >= o) { kfn_then(left, x, N, reset); x = left; }
         }
+        KFn ex = kfn_shfl_up(x, 1);
+        if (lane == 0) ex = KFn{0, 0, 0, 0};
+        s_w[lane] = ex;
     }
     __syncthreads();
-    k = s_k[t]; fl = s_fl[t]; mk = s_mk[t]; mb = s_mb[t];
+    KFn f = s_w[w];                                                 // everything before my warp ...
+    KFn prev = kfn_shfl_up(inc, 1);
+    if (lane > 0) kfn_then(f, prev, N, reset);                      // ... then the lanes before me
     for (u32 r = r0; r < r1; ++r) {
-        a.r_in_c[r] = k; a.r_in_mkey[r] = mk; a.r_in_mbits[r] = mb;
-        compose(k, fl, mk, mb, a.r_fn_k[r], a.r_fn_flags[r], a.r_fn_mkey[r], a.r_fn_mbits[r]);
+        a.r_in_c[r] = f.k; a.r_in_mkey[r] = f.mk; a.r_in_mbits[r] = f.mb;
+        kfn_then(f, KFn{a.r_fn_k[r], a.r_fn_flags[r], a.r_fn_mkey[r], a.r_fn_mbits[r]}, N, reset);
     }
 }
 
