@@ -704,11 +704,19 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
             if (live) {
                 for (i64 p = p0; p <= p1; ++p) {
                     const u64 cell = (u64)((u32)p & a.g.ring_mask) * C + slot;
-                    for (int r = 0; r < a.world; ++r) {                    // fixed rank order: deterministic double sums
-                        const ulonglong4 q = *reinterpret_cast<const ulonglong4*>(a.peer_acc[r] + cell);
-                        if (is_f64) { cnt_d += __longlong_as_double((i64)q.x); sum_d += __longlong_as_double((i64)q.y); }
-                        else        { cnt_i += q.x; sum_i += q.y; }
-                        mx = q.z > mx ? q.z : mx; mn = q.w > mn ? q.w : mn;
+                    // every peer's cell is requested before the first one is used: over NVLink a load takes
+                    // microseconds, and a dependent chain of `world` of them per thread was what made the
+                    // fire chain grow with the GPU count
+                    ulonglong4 q[FMQ_MAX_PEERS];
+#pragma unroll
+                    for (int r = 0; r < FMQ_MAX_PEERS; ++r)
+                        q[r] = r < a.world ? *reinterpret_cast<const ulonglong4*>(a.peer_acc[r] + cell) : make_ulonglong4(0, 0, 0, 0);
+#pragma unroll
+                    for (int r = 0; r < FMQ_MAX_PEERS; ++r) {              // fixed rank order: deterministic double sums
+                        if (r >= a.world) break;
+                        if (is_f64) { cnt_d += __longlong_as_double((i64)q[r].x); sum_d += __longlong_as_double((i64)q[r].y); }
+                        else        { cnt_i += q[r].x; sum_i += q[r].y; }
+                        mx = q[r].z > mx ? q[r].z : mx; mn = q[r].w > mn ? q[r].w : mn;
                     }
                 }
             }
