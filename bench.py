@@ -284,6 +284,8 @@ def main():
         ev0.record(stream)
         for b in range(W, W + K):
             step(b)
+        if hasattr(sharded, "join"):
+            sharded.join()                     # the last fire / retire run on a second stream: the clock stops after them
         ev1.record(stream)
         eng.synchronize()
         torch.cuda.synchronize()
@@ -466,7 +468,7 @@ def main():
                        "events_per_step_per_gpu": B, "global_events_per_ms": spec.events_per_ms, "keys": args.keys, "key_mode": args.key_mode, "window_ms": WINDOW_MS, "bound_ms": BOUND_MS,
                        "l2": "inputs larger than L2 (each batch = 24 B x 2^%d = %.0f MB, read once)" % (args.batch_log2, 24 * B / 1e6),
                        "parallelism": "1 GPU" if world == 1 else (
-                           f"{world} GPUs, combiner: local accumulate + 32 B all-reduce per batch + fire over NVLink peer memory"
+                           f"{world} GPUs, combiner: local accumulate + 32 B all-reduce per batch + fire over NVLink peer memory, fire/retire of batch k overlapped with the ingest of batch k+1"
                            if (args.multi == "combiner" and args.key_mode == "dense") else (
                                f"keyBy sharded over {world} GPUs, buckets pulled from peer memory over NVLink" if args.multi == "peerpull"
                                else f"keyBy hash-sharded over {world} GPUs, NCCL all-to-all"))},

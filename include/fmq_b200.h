@@ -384,6 +384,20 @@ int32_t fmq_push_local(fmq_handle* h, const int64_t* ts, const uint64_t* key, co
 int32_t fmq_push_local_packed(fmq_handle* h, const fmq_packed_columns* cols, size_t n, int32_t mem);
 int32_t fmq_fire_global(fmq_handle* h, int64_t watermark_after);
 int32_t fmq_retire(fmq_handle* h);
+/* Tumbling windows only: run everything from the fire kernel on (fire, the barrier, fmq_retire) on a second
+ * stream, fmq_fire_stream(h), so that it overlaps the NEXT micro-batch's fmq_push_local and first
+ * all-reduce.  A tumbling fire only reads panes no later record can reach, and the ingest kernel keeps
+ * away from ring cells whose clear is still pending, so the results are the same; what changes is the
+ * schedule.  Per micro-batch:
+ *     fmq_push_local(..); all-reduce(MAX) of fmq_exchange_ptr(h) on fmq_stream(h);
+ *     fmq_fire_global(h, wm)     [waits for the previous fmq_retire, plans on fmq_stream(h), fires on fmq_fire_stream(h)]
+ *     barrier on fmq_fire_stream(h) — through a SECOND communicator, the two streams' collectives interleave;
+ *     fmq_retire(h)              [on fmq_fire_stream(h)]
+ * A fire with no preceding local push (end-of-input flush) calls fmq_push_local with n = 0 first.
+ * pane_ring must cover the live panes plus the panes that expire in one step (else FMQ_ERR_RING_OVERFLOW).
+ * No reference counterpart (Flink fires windows on the task thread between records). */
+int32_t fmq_combiner_overlap(fmq_handle* h, int32_t enable);
+void*   fmq_fire_stream(fmq_handle* h);
 
 /* ---- keyBy exchange over NVLink peer memory ("peer pull", A4) --------------------------------------
  * Replaces: the keyBy network exchange (KeyGroupStreamPartitioner + Netty/local channels behind

@@ -178,6 +178,8 @@ def _declare(lib, p: str, has_mem: bool = True):
         sig("push_local", [vp, vp, vp, vp, sz, i32])
         sig("fire_global", [vp, i64])
         sig("retire", [vp])
+        sig("combiner_overlap", [vp, i32])
+        sig("fire_stream", [vp], vp)
         sig("push_packed", [vp, C.POINTER(FmqPackedColumns), sz, i64, i32])
         sig("stage_host", [vp, C.POINTER(FmqPackedColumns), sz])
         sig("push_local_packed", [vp, C.POINTER(FmqPackedColumns), sz, i32])
@@ -522,6 +524,13 @@ class Engine(EngineBase):
 
     def retire(self):
         self._check(self._lib.fmq_retire(self._h))
+
+    def combiner_overlap(self, enable: bool = True):
+        self._check(self._lib.fmq_combiner_overlap(self._h, 1 if enable else 0))
+
+    @property
+    def fire_stream(self) -> int:
+        return self._lib.fmq_fire_stream(self._h)
 
     # ---- peer-pull keyBy exchange ---------------------------------------------------------------
     def exchange_alloc(self) -> bytes:

@@ -53,7 +53,8 @@ struct DevState {
     u64 n_fired, n_walert, n_ealert, n_calert;
     // skew adaptation: one warp per block samples how many lanes of a warp hit the same cell; the plan
     // kernel turns warp-level pre-aggregation on for the next batch when that is common
-    u64 dup_sampled, dup_found; u32 combine_dups; u32 pad2;
+    u64 dup_sampled, dup_found; u32 combine_dups;
+    u32 pending_clear;               // panes whose clear is still in flight while the next batch is ingested (overlapped combiner mode)
     u64 n_late;                      // rows in the late side output
     u64 n_mlog, n_mwork, n_median;   // median path: logged records, records selected for the window being fired, emitted rows
     u32 err_flags;

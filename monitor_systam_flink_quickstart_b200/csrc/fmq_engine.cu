@@ -67,6 +67,8 @@ struct fmq_handle {
     int world = 1, rank = 0;
     const Acc32* peer_acc[FMQ_MAX_PEERS] = {};
     i64* d_xchg = nullptr;               // 4 x int64 exchange buffer for the all-reduce of the batch scalars
+    // overlapped combiner mode (fmq_combiner_overlap): fire / retire run on fire_stream while the next batch is ingested
+    bool overlap = false; cudaStream_t fire_stream = nullptr; cudaEvent_t ev_plan = nullptr, ev_bdone = nullptr;
     size_t pending_n = 0;
     // peer-pull keyBy exchange: two parities x three columns of owner-bucketed events, mapped by every peer
     char* d_xsend = nullptr; const char* peer_xsend[FMQ_MAX_PEERS] = {}; int x_world = 0, x_rank = 0;
@@ -123,6 +125,9 @@ static void free_all(fmq_handle* h) {
     for (auto& q : h->ev_piece) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->out_stream) cudaStreamDestroy(h->out_stream);
+    if (h->fire_stream) cudaStreamDestroy(h->fire_stream);
+    if (h->ev_plan) cudaEventDestroy(h->ev_plan);
+    if (h->ev_bdone) cudaEventDestroy(h->ev_bdone);
     if (h->ev_out) cudaEventDestroy(h->ev_out);
     if (h->h_st) cudaFreeHost(h->h_st);
     for (auto& q : h->tev) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
@@ -298,6 +303,7 @@ static int status_from_flags(fmq_handle* h, u32 flags) {
 // synchronise the stream and refresh the pinned mirror of DevState
 static int sync_state(fmq_handle* h) {
     CU(h, cudaSetDevice(h->device));
+    if (h->fire_stream) CU(h, cudaStreamSynchronize(h->fire_stream));
     CU(h, cudaMemcpyAsync(h->h_st, h->d_st, sizeof(DevState), cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
     if (h->h_st->anchored) h->anchored_known = true;
@@ -489,8 +495,14 @@ static int fire_medians(fmq_handle* h) {
 template <typename V>
 static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now) {
     const fmq_config& c = h->cfg;
-    PlanArgs p{h->d_st, h->g, c.max_out_of_orderness_ms, wm_after, (u64)n, c.window_enabled, wm_after == FMQ_WM_AUTO};
+    PlanArgs p{h->d_st, h->g, c.max_out_of_orderness_ms, wm_after, (u64)n, c.window_enabled, wm_after == FMQ_WM_AUTO, h->overlap ? 1 : 0};
     plan_kernel<<<1, 32, 0, h->stream>>>(p); LAUNCHED(h, "plan_kernel");
+    cudaStream_t fs = h->stream;
+    if (h->overlap) {                                          // everything from the fire kernel on runs beside the next ingest
+        CU(h, cudaEventRecord(h->ev_plan, h->stream));
+        CU(h, cudaStreamWaitEvent(h->fire_stream, h->ev_plan, 0));
+        fs = h->fire_stream;
+    }
     if (c.window_enabled && wm_after != FMQ_WM_AUTO && wm_after > INT64_MIN) h->anchored_known = true;
     if (c.window_enabled && h->ml_cap > 0) { int s_ = fire_medians(h); if (s_) return s_; }
     if (c.window_enabled) {
@@ -509,7 +521,9 @@ static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now
         size_t blocks = (f.slot_hi - f.slot_lo + FIRE_THREADS - 1) / FIRE_THREADS; const size_t maxb = (size_t)h->num_sms * 8;
         if (blocks > maxb) blocks = maxb;
         if (blocks == 0) blocks = 1;
-        fire_kernel<V><<<(unsigned)blocks, FIRE_THREADS, 0, h->stream>>>(f); LAUNCHED(h, "fire_kernel");
+        if (h->world > 1) fire_kernel<V, true><<<(unsigned)blocks, FIRE_THREADS, 0, fs>>>(f);
+        else              fire_kernel<V, false><<<(unsigned)blocks, FIRE_THREADS, 0, fs>>>(f);
+        LAUNCHED(h, "fire_kernel");
         if (retire_now) { commit_kernel<<<1, 32, 0, h->stream>>>(h->d_st); LAUNCHED(h, "commit_kernel"); }
     }
     return FMQ_OK;
@@ -929,6 +943,7 @@ int32_t fmq_fire_global(fmq_handle* h, int64_t watermark_after) {
     if (!h) return FMQ_ERR_BAD_ARG;
     if (h->sticky) return FMQ_ERR_POISONED;
     CU(h, cudaSetDevice(h->device));
+    if (h->overlap) CU(h, cudaStreamWaitEvent(h->stream, h->ev_bdone, 0));     // the previous batch's retire / commit
     unpack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "unpack_scalars_kernel");
     int s = (h->cfg.value_type == FMQ_VAL_F64) ? stage_fire<double>(h, h->pending_n, watermark_after, false)
                                                : stage_fire<i64>(h, h->pending_n, watermark_after, false);
@@ -940,14 +955,37 @@ int32_t fmq_retire(fmq_handle* h) {
     if (!h) return FMQ_ERR_BAD_ARG;
     if (h->sticky) return FMQ_ERR_POISONED;
     CU(h, cudaSetDevice(h->device));
-    retire_kernel<<<(unsigned)h->num_sms * 4, 256, 0, h->stream>>>(h->d_st, h->d_acc, h->capacity, h->g.ring_mask); LAUNCHED(h, "retire_kernel");
-    commit_kernel<<<1, 32, 0, h->stream>>>(h->d_st); LAUNCHED(h, "commit_kernel");
-    // pre-arm the exchange buffer so that a fire with no preceding local push contributes nothing
-    pack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "pack_scalars_kernel");
-    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][3], h->stream));
+    cudaStream_t fs = h->overlap ? h->fire_stream : h->stream;
+    retire_kernel<<<(unsigned)h->num_sms * 4, 256, 0, fs>>>(h->d_st, h->d_acc, h->capacity, h->g.ring_mask); LAUNCHED(h, "retire_kernel");
+    if (h->overlap) {
+        commit_overlapped_kernel<<<1, 32, 0, fs>>>(h->d_st); LAUNCHED(h, "commit_overlapped_kernel");
+        CU(h, cudaEventRecord(h->ev_bdone, fs));
+    } else {
+        commit_kernel<<<1, 32, 0, fs>>>(h->d_st); LAUNCHED(h, "commit_kernel");
+        // pre-arm the exchange buffer so that a fire with no preceding local push contributes nothing
+        pack_scalars_kernel<<<1, 32, 0, fs>>>(h->d_st, h->d_xchg); LAUNCHED(h, "pack_scalars_kernel");
+    }
+    CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][3], fs));
     h->pushes++;
     return FMQ_OK;
 }
+int32_t fmq_combiner_overlap(fmq_handle* h, int32_t enable) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (h->world < 2) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_combiner_overlap follows fmq_attach_peers");
+    if (enable && h->g.size != h->g.slide) return set_err(h, FMQ_ERR_BAD_ARG, "only tumbling windows can fire beside the next ingest (a sliding window's panes are still being updated)");
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaStreamSynchronize(h->stream));
+    if (h->fire_stream) CU(h, cudaStreamSynchronize(h->fire_stream));
+    if (enable && !h->fire_stream) {
+        CU(h, cudaStreamCreateWithFlags(&h->fire_stream, cudaStreamNonBlocking));
+        CU(h, cudaEventCreateWithFlags(&h->ev_plan, cudaEventDisableTiming));
+        CU(h, cudaEventCreateWithFlags(&h->ev_bdone, cudaEventDisableTiming));
+    }
+    h->overlap = enable != 0;
+    return FMQ_OK;
+}
+void* fmq_fire_stream(fmq_handle* h) { return h ? (void*)(h->overlap ? h->fire_stream : h->stream) : nullptr; }
 
 // ---- text ingest ------------------------------------------------------------------------------------
 uint64_t fmq_text_key_hash(const char* s, size_t len) {
@@ -1096,6 +1134,7 @@ int32_t fmq_synchronize(fmq_handle* h) {
     if (!h) return FMQ_ERR_BAD_ARG;
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaStreamSynchronize(h->stream));
+    if (h->fire_stream) CU(h, cudaStreamSynchronize(h->fire_stream));
     return FMQ_OK;
 }
 int32_t fmq_last_device_ms(fmq_handle* h, float* ms) {

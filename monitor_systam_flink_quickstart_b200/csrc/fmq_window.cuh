@@ -368,7 +368,8 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
     k.origin_ring = (u32)st->origin_pane & a.g.ring_mask;
     k.slide = a.g.slide32;
     k.recip = 0xFFFFFFFFu / k.slide;                             // floor((2^32-1)/slide): quotient estimate, never too big
-    k.span = (u64)(a.g.ring_mask + 1) * k.slide;                 // first d that falls outside the ring (< 2^32)
+    // first d that falls outside the ring (< 2^32); panes still being cleared are not yet reusable
+    k.span = (u64)(a.g.ring_mask + 1 - st->pending_clear) * k.slide;
     k.nbuckets = a.g.capacity >> 2;
     IngestRun r;
     if (k.combine) hot_init(&hot_tab);                           // ordered before its first use by the barrier after the prologue
@@ -487,7 +488,7 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
     const int anchored = st->anchored;
     const i64 origin_ts = anchored ? st->origin_ts : (a.g.off - a.g.slide);
     const i64 origin_pane = anchored ? st->origin_pane : -1;
-    const u32 R = a.g.ring_mask + 1;
+    const u32 R = a.g.ring_mask + 1 - st->pending_clear;
 
     u64 late = 0, nea = 0; i64 max_ts = I64_MIN_; i64 pmin = I64_MAX_, pmax = I64_MIN_; u32 err = 0;
 
@@ -568,13 +569,14 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
 // ---- plan: one thread turns "watermark_after" into a fire / expire schedule ---------------------
 struct PlanArgs {
     DevState* st; WindowGeom g; i64 bound; i64 watermark_after; u64 n_events; int window_enabled; int is_auto;
+    int overlap;      // combiner mode with fire / retire on a second stream: the next ingest starts before the expired panes are cleared
 };
 
 __global__ void plan_kernel(const PlanArgs a) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     DevState* st = a.st;
     st->events_in += a.n_events;
-    st->fire_count = 0; st->expire_lo = 1; st->expire_hi = 0;
+    st->fire_count = 0; st->expire_lo = 1; st->expire_hi = 0; st->pending_clear = 0;
     if (!a.window_enabled) return;
     // skew adaptation for the next batch: pre-aggregate inside warps when > 3 % of the sampled lanes
     // shared their cell with another lane of the same warp
@@ -616,7 +618,10 @@ __global__ void plan_kernel(const PlanArgs a) {
         if (e_hi >= e_lo) { st->fire_first_end = e_lo; st->fire_count = (e_hi - e_lo) / slide + 1; }
         // panes whose last window has now fired
         const i64 x_hi = (new_lo - 1 < st->max_pane) ? new_lo - 1 : st->max_pane;
-        if (x_hi >= st->min_pane) { st->expire_lo = st->min_pane; st->expire_hi = x_hi; }
+        if (x_hi >= st->min_pane) {
+            st->expire_lo = st->min_pane; st->expire_hi = x_hi;
+            if (a.overlap) { const i64 cnt = x_hi - st->min_pane + 1; st->pending_clear = cnt > (i64)a.g.ring_mask ? a.g.ring_mask + 1 : (u32)cnt; }
+        }
     }
     st->anchored = 1;
     st->origin_pane = new_lo;
@@ -631,6 +636,14 @@ __global__ void commit_kernel(DevState* st) {
         if (st->min_pane > st->max_pane) { st->min_pane = I64_MAX_; st->max_pane = I64_MIN_; }
     }
     st->fire_count = 0; st->expire_lo = 1; st->expire_hi = 0;
+}
+// Overlapped combiner mode: the next batch's ingest kernel is already updating min_pane / max_pane with
+// atomics while this runs, so the live range is only ever moved with an atomic (and never reset to
+// "empty": a stale lower bound is corrected by pack_scalars_kernel's clamp to the pane origin); the
+// plan of the next batch resets the fire / expire fields.
+__global__ void commit_overlapped_kernel(DevState* st) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (st->expire_lo <= st->expire_hi) atomicMax(reinterpret_cast<long long*>(&st->min_pane), (long long)(st->expire_hi + 1));
 }
 
 // ---- fire: thread per key slot; combine panes, emit, evaluate the alert, clear expired panes -----
@@ -656,8 +669,12 @@ constexpr int FIRE_THREADS = 256;
 __global__ void pack_scalars_kernel(const DevState* st, i64* x) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     x[0] = st->batch_max_ts;
-    x[1] = (st->min_pane <= st->max_pane) ? -st->min_pane : I64_MIN_;
-    x[2] = (st->min_pane <= st->max_pane) ? st->max_pane : I64_MIN_;
+    // panes before the origin have expired (plan_kernel): with fire / retire overlapped, the commit that
+    // moves min_pane past them may not have run yet
+    i64 lo = st->min_pane;
+    if (st->anchored && lo < st->origin_pane) lo = st->origin_pane;
+    x[1] = (lo <= st->max_pane) ? -lo : I64_MIN_;
+    x[2] = (lo <= st->max_pane) ? st->max_pane : I64_MIN_;
     x[3] = 0;
 }
 __global__ void unpack_scalars_kernel(DevState* st, const i64* x) {
@@ -677,7 +694,7 @@ __global__ void __launch_bounds__(256) retire_kernel(DevState* st, Acc32* acc, u
     }
 }
 
-template <typename V>
+template <typename V, bool PEERS>
 __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constant__ FireArgs a) {
     DevState* st = a.st;
     const i64 nfire = st->fire_count;
@@ -704,19 +721,26 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
             if (live) {
                 for (i64 p = p0; p <= p1; ++p) {
                     const u64 cell = (u64)((u32)p & a.g.ring_mask) * C + slot;
-                    // every peer's cell is requested before the first one is used: over NVLink a load takes
-                    // microseconds, and a dependent chain of `world` of them per thread was what made the
-                    // fire chain grow with the GPU count
-                    ulonglong4 q[FMQ_MAX_PEERS];
+                    if constexpr (!PEERS) {
+                        const ulonglong4 q = *reinterpret_cast<const ulonglong4*>(a.acc + cell);
+                        if (is_f64) { cnt_d += __longlong_as_double((i64)q.x); sum_d += __longlong_as_double((i64)q.y); }
+                        else        { cnt_i += q.x; sum_i += q.y; }
+                        mx = q.z > mx ? q.z : mx; mn = q.w > mn ? q.w : mn;
+                    } else {
+                        // every peer's cell is requested before the first one is used: over NVLink a load takes
+                        // microseconds, and a dependent chain of `world` of them per thread was what made the
+                        // fire chain grow with the GPU count
+                        ulonglong4 q[FMQ_MAX_PEERS];
 #pragma unroll
-                    for (int r = 0; r < FMQ_MAX_PEERS; ++r)
-                        q[r] = r < a.world ? *reinterpret_cast<const ulonglong4*>(a.peer_acc[r] + cell) : make_ulonglong4(0, 0, 0, 0);
+                        for (int r = 0; r < FMQ_MAX_PEERS; ++r)
+                            q[r] = r < a.world ? *reinterpret_cast<const ulonglong4*>(a.peer_acc[r] + cell) : make_ulonglong4(0, 0, 0, 0);
 #pragma unroll
-                    for (int r = 0; r < FMQ_MAX_PEERS; ++r) {              // fixed rank order: deterministic double sums
-                        if (r >= a.world) break;
-                        if (is_f64) { cnt_d += __longlong_as_double((i64)q[r].x); sum_d += __longlong_as_double((i64)q[r].y); }
-                        else        { cnt_i += q[r].x; sum_i += q[r].y; }
-                        mx = q[r].z > mx ? q[r].z : mx; mn = q[r].w > mn ? q[r].w : mn;
+                        for (int r = 0; r < FMQ_MAX_PEERS; ++r) {          // fixed rank order: deterministic double sums
+                            if (r >= a.world) break;
+                            if (is_f64) { cnt_d += __longlong_as_double((i64)q[r].x); sum_d += __longlong_as_double((i64)q[r].y); }
+                            else        { cnt_i += q[r].x; sum_i += q[r].y; }
+                            mx = q[r].z > mx ? q[r].z : mx; mn = q[r].w > mn ? q[r].w : mn;
+                        }
                     }
                 }
             }

@@ -161,7 +161,9 @@ class CombinerOperator:
     :class:`ShardedOperator`.
     """
 
-    def __init__(self, engine, rank: int, world: int, group=None):
+    def __init__(self, engine, rank: int, world: int, group=None, overlap=None):
+        """overlap (default: on for tumbling windows): fire / barrier / retire of batch k run on a second
+        stream with a second communicator while batch k+1 is ingested (fmq_combiner_overlap)."""
         import torch
         import torch.distributed as dist
         self.dist, self.engine, self.rank, self.world, self.group = dist, engine, rank, world, group
@@ -170,31 +172,50 @@ class CombinerOperator:
         dist.all_gather_object(blobs, engine.ipc_export(), group=group)
         tables = [engine.table_ptr if r == rank else engine.ipc_open(blobs[r]) for r in range(world)]
         engine.attach_peers(rank, world, tables)
+        tumbling = engine.cfg.window_size_ms == engine.cfg.window_slide_ms
+        self.overlap = tumbling if overlap is None else bool(overlap)
         self._ext = torch.cuda.ExternalStream(engine.stream, device=dev)
+        self._ext2, self.group2 = self._ext, group
+        if self.overlap:
+            engine.combiner_overlap(True)
+            self._ext2 = torch.cuda.ExternalStream(engine.fire_stream, device=dev)
+            ranks = list(range(world)) if group is None else dist.get_process_group_ranks(group)
+            self.group2 = dist.new_group(ranks=ranks, backend=dist.get_backend(group))   # its own communicator: no ordering against the first one
         self._x = exchange_tensor(engine, dev)
         self._token = torch.zeros(1, dtype=torch.int64, device=dev)
+        self._empty = (np.zeros(0, np.int64), np.zeros(0, np.uint64), np.zeros(0, np.float64 if engine.cfg.value_type == capi.FMQ_VAL_F64 else np.int64))
         dist.barrier(group=group)
 
-    def process_batch(self, ts, key, val, watermark_after: int = capi.FMQ_WM_AUTO, ts_base: int = 0):
-        """One micro-batch: everything below is queued on the engine's stream, no host round trip
-        (host columns: the call returns once they are copied in)."""
+    def _fire(self, watermark_after):
         import torch
         dist = self.dist
         with torch.cuda.stream(self._ext):
-            self.engine.push_local(ts, key, val, ts_base)
             dist.all_reduce(self._x, op=dist.ReduceOp.MAX, group=self.group)     # global scalars + "all ingested"
             self.engine.fire_global(watermark_after)
-            dist.all_reduce(self._token, group=self.group)                         # "all peers done reading"
+        with torch.cuda.stream(self._ext2):
+            dist.all_reduce(self._token, group=self.group2)                        # "all peers done reading"
             self.engine.retire()
 
-    def flush(self, wm: int = capi.FMQ_WM_FINAL):
+    def process_batch(self, ts, key, val, watermark_after: int = capi.FMQ_WM_AUTO, ts_base: int = 0):
+        """One micro-batch: everything below is queued on the engine's streams, no host round trip
+        (host columns: the call returns once they are copied in)."""
         import torch
-        dist = self.dist
         with torch.cuda.stream(self._ext):
-            dist.all_reduce(self._x, op=dist.ReduceOp.MAX, group=self.group)
-            self.engine.fire_global(wm)
-            dist.all_reduce(self._token, group=self.group)
-            self.engine.retire()
+            self.engine.push_local(ts, key, val, ts_base)
+        self._fire(watermark_after)
+
+    def flush(self, wm: int = capi.FMQ_WM_FINAL):
+        if self.overlap:                      # the exchange buffer is not pre-armed by retire in this mode
+            self.engine.push_local(*self._empty)
+        self._fire(wm)
+
+    def join(self):
+        """Order the engine's main stream after everything queued on the fire stream (timing, hand-over)."""
+        if self.overlap:
+            import torch
+            ev = torch.cuda.Event()
+            ev.record(self._ext2)
+            self._ext.wait_event(ev)
 
 
 class PeerPullOperator:

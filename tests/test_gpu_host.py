@@ -54,6 +54,7 @@ KW = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=
           efilter_enabled=1, efilter_threshold=90.0, consec_n=3, consec_threshold=50.0, consec_reset_on_fire=1,
           table_capacity=1 << 12, pane_ring=64, max_batch=1 << 16)
 NB, B = 5, 20_000
+NBC = 12           # batches of the 2-GPU combiner test (enough steps for fire / retire to run beside a later ingest)
 
 
 def _nccl_worker(rank, world, port, outdir, key_mode=0):
@@ -113,7 +114,8 @@ CKW = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms
 
 @pytest.mark.parametrize("world", [2, 3])
 @pytest.mark.parametrize("vt", ["f64", "i64"])
-def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt):
+@pytest.mark.parametrize("overlap", [0, 1])
+def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt, overlap):
     """`world` engines in ONE process on one GPU play the ranks (their tables are attached to each other
     as plain device pointers); the two collectives are done by hand between synchronised streams.
     Union of the ranks' outputs == oracle over the whole stream."""
@@ -122,6 +124,8 @@ def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt):
     from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy, generate_torch
     from oracle_lib import sort_walerts
     kw = dict(CKW, value_type=capi.FMQ_VAL_F64 if vt == "f64" else capi.FMQ_VAL_I64)
+    if overlap:
+        kw["window_slide_ms"] = kw["window_size_ms"]          # tumbling: fire / retire may run beside the next ingest
     if vt == "i64":
         kw.update(walert_source=capi.FMQ_ALERT_SUM, walert_op=capi.FMQ_CMP_LT, walert_mul=8.0, walert_div0=60.0, walert_div1=1024.0,
                   walert_div2=1024.0, walert_threshold=0.9)
@@ -129,6 +133,8 @@ def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt):
     engs = [capi.Engine(**kw) for _ in range(world)]
     for r, e in enumerate(engs):
         e.attach_peers(r, world, [x.table_ptr for x in engs])
+        if overlap:
+            e.combiner_overlap(True)
     xs = [exchange_tensor(e, "cuda:0") for e in engs]
     ref = OracleEngine(**{k: v for k, v in kw.items()})
     nb, b = 6, 7001
@@ -168,6 +174,9 @@ def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt):
             e.synchronize()
         fire(capi.FMQ_WM_AUTO)
         ref.push_batch(*[np.concatenate([p[j] for p in parts]) for j in range(3)])
+    if overlap:                                   # this mode does not pre-arm the exchange buffer in retire
+        for e in engs:
+            e.push_local(np.zeros(0, np.int64), np.zeros(0, np.uint64), np.zeros(0, np.float64 if vt == "f64" else np.int64))
     fire(capi.FMQ_WM_FINAL)
     ref.flush()
     res = [dict(fired=e.poll_fired(), wal=e.poll_window_alerts(), eal=e.poll_event_alerts(), c=e.counters()) for e in engs]
@@ -187,7 +196,7 @@ def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt):
         assert len(x["fired"]) > 0 and x["fired"].key.min() >= per * r and x["fired"].key.max() < per * (r + 1)
 
 
-def _combiner_worker(rank, world, port, outdir):
+def _combiner_worker(rank, world, port, outdir, tumbling=False):
     import torch
     import torch.distributed as dist
     from monitor_systam_flink_quickstart_b200.shard import CombinerOperator
@@ -196,13 +205,15 @@ def _combiner_worker(rank, world, port, outdir):
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
-    eng = capi.Engine(device=rank, **CKW)
+    kw = dict(CKW, window_slide_ms=CKW["window_size_ms"]) if tumbling else CKW
+    eng = capi.Engine(device=rank, **kw)
     op = CombinerOperator(eng, rank, world)
-    for b in range(NB):
-        ts, key, val = generate_torch(spec, (b * world + rank) * B, B, device=f"cuda:{rank}")
-        torch.cuda.synchronize()
-        op.process_batch(ts, key, val)
-        eng.synchronize()          # the columns are freed at the next iteration: wait until they have been consumed
+    assert op.overlap == tumbling
+    cols = [generate_torch(spec, (b * world + rank) * B, B, device=f"cuda:{rank}") for b in range(NBC)]
+    torch.cuda.synchronize()
+    for b in range(NBC):
+        op.process_batch(*cols[b])     # no host synchronisation between batches: the streams order everything
+    eng.synchronize()
     op.flush()
     res = dict(fired=eng.poll_fired(), ealerts=eng.poll_event_alerts(), counters=eng.counters())
     pickle.dump(res, open(os.path.join(outdir, f"r{rank}.pkl"), "wb"))
@@ -210,7 +221,8 @@ def _combiner_worker(rank, world, port, outdir):
     dist.destroy_process_group()
 
 
-def test_two_gpu_combiner_over_nvlink_equals_oracle():
+@pytest.mark.parametrize("tumbling", [False, True])       # True: fire / retire overlapped with the next batch's ingest
+def test_two_gpu_combiner_over_nvlink_equals_oracle(tumbling):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
@@ -218,11 +230,11 @@ def test_two_gpu_combiner_over_nvlink_equals_oracle():
     from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy
     world, port = 2, 29700 + os.getpid() % 2000
     with tempfile.TemporaryDirectory() as d:
-        mp.spawn(_combiner_worker, args=(world, port, d), nprocs=world, join=True)
+        mp.spawn(_combiner_worker, args=(world, port, d, tumbling), nprocs=world, join=True)
         res = [pickle.load(open(os.path.join(d, f"r{r}.pkl"), "rb")) for r in range(world)]
     spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
-    ref = OracleEngine(**{k: v for k, v in CKW.items()})
-    for b in range(NB):
+    ref = OracleEngine(**dict(CKW, window_slide_ms=CKW["window_size_ms"] if tumbling else CKW["window_slide_ms"]))
+    for b in range(NBC):
         parts = [generate_numpy(spec, (b * world + r) * B, B) for r in range(world)]
         ref.push_batch(*[np.concatenate([p[i] for p in parts]) for i in range(3)])
     ref.flush()
