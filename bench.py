@@ -353,6 +353,8 @@ def main():
     roofline = {"bound": "hbm", "kernel": "ingest_fast_kernel<double,%s>" % args.key_mode, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": ncu_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                 "avg_launch_ms": ing_ms, "fire_chain_ms": fire_ms, "share_of_step": ing_ms * K / ms}
+    if world > 1 and args.multi == "combiner" and args.key_mode == "dense":
+        roofline["fire_chain_note"] = "runs on a second stream beside the next batch's ingest: latency from the end of ingest to the end of retire, not part of the step's critical path"
 
     # -------- e2e: host columns through the C ABI, outputs read back --------
     # What a JVM shim would do per micro-batch: hand over three pinned host columns (direct
