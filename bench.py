@@ -56,6 +56,30 @@ def stream_spec(StreamSpec, n_keys=N_KEYS, world=1):
                       value_type="f64", key_kind="uniform", seed=42)
 
 
+def bind_host_to_gpu_numa(index):
+    """Pin this process to the CPUs of the NUMA node its GPU hangs off, before any pinned host buffer is
+    allocated (first touch puts the pages there).  At N=8 every rank streams ~50 GB/s out of host memory;
+    pages on the other socket halve that.  Returns a description for the JSON line (None if unknown)."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(index)
+        bus = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return {"numa_node": node, "cpus": len(cpus), "pci": bus}
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """SM clock and throttle reasons while the timed region runs, read through NVML in a thread.
     (An `nvidia-smi -lms` child process was measured to stall every synchronising CUDA call of the
@@ -198,6 +222,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    numa = bind_host_to_gpu_numa(local_rank) if world > 1 else None
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -438,7 +463,7 @@ def main():
             eng2.close()
             per_event = sum(c.element_size() for c in host[0][:3])
             return {"value": e2e_steps * B * world / dt, "unit": "events/s", "h2d_bytes_per_step": per_event * B * world, "d2h_bytes_per_step": d2h // e2e_steps,
-                    "steps": e2e_steps, "ms_per_step": dt / e2e_steps * 1e3,
+                    "steps": e2e_steps, "ms_per_step": dt / e2e_steps * 1e3, "host_numa_binding": numa,
                     "entry_point": ("CombinerOperator: fmq_push_local_packed + fmq_stage_host + 2 all-reduces + fmq_fire_global/fmq_retire, " if combiner else "fmq_push_packed + fmq_stage_host, ") + ("uint32 ts offset + uint32 host id + double" if packed else "int64 ts + uint64 key + double (the fmq_push_batch format)"),
                     "timing": "host wall clock around K x [push of pinned host columns + fmq_poll_all_begin/end into pinned host buffers]; "
                               "the D2H of step s overlaps the H2D of step s+1; every row is on the host when the clock stops"}
