@@ -268,6 +268,8 @@ def main():
     batches = [dev_batch(s) for s in range(W + K)]
     torch.cuda.synchronize()
 
+    host_issue_ms = [0.0]
+
     def measure(kw, with_clocks):
         """W warm-up + K timed steps with device-resident inputs; CUDA events on the engine's stream
         (every kernel, copy and collective of a step is ordered on it)."""
@@ -307,8 +309,10 @@ def main():
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t_wall0 = time.time()
         ev0.record(stream)
+        t_issue0 = time.perf_counter()
         for b in range(W, W + K):
             step(b)
+        host_issue_ms[0] = (time.perf_counter() - t_issue0) * 1e3 / K     # how long the host needs to queue one step
         if hasattr(sharded, "join"):
             sharded.join()                     # the last fire / retire run on a second stream: the clock stops after them
         ev1.record(stream)
@@ -329,6 +333,7 @@ def main():
         return ms, float(np.mean(ing)), float(np.mean(fire)), delta, clocks
 
     ms, ing_ms, fire_ms, delta, clocks = measure(kw, True)
+    issue_ms = host_issue_ms[0]
     launches, n_ealert, n_late, n_fired = delta["gpu_launches"], delta["event_alerts"], delta["late_dropped"], delta["windows_fired"]
     ealert_rank, events_rank = delta["event_alerts"] / K, delta["events_in"] / K
     if dist:
@@ -377,7 +382,8 @@ def main():
     achieved = alg_bytes / (ing_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": "ingest_fast_kernel<double,%s>" % args.key_mode, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": ncu_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
-                "avg_launch_ms": ing_ms, "fire_chain_ms": fire_ms, "share_of_step": ing_ms * K / ms}
+                "avg_launch_ms": ing_ms, "fire_chain_ms": fire_ms, "share_of_step": ing_ms * K / ms,
+                "host_issue_ms_per_step": issue_ms}
     if world > 1 and args.multi == "combiner" and args.key_mode == "dense":
         roofline["fire_chain_note"] = "runs on a second stream beside the next batch's ingest: latency from the end of ingest to the end of retire, not part of the step's critical path"
 

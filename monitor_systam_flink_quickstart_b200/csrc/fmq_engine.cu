@@ -69,7 +69,7 @@ struct fmq_handle {
     i64* d_xchg = nullptr;               // 4 x int64 exchange buffer for the all-reduce of the batch scalars
     // overlapped combiner mode (fmq_combiner_overlap): fire / retire run on fire_stream while the next batch is ingested
     bool overlap = false; cudaStream_t fire_stream = nullptr; cudaEvent_t ev_plan = nullptr, ev_bdone = nullptr;
-    size_t pending_n = 0;
+    size_t pending_n = 0;                // events ingested by fmq_push_local and not yet accounted by fmq_fire_global
     // peer-pull keyBy exchange: two parities x three columns of owner-bucketed events, mapped by every peer
     char* d_xsend = nullptr; const char* peer_xsend[FMQ_MAX_PEERS] = {}; int x_world = 0, x_rank = 0;
     // second set of fired / window-alert / event-alert columns + a copy-out stream, for overlapped polls
@@ -80,7 +80,7 @@ struct fmq_handle {
     u64* mw_items[2] = {nullptr, nullptr}; u64* mw_vals = nullptr;
     u64* md_key = nullptr; i64* md_wend = nullptr; double* md_val = nullptr; u64 md_cap = 0; size_t cur_median = 0;
     // text ingest
-    char* d_text = nullptr; u64* d_line_start = nullptr; u32* d_txt_status = nullptr; unsigned long long* d_txt_bad = nullptr;                // events ingested by fmq_push_local and not yet accounted by fmq_fire_global
+    char* d_text = nullptr; u64* d_line_start = nullptr; u32* d_txt_status = nullptr; unsigned long long* d_txt_bad = nullptr;
 };
 
 #define CU(h, call)                                                                                   \

@@ -12,5 +12,5 @@ python - <<PY
 import json
 d = json.load(open('gpurun_out/bench_n$N.json'))
 r = d['roofline']
-print(d['n_gpus'], 'GPUs', round(d['value'] / 1e9, 2), 'Gev/s', round(d['ms_per_step'], 4), 'ms/step  ingest', round(r['avg_launch_ms'], 4), 'fire', round(r['fire_chain_ms'], 4), 'frac', round(r['frac'], 4), d['clocks'])
+print(d["n_gpus"], "GPUs", "issue", round(r.get("host_issue_ms_per_step", 0), 4), round(d['value'] / 1e9, 2), 'Gev/s', round(d['ms_per_step'], 4), 'ms/step  ingest', round(r['avg_launch_ms'], 4), 'fire', round(r['fire_chain_ms'], 4), 'frac', round(r['frac'], 4), d['clocks'])
 PY
