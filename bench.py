@@ -440,7 +440,7 @@ def main():
                 else:
                     eng2.push_packed(ts, key, val, ts_base=base)                           # H2D (already under way); returns when the copy is done
                 if nxt is not None:
-                    eng2.stage_host(*nxt[:3], ts_base=nxt[3])                              # next batch's H2D runs under this step's kernels and polls
+                    eng2.stage_host(*nxt[:3], ts_base=nxt[3])                              # a later batch's H2D is queued: the copy engine never waits for the host
                 eng2.poll_all_end()                                                         # previous step's rows are now on the host
                 nf, na, ne = eng2.poll_all_begin(*out_sets[step_no[0] % 2])                # waits for this step's kernels, starts its D2H
                 step_no[0] += 1
@@ -454,8 +454,11 @@ def main():
             if dist:
                 dist.barrier()
             t0 = time.perf_counter()
+            eng2.stage_host(*seq[W][:3], ts_base=seq[W][3])                                 # inside the timed region: two batches are staged ahead
+            if e2e_steps > 1:
+                eng2.stage_host(*seq[W + 1][:3], ts_base=seq[W + 1][3])
             for s in range(e2e_steps):
-                d2h += e2e_step(seq[W + s], seq[W + s + 1] if s + 1 < e2e_steps else None)
+                d2h += e2e_step(seq[W + s], seq[W + s + 2] if s + 2 < e2e_steps else None)
             eng2.poll_all_end()
             eng2.synchronize()
             dt = time.perf_counter() - t0

@@ -228,7 +228,8 @@ int32_t fmq_push_packed(fmq_handle* h, const fmq_packed_columns* cols, size_t n,
  * columns (pinned memory for a truly asynchronous copy; all widths 8 = the fmq_push_batch format).
  * The columns must stay untouched until the consuming call returns: the next fmq_push_batch /
  * fmq_push_packed with FMQ_MEM_HOST must pass the same pointers, widths, ts_base and n, and finds
- * them staged.  At most one batch is staged ahead.  Network-buffer hand-over in Flink
+ * them staged.  Up to two batches can be staged ahead (first in, first out), which keeps the copy engine
+ * busy across the host's own latency between calls.  Network-buffer hand-over in Flink
  * (RecordWriter -> InputGate) is the nearest reference notion; it has no direct counterpart. */
 int32_t fmq_stage_host(fmq_handle* h, const fmq_packed_columns* cols, size_t n);
 

@@ -47,10 +47,12 @@ struct fmq_handle {
     i64* d_in_ts = nullptr; u64* d_in_key = nullptr; u64* d_in_val = nullptr;
     // host pushes: two staging sets filled on a copy stream, so that the copy-in of batch k+1 runs
     // while the kernels of batch k do (allocated by the first host push)
-    i64* hs_ts[2] = {nullptr, nullptr}; u64* hs_key[2] = {nullptr, nullptr}; u64* hs_val[2] = {nullptr, nullptr};
-    u32* hs_narrow[2] = {nullptr, nullptr};      // 3 x max_batch 4-byte columns of fmq_push_packed
-    cudaStream_t copy_stream = nullptr; cudaEvent_t ev_free[2] = {nullptr, nullptr}, ev_piece[2][4] = {}; uint64_t host_pushes = 0;
-    struct Staged { bool valid = false; InCols c{}; size_t n = 0, chunk = 0; int set = 0, pieces = 0; } staged;   // fmq_stage_host
+    static constexpr int HOST_SETS = 3;          // one being consumed + up to two staged ahead (fmq_stage_host)
+    i64* hs_ts[HOST_SETS] = {}; u64* hs_key[HOST_SETS] = {}; u64* hs_val[HOST_SETS] = {};
+    u32* hs_narrow[HOST_SETS] = {};              // 3 x max_batch 4-byte columns of fmq_push_packed
+    cudaStream_t copy_stream = nullptr; cudaEvent_t ev_free[HOST_SETS] = {}, ev_piece[HOST_SETS][4] = {}; uint64_t host_pushes = 0;
+    struct Staged { InCols c{}; size_t n = 0, chunk = 0; int set = 0, pieces = 0; };
+    Staged staged[2]; int n_staged = 0;          // FIFO of batches whose copy-in has been queued but not consumed
     // outputs
     u64 *f_key = nullptr, *f_sum = nullptr, *f_min = nullptr, *f_max = nullptr; i64 *f_wend = nullptr, *f_count = nullptr; u64 f_cap = 0;
     u64* wa_key = nullptr; i64* wa_wend = nullptr; double* wa_val = nullptr; u64 wa_cap = 0;
@@ -116,7 +118,7 @@ static void free_all(fmq_handle* h) {
                     h->md_key, h->md_wend, h->md_val, h->lt_ts, h->lt_key, h->lt_val};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : h->alt_out) if (p) cudaFree(p);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < fmq_handle::HOST_SETS; ++i) {
         void* q[] = {h->hs_ts[i], h->hs_key[i], h->hs_val[i], h->hs_narrow[i]};
         for (void* p : q) if (p) cudaFree(p);
         if (h->ev_free[i]) cudaEventDestroy(h->ev_free[i]);
@@ -551,11 +553,11 @@ __global__ void __launch_bounds__(256) widen_columns_kernel(const u32* __restric
 static int ensure_host_staging(fmq_handle* h, bool narrow) {
     if (!h->copy_stream) {
         CU(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
-        for (int i = 0; i < 2; ++i) CU(h, cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming));
+        for (cudaEvent_t& e : h->ev_free) CU(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         for (auto& q : h->ev_piece) for (cudaEvent_t& e : q) CU(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     }
     const size_t mb = h->max_batch ? h->max_batch : 1;
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < fmq_handle::HOST_SETS; ++i) {
         if (!h->hs_ts[i]) { CU(h, dalloc(&h->hs_ts[i], mb)); CU(h, dalloc(&h->hs_key[i], mb)); CU(h, dalloc(&h->hs_val[i], mb)); }
         if (narrow && !h->hs_narrow[i]) CU(h, dalloc(&h->hs_narrow[i], 3 * mb));
     }
@@ -573,15 +575,15 @@ constexpr size_t HOST_CHUNK_MIN = 1u << 18;
 static int queue_host_copy(fmq_handle* h, const InCols& c, size_t n) {
     const bool narrow = c.ts_w == 4 || c.key_w == 4 || c.val_w == 4;
     int s_ = ensure_host_staging(h, narrow); if (s_) return s_;
-    fmq_handle::Staged& g = h->staged;
-    g.c = c; g.n = n; g.set = (int)(h->host_pushes++ & 1); g.pieces = 0;
+    fmq_handle::Staged& g = h->staged[h->n_staged];
+    g.c = c; g.n = n; g.set = (int)(h->host_pushes++ % fmq_handle::HOST_SETS); g.pieces = 0;
     const size_t mb = h->max_batch;
     u32* nar = h->hs_narrow[g.set];
     size_t chunk = (n + HOST_CHUNKS - 1) / HOST_CHUNKS;
     if (chunk < HOST_CHUNK_MIN) chunk = HOST_CHUNK_MIN;
     if (h->cfg.rolling_max_enabled) chunk = n;                          // its output column is indexed by position in the push
     g.chunk = (chunk + 3) & ~(size_t)3;                                 // keeps every piece 32-byte aligned
-    // the kernels of the push before last read this set: wait for them, on the copy stream only
+    // the kernels of the push that used this set last: wait for them, on the copy stream only
     CU(h, cudaStreamWaitEvent(h->copy_stream, h->ev_free[g.set], 0));
     for (size_t off = 0; off < n; off += g.chunk, ++g.pieces) {
         const size_t m = n - off < g.chunk ? n - off : g.chunk;
@@ -590,7 +592,7 @@ static int queue_host_copy(fmq_handle* h, const InCols& c, size_t n) {
         CU(h, cudaMemcpyAsync(c.val_w == 8 ? (void*)(h->hs_val[g.set] + off) : (void*)(nar + 2 * mb + off), (const char*)c.val + off * c.val_w, m * c.val_w, cudaMemcpyHostToDevice, h->copy_stream));
         CU(h, cudaEventRecord(h->ev_piece[g.set][g.pieces], h->copy_stream));
     }
-    g.valid = true;
+    h->n_staged++;
     return FMQ_OK;
 }
 
@@ -606,10 +608,11 @@ static int ingest_cols(fmq_handle* h, const InCols& c, size_t n, int32_t mem, cu
     const unsigned wgrid = (unsigned)h->num_sms * 8;
     *wait_copy = nullptr;
     if (mem == FMQ_MEM_HOST && n > 0) {
-        fmq_handle::Staged& g = h->staged;
-        if (g.valid && !(g.n == n && same_cols(g.c, c))) return set_err(h, FMQ_ERR_BAD_ARG, "a batch was staged with fmq_stage_host: the next host push must pass the same columns and n");
-        if (!g.valid) { int s_ = queue_host_copy(h, c, n); if (s_) return s_; }
-        g.valid = false;
+        if (h->n_staged > 0 && !(h->staged[0].n == n && same_cols(h->staged[0].c, c)))
+            return set_err(h, FMQ_ERR_BAD_ARG, "batches were staged with fmq_stage_host: the next host push must pass the columns and n of the oldest one");
+        if (h->n_staged == 0) { int s_ = queue_host_copy(h, c, n); if (s_) return s_; }
+        const fmq_handle::Staged g = h->staged[0];                   // consume the oldest staged batch
+        h->staged[0] = h->staged[1]; h->n_staged--;
         const size_t mb = h->max_batch;
         const u32* nar = h->hs_narrow[g.set];
         i64* sts = h->hs_ts[g.set]; u64* skey = h->hs_key[g.set]; u64* sval = h->hs_val[g.set];
@@ -713,7 +716,7 @@ int32_t fmq_stage_host(fmq_handle* h, const fmq_packed_columns* p, size_t n) {
     int s = check_packed(h, p); if (s) return s;
     if (n == 0 || !p->ts || !p->key || !p->val) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_stage_host needs a non-empty batch");
     if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_config.max_batch");
-    if (h->staged.valid) return set_err(h, FMQ_ERR_BAD_ARG, "one batch is already staged: push it first");
+    if (h->n_staged >= 2) return set_err(h, FMQ_ERR_BAD_ARG, "two batches are already staged: push the oldest first");
     CU(h, cudaSetDevice(h->device));
     const InCols c{p->ts, p->key, p->val, (int)p->ts_width, (int)p->key_width, (int)p->val_width, p->ts_width == 4 ? p->ts_base : 0};
     return queue_host_copy(h, c, n);

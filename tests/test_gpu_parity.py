@@ -568,16 +568,19 @@ def test_staging_the_next_host_batch_ahead():
         else:
             packed.append((ts, key, val, 0))
     gpu.stage_host(*packed[0][:3], ts_base=packed[0][3])
+    gpu.stage_host(*packed[1][:3], ts_base=packed[1][3])                # two batches ahead, first in first out
     for i, cols in enumerate(packed):
         if i == 2:
             with pytest.raises(capi.FmqError) as e:
-                gpu.push_batch(*batches[0])                     # not the staged columns
+                gpu.push_batch(*batches[0])                     # not the oldest staged columns
             assert e.value.status == 1 and "staged" in str(e.value)
             with pytest.raises(capi.FmqError):
-                gpu.stage_host(*packed[3][:3], ts_base=packed[3][3])    # only one batch ahead
+                gpu.push_packed(*packed[3][:3], ts_base=packed[3][3])   # staged, but not the oldest
+            with pytest.raises(capi.FmqError):
+                gpu.stage_host(*packed[4][:3], ts_base=packed[4][3])    # only two batches ahead
         gpu.push_packed(*cols[:3], ts_base=cols[3])
-        if i + 1 < len(packed):
-            gpu.stage_host(*packed[i + 1][:3], ts_base=packed[i + 1][3])
+        if i + 2 < len(packed):
+            gpu.stage_host(*packed[i + 2][:3], ts_base=packed[i + 2][3])
         cpu.push_batch(*batches[i])
         compare_all(gpu, cpu)
     gpu.flush(); cpu.flush()
