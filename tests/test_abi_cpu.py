@@ -30,13 +30,14 @@ def test_library_exports_every_declared_symbol():
 def test_config_struct_layout_matches_header():
     """sizeof(fmq_config) as the C compiler sees it == ctypes mirror."""
     import subprocess, tempfile
-    src = '#include "fmq_b200.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu", sizeof(fmq_config), sizeof(fmq_counters), sizeof(fmq_fired_cols));return 0;}\n'
+    src = '#include "fmq_b200.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu", sizeof(fmq_config), sizeof(fmq_counters), sizeof(fmq_fired_cols), sizeof(fmq_packed_columns));return 0;}\n'
     with tempfile.TemporaryDirectory() as d:
         c = os.path.join(d, "s.c"); open(c, "w").write(src)
         exe = os.path.join(d, "s")
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", exe, c])
-        a, b, f = map(int, subprocess.check_output([exe]).split())
+        a, b, f, p = map(int, subprocess.check_output([exe]).split())
     assert a == C.sizeof(capi.FmqConfig) and b == C.sizeof(capi.FmqCounters) and f == C.sizeof(capi.FmqFiredCols)
+    assert p == C.sizeof(capi.FmqPackedColumns)
 
 
 def test_bad_arguments_are_rejected_before_touching_a_device():
