@@ -51,6 +51,12 @@ def test_bad_arguments_are_rejected_before_touching_a_device():
     assert lib.fmq_create(C.byref(cfg), C.byref(h)) == 1          # size % slide != 0
     cfg = capi.make_config(window_enabled=1, window_size_ms=10, window_slide_ms=10, max_out_of_orderness_ms=-1)
     assert lib.fmq_create(C.byref(cfg), C.byref(h)) == 1          # chapter3/README.md:356-359
+    # entry points that take a handle answer FMQ_ERR_BAD_ARG to a null one (no device is touched)
+    pc = capi.FmqPackedColumns(C.sizeof(capi.FmqPackedColumns), 4, 4, 8, 0, None, None, None)
+    assert lib.fmq_push_packed(None, C.byref(pc), 0, 0, capi.FMQ_MEM_HOST) == 1
+    assert lib.fmq_stage_host(None, C.byref(pc), 1) == 1
+    assert lib.fmq_push_local_packed(None, C.byref(pc), 0, capi.FMQ_MEM_HOST) == 1
+    assert lib.fmq_combiner_overlap(None, 1) == 1 and lib.fmq_fire_stream(None) is None
 
 
 def test_no_cpu_fallback_without_gpu():
