@@ -76,6 +76,12 @@ typedef enum fmq_alert_source {
 /* watermark_after value meaning "derive it from the data": wm = max(wm, maxTsSeen - bound)
  * (BoundedOutOfOrdernessTimestampExtractor, chapter3/README.md:379-396). */
 #define FMQ_WM_AUTO INT64_MIN
+/* watermark_after value meaning "no watermark arrives with this batch": the records are ingested (and
+ * judged against the watermark already in force), the max-timestamp tracking of the extractor moves on,
+ * but the watermark itself stays where it is and nothing fires.  This is what a shim behind Flink's own
+ * watermark assigner passes when its buffer fills up BETWEEN two upstream watermarks: WindowOperator only
+ * moves event time in processWatermark ([Flink 1.8.0] WindowOperator#processElement never advances it). */
+#define FMQ_WM_KEEP (INT64_MIN + 1)
 /* watermark that fires every remaining window (Flink's end-of-input Watermark(Long.MAX_VALUE)) */
 #define FMQ_WM_FINAL INT64_MAX
 
@@ -177,7 +183,8 @@ typedef struct fmq_counters {
     uint64_t window_alerts;
     uint64_t event_alerts;
     uint64_t consec_alerts;
-    uint64_t keys;                   /* distinct keys in the directory                           */
+    uint64_t keys;                   /* distinct keys in the directory (FMQ_KEYS_HASHED and keyed
+                                        state only; a FMQ_KEYS_DENSE handle has no directory: 0) */
     int64_t  watermark;              /* current watermark                                        */
     uint64_t gpu_launches;           /* kernels launched by this handle so far                   */
 } fmq_counters;
@@ -421,8 +428,11 @@ int32_t fmq_exchange_pull_push(fmq_handle* h, int32_t parity, const uint64_t* ma
 /* Largest batch fmq_partition_by_owner_noalloc accepts (events). */
 #define FMQ_NOALLOC_MAX_EVENTS 4194304
 
-/* No counterpart in the reference.  The same stable owner split as fmq_partition_by_owner, for
- * callers that may not allocate device memory while they run: an operator thread that shares its
+/* No counterpart in the reference.  The stable owner split of fmq_partition_by_owner in its
+ * FMQ_KEYS_HASHED form — owner = fmq_owner_of(key, world) = mix64(key) % world, key column copied
+ * unchanged — for callers that may not allocate device memory while they run.  (It has no handle and
+ * therefore no key mode: a FMQ_KEYS_DENSE job, whose handle-based split routes by id % world and
+ * rewrites the ids to id / world, must not switch to this call.)  Such callers are: an operator thread that shares its
  * GPU with other subtasks (cudaMalloc / cudaFree synchronise the whole device and would stall
  * their kernels), or a process that has handed all device memory to its own arena, where a
  * driver allocation can simply fail.  The call needs no handle and calls no cudaMalloc, cudaFree
@@ -433,8 +443,14 @@ int32_t fmq_exchange_pull_push(fmq_handle* h, int32_t parity, const uint64_t* ma
  *   - ts/key/val and the *_out columns are device pointers owned by the caller; counts[world] is
  *     host memory.  The work is queued on `stream` (a cudaStream_t, NULL = default stream) of
  *     `device`, and the call returns after that stream has drained (the counts are read back).
- *   - The first call on each device looks up the device address of the built-in scratch once.
- *     Make that first call before starting any stream capture.
+ *   - The first call on each device looks up the device address of the built-in scratch once, and
+ *     like any first use of a kernel it makes the CUDA runtime load this library's device code
+ *     (which includes the scratch array) onto that GPU — work the driver may allocate for.  Make
+ *     that first call per device while the job is being set up: before any stream capture, before
+ *     an arena takes the rest of the device memory, and before other subtasks depend on the GPU
+ *     being undisturbed.  Every later call allocates nothing.
+ *   - The call makes `device` current while it runs and puts the caller's current device back
+ *     before it returns.
  *   - All calls on one device share the one scratch array, which keeps whatever the previous call
  *     left in it.  Nothing in it needs clearing (every counter is stored before it is read), but
  *     two calls whose kernels can overlap on the same GPU — different streams, different

@@ -38,6 +38,7 @@ public class GpuWindowAggOperator extends AbstractStreamOperator<Tuple3<String, 
     private static native String nLastError(long h);                                                        // fmq_last_error
     private static native void nDestroy(long h);                                                            // fmq_destroy
 
+    private static final long FMQ_WM_KEEP = Long.MIN_VALUE + 1;   // include/fmq_b200.h: no watermark arrives with this batch
     private static final int CAP = 1 << 20;                 // records per micro-batch
     private final byte[] configBytes;                       // a serialized fmq_config (see GpuWindowAggConfig)
 
@@ -66,7 +67,7 @@ public class GpuWindowAggOperator extends AbstractStreamOperator<Tuple3<String, 
 
     @Override
     public void processElement(StreamRecord<Tuple3<Integer, String, Long>> record) throws Exception {
-        if (n == CAP) pushAndDrain(Long.MIN_VALUE);          // FMQ_WM_AUTO: buffer full between two watermarks
+        if (n == CAP) pushAndDrain(FMQ_WM_KEEP);             // buffer full between two upstream watermarks: event time does not move
         Tuple3<Integer, String, Long> v = record.getValue();
         Long id = dict.get(v.f1);
         if (id == null) { id = (long) names.size(); dict.put(v.f1, id); names.add(v.f1); }
@@ -107,7 +108,7 @@ public class GpuWindowAggOperator extends AbstractStreamOperator<Tuple3<String, 
     @Override
     public void close() throws Exception {
         if (handle != 0) {
-            if (n > 0) pushAndDrain(Long.MIN_VALUE);
+            if (n > 0) pushAndDrain(FMQ_WM_KEEP);
             check(nFlush(handle, Long.MAX_VALUE));           // end of a finite source: Watermark(Long.MAX_VALUE)
             pushAndDrain(Long.MAX_VALUE);
             nDestroy(handle);

@@ -24,6 +24,7 @@ FMQ_CMP_GT, FMQ_CMP_LT, FMQ_CMP_GE, FMQ_CMP_LE = 0, 1, 2, 3
 FMQ_AGG_COUNT, FMQ_AGG_SUM, FMQ_AGG_MIN, FMQ_AGG_MAX = 1, 2, 4, 8
 FMQ_ALERT_NONE, FMQ_ALERT_SUM, FMQ_ALERT_AVG, FMQ_ALERT_MIN, FMQ_ALERT_MAX, FMQ_ALERT_COUNT = range(6)
 FMQ_WM_AUTO = -(2 ** 63)
+FMQ_WM_KEEP = -(2 ** 63) + 1
 FMQ_WM_FINAL = 2 ** 63 - 1
 
 STATUS_NAMES = {0: "OK", 1: "BAD_ARG", 2: "TABLE_FULL", 3: "RING_OVERFLOW", 4: "OUTPUT_OVERFLOW",
@@ -120,8 +121,11 @@ def load_library() -> C.CDLL:
     return lib
 
 
-def _declare(lib, p: str, has_mem: bool = True):
-    """Attach argtypes/restype for every entry point; `p` is the symbol prefix."""
+def _declare(lib, p: str, has_mem: bool = True, side_outputs: Optional[bool] = None):
+    """Attach argtypes/restype for every entry point; `p` is the symbol prefix.  `has_mem`: the calls
+    take the host/device `mem` argument (the product does); `side_outputs`: the library exports
+    poll_late / poll_medians (default: same as has_mem)."""
+    side_outputs = has_mem if side_outputs is None else side_outputs
     vp, sz, i32, i64 = C.c_void_p, C.c_size_t, C.c_int32, C.c_int64
     psz = C.POINTER(C.c_size_t)
     mem = [i32] if has_mem else []
@@ -135,7 +139,7 @@ def _declare(lib, p: str, has_mem: bool = True):
     sig("poll_fired", [vp, C.POINTER(FmqFiredCols), sz] + mem + [psz, psz])
     sig("poll_window_alerts", [vp, C.POINTER(FmqWAlertCols), sz] + mem + [psz, psz])
     sig("poll_event_alerts", [vp, C.POINTER(FmqEventCols), sz] + mem + [psz, psz])
-    if has_mem or p == "orc_":
+    if side_outputs:
         sig("poll_late", [vp, C.POINTER(FmqEventCols), sz] + mem + [psz, psz])
         sig("poll_medians", [vp, C.POINTER(FmqWAlertCols), sz] + mem + [psz, psz])
     sig("poll_consec_alerts", [vp, C.POINTER(FmqEventCols), sz] + mem + [psz, psz])
@@ -233,8 +237,9 @@ class EventRows:
 
 
 class EngineBase:
-    """Shared driver for anything exporting the fmq-shaped ABI (the product, and — in tests only —
-    the CPU oracle, which exports the same calls under the ``orc_`` prefix without ``mem``)."""
+    """Shared driver for anything exporting the fmq-shaped ABI: the product library, and any other
+    library with the same call shapes under another symbol prefix (with or without the ``mem``
+    argument) that a caller loads itself."""
 
     def __init__(self, lib, prefix: str, cfg: FmqConfig, has_mem: bool):
         self._lib, self._p, self._has_mem = lib, prefix, has_mem
@@ -250,9 +255,10 @@ class EngineBase:
         return getattr(self._lib, self._p + name)
 
     def _err(self, h) -> str:
-        if not self._has_mem:
-            return "oracle error"
-        m = self._lib.fmq_last_error(h)
+        f = getattr(self._lib, self._p + "last_error", None)
+        if f is None:
+            return "(the library exports no last_error)"
+        m = f(h)
         return m.decode() if m else ""
 
     def _check(self, st):

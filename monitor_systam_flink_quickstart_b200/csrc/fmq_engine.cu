@@ -497,7 +497,7 @@ static int fire_medians(fmq_handle* h) {
 template <typename V>
 static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now) {
     const fmq_config& c = h->cfg;
-    PlanArgs p{h->d_st, h->g, c.max_out_of_orderness_ms, wm_after, (u64)n, c.window_enabled, wm_after == FMQ_WM_AUTO, h->overlap ? 1 : 0};
+    PlanArgs p{h->d_st, h->g, c.max_out_of_orderness_ms, wm_after, (u64)n, c.window_enabled, wm_after == FMQ_WM_AUTO, wm_after == FMQ_WM_KEEP, h->overlap ? 1 : 0};
     plan_kernel<<<1, 32, 0, h->stream>>>(p); LAUNCHED(h, "plan_kernel");
     cudaStream_t fs = h->stream;
     if (h->overlap) {                                          // everything from the fire kernel on runs beside the next ingest
@@ -505,7 +505,8 @@ static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now
         CU(h, cudaStreamWaitEvent(h->fire_stream, h->ev_plan, 0));
         fs = h->fire_stream;
     }
-    if (c.window_enabled && wm_after != FMQ_WM_AUTO && wm_after > INT64_MIN) h->anchored_known = true;
+    if (c.window_enabled && wm_after != FMQ_WM_AUTO && wm_after != FMQ_WM_KEEP &&
+        wm_after >= INT64_MIN + c.window_size_ms + c.window_offset_ms + c.window_slide_ms + 2) h->anchored_known = true;
     if (c.window_enabled && h->ml_cap > 0) { int s_ = fire_medians(h); if (s_) return s_; }
     if (c.window_enabled) {
         FireArgs f{};
@@ -734,7 +735,7 @@ int32_t fmq_push_packed(fmq_handle* h, const fmq_packed_columns* p, size_t n, in
 int32_t fmq_flush(fmq_handle* h, int64_t watermark) {
     if (!h) return FMQ_ERR_BAD_ARG;
     if (h->sticky) return FMQ_ERR_POISONED;
-    if (watermark == FMQ_WM_AUTO) return set_err(h, FMQ_ERR_BAD_ARG, "flush needs an explicit watermark");
+    if (watermark == FMQ_WM_AUTO || watermark == FMQ_WM_KEEP) return set_err(h, FMQ_ERR_BAD_ARG, "flush needs an explicit watermark");
     if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: use fmq_fire_global / fmq_retire");
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][0], h->stream));
@@ -886,8 +887,10 @@ int32_t fmq_get_key_state(fmq_handle* h, const uint64_t* keys, size_t n, int32_t
     if (!keyed_enabled(h->cfg)) return set_err(h, FMQ_ERR_BAD_ARG, "no keyed state operator is enabled");
     if (n == 0) return FMQ_OK;
     CU(h, cudaSetDevice(h->device));
-    u64* dk = nullptr; int *df = nullptr, *dc = nullptr; u64* dr = nullptr;
-    CU(h, dalloc(&dk, n)); CU(h, dalloc(&df, n)); CU(h, dalloc(&dc, n)); CU(h, dalloc(&dr, n));
+    // one temporary buffer, released on every path out of this function
+    struct Tmp { void* p = nullptr; ~Tmp() { if (p) cudaFree(p); } } tmp;
+    CU(h, cudaMalloc(&tmp.p, n * 24));
+    u64* dk = static_cast<u64*>(tmp.p); u64* dr = dk + n; int* df = reinterpret_cast<int*>(dr + n); int* dc = df + n;
     CU(h, cudaMemcpyAsync(dk, keys, n * 8, cudaMemcpyHostToDevice, h->stream));
     key_state_lookup_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(dk, n, h->d_keys, h->capacity, h->cfg.key_mode == FMQ_KEYS_DENSE, h->d_kflags, h->d_kmax, df, dc, dr);
     LAUNCHED(h, "key_state_lookup_kernel");
@@ -895,7 +898,6 @@ int32_t fmq_get_key_state(fmq_handle* h, const uint64_t* keys, size_t n, int32_t
     CU(h, cudaMemcpyAsync(consec, dc, n * 4, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaMemcpyAsync(rolling, dr, n * 8, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
-    cudaFree(dk); cudaFree(df); cudaFree(dc); cudaFree(dr);
     return FMQ_OK;
 }
 
@@ -1117,11 +1119,14 @@ int32_t fmq_restore(fmq_handle* h, const void* buf, size_t bytes) {
     if (hd.magic != SNAP_MAGIC || hd.version != 1 || hd.header_bytes != sizeof(SnapHeader)) return set_err(h, FMQ_ERR_BAD_ARG, "not a snapshot of this library version");
     if (hd.capacity != h->capacity || hd.ring != h->ring || !same_job(hd.cfg, h->cfg) || hd.total_bytes != snap_bytes(h) || bytes < hd.total_bytes)
         return set_err(h, FMQ_ERR_BAD_ARG, "snapshot was taken with a different job geometry (capacity, ring, window, value type, key mode)");
+    if (h->n_staged > 0 || h->out_pending) return set_err(h, FMQ_ERR_BAD_ARG, "restore while host batches are staged or an overlapped poll is pending: consume them first");
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaStreamSynchronize(h->stream));
+    if (h->fire_stream) CU(h, cudaStreamSynchronize(h->fire_stream));
+    if (h->copy_stream) CU(h, cudaStreamSynchronize(h->copy_stream));
     const char* p = static_cast<const char*>(buf) + sizeof(SnapHeader);
     DevState d; memcpy(&d, p, sizeof(d)); p += sizeof(d);
-    d.n_fired = d.n_walert = d.n_ealert = d.n_calert = 0; d.n_late = 0; d.err_flags = 0;
+    d.n_fired = d.n_walert = d.n_ealert = d.n_calert = 0; d.n_late = 0; d.n_median = 0; d.n_mlog = 0; d.n_mwork = 0; d.err_flags = 0;
     CU(h, cudaMemcpyAsync(h->d_st, &d, sizeof(d), cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaMemcpyAsync(h->d_keys, p, h->capacity * 8, cudaMemcpyHostToDevice, h->stream)); p += h->capacity * 8;
     if (hd.has_window) { const size_t b = (size_t)h->ring * h->capacity * sizeof(Acc32); CU(h, cudaMemcpyAsync(h->d_acc, p, b, cudaMemcpyHostToDevice, h->stream)); p += b; }
@@ -1130,7 +1135,8 @@ int32_t fmq_restore(fmq_handle* h, const void* buf, size_t bytes) {
         CU(h, cudaMemcpyAsync(h->d_kmax, p, h->capacity * 8, cudaMemcpyHostToDevice, h->stream)); p += h->capacity * 8;
     }
     CU(h, cudaStreamSynchronize(h->stream));
-    h->cur_fired = h->cur_walert = h->cur_ealert = h->cur_calert = 0; h->rolling_n = 0; h->sticky = 0;
+    h->cur_fired = h->cur_walert = h->cur_ealert = h->cur_calert = 0; h->cur_late = 0; h->cur_median = 0;
+    h->rolling_n = 0; h->pending_n = 0; h->sticky = 0;
     h->anchored_known = hd.anchored_known != 0;
     return FMQ_OK;
 }
@@ -1310,7 +1316,11 @@ extern "C" int32_t fmq_partition_by_owner_noalloc(int32_t device, void* stream_,
     for (uint32_t w = 0; w < world; ++w) counts[w] = 0;
     if (n == 0) return FMQ_OK;
     if (!ts || !key || !val || !ts_out || !key_out || !val_out) { g_create_err = "null column pointer"; return FMQ_ERR_BAD_ARG; }
-    NA_CU(cudaSetDevice(device));
+    // the caller's current device is put back before returning (success or failure)
+    struct DeviceGuard { int prev = -1; ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); } } guard;
+    int cur = -1;
+    NA_CU(cudaGetDevice(&cur));
+    if (cur != device) { NA_CU(cudaSetDevice(device)); guard.prev = cur; }
     u32* scratch = nullptr;
     int st = noalloc_scratch_for(device, &scratch); if (st) return st;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);

@@ -569,6 +569,7 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
 // ---- plan: one thread turns "watermark_after" into a fire / expire schedule ---------------------
 struct PlanArgs {
     DevState* st; WindowGeom g; i64 bound; i64 watermark_after; u64 n_events; int window_enabled; int is_auto;
+    int is_keep;      // FMQ_WM_KEEP: bookkeeping only, the watermark stays where it is
     int overlap;      // combiner mode with fire / retire on a second stream: the next ingest starts before the expired panes are cleared
 };
 
@@ -593,9 +594,14 @@ __global__ void plan_kernel(const PlanArgs a) {
     // ring validity: every pane that holds data must fit the ring at once
     const bool has_data = st->min_pane <= st->max_pane;
     if (has_data && (st->max_pane - st->min_pane) >= (i64)(a.g.ring_mask + 1)) st->err_flags |= ERRB_RING;
+    if (a.is_keep) return;                                     // no watermark came with this batch
     if (target <= st->wm) return;                              // watermarks never go backwards
     const i64 wm_old = st->wm;
     st->wm = target;
+    // a watermark this close to INT64_MIN cannot make anything late or fire anything (ts >= 0) and would
+    // overflow the pane arithmetic below: it is recorded and otherwise leaves the stream un-anchored
+    const i64 wm_floor = I64_MIN_ + a.g.size + a.g.off + a.g.slide + 2;
+    if (target < wm_floor) return;
     const i64 size = a.g.size, slide = a.g.slide, off = a.g.off;
     const bool final_wm = (target == I64_MAX_);
     // first pane that stays live: p*slide + off + size - 1 > target
@@ -607,7 +613,7 @@ __global__ void plan_kernel(const PlanArgs a) {
         const i64 e_data_lo = st->min_pane * slide + off + slide;      // window whose last pane is min_pane
         const i64 e_data_hi = st->max_pane * slide + off + size;       // window whose first pane is max_pane
         i64 e_lo = e_data_lo, e_hi = e_data_hi;
-        if (wm_old != I64_MIN_) {
+        if (wm_old >= wm_floor) {
             const i64 e_wm_lo = (floor_div(wm_old + 1 - off, slide) + 1) * slide + off;   // smallest end > wm_old + 1
             if (e_wm_lo > e_lo) e_lo = e_wm_lo;
         }

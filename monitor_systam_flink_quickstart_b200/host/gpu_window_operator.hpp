@@ -37,12 +37,12 @@ public:
     template <typename V>
     void processElement(int64_t ts, const std::string& key, V value) {  // #processElement
         static_assert(sizeof(V) == 8, "values are 8-byte (double or int64_t)");
-        if (n_ == cap_) push(FMQ_WM_AUTO);
+        if (n_ == cap_) push(FMQ_WM_KEEP);                               // buffer full between two upstream watermarks: time does not move
         ts_[n_] = ts; key_[n_] = encode(key); std::memcpy(&val_[n_], &value, 8); ++n_;
     }
     void processWatermark(int64_t wm) { push(wm); }                     // #processWatermark
     void close() {                                                      // #close: Watermark(Long.MAX_VALUE)
-        if (n_) push(FMQ_WM_AUTO);
+        if (n_) push(FMQ_WM_KEEP);
         check(fmq_flush(h_, FMQ_WM_FINAL), h_); drain();
         fmq_destroy(h_); h_ = nullptr;
     }

@@ -24,8 +24,14 @@ class GpuWindowAggOperator:
     ("window_alert", (key, window_end-1, value)), ("event_alert", (ts, key, val)),
     ("consec_alert", (ts, key, val)), ("rolling_max", (key, value))."""
 
-    def __init__(self, collector: Callable, batch_capacity: int = 1 << 16, engine_factory: Optional[Callable] = None, **config):
+    def __init__(self, collector: Callable, batch_capacity: int = 1 << 16, engine_factory: Optional[Callable] = None,
+                 auto_watermark: bool = False, **config):
+        """auto_watermark: False (default) = watermarks come from upstream through process_watermark, like in a
+        Flink job whose assigner sits in front of the keyBy; a buffer that fills up between two of them is pushed
+        with FMQ_WM_KEEP, so event time only ever moves in process_watermark ([Flink 1.8.0] WindowOperator).
+        True = the engine derives the watermark itself at every micro-batch boundary (FMQ_WM_AUTO)."""
         self._collector = collector
+        self._between = capi.FMQ_WM_AUTO if auto_watermark else capi.FMQ_WM_KEEP
         self._cap = batch_capacity
         self._config = dict(config)
         self._config.setdefault("max_batch", batch_capacity)
@@ -47,7 +53,7 @@ class GpuWindowAggOperator:
     def process_element(self, timestamp_ms: int, key, value):
         """`key` may be a string (dictionary-encoded here, like the Java shim) or an integer id."""
         if self._n == self._cap:
-            self._push(capi.FMQ_WM_AUTO if self._config.get("max_out_of_orderness_ms") is not None else None)
+            self._push(self._between)
         i = self._n
         self._ts[i] = timestamp_ms
         self._key[i] = self.keys.encode(key) if isinstance(key, str) else key
@@ -105,7 +111,7 @@ class GpuWindowAggOperator:
         if self._engine is None:
             return
         if self._n:
-            self._push(capi.FMQ_WM_AUTO)
+            self._push(self._between)
         self._engine.flush(capi.FMQ_WM_FINAL)
         self._drain(0, np.empty(0, np.uint64))
         self._engine.close()

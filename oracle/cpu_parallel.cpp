@@ -5,7 +5,7 @@
 // instances, each doing per-record / per-window work (assignWindows fan-out, late test, keyed
 // accumulator update) and firing on the watermark.  It is the timed CPU baseline of bench.py
 // ("C++ restatement of the reference semantics", kind "port" — NOT Flink, which cannot run on
-// this box: no JVM).  tests/test_cpu_parallel.py checks it row-for-row against the literal oracle.
+// this box: no JVM).  tests/test_oracle_cross.py checks it row-for-row against the literal oracle.
 #include <cstdint>
 #include <cstring>
 #include <cmath>
@@ -167,8 +167,8 @@ struct Par : ParBase {
         if (cfg.window_enabled) {
             for (int t = 0; t < T; t++) if (lmax[t] > cur_max_ts) cur_max_ts = lmax[t];
             int64_t w = wm_after;
-            if (w == FMQ_WM_AUTO) { int64_t p = cur_max_ts - cfg.max_out_of_orderness_ms; if (p >= last_wm) last_wm = p; w = last_wm; }
-            advance(w);
+            if (wm_after == FMQ_WM_AUTO) { int64_t p = cur_max_ts - cfg.max_out_of_orderness_ms; if (p >= last_wm) last_wm = p; w = last_wm; }
+            if (wm_after != FMQ_WM_KEEP) advance(w);
         }
         collect();
         return FMQ_OK;

@@ -210,7 +210,8 @@ struct Oracle : OracleBase {
             if (ts[i] < 0 || key[i] == UINT64_MAX) { err = "negative timestamp or reserved key"; return FMQ_ERR_BAD_TS; }
             process_element(ts[i], key[i], v[i]);
         }
-        if (cfg.window_enabled) advance_watermark(wm_after == FMQ_WM_AUTO ? auto_watermark() : wm_after);
+        // FMQ_WM_KEEP: no Watermark element follows these records (WindowOperator#processElement never moves time)
+        if (cfg.window_enabled && wm_after != FMQ_WM_KEEP) advance_watermark(wm_after == FMQ_WM_AUTO ? auto_watermark() : wm_after);
         ctr.keys = kstate.size();
         return FMQ_OK;
     }

@@ -178,6 +178,8 @@ class NaiveFlinkModel:
         for t, k, v in zip(ts, key, val):
             self._element(int(t), int(k), float(v) if self.is_f64 else int(v))
         if self.window:
+            if watermark_after == I64_MIN + 1:       # FMQ_WM_KEEP: no watermark follows this batch
+                return
             if watermark_after == I64_MIN:
                 pot = self.cur_max_ts - self.bound
                 if pot >= self.last_wm:

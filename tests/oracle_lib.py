@@ -19,7 +19,7 @@ def lib():
         if not os.path.exists(_SO):
             subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
         _lib = C.CDLL(_SO)
-        capi._declare(_lib, "orc_", has_mem=False)
+        capi._declare(_lib, "orc_", has_mem=False, side_outputs=True)
         vp, sz, i32, i64 = C.c_void_p, C.c_size_t, C.c_int32, C.c_int64
         psz = C.POINTER(C.c_size_t)
         _lib.orc_java_string_hash.argtypes, _lib.orc_java_string_hash.restype = [C.c_char_p, sz], i32

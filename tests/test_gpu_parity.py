@@ -168,6 +168,38 @@ def test_window_parity_skewed_keys_switch_on_warp_combining(vt):
     assert c.max() > 0.1 * 300_000                      # the stream really is skewed
 
 
+def test_full_buffers_between_two_upstream_watermarks_do_not_move_time():
+    """FMQ_WM_KEEP: a shim behind Flink's own assigner pushes a full buffer without a watermark; records that an
+    early watermark would have made late must still be counted (WindowOperator moves time in processWatermark only)."""
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=5000, window_slide_ms=1000, max_out_of_orderness_ms=0, late_capacity=1 << 12, **SMALL)
+    gpu, cpu = pair(**kw)
+    spec = StreamSpec(n_keys=200, events_per_ms=1, jitter_ms=6000, late_frac_ppm=0, t0=1_000_000)
+    plan = [1_003_000, capi.FMQ_WM_KEEP, capi.FMQ_WM_KEEP, 1_012_500, capi.FMQ_WM_KEEP, capi.FMQ_WM_AUTO, capi.FMQ_WM_KEEP]
+    for i, wm in enumerate(plan):
+        ts, key, val = generate_numpy(spec, i * 4000, 4000)
+        for e in (gpu, cpu):
+            e.push_batch(ts, key, val, wm)
+        assert gpu.counters()["watermark"] == cpu.counters()["watermark"]
+    compare_all(gpu, cpu)
+    for e in (gpu, cpu):
+        e.flush()
+    compare_all(gpu, cpu)
+    assert cpu.counters()["late_dropped"] > 0
+
+
+def test_keep_before_any_watermark_leaves_the_stream_unanchored():
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=4000, window_slide_ms=2000, max_out_of_orderness_ms=1000, **SMALL)
+    gpu, cpu = pair(**kw)
+    spec = StreamSpec(n_keys=64, events_per_ms=1, jitter_ms=3000, late_frac_ppm=0, t0=50_000)
+    for i, wm in enumerate([capi.FMQ_WM_KEEP, capi.FMQ_WM_KEEP, capi.FMQ_WM_AUTO, capi.FMQ_WM_KEEP]):
+        ts, key, val = generate_numpy(spec, i * 3000, 3000)
+        for e in (gpu, cpu):
+            e.push_batch(ts, key, val, wm)
+    for e in (gpu, cpu):
+        e.flush()
+    compare_all(gpu, cpu)
+
+
 def test_explicit_watermarks_and_empty_batches():
     kw = dict(window_enabled=1, agg_mask=15, window_size_ms=5000, window_slide_ms=5000, **SMALL)
     gpu, cpu = pair(**kw)

@@ -49,7 +49,7 @@ def small_stream(draw, f64):
             val = np.array([draw(st.one_of(st.floats(0, 100, allow_nan=False), st.sampled_from([0.0, -0.0, 90.0, 50.0]))) for _ in range(n)], np.float64)
         else:
             val = np.array([draw(st.integers(0, 1 << 20)) for _ in range(n)], np.int64)
-        wm = draw(st.sampled_from([capi.FMQ_WM_AUTO, capi.FMQ_WM_AUTO, t - 5000, t + 10_000]))
+        wm = draw(st.sampled_from([capi.FMQ_WM_AUTO, capi.FMQ_WM_AUTO, capi.FMQ_WM_KEEP, t - 5000, t + 10_000]))
         batches.append((ts, key, val, wm))
         t += draw(st.integers(0, 30_000))
     return batches
@@ -84,7 +84,8 @@ def test_parallel_baseline_matches_literal_oracle(name, threads):
     a, b = OracleEngine(**kw), ParallelOracle(threads=threads, **kw)
     for bi in range(6):
         ts, key, val = generate_numpy(spec, bi * 20000, 20000)
-        a.push_batch(ts, key, val); b.push_batch(ts, key, val)
+        wm = capi.FMQ_WM_KEEP if bi in (2, 3) else capi.FMQ_WM_AUTO       # two buffers fill up between watermarks
+        a.push_batch(ts, key, val, wm); b.push_batch(ts, key, val, wm)
     a.flush(); b.flush()
     assert_fired_equal(a.poll_fired(), b.poll_fired(), f64_sum_rtol=0.0)
     wa, wb = sort_walerts(a.poll_window_alerts()), sort_walerts(b.poll_window_alerts())

@@ -3,7 +3,8 @@ device memory while they run (an operator thread whose GPU is shared with other 
 cudaMalloc or cudaFree would stall everybody's kernels — or a process whose device memory all
 belongs to its own arena).  Its scratch is a fixed array inside the library, so this test calls it
 through the C ABI twice in a row (the second call finds the first call's leftovers in that array)
-and checks both results, bit for bit, against the handle-based fmq_partition_by_owner.
+and checks both results, bit for bit, against the handle-based fmq_partition_by_owner and against
+a numpy stable sort by mix64(key) % world; a third call runs the largest batch it accepts.
 
 Kept in a file pytest collects last: a failure here cannot hide a failure anywhere else."""
 import ctypes as C
@@ -12,6 +13,7 @@ import numpy as np
 import pytest
 
 from monitor_systam_flink_quickstart_b200 import capi
+from monitor_systam_flink_quickstart_b200.shard import owner_of_numpy
 from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy
 
 pytestmark = pytest.mark.gpu
@@ -54,6 +56,29 @@ def test_noalloc_split_matches_handle_based_split_twice_in_a_row():
         assert int(got_counts.sum()) == n
         for g, w in zip(got, want):                                    # bit-exact: integer / byte work
             assert torch.equal(g.view(torch.int64), w.view(torch.int64))
+        _check_against_numpy(cols, got, got_counts, world)
+
+
+def _check_against_numpy(cols, got, got_counts, world):
+    """Independent of the library: a stable argsort of the owner column is the expected permutation."""
+    owner = owner_of_numpy(cols[1].cpu().numpy().view(np.uint64), world)
+    order = np.argsort(owner, kind="stable")
+    np.testing.assert_array_equal(got_counts, np.bincount(owner, minlength=world).astype(np.uint64))
+    for g, c in zip(got, cols):
+        np.testing.assert_array_equal(g.cpu().numpy().view(np.int64), c.cpu().numpy().view(np.int64)[order])
+
+
+def test_noalloc_split_at_its_largest_batch():
+    """n == FMQ_NOALLOC_MAX_EVENTS uses every counter of the built-in scratch."""
+    import torch
+    lib = capi.load_library()
+    n = 4194304
+    cols = _device_columns(StreamSpec(n_keys=3_000_000, events_per_ms=500), 12_345, n)
+    torch.cuda.synchronize()
+    for world in (256, 5):
+        got, got_counts = _noalloc_split(lib, cols, world)
+        assert int(got_counts.sum()) == n
+        _check_against_numpy(cols, got, got_counts, world)
 
 
 def test_noalloc_split_rejects_batches_beyond_its_scratch():
