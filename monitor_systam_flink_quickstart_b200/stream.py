@@ -83,6 +83,12 @@ def _zipf_table(spec: StreamSpec, size: int = 1 << 16) -> np.ndarray:
     return spec._zipf_cdf
 
 
+def _zipf_next(spec: StreamSpec) -> np.ndarray:
+    """First rank of the following quantile (n_keys after the last one)."""
+    tab = _zipf_table(spec)
+    return np.append(tab[1:], np.uint64(spec.n_keys))
+
+
 def generate_numpy(spec: StreamSpec, start: int, n: int):
     """Events [start, start+n) on the host.  Returns (ts:int64, key:uint64, val:f64|i64)."""
     i = np.arange(start, start + n, dtype=np.uint64)
@@ -98,7 +104,11 @@ def generate_numpy(spec: StreamSpec, start: int, n: int):
         key = ((h1 % hosts) << np.uint64(32)) + ((h1 >> np.uint64(40)) % np.uint64(spec.metrics_per_host))
     elif spec.key_kind == "zipf":
         tab = _zipf_table(spec)
-        rank = tab[(h1 >> np.uint64(48)).astype(np.int64)]
+        q = (h1 >> np.uint64(48)).astype(np.int64)
+        # a quantile of the tail covers many ranks: spread the draw over all of them, so that a stream
+        # over 10^8 ids really touches millions of distinct ids (the head quantiles are single ranks)
+        span = np.maximum(_zipf_next(spec)[q] - tab[q], np.uint64(1))
+        rank = tab[q] + (h1 & np.uint64((1 << 48) - 1)) % span
         # spread ranks over the id space so hot keys are not adjacent ids
         key = (rank * np.uint64(0x9E3779B1)) % np.uint64(spec.n_keys)
     else:
@@ -138,7 +148,10 @@ def generate_torch(spec: StreamSpec, start: int, n: int, device="cuda"):
         key = (umod(h1, hosts) << 32) + (_lsr_t(h1, 40) % spec.metrics_per_host)
     elif spec.key_kind == "zipf":
         tab = torch.from_numpy(_zipf_table(spec).astype(np.int64)).to(device)
-        rank = tab[_lsr_t(h1, 48)]
+        nxt = torch.from_numpy(_zipf_next(spec).astype(np.int64)).to(device)
+        q = _lsr_t(h1, 48)
+        span = torch.clamp(nxt[q] - tab[q], min=1)
+        rank = tab[q] + (h1 & ((1 << 48) - 1)) % span
         key = (rank * 0x9E3779B1) % spec.n_keys
     else:
         raise ValueError(spec.key_kind)

@@ -27,6 +27,14 @@ template <typename T> struct FlatMap {            // open addressing, linear pro
         keys.assign(cap, UINT64_MAX); vals.assign(cap, T{}); mask = cap - 1; used = 0;
         for (size_t i = 0; i < ok.size(); i++) if (ok[i] != UINT64_MAX) { bool f; *get(ok[i], &f) = ov[i]; }
     }
+    const T* find(uint64_t k) const {
+        size_t h = mix64(k) & mask;
+        while (true) {
+            if (keys[h] == k) return &vals[h];
+            if (keys[h] == UINT64_MAX) return nullptr;
+            h = (h + 1) & mask;
+        }
+    }
     T* get(uint64_t k, bool* fresh) {
         if ((used + 1) * 10 > keys.size() * 6) rehash(keys.size() * 2);
         size_t h = mix64(k) & mask;
@@ -62,6 +70,7 @@ struct ParBase {
     virtual int push(const int64_t*, const uint64_t*, const void*, size_t, int64_t) = 0;
     virtual int flush(int64_t) = 0;
     virtual void counters(fmq_counters*) = 0;
+    virtual int key_state(uint64_t key, int32_t* consec, uint64_t* rolling_bits) = 0;
     std::vector<FiredRow> fired; std::vector<WAlert> walerts; std::vector<EvRow> ealerts, calerts;
 };
 
@@ -174,6 +183,11 @@ struct Par : ParBase {
         return FMQ_OK;
     }
     int flush(int64_t w) override { if (cfg.window_enabled) advance(w); collect(); return FMQ_OK; }
+    int key_state(uint64_t key, int32_t* consec, uint64_t* rolling_bits) override {
+        const KState* st = subs[mix64(key) % T].kstate.find(key);
+        if (!st) return 0;
+        *consec = st->c; *rolling_bits = st->has ? bits_of(st->mx) : 0; return 1;
+    }
     void counters(fmq_counters* c) override {
         std::memset(c, 0, sizeof(*c)); c->events_in = events_in; c->watermark = wm;
         for (auto& s : subs) { c->late_dropped += s.late; c->windows_fired += s.nfired; c->keys += s.kstate.used; }
@@ -211,5 +225,10 @@ static int32_t poll_ev(std::vector<EvRow>& v, const fmq_event_cols* o, size_t ca
 int32_t orcp_poll_event_alerts(void* h, const fmq_event_cols* o, size_t cap, size_t* n_out, size_t* n_left) { return poll_ev(static_cast<ParBase*>(h)->ealerts, o, cap, n_out, n_left); }
 int32_t orcp_poll_consec_alerts(void* h, const fmq_event_cols* o, size_t cap, size_t* n_out, size_t* n_left) { return poll_ev(static_cast<ParBase*>(h)->calerts, o, cap, n_out, n_left); }
 int32_t orcp_discard_outputs(void* h) { auto* b = static_cast<ParBase*>(h); b->fired.clear(); b->walerts.clear(); b->ealerts.clear(); b->calerts.clear(); return FMQ_OK; }
+int32_t orcp_get_key_state(void* h, const uint64_t* keys, size_t n, int32_t* found, int32_t* consec, void* rolling) {
+    auto* b = static_cast<ParBase*>(h);
+    for (size_t i = 0; i < n; i++) { consec[i] = 0; ((uint64_t*)rolling)[i] = 0; found[i] = b->key_state(keys[i], &consec[i], &((uint64_t*)rolling)[i]); }
+    return FMQ_OK;
+}
 int32_t orcp_destroy(void* h) { delete static_cast<ParBase*>(h); return FMQ_OK; }
 }

@@ -35,6 +35,7 @@ def lib():
         _lib.orcp_poll_window_alerts.argtypes = [vp, C.POINTER(capi.FmqWAlertCols), sz, psz, psz]
         _lib.orcp_poll_event_alerts.argtypes = [vp, C.POINTER(capi.FmqEventCols), sz, psz, psz]
         _lib.orcp_poll_consec_alerts.argtypes = [vp, C.POINTER(capi.FmqEventCols), sz, psz, psz]
+        _lib.orcp_get_key_state.argtypes, _lib.orcp_get_key_state.restype = [vp, vp, sz, vp, vp, vp], i32
         _lib.orcp_discard_outputs.argtypes = [vp]
         _lib.orcp_destroy.argtypes = [vp]
     return _lib
