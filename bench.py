@@ -172,7 +172,7 @@ def cpu_reference_run(steps, warmup, sample_events, threads, capi, ParallelOracl
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch-log2", type=int, default=24, help="events per micro-batch per GPU (log2)")
@@ -357,6 +357,19 @@ def main():
         variants = {f"key_mode={other}": {"value": B * K / (ms2 * 1e-3), "unit": "events/s", "ms_per_step": ms2 / K, "ingest_kernel_ms": ing2,
                                           "roofline_frac": (24.0 * B + 24.0 * d2["event_alerts"] / K) / (ing2 * 1e-3) / 1e9 / measured_peak()[0]}}
 
+        # the same stream through two narrower jobs (both inside the headline kernel's code path):
+        #   C1 (BASELINE.json configs[0]): chapter1's per-event `> 90` filter alone — no table, the streaming skeleton itself
+        #   count+sum: chapter3's own aggregate (BandwidthMonitor.java:37) — ONE accumulator request per event instead of two
+        def narrow(tag, kwn, alg_rows):
+            msn, ingn, firen, dn, _ = measure(kwn, False)
+            bytes_ = 24.0 * B + 24.0 * dn["event_alerts"] / K
+            variants[tag] = {"value": B * K / (msn * 1e-3), "unit": "events/s", "ms_per_step": msn / K, "ingest_kernel_ms": ingn,
+                             "roofline_frac": bytes_ / (ingn * 1e-3) / 1e9 / measured_peak()[0], "algorithmic_bytes_per_launch": bytes_}
+        kw_c1 = dict(kw); kw_c1.update(window_enabled=0, walert_source=0)
+        narrow("workload=C1 per-event >90 filter only (BASELINE.json configs[0])", kw_c1, 0)
+        kw_cs = dict(kw); kw_cs.update(agg_mask=capi.FMQ_AGG_COUNT | capi.FMQ_AGG_SUM, efilter_enabled=0)
+        narrow("aggregate=count+sum only, no per-event filter (one RED request per event)", kw_cs, 0)
+
         # BASELINE.json configs[1] (chapter2 keyed ValueState rule, 100 K hosts) beside the headline:
         # resolve -> radix sort by slot -> segmented scan of the per-record transition functions
         spec_c2 = StreamSpec(n_keys=100_000)
@@ -392,7 +405,7 @@ def main():
     # ByteBuffers), then drain every output column into pinned host buffers.  H2D and D2H copies are
     # inside the timed region; host wall clock with a full synchronise at both ends.
     e2e = None
-    e2e_wide = None
+    e2e_packed = None
     combiner = sharded and args.multi == "combiner" and args.key_mode == "dense"
     if not args.no_e2e and (not sharded or combiner):
         e2e_steps = min(K, 8)
@@ -479,9 +492,10 @@ def main():
         # What a JVM shim would do per micro-batch: hand over three pinned host columns (direct
         # ByteBuffers), then drain every output column into pinned host buffers.  H2D and D2H copies are
         # inside the timed region; host wall clock with a full synchronise at both ends.  The host path
-        # is PCIe-bound, so the headline uses the 16 B/event wire format; the 24 B one is beside it.
-        e2e = run_e2e(True)
-        e2e_wide = run_e2e(False) if world == 1 else None
+        # headline = the 24 B/event columns of the boundary (int64 ts, uint64 key, 8-byte value);
+        # the 16 B/event packed wire format is reported beside it
+        e2e = run_e2e(False)
+        e2e_packed = run_e2e(True)
 
     if rank != 0:
         if dist:
@@ -495,7 +509,20 @@ def main():
         from oracle_lib import ParallelOracle
         threads = os.cpu_count() or 1
         v, dt, _ = cpu_reference_run(12, 1, 1 << args.cpu_sample_log2, threads, capi, ParallelOracle, StreamSpec, generate_numpy)
+        # the single-thread literal restatement (oracle/flink_literal.cpp: ordered map of (key, window), explicit
+        # timers) on a smaller sample: what one core does per-record, beside the key-partitioned port above
+        from oracle_lib import OracleEngine
+        lit_n = 1 << 21
+        lit = OracleEngine(**workload_kwargs(capi, lit_n))
+        lit_batches = [generate_numpy(stream_spec(StreamSpec), b * lit_n, lit_n) for b in range(3)]
+        lit.push_batch(*lit_batches[0])
+        t_l = time.perf_counter()
+        for b in (1, 2):
+            lit.push_batch(*lit_batches[b])
+        lit_v = 2 * lit_n / (time.perf_counter() - t_l)
+        lit.close()
         cpu_baseline = {"value": v, "unit": "events/s", "cores": threads, "kind": "port",
+                        "single_thread_literal_oracle": {"value": lit_v, "unit": "events/s", "cores": 1, "sample": "2 steps x 2^21 events after 1 warm-up step"},
                         "sample": f"12 steps x 2^{args.cpu_sample_log2} events of the same stream: {dt:.1f} s wall x {threads} threads = {dt * threads:.0f} core-seconds"}
 
     line = {"metric": "events/sec keyed window-agg+alert", "value": value, "unit": "events/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -508,7 +535,7 @@ def main():
                            if (args.multi == "combiner" and args.key_mode == "dense") else (
                                f"keyBy sharded over {world} GPUs, buckets pulled from peer memory over NVLink" if args.multi == "peerpull"
                                else f"keyBy hash-sharded over {world} GPUs, NCCL all-to-all"))},
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "e2e_wide_columns": e2e_wide, "gpu_launches": int(launches), "clocks": clocks, "variants": variants,
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "e2e_packed": e2e_packed, "gpu_launches": int(launches), "clocks": clocks, "variants": variants,
             "step_counts": {"event_alert_rows": int(n_ealert), "late_dropped": int(n_late), "fired_rows": int(n_fired)}}
     print(json.dumps(line))
     if dist:

@@ -400,6 +400,12 @@ static int stage_keyed(fmq_handle* h, const i64* ts, const u64* key, const V* va
     return FMQ_OK;
 }
 
+// A/B switch for measurements: FMQ_INGEST_LEGACY=1 runs round 1's block-staged ingest kernel instead of the warp-ring one
+static bool ingest_legacy() {
+    static const bool v = [] { const char* e = getenv("FMQ_INGEST_LEGACY"); return e && e[0] == '1'; }();
+    return v;
+}
+
 // stage 1 of a push: everything that touches only this handle's own events
 template <typename V>
 static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n) {
@@ -413,25 +419,39 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         a.ea_ts = h->ea_ts; a.ea_key = h->ea_key; a.ea_val = h->ea_val; a.ea_cap = h->ea_cap;
         a.lt_ts = h->lt_ts; a.lt_key = h->lt_key; a.lt_val = h->lt_val; a.lt_cap = h->lt_cap;
         a.mlog_enabled = h->ml_cap > 0; a.ml_pane = h->ml_pane[h->ml_cur]; a.ml_slot = h->ml_slot[h->ml_cur]; a.ml_val = h->ml_val[h->ml_cur]; a.ml_cap = h->ml_cap;
+        // The kernels pick themselves on the device-resident stream position (no host round trip):
+        // the fast kernel returns at once unless a watermark anchors the pane origin (filter-only jobs
+        // need none), the generic one unless it does not.  Launches known to be no-ops are skipped.
+        const bool fast_geom = !c.window_enabled || (h->g.slide32 != 0 && (u64)h->ring * h->g.slide32 < 0x100000000ull);
+        const bool dense = c.key_mode == FMQ_KEYS_DENSE;
+        const bool extras = h->ml_cap > 0 || h->lt_cap > 0;
+        if (fast_geom && !ingest_legacy()) {
+            // persistent grid: every warp streams its own ring of 128-event tiles
+            size_t blocks = (n + (size_t)IW_TILE * IW_WARPS - 1) / ((size_t)IW_TILE * IW_WARPS);
+            const size_t maxb = (size_t)h->num_sms * FMQ_IW_BLOCKS;
+            if (blocks > maxb) blocks = maxb;
+            auto kfn = dense ? (extras ? ingest_ring_kernel<V, true, true> : ingest_ring_kernel<V, true, false>)
+                             : (extras ? ingest_ring_kernel<V, false, true> : ingest_ring_kernel<V, false, false>);
+            const int smem = iw_smem_bytes(extras);
+            CU(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            kfn<<<(unsigned)blocks, IW_THREADS, smem, h->stream>>>(a);
+            LAUNCHED(h, "ingest_ring_kernel");
+        }
         const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
         size_t blocks = (n + tile - 1) / tile; const size_t maxb = (size_t)h->num_sms * FMQ_INGEST_MIN_BLOCKS;   // persistent: resident blocks only
         if (blocks > maxb) blocks = maxb;
-        // The kernels pick themselves on the device-resident stream position (no host round trip):
-        // the fast kernel returns at once unless a watermark anchors the pane origin, the generic
-        // one unless it does not.  Launches that are known to be no-ops are skipped.
-        const bool fast_geom = !c.window_enabled || (h->g.slide32 != 0 && (u64)h->ring * h->g.slide32 < 0x100000000ull);
-        const bool dense = c.key_mode == FMQ_KEYS_DENSE;
-        if (c.window_enabled && fast_geom) {
-            const bool extras = h->ml_cap > 0 || h->lt_cap > 0;
+        if (c.window_enabled && fast_geom && ingest_legacy()) {          // A/B: the block-staged kernel of round 1
             auto kfn = dense ? (extras ? ingest_fast_kernel<V, true, true> : ingest_fast_kernel<V, true, false>)
                              : (extras ? ingest_fast_kernel<V, false, true> : ingest_fast_kernel<V, false, false>);
             CU(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, INGEST_SMEM_BYTES));
             kfn<<<(unsigned)blocks, INGEST_THREADS, INGEST_SMEM_BYTES, h->stream>>>(a);
             LAUNCHED(h, "ingest_fast_kernel");
         }
-        if (!c.window_enabled || !fast_geom || !h->anchored_known) {
-            if (dense) ingest_generic_kernel<V, true><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a);
-            else       ingest_generic_kernel<V, false><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(a);
+        if ((c.window_enabled && (!fast_geom || !h->anchored_known)) || (!c.window_enabled && ingest_legacy())) {
+            IngestArgs g = a;
+            g.force_generic = c.window_enabled ? 0 : 1;          // (legacy A/B only: filter-only jobs went through this kernel)
+            if (dense) ingest_generic_kernel<V, true><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(g);
+            else       ingest_generic_kernel<V, false><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(g);
             LAUNCHED(h, "ingest_generic_kernel");
         }
     }
@@ -497,7 +517,9 @@ static int fire_medians(fmq_handle* h) {
 template <typename V>
 static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now) {
     const fmq_config& c = h->cfg;
-    PlanArgs p{h->d_st, h->g, c.max_out_of_orderness_ms, wm_after, (u64)n, c.window_enabled, wm_after == FMQ_WM_AUTO, wm_after == FMQ_WM_KEEP, h->overlap ? 1 : 0};
+    PlanArgs p{};
+    p.st = h->d_st; p.g = h->g; p.bound = c.max_out_of_orderness_ms; p.watermark_after = wm_after; p.n_events = (u64)n; p.window_enabled = c.window_enabled;
+    p.is_auto = wm_after == FMQ_WM_AUTO; p.is_keep = wm_after == FMQ_WM_KEEP; p.overlap = h->overlap ? 1 : 0;
     plan_kernel<<<1, 32, 0, h->stream>>>(p); LAUNCHED(h, "plan_kernel");
     cudaStream_t fs = h->stream;
     if (h->overlap) {                                          // everything from the fire kernel on runs beside the next ingest

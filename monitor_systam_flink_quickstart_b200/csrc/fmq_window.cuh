@@ -17,6 +17,11 @@ struct WindowGeom {
 
 struct IngestArgs {
     const i64* ts; const u64* key; const void* val; size_t n;
+    // Segmented input (keyBy exchange: one segment per source rank, filled by that rank's scatter kernel):
+    // segment s of every column starts seg_stride elements after segment s-1 and holds seg_n[s] events,
+    // a count that lives in device memory (n is then the capacity of a segment).  nseg <= 1: one plain batch of n.
+    u32 nseg; size_t seg_stride; const u64* seg_n;
+    int force_generic;          // the generic kernel runs whatever the stream position says
     DevState* st;
     u64* dkeys;
     Acc32* acc;
@@ -202,6 +207,30 @@ __device__ __forceinline__ void load_events(const IngestArgs& a, size_t i, i64 (
     }
 }
 
+// Same for the tile that starts `off` elements into the columns and holds `cnt` events; `i` = this thread's first event in it.
+template <typename V>
+__device__ __forceinline__ void load_events_at(const IngestArgs& a, size_t off, u32 cnt, u32 i, i64 (&ts_)[INGEST_EPT], u64 (&key_)[INGEST_EPT],
+                                               u64 (&vb_)[INGEST_EPT], u32& in_mask) {
+    const u64* ts = reinterpret_cast<const u64*>(a.ts) + off; const u64* key = a.key + off; const u64* val = static_cast<const u64*>(a.val) + off;
+    if (a.vec32 && i + INGEST_EPT <= cnt) {
+        const ulonglong4 x = ldg_stream_v4(ts + i), y = ldg_stream_v4(key + i), z = ldg_stream_v4(val + i);
+        ts_[0] = (i64)x.x; ts_[1] = (i64)x.y; ts_[2] = (i64)x.z; ts_[3] = (i64)x.w;
+        key_[0] = y.x; key_[1] = y.y; key_[2] = y.z; key_[3] = y.w;
+        vb_[0] = z.x; vb_[1] = z.y; vb_[2] = z.z; vb_[3] = z.w;
+        in_mask = 0xFu;
+    } else {
+        in_mask = 0;
+#pragma unroll
+        for (int e = 0; e < INGEST_EPT; ++e) {
+            const bool in = i + e < cnt;
+            in_mask |= in ? (1u << e) : 0u;
+            ts_[e] = in ? (i64)ldg_stream(ts + i + e) : 0;
+            key_[e] = in ? ldg_stream(key + i + e) : 0;
+            vb_[e] = in ? ldg_stream(val + i + e) : 0;
+        }
+    }
+}
+
 // A6-i: per-event threshold filter + compaction (Main.java:31); one reservation per block tile,
 // rows keep arrival order inside the tile.  Called by every thread of the block.
 template <typename V>
@@ -226,8 +255,36 @@ __device__ __forceinline__ u32 filter_events(const IngestArgs& a, DevState* st, 
 
 // Chooses the kernel on the device-resident stream position without a host round trip: the fast
 // kernel is launched first and returns immediately unless its preconditions hold, and vice versa.
-__device__ __forceinline__ bool ingest_fast_ok(const DevState* st, const WindowGeom& g) {
+__device__ __forceinline__ bool ingest_fast_ok(const DevState* st, const WindowGeom& g, int window_enabled = 1) {
+    if (!window_enabled) return true;                            // filter-only jobs (chapter1) need no pane origin
     return st->anchored && g.slide32 != 0 && (u64)(g.ring_mask + 1) * g.slide32 < 0x100000000ull;
+}
+
+// ---- segmented input ---------------------------------------------------------------------------------
+// Where a batch is and how large it is, as the kernels see it: up to FMQ_MAX_PEERS segments whose sizes may
+// live in device memory (so that a batch received from peers is consumed without a host round trip).
+struct SegTab { u64 n[FMQ_MAX_PEERS]; u64 tile_end[FMQ_MAX_PEERS]; };
+
+template <int TILE>
+__device__ __forceinline__ void seg_tab_fill(const IngestArgs& a, SegTab* t, DevState* st) {      // one thread
+    u64 acc = 0; const u32 ns = a.nseg ? a.nseg : 1;
+    for (u32 s = 0; s < FMQ_MAX_PEERS; ++s) {
+        u64 n = 0;
+        if (s < ns) {
+            n = a.seg_n ? a.seg_n[s] : a.n;
+            if (n > a.n) { n = a.n; atomicOr(&st->err_flags, ERRB_BAD_INPUT); }   // a count beyond the segment's capacity
+        }
+        t->n[s] = n; acc += (n + TILE - 1) / TILE; t->tile_end[s] = acc;
+    }
+}
+// tile index -> element offset of its first event (same for every column) and number of events in it
+template <int TILE>
+__device__ __forceinline__ size_t seg_locate(const IngestArgs& a, const SegTab& t, u64 tile, u32& cnt) {
+    u32 s = 0;
+    while (tile >= t.tile_end[s]) ++s;                           // <= 8 steps, uniform across the warp
+    const u64 first = (tile - (s ? t.tile_end[s - 1] : 0)) * TILE, rem = t.n[s] - first;
+    cnt = rem < (u64)TILE ? (u32)rem : (u32)TILE;
+    return (size_t)s * a.seg_stride + first;
 }
 
 // ---- ingest, fast kernel --------------------------------------------------------------------------
@@ -275,21 +332,16 @@ struct IngestConst {
     i64 origin_ts, origin_pane; u32 origin_ring, slide, recip; u64 span, nbuckets; bool combine;
 };
 
-// One tile of the fast path: the four events held by this thread.  Called by every thread of the block.
-template <typename V, bool DENSE, bool EXTRAS>      // EXTRAS: late side output and/or the median value log are enabled
-__device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
-                                            const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 in_mask,
-                                            HotTable* hot, bool do_filter = true) {
-    u32 ok_mask = 0;
-#pragma unroll
-    for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
-    if ((ok_mask & in_mask) != in_mask) r.err |= ERRB_BAD_INPUT;
-    ok_mask &= in_mask;
-    if (a.efilter_enabled && do_filter) r.nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
-    if (!a.window_enabled) return;
+// The window part of one tile (A1 max-ts, A3 late test, A2 pane, A5 accumulate) for the four events held by
+// this lane.  Must be reached by all 32 lanes of the warp.  Returns which of the four were late / accumulated,
+// their pane quotient and slot (for the side outputs the callers append in their own way).
+template <typename V, bool DENSE>
+__device__ __forceinline__ void ingest_core(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
+                                            const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 ok_mask,
+                                            HotTable* hot, bool sample, u32& late_mask, u32& vmask, u32 (&q_)[INGEST_EPT], u32 (&slot_)[INGEST_EPT]) {
     // ---- per event: A1 max-ts, A3 late test, A2 pane, and (hashed keys) the home-bucket load:
     //      all four directory loads are in flight before any of them is consumed ----
-    u32 ring_[INGEST_EPT]; u32 q_[INGEST_EPT]; u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0, late_mask = 0;
+    u32 ring_[INGEST_EPT]; u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0; late_mask = 0;
 #pragma unroll
     for (int e = 0; e < INGEST_EPT; ++e) {
         const bool ok = ok_mask & (1u << e);
@@ -318,7 +370,7 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
         act_mask |= act ? (1u << e) : 0u;
     }
     // ---- A5: slot -> pair-lane accumulate ----
-    u32 slot_[INGEST_EPT]; u32 vmask = 0;
+    vmask = 0;
 #pragma unroll
     for (int e = 0; e < INGEST_EPT; ++e) {
         bool valid = act_mask & (1u << e);
@@ -329,9 +381,25 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
         }
         const u64 idx = (u64)ring_[e] * a.g.capacity + slot;
         V v; memcpy(&v, &vb_[e], 8);
-        accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask, k.combine, e == 0 && threadIdx.x < 32, r.dup, hot);
+        accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask, k.combine, e == 0 && sample, r.dup, hot);
         slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
     }
+}
+
+// One tile of the block-staged fast path: the four events held by this thread.  Called by every thread of the block.
+template <typename V, bool DENSE, bool EXTRAS>      // EXTRAS: late side output and/or the median value log are enabled
+__device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
+                                            const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 in_mask,
+                                            HotTable* hot, bool do_filter = true) {
+    u32 ok_mask = 0;
+#pragma unroll
+    for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
+    if ((ok_mask & in_mask) != in_mask) r.err |= ERRB_BAD_INPUT;
+    ok_mask &= in_mask;
+    if (a.efilter_enabled && do_filter) r.nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
+    if (!a.window_enabled) return;
+    u32 late_mask, vmask, q_[INGEST_EPT], slot_[INGEST_EPT];
+    ingest_core<V, DENSE>(a, st, k, r, ts_, key_, vb_, ok_mask, hot, threadIdx.x < 32, late_mask, vmask, q_, slot_);
     // ---- late side output (chapter3/README.md:213-228, option 3: "a separate stream of the late data") ----
     if (EXTRAS && a.lt_cap) {
         u64 row = block_append<INGEST_THREADS>(__popc(late_mask), &st->n_late, a.lt_cap, st);
@@ -478,13 +546,203 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
     }
 }
 
+// ---- ingest, warp-ring kernel ------------------------------------------------------------------------
+// Same preconditions and per-event work as the block-staged kernel above, without a single block-wide
+// barrier in the streaming loop: every WARP owns a private ring of IW_STAGES tiles of 128 events (3 x 1 KB
+// bulk copies per tile, cp.async.bulk completing on the warp's own mbarrier, L2 evict-first), refilled by
+// its lane 0 as soon as the 32 lanes hold the tile in registers (__syncwarp + cross-proxy fence).  Rows of
+// the per-event filter (and of the late / median side outputs) are staged per warp in shared memory and
+// written out behind ONE reservation per ~100 rows, so warps never wait for each other: what is left to
+// stall a warp is the RED / store path itself.  (ncu of the block-staged kernel: `barrier` was the top
+// stall, 20 % of the samples sat in the mbarrier spin while the L2 ran at 66 %, profiles/r01_notes.md.)
+#ifndef FMQ_IW_WARPS
+#define FMQ_IW_WARPS 4
+#endif
+#ifndef FMQ_IW_STAGES
+#define FMQ_IW_STAGES 3
+#endif
+#ifndef FMQ_IW_BLOCKS
+#define FMQ_IW_BLOCKS 4
+#endif
+constexpr int IW_WARPS = FMQ_IW_WARPS, IW_STAGES = FMQ_IW_STAGES, IW_THREADS = IW_WARPS * 32;
+constexpr int IW_TILE = 32 * INGEST_EPT;                    // 128 events per warp tile
+constexpr int IW_STAGE_BYTES = 3 * IW_TILE * 8;             // 3 KB
+constexpr int IW_ROWS = 128;                                // rows a warp stages before it reserves output space
+constexpr int IW_ROWBUF_BYTES = 3 * IW_ROWS * 8;            // 3 KB
+__host__ __device__ constexpr int iw_warp_bytes(bool extras) { return IW_STAGES * IW_STAGE_BYTES + (extras ? 3 : 1) * IW_ROWBUF_BYTES; }
+__host__ __device__ constexpr int iw_smem_bytes(bool extras) { return IW_WARPS * iw_warp_bytes(extras); }
+
+__device__ __forceinline__ void mbar_arrive(u64* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// rows (3 x 8 B) staged by one warp; n is warp-uniform
+struct WarpRows { u64* buf; u32 n; };
+__device__ __forceinline__ void wr_push(WarpRows& w, bool pred, u64 c0, u64 c1, u64 c2) {      // all 32 lanes; needs room for 32 rows
+    const u32 lane = threadIdx.x & 31;
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (pred) { const u32 i = w.n + __popc(m & ((1u << lane) - 1)); w.buf[i] = c0; w.buf[IW_ROWS + i] = c1; w.buf[2 * IW_ROWS + i] = c2; }
+    w.n += __popc(m);
+}
+template <typename T0, typename T1>
+__device__ __forceinline__ void wr_flush(WarpRows& w, u64* counter, u64 cap, T0* d0, T1* d1, u64* d2, u32& err) {   // all 32 lanes
+    if (w.n == 0) return;
+    const u32 lane = threadIdx.x & 31;
+    __syncwarp();
+    u64 base = 0;
+    if (lane == 0) base = atomicAdd(counter, (u64)w.n);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base + w.n > cap) err |= ERRB_OUTPUT;
+    else for (u32 i = lane; i < w.n; i += 32) { d0[base + i] = (T0)w.buf[i]; d1[base + i] = (T1)w.buf[IW_ROWS + i]; d2[base + i] = w.buf[2 * IW_ROWS + i]; }
+    __syncwarp();
+    w.n = 0;
+}
+
+template <typename V, bool DENSE, bool EXTRAS>
+__global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(const __grid_constant__ IngestArgs a) {
+    extern __shared__ __align__(128) unsigned char iw_smem[];
+    __shared__ __align__(8) u64 bars[IW_WARPS][IW_STAGES];
+    __shared__ SegTab seg;
+    __shared__ HotTable hot_tab;
+    DevState* st = a.st;
+    if (!ingest_fast_ok(st, a.g, a.window_enabled)) return;      // the generic kernel handles this batch
+    const u32 lane = threadIdx.x & 31, wl = threadIdx.x >> 5;
+    IngestConst k{};
+    if (a.window_enabled) {
+        k.origin_ts = st->origin_ts;
+        k.origin_pane = st->origin_pane;
+        k.combine = st->combine_dups != 0;
+        k.origin_ring = (u32)st->origin_pane & a.g.ring_mask;
+        k.slide = a.g.slide32;
+        k.recip = 0xFFFFFFFFu / k.slide;
+        k.span = (u64)(a.g.ring_mask + 1 - st->pending_clear) * k.slide;
+        k.nbuckets = a.g.capacity >> 2;
+    }
+    IngestRun r;
+    if (threadIdx.x == 0) seg_tab_fill<IW_TILE>(a, &seg, st);
+    if (k.combine) hot_init(&hot_tab);
+    if (lane == 0) {
+        for (int s = 0; s < IW_STAGES; ++s) mbar_init(&bars[wl][s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();                                             // the only block barrier before the epilogue
+    const u64 ntiles = seg.tile_end[FMQ_MAX_PEERS - 1];
+    const u64 gw = (u64)blockIdx.x * IW_WARPS + wl, nw = (u64)gridDim.x * IW_WARPS;
+    unsigned char* wbase = iw_smem + (size_t)wl * iw_warp_bytes(EXTRAS);
+    WarpRows ea{reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES), 0};
+    WarpRows lt{reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES + IW_ROWBUF_BYTES), 0};
+    WarpRows ml{reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES + 2 * IW_ROWBUF_BYTES), 0};
+    const u64* cts = reinterpret_cast<const u64*>(a.ts); const u64* cval = static_cast<const u64*>(a.val);
+    u64 policy;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+    auto stage_col = [&](int s, int c) { return reinterpret_cast<u64*>(wbase + s * IW_STAGE_BYTES + c * IW_TILE * 8); };
+    auto issue = [&](u64 t, int s) {                             // lane 0: start the three copies of tile t, or just arrive
+        u32 cnt; const size_t off = seg_locate<IW_TILE>(a, seg, t, cnt);
+        if (a.vec32 && cnt == IW_TILE) {
+            mbar_expect_tx(&bars[wl][s], 3u * IW_TILE * 8u);
+            tma_load_1d(stage_col(s, 0), cts + off, IW_TILE * 8u, &bars[wl][s], policy);
+            tma_load_1d(stage_col(s, 1), a.key + off, IW_TILE * 8u, &bars[wl][s], policy);
+            tma_load_1d(stage_col(s, 2), cval + off, IW_TILE * 8u, &bars[wl][s], policy);
+        } else {
+            mbar_arrive(&bars[wl][s]);                            // ragged or unaligned tile: the lanes load it themselves
+        }
+    };
+    if (lane == 0)
+        for (int s = 0; s < IW_STAGES; ++s) { const u64 t = gw + (u64)s * nw; if (t < ntiles) issue(t, s); }
+    u64 it = 0;
+    for (u64 t = gw; t < ntiles; t += nw, ++it) {
+        const int s = (int)(it % IW_STAGES);
+        mbar_wait(&bars[wl][s], (u32)((it / IW_STAGES) & 1));
+        u32 cnt; const size_t off = seg_locate<IW_TILE>(a, seg, t, cnt);
+        // lane x takes events x, x+32, x+64, x+96 of the tile: conflict-free 8-byte shared loads
+        i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; u32 in_mask = 0xFu;
+        if (a.vec32 && cnt == IW_TILE) {
+            const u64 *sts = stage_col(s, 0), *skey = stage_col(s, 1), *sval = stage_col(s, 2);
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e) { ts_[e] = (i64)sts[lane + 32 * e]; key_[e] = skey[lane + 32 * e]; vb_[e] = sval[lane + 32 * e]; }
+        } else {
+            in_mask = 0;
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e) {
+                const u32 i = lane + 32 * e; const bool in = i < cnt;
+                in_mask |= in ? (1u << e) : 0u;
+                ts_[e] = in ? (i64)ldg_stream(cts + off + i) : 0; key_[e] = in ? ldg_stream(a.key + off + i) : 0; vb_[e] = in ? ldg_stream(cval + off + i) : 0;
+            }
+        }
+        __syncwarp();                                            // every lane holds its events: the stage is free
+        if (lane == 0) {
+            // generic-proxy reads of the stage (all lanes, ordered by the warp barrier) before the async-proxy refill
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            const u64 tn = t + (u64)IW_STAGES * nw;
+            if (tn < ntiles) issue(tn, s);
+        }
+        u32 ok_mask = 0;
+#pragma unroll
+        for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
+        if ((ok_mask & in_mask) != in_mask) r.err |= ERRB_BAD_INPUT;
+        ok_mask &= in_mask;
+        if (a.efilter_enabled) {                                 // A6-i (Main.java:31)
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e) {
+                V v; memcpy(&v, &vb_[e], 8);
+                const bool hit = (ok_mask & (1u << e)) && cmp_op((double)v, a.efilter_op, a.efilter_thr);
+                if (ea.n + 32 > IW_ROWS) wr_flush(ea, &st->n_ealert, a.ea_cap, a.ea_ts, a.ea_key, a.ea_val, r.err);
+                const u32 before = ea.n;
+                wr_push(ea, hit, (u64)ts_[e], key_[e], vb_[e]);
+                if (lane == 0) r.nea += ea.n - before;
+            }
+        }
+        if (!a.window_enabled) continue;
+        u32 late_mask, vmask, q_[INGEST_EPT], slot_[INGEST_EPT];
+        ingest_core<V, DENSE>(a, st, k, r, ts_, key_, vb_, ok_mask, &hot_tab, wl == 0, late_mask, vmask, q_, slot_);
+        if (EXTRAS && a.lt_cap) {                                // late side output (chapter3/README.md:213-228, option 3)
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e) {
+                if (lt.n + 32 > IW_ROWS) wr_flush(lt, &st->n_late, a.lt_cap, a.lt_ts, a.lt_key, a.lt_val, r.err);
+                wr_push(lt, (late_mask >> e) & 1u, (u64)ts_[e], key_[e], vb_[e]);
+            }
+        }
+        if (EXTRAS && a.mlog_enabled) {                          // N3: every accepted value is logged (ComputeCpuMiddle.java:36-38)
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e) {
+                if (ml.n + 32 > IW_ROWS) wr_flush(ml, &st->n_mlog, a.ml_cap, a.ml_pane, a.ml_slot, a.ml_val, r.err);
+                wr_push(ml, (vmask >> e) & 1u, (u64)(k.origin_pane + (i64)q_[e]), (u64)slot_[e], vb_[e]);
+            }
+        }
+    }
+    if (a.efilter_enabled) wr_flush(ea, &st->n_ealert, a.ea_cap, a.ea_ts, a.ea_key, a.ea_val, r.err);
+    if (EXTRAS && a.lt_cap) wr_flush(lt, &st->n_late, a.lt_cap, a.lt_ts, a.lt_key, a.lt_val, r.err);
+    if (EXTRAS && a.mlog_enabled) wr_flush(ml, &st->n_mlog, a.ml_cap, a.ml_pane, a.ml_slot, a.ml_val, r.err);
+    if (k.combine && a.window_enabled) { __syncthreads(); hot_flush<V>(&hot_tab, a.acc, a.g.agg_mask); }
+    // ---- per-warp reduction of the batch scalars, one atomic each per warp ----
+    r.nea = warp_sum_u64(r.nea);
+    for (int o = 16; o > 0; o >>= 1) r.err |= __shfl_xor_sync(0xffffffffu, r.err, o);
+    if (a.window_enabled) {
+        r.late = warp_sum_u64(r.late); r.dmax = warp_max_i64(r.dmax);
+        r.pmin = __reduce_min_sync(0xffffffffu, r.pmin); r.pmax = __reduce_max_sync(0xffffffffu, r.pmax);
+    }
+    if (threadIdx.x == 0 && r.dup[0]) { atomicAdd(&st->dup_sampled, (u64)r.dup[0]); atomicAdd(&st->dup_found, (u64)r.dup[1]); }
+    if (lane == 0) {
+        if (r.nea) atomicAdd(&st->event_alerts, r.nea);
+        if (r.err) atomicOr(&st->err_flags, r.err);
+        if (a.window_enabled) {
+            if (r.late) atomicAdd(&st->late_dropped, r.late);
+            if (r.dmax != I64_MIN_) atomicMax(&st->batch_max_ts, k.origin_ts + r.dmax);
+            if (r.pmin <= r.pmax) { atomicMin(&st->min_pane, st->origin_pane + (i64)r.pmin); atomicMax(&st->max_pane, st->origin_pane + (i64)r.pmax); }
+        }
+    }
+}
+
 // ---- ingest, generic kernel -------------------------------------------------------------------------
 // Used while the stream is not anchored yet (no watermark: nothing can be late and the pane origin
 // is unknown, so pane indices need a 64-bit division) or when the geometry does not fit 32 bits.
 template <typename V, bool DENSE>
 __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __grid_constant__ IngestArgs a) {
     DevState* st = a.st;
-    if (ingest_fast_ok(st, a.g)) return;                         // the fast kernel handles this batch
+    __shared__ SegTab seg;
+    if (!a.force_generic && ingest_fast_ok(st, a.g, a.window_enabled)) return;       // the fast kernel handles this batch
+    if (threadIdx.x == 0) seg_tab_fill<INGEST_THREADS * INGEST_EPT>(a, &seg, st);
+    __syncthreads();
     const int anchored = st->anchored;
     const i64 origin_ts = anchored ? st->origin_ts : (a.g.off - a.g.slide);
     const i64 origin_pane = anchored ? st->origin_pane : -1;
@@ -492,12 +750,12 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
 
     u64 late = 0, nea = 0; i64 max_ts = I64_MIN_; i64 pmin = I64_MAX_, pmax = I64_MIN_; u32 err = 0;
 
-    const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
-    const size_t ntiles = (a.n + tile - 1) / tile;
-    for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const size_t i = t * tile + (size_t)threadIdx.x * INGEST_EPT;
+    constexpr int tile = INGEST_THREADS * INGEST_EPT;
+    const u64 ntiles = seg.tile_end[FMQ_MAX_PEERS - 1];
+    for (u64 t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        u32 cnt; const size_t off = seg_locate<tile>(a, seg, t, cnt);
         i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; u32 in_mask;
-        load_events<V>(a, i, ts_, key_, vb_, in_mask);
+        load_events_at<V>(a, off, cnt, threadIdx.x * INGEST_EPT, ts_, key_, vb_, in_mask);
         u32 ok_mask = 0;
 #pragma unroll
         for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
@@ -570,13 +828,16 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
 struct PlanArgs {
     DevState* st; WindowGeom g; i64 bound; i64 watermark_after; u64 n_events; int window_enabled; int is_auto;
     int is_keep;      // FMQ_WM_KEEP: bookkeeping only, the watermark stays where it is
+    const u64* seg_n; u32 nseg; u64 seg_cap;   // segmented input: the event count lives in device memory (n_events is then ignored)
     int overlap;      // combiner mode with fire / retire on a second stream: the next ingest starts before the expired panes are cleared
 };
 
 __global__ void plan_kernel(const PlanArgs a) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     DevState* st = a.st;
-    st->events_in += a.n_events;
+    u64 n_events = a.n_events;
+    if (a.seg_n) { n_events = 0; for (u32 s = 0; s < a.nseg; ++s) n_events += a.seg_n[s] < a.seg_cap ? a.seg_n[s] : a.seg_cap; }
+    st->events_in += n_events;
     st->fire_count = 0; st->expire_lo = 1; st->expire_hi = 0; st->pending_clear = 0;
     if (!a.window_enabled) return;
     // skew adaptation for the next batch: pre-aggregate inside warps when > 3 % of the sampled lanes
