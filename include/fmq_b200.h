@@ -44,7 +44,8 @@ typedef enum fmq_status {
     FMQ_ERR_CUDA = 5,           /* a CUDA call failed; see fmq_last_error                     */
     FMQ_ERR_BAD_TS = 6,         /* negative timestamp or reserved key seen                    */
     FMQ_ERR_NO_DEVICE = 7,      /* no usable CUDA device: there is NO CPU fallback            */
-    FMQ_ERR_POISONED = 8        /* a previous sticky error invalidated this handle's state    */
+    FMQ_ERR_POISONED = 8,       /* a previous sticky error invalidated this handle's state    */
+    FMQ_ERR_PEER_TIMEOUT = 9    /* a peer rank did not publish / acknowledge a batch in time  */
 } fmq_status;
 
 typedef enum fmq_value_type { FMQ_VAL_F64 = 0, FMQ_VAL_I64 = 1 } fmq_value_type;

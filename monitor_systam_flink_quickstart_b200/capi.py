@@ -28,7 +28,7 @@ FMQ_WM_KEEP = -(2 ** 63) + 1
 FMQ_WM_FINAL = 2 ** 63 - 1
 
 STATUS_NAMES = {0: "OK", 1: "BAD_ARG", 2: "TABLE_FULL", 3: "RING_OVERFLOW", 4: "OUTPUT_OVERFLOW",
-                5: "CUDA", 6: "BAD_TS", 7: "NO_DEVICE", 8: "POISONED"}
+                5: "CUDA", 6: "BAD_TS", 7: "NO_DEVICE", 8: "POISONED", 9: "PEER_TIMEOUT"}
 
 
 class FmqConfig(C.Structure):
@@ -188,6 +188,12 @@ def _declare(lib, p: str, has_mem: bool = True, side_outputs: Optional[bool] = N
         sig("stage_host", [vp, C.POINTER(FmqPackedColumns), sz])
         sig("push_local_packed", [vp, C.POINTER(FmqPackedColumns), sz, i32])
         sig("partition_by_owner_noalloc", [i32, vp, vp, vp, vp, sz, C.c_uint32, vp, vp, vp, vp])
+        sig("shard_alloc", [vp, i32, sz, vp])
+        sig("shard_base", [vp], vp)
+        sig("shard_attach", [vp, i32, i32, C.POINTER(vp)])
+        sig("shard_attach_ipc", [vp, i32, i32, vp])
+        sig("shard_send", [vp, vp, vp, vp, sz, i32])
+        sig("shard_recv", [vp, i64, psz])
 
 
 def _ptr(a) -> int:
@@ -562,6 +568,41 @@ class Engine(EngineBase):
         n = C.c_size_t(0)
         self._check(self._lib.fmq_exchange_pull_push(self._h, parity, m.ctypes.data, watermark_after, C.byref(n)))
         return n.value
+
+    # ---- keyBy exchange on the device (fmq_shard_*) ------------------------------------------------
+    def shard_alloc(self, world: int, max_send: int) -> bytes:
+        """Allocates this rank's receive buffer; returns the 64-byte CUDA IPC blob the peers attach."""
+        buf = C.create_string_buffer(64)
+        self._check(self._lib.fmq_shard_alloc(self._h, world, max_send, buf))
+        return buf.raw
+
+    @property
+    def shard_base(self) -> int:
+        return self._lib.fmq_shard_base(self._h) or 0
+
+    def shard_attach(self, rank: int, world: int, bases):
+        """Peers in this process: their fmq_shard_base pointers."""
+        arr = (C.c_void_p * world)(*[C.c_void_p(b) for b in bases])
+        self._check(self._lib.fmq_shard_attach(self._h, rank, world, arr))
+
+    def shard_attach_ipc(self, rank: int, world: int, blobs):
+        """Peers in other processes: the blobs of every rank's shard_alloc, in rank order."""
+        raw = b"".join(blobs)
+        assert len(raw) == 64 * world
+        self._check(self._lib.fmq_shard_attach_ipc(self._h, rank, world, raw))
+
+    def shard_send(self, ts, key, val):
+        n = len(ts)
+        dev = _is_device(ts)
+        if not dev:
+            ts = np.ascontiguousarray(ts, dtype=np.int64); key = np.ascontiguousarray(key, dtype=np.uint64)
+            val = np.ascontiguousarray(val, dtype=self._vdtype)
+        self._check(self._lib.fmq_shard_send(self._h, _ptr(ts), _ptr(key), _ptr(val), n, FMQ_MEM_DEVICE if dev else FMQ_MEM_HOST))
+
+    def shard_recv(self, watermark_after: int = FMQ_WM_AUTO, want_count: bool = False):
+        n = C.c_size_t(0)
+        self._check(self._lib.fmq_shard_recv(self._h, watermark_after, C.byref(n) if want_count else None))
+        return n.value if want_count else None
 
     def partition_by_owner(self, ts, key, val, world: int, ts_out, key_out, val_out) -> np.ndarray:
         counts = np.zeros(world, np.uint64)

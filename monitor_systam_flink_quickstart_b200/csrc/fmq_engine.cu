@@ -14,6 +14,7 @@
 #include "fmq_keyed.cuh"
 #include "fmq_text.cuh"
 #include "fmq_median.cuh"
+#include "fmq_shard.cuh"
 
 using namespace fmq;
 
@@ -42,6 +43,7 @@ struct fmq_handle {
     size_t max_batch = 0;
     // device state
     DevState* d_st = nullptr; DevState* h_st = nullptr;   // h_st: pinned mirror
+    u32* h_hint = nullptr;                                // pinned word the plan kernel writes: skewed keys seen (picks the ingest variant)
     u64* d_keys = nullptr; Acc32* d_acc = nullptr; u32* d_kflags = nullptr; u64* d_kmax = nullptr;
     // staging for host-resident inputs
     i64* d_in_ts = nullptr; u64* d_in_key = nullptr; u64* d_in_val = nullptr;
@@ -74,6 +76,15 @@ struct fmq_handle {
     size_t pending_n = 0;                // events ingested by fmq_push_local and not yet accounted by fmq_fire_global
     // peer-pull keyBy exchange: two parities x three columns of owner-bucketed events, mapped by every peer
     char* d_xsend = nullptr; const char* peer_xsend[FMQ_MAX_PEERS] = {}; int x_world = 0, x_rank = 0;
+    // keyBy exchange on the device (fmq_shard_*): receive buffer all peers map, control block at its start
+    char* d_xbuf = nullptr; size_t xs_seg_cap = 0; int xs_world = 0, xs_rank = -1; bool xs_attached = false;
+    XCtl* xs_ctl[FMQ_MAX_PEERS] = {}; char* xs_base[FMQ_MAX_PEERS] = {}; void* xs_opened[FMQ_MAX_PEERS] = {};
+    cudaStream_t send_stream = nullptr; u32* d_xcounts = nullptr; u32* d_xtiles = nullptr; i64* d_send_max = nullptr;
+    u64* d_seg_n = nullptr;              // [FMQ_MAX_PEERS] counts of the batch being received + [1] their sum
+    u64* h_ntotal = nullptr;             // pinned: the sum read back for the keyed chain (which sizes its launches on the host)
+    u64* xs_stage = nullptr;             // 3 x seg_cap: host columns of a send are copied here first
+    uint64_t xs_send_seq = 0, xs_recv_seq = 0;
+    uint64_t cmb_seq = 0; bool cmb_flags = false;   // combiner mode over the same control block instead of a collective library
     // second set of fired / window-alert / event-alert columns + a copy-out stream, for overlapped polls
     void* alt_out[12] = {}; cudaStream_t out_stream = nullptr; cudaEvent_t ev_out = nullptr; bool out_pending = false;
     i64* lt_ts = nullptr; u64 *lt_key = nullptr, *lt_val = nullptr; u64 lt_cap = 0; size_t cur_late = 0;
@@ -118,6 +129,10 @@ static void free_all(fmq_handle* h) {
                     h->md_key, h->md_wend, h->md_val, h->lt_ts, h->lt_key, h->lt_val};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : h->alt_out) if (p) cudaFree(p);
+    for (void* p : h->xs_opened) if (p) cudaIpcCloseMemHandle(p);
+    { void* xs[] = {h->d_xbuf, h->d_xcounts, h->d_xtiles, h->d_send_max, h->d_seg_n, h->xs_stage}; for (void* p : xs) if (p) cudaFree(p); }
+    if (h->h_ntotal) cudaFreeHost(h->h_ntotal);
+    if (h->send_stream) { cudaStreamSynchronize(h->send_stream); cudaStreamDestroy(h->send_stream); }
     for (int i = 0; i < fmq_handle::HOST_SETS; ++i) {
         void* q[] = {h->hs_ts[i], h->hs_key[i], h->hs_val[i], h->hs_narrow[i]};
         for (void* p : q) if (p) cudaFree(p);
@@ -132,6 +147,7 @@ static void free_all(fmq_handle* h) {
     if (h->ev_bdone) cudaEventDestroy(h->ev_bdone);
     if (h->ev_out) cudaEventDestroy(h->ev_out);
     if (h->h_st) cudaFreeHost(h->h_st);
+    if (h->h_hint) cudaFreeHost(h->h_hint);
     for (auto& q : h->tev) for (cudaEvent_t e : q) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -183,6 +199,7 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     if (cfg->window_enabled && h->g.panes_per_window >= h->ring) return fail(FMQ_ERR_BAD_ARG, "pane_ring must exceed window_size_ms / window_slide_ms");
 
     CUC(dalloc(&h->d_st, 1)); CUC(cudaMallocHost((void**)&h->h_st, sizeof(DevState)));
+    CUC(cudaMallocHost((void**)&h->h_hint, 64)); memset(h->h_hint, 0, 64);
     DevState init; memset(&init, 0, sizeof(init));
     init.wm = I64_MIN_; init.cur_max_ts = I64_MIN_ + cfg->max_out_of_orderness_ms; init.last_emitted_wm = I64_MIN_; init.batch_max_ts = I64_MIN_;
     init.min_pane = I64_MAX_; init.max_pane = I64_MIN_; init.expire_lo = 1; init.expire_hi = 0;
@@ -217,7 +234,7 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
         }
     }
     // radix counter matrix (keyed path and owner partition)
-    h->counts_len = (size_t)RS_DIGITS * rs_num_chunks(h->max_batch);
+    h->counts_len = (size_t)RS_DIGITS * xs_num_chunks(h->max_batch);
     if (keyed_enabled(*cfg)) { const size_t k = (size_t)2048 * ps_num_chunks(h->max_batch); if (k > h->counts_len) h->counts_len = k; }
     if (cfg->median_log_capacity > 0) { const size_t k = (size_t)2048 * ps_num_chunks(cfg->median_log_capacity); if (k > h->counts_len) h->counts_len = k; }
     h->tiles_len = (h->counts_len + SCAN_TILE - 1) / SCAN_TILE;
@@ -273,29 +290,48 @@ static int launch_check(fmq_handle* h, const char* what) {
 }
 #define LAUNCHED(h, what) do { int s_ = launch_check(h, what); if (s_) return s_; } while (0)
 
-static int exclusive_scan_counts(fmq_handle* h, size_t len) {
+// exclusive scan of `len` u32 counters in place (three small kernels); `tiles` holds one partial sum per 4096 counters
+static cudaError_t scan_counts_on(cudaStream_t stream, u32* counts, u32* tiles, size_t len) {
     const u32 ntiles = (u32)((len + SCAN_TILE - 1) / SCAN_TILE);
-    scan_tile_sums<<<ntiles, SCAN_THREADS, 0, h->stream>>>(h->d_counts, len, h->d_tiles); LAUNCHED(h, "scan_tile_sums");
-    scan_tile_offsets<<<1, SCAN_THREADS, 0, h->stream>>>(h->d_tiles, ntiles); LAUNCHED(h, "scan_tile_offsets");
-    scan_apply<<<ntiles, SCAN_THREADS, 0, h->stream>>>(h->d_counts, len, h->d_tiles); LAUNCHED(h, "scan_apply");
+    scan_tile_sums<<<ntiles, SCAN_THREADS, 0, stream>>>(counts, len, tiles);
+    scan_tile_offsets<<<1, SCAN_THREADS, 0, stream>>>(tiles, ntiles);
+    scan_apply<<<ntiles, SCAN_THREADS, 0, stream>>>(counts, len, tiles);
+    return cudaGetLastError();
+}
+static int exclusive_scan_counts(fmq_handle* h, size_t len) {
+    cudaError_t e = scan_counts_on(h->stream, h->d_counts, h->d_tiles, len);
+    if (e != cudaSuccess) { h->err = std::string("scan kernels: ") + cudaGetErrorString(e); return FMQ_ERR_CUDA; }
+    h->launches += 3;
     return FMQ_OK;
 }
 
-template <typename DigitFn, typename Emit>
-static int multisplit(fmq_handle* h, size_t n, DigitFn digit, Emit emit) {
-    const u32 nchunks = rs_num_chunks(n);
-    const u32 nblocks = (nchunks + RS_WARPS - 1) / RS_WARPS;
-    rs_hist_kernel<<<nblocks, RS_THREADS, 0, h->stream>>>(n, nchunks, digit, h->d_counts); LAUNCHED(h, "rs_hist_kernel");
-    int s = exclusive_scan_counts(h, (size_t)RS_DIGITS * nchunks); if (s) return s;
-    rs_scatter_kernel<<<nblocks, RS_THREADS, 0, h->stream>>>(n, nchunks, digit, emit, h->d_counts); LAUNCHED(h, "rs_scatter_kernel");
-    return FMQ_OK;
+// Stable owner split of a device-resident batch (A4): count -> scan -> block-staged scatter, 5 launches on `stream`.
+// 3-bit digits while world <= 8 (one NVSwitch node), 8-bit digits up to 256.  After it, counts[d * nchunks] is the
+// start of owner d's bucket (single-output mode) or what precedes owner d's events in digit-major order.
+struct SplitScratch { u32* counts; u32* tiles; };
+static cudaError_t owner_split(cudaStream_t stream, const SplitScratch& sc, const u64* ts, const u64* key, const u64* val, size_t n, u32 world, u32 dense,
+                               const SplitDst& dst, bool per_owner, i64* max_ts) {
+    const u32 nchunks = xs_num_chunks(n);
+    SplitArgs a{ts, key, val, n, nchunks, world, dense, sc.counts, dst, max_ts};
+    auto run = [&](auto hist, auto scat_single, auto scat_owner, u32 nb) -> cudaError_t {
+        hist<<<nchunks, XS_THREADS, 0, stream>>>(key, n, nchunks, world, dense, sc.counts);
+        cudaError_t e = scan_counts_on(stream, sc.counts, sc.tiles, (size_t)nb * nchunks); if (e != cudaSuccess) return e;
+        const size_t smem = xs_scatter_smem(nb);
+        if (per_owner) { e = cudaFuncSetAttribute(scat_owner, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_owner<<<nchunks, XS_THREADS, smem, stream>>>(a); }
+        else           { e = cudaFuncSetAttribute(scat_single, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_single<<<nchunks, XS_THREADS, smem, stream>>>(a); }
+        return cudaGetLastError();
+    };
+    if (world <= 8) return run(xs_hist_kernel<3>, xs_scatter_kernel<3, false>, xs_scatter_kernel<3, true>, 8u);
+    return run(xs_hist_kernel<8>, xs_scatter_kernel<8, false>, xs_scatter_kernel<8, false>, 256u);
 }
+static u32 split_digits(u32 world) { return world <= 8 ? 8u : 256u; }
 
 static int status_from_flags(fmq_handle* h, u32 flags) {
     if (!flags) return FMQ_OK;
     int st; const char* m;
     if (flags & ERRB_TABLE_FULL) { st = FMQ_ERR_TABLE_FULL; m = "key directory full: raise fmq_config.table_capacity"; }
     else if (flags & ERRB_RING) { st = FMQ_ERR_RING_OVERFLOW; m = "open event-time span exceeds pane_ring panes: raise fmq_config.pane_ring or push smaller batches"; }
+    else if (flags & ERRB_PEER) { st = FMQ_ERR_PEER_TIMEOUT; m = "a peer rank did not publish or acknowledge a batch in time (keyBy exchange / combiner flags)"; }
     else if (flags & ERRB_OUTPUT) { st = FMQ_ERR_OUTPUT_OVERFLOW; m = "an output buffer overflowed before it was polled: poll more often or raise its capacity"; }
     else { st = FMQ_ERR_BAD_TS; m = "negative timestamp or reserved key (0xFFFFFFFFFFFFFFFF) in input"; }
     h->err = m; h->sticky = st;
@@ -407,12 +443,14 @@ static bool ingest_legacy() {
 }
 
 // stage 1 of a push: everything that touches only this handle's own events
+struct SegIn { u32 nseg = 0; size_t stride = 0; const u64* seg_n = nullptr; };   // segmented input with device-side counts (keyBy exchange)
 template <typename V>
-static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n) {
+static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n, const SegIn& seg = SegIn()) {
     const fmq_config& c = h->cfg;
     cudaEvent_t* tev = h->tev[h->pushes % fmq_handle::TIMING_RING];
     if (n > 0 && (c.window_enabled || c.efilter_enabled)) {
         IngestArgs a{};
+        a.nseg = seg.nseg; a.seg_stride = seg.stride; a.seg_n = seg.seg_n;
         a.ts = ts; a.key = key; a.val = val; a.n = n; a.st = h->d_st; a.dkeys = h->d_keys; a.acc = h->d_acc; a.g = h->g;
         a.window_enabled = c.window_enabled; a.vec32 = ((((uintptr_t)ts | (uintptr_t)key | (uintptr_t)val) & 31) == 0);
         a.efilter_enabled = c.efilter_enabled; a.efilter_op = c.efilter_op; a.efilter_thr = c.efilter_threshold;
@@ -422,25 +460,30 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         // The kernels pick themselves on the device-resident stream position (no host round trip):
         // the fast kernel returns at once unless a watermark anchors the pane origin (filter-only jobs
         // need none), the generic one unless it does not.  Launches known to be no-ops are skipped.
-        const bool fast_geom = !c.window_enabled || (h->g.slide32 != 0 && (u64)h->ring * h->g.slide32 < 0x100000000ull);
+        const bool fast_geom = !c.window_enabled || (h->g.slide32 != 0 && (u64)h->ring * h->g.slide32 < 0x100000000ull &&
+                                                     (u64)h->ring * h->capacity < 0x80000000ull);
         const bool dense = c.key_mode == FMQ_KEYS_DENSE;
         const bool extras = h->ml_cap > 0 || h->lt_cap > 0;
         if (fast_geom && !ingest_legacy()) {
             // persistent grid: every warp streams its own ring of 128-event tiles
-            size_t blocks = (n + (size_t)IW_TILE * IW_WARPS - 1) / ((size_t)IW_TILE * IW_WARPS);
+            size_t blocks = (n * (seg.nseg ? seg.nseg : 1) + (size_t)IW_TILE * IW_WARPS - 1) / ((size_t)IW_TILE * IW_WARPS);
             const size_t maxb = (size_t)h->num_sms * FMQ_IW_BLOCKS;
             if (blocks > maxb) blocks = maxb;
-            auto kfn = dense ? (extras ? ingest_ring_kernel<V, true, true> : ingest_ring_kernel<V, true, false>)
-                             : (extras ? ingest_ring_kernel<V, false, true> : ingest_ring_kernel<V, false, false>);
+            const bool comb = c.window_enabled && h->h_hint && *(volatile u32*)h->h_hint != 0;     // skew seen by an earlier batch's sample
+            auto pick = [&](auto lean, auto combining) { return comb ? combining : lean; };
+            auto kfn = dense ? (extras ? pick(ingest_ring_kernel<V, true, true, false>, ingest_ring_kernel<V, true, true, true>)
+                                       : pick(ingest_ring_kernel<V, true, false, false>, ingest_ring_kernel<V, true, false, true>))
+                             : (extras ? pick(ingest_ring_kernel<V, false, true, false>, ingest_ring_kernel<V, false, true, true>)
+                                       : pick(ingest_ring_kernel<V, false, false, false>, ingest_ring_kernel<V, false, false, true>));
             const int smem = iw_smem_bytes(extras);
             CU(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
             kfn<<<(unsigned)blocks, IW_THREADS, smem, h->stream>>>(a);
             LAUNCHED(h, "ingest_ring_kernel");
         }
         const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
-        size_t blocks = (n + tile - 1) / tile; const size_t maxb = (size_t)h->num_sms * FMQ_INGEST_MIN_BLOCKS;   // persistent: resident blocks only
+        size_t blocks = (n * (seg.nseg ? seg.nseg : 1) + tile - 1) / tile; const size_t maxb = (size_t)h->num_sms * FMQ_INGEST_MIN_BLOCKS;   // persistent: resident blocks only
         if (blocks > maxb) blocks = maxb;
-        if (c.window_enabled && fast_geom && ingest_legacy()) {          // A/B: the block-staged kernel of round 1
+        if (c.window_enabled && fast_geom && ingest_legacy() && seg.nseg <= 1) {          // A/B: the block-staged kernel of round 1
             auto kfn = dense ? (extras ? ingest_fast_kernel<V, true, true> : ingest_fast_kernel<V, true, false>)
                              : (extras ? ingest_fast_kernel<V, false, true> : ingest_fast_kernel<V, false, false>);
             CU(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, INGEST_SMEM_BYTES));
@@ -456,6 +499,7 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         }
     }
     CU(h, cudaEventRecord(tev[1], h->stream));
+    if (n > 0 && keyed_enabled(c) && seg.nseg > 1) return set_err(h, FMQ_ERR_BAD_ARG, "internal: the keyed chain needs one contiguous batch");
     if (n > 0 && keyed_enabled(c)) {
         // Rolling max gathers every value by arrival index and scatters every output back to it: random
         // 8-byte accesses.  Sub-batches whose value / output columns are L2-sized (2^23 records = 64 MB each)
@@ -515,11 +559,13 @@ static int fire_medians(fmq_handle* h) {
 // stage 2 of a push: watermark, fire, cleanup.  In combiner mode (`retire_now` false) the cleanup is
 // a separate step (fmq_retire) because peers may still be reading this rank's table.
 template <typename V>
-static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now) {
+static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now, const SegIn& seg = SegIn(), size_t seg_cap = 0) {
     const fmq_config& c = h->cfg;
     PlanArgs p{};
+    p.seg_n = seg.seg_n; p.nseg = seg.nseg; p.seg_cap = seg_cap;
     p.st = h->d_st; p.g = h->g; p.bound = c.max_out_of_orderness_ms; p.watermark_after = wm_after; p.n_events = (u64)n; p.window_enabled = c.window_enabled;
     p.is_auto = wm_after == FMQ_WM_AUTO; p.is_keep = wm_after == FMQ_WM_KEEP; p.overlap = h->overlap ? 1 : 0;
+    p.combine_hint = h->h_hint;
     plan_kernel<<<1, 32, 0, h->stream>>>(p); LAUNCHED(h, "plan_kernel");
     cudaStream_t fs = h->stream;
     if (h->overlap) {                                          // everything from the fire kernel on runs beside the next ingest
@@ -1213,11 +1259,12 @@ int32_t fmq_partition_by_owner(fmq_handle* h, const int64_t* ts, const uint64_t*
     if (!ts || !key || !val || !ts_out || !key_out || !val_out) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
     CU(h, cudaSetDevice(h->device));
     const u32 dense = h->cfg.key_mode == FMQ_KEYS_DENSE;
-    OwnerDigit dg{(const u64*)key, world, dense};
-    MoveEvent3 mv{(const u64*)ts, (const u64*)key, (const u64*)val, (u64*)ts_out, (u64*)key_out, (u64*)val_out, world, dense};
-    int s = multisplit(h, n, dg, mv); if (s) return s;
+    SplitDst dst{}; dst.out_ts = (u64*)ts_out; dst.out_key = (u64*)key_out; dst.out_val = (u64*)val_out;
+    cudaError_t e = owner_split(h->stream, SplitScratch{h->d_counts, h->d_tiles}, (const u64*)ts, (const u64*)key, (const u64*)val, n, world, dense, dst, false, nullptr);
+    if (e != cudaSuccess) { h->err = std::string("owner split: ") + cudaGetErrorString(e); return FMQ_ERR_CUDA; }
+    h->launches += 5;
     // bucket starts = scanned offsets of chunk 0 for each digit
-    const u32 nchunks = rs_num_chunks(n);
+    const u32 nchunks = xs_num_chunks(n);
     u32 starts[RS_DIGITS];
     CU(h, cudaMemcpy2DAsync(starts, 4, h->d_counts, (size_t)nchunks * 4, 4, world, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
@@ -1291,12 +1338,173 @@ int32_t fmq_exchange_pull_push(fmq_handle* h, int32_t parity, const uint64_t* ma
 }
 }  // extern "C"
 
+// ---- keyBy exchange on the device (fmq_shard_*; protocol in fmq_shard.cuh) ---------------------------------------
+static u64 peer_timeout_ns() {
+    static const u64 v = [] { const char* e = getenv("FMQ_PEER_TIMEOUT_MS"); const long ms = e ? atol(e) : 20000; return (u64)(ms < 1 ? 1 : ms) * 1000000ull; }();
+    return v;
+}
+static u64* xs_segment(char* base, int world, size_t seg_cap, u32 parity, int src) {
+    return reinterpret_cast<u64*>(base + XCTL_BYTES) + ((size_t)parity * world + src) * 3 * seg_cap;
+}
+static XPeers xs_peers(const fmq_handle* h) { XPeers p{}; for (int r = 0; r < h->xs_world; ++r) p.ctl[r] = h->xs_ctl[r]; return p; }
+
+extern "C" {
+int32_t fmq_shard_alloc(fmq_handle* h, int32_t world, size_t max_send, void* handle64) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (world < 1 || world > FMQ_MAX_PEERS) return set_err(h, FMQ_ERR_BAD_ARG, "need 1 <= world <= 8");
+    if (max_send == 0 || max_send >= 0xFFFFFFF0ull) return set_err(h, FMQ_ERR_BAD_ARG, "max_send must be in [1, 2^32)");
+    if (h->d_xbuf) return set_err(h, FMQ_ERR_BAD_ARG, "the exchange buffer of this handle exists already");
+    CU(h, cudaSetDevice(h->device));
+    h->xs_seg_cap = (max_send + 3) & ~(size_t)3;                              // whole 32-byte groups: segments stay aligned for the bulk copies
+    h->xs_world = world;
+    const size_t bytes = XCTL_BYTES + (size_t)2 * world * 3 * h->xs_seg_cap * 8;
+    CU(h, cudaMalloc((void**)&h->d_xbuf, bytes));
+    CU(h, cudaMemset(h->d_xbuf, 0, XCTL_BYTES));
+    const size_t nc = (size_t)8 * xs_num_chunks(h->xs_seg_cap);
+    CU(h, dalloc(&h->d_xcounts, nc)); CU(h, dalloc(&h->d_xtiles, (nc + SCAN_TILE - 1) / SCAN_TILE + 1));
+    CU(h, dalloc(&h->d_send_max, 1)); CU(h, dalloc(&h->d_seg_n, FMQ_MAX_PEERS + 1));
+    const i64 imin = I64_MIN_;
+    CU(h, cudaMemcpy(h->d_send_max, &imin, 8, cudaMemcpyHostToDevice));
+    CU(h, cudaMemset(h->d_seg_n, 0, (FMQ_MAX_PEERS + 1) * 8));
+    CU(h, cudaMallocHost((void**)&h->h_ntotal, 8));
+    CU(h, cudaStreamCreateWithFlags(&h->send_stream, cudaStreamNonBlocking));
+    if (handle64) { cudaIpcMemHandle_t ih; CU(h, cudaIpcGetMemHandle(&ih, h->d_xbuf)); memcpy(handle64, &ih, 64); }
+    CU(h, cudaDeviceSynchronize());
+    return FMQ_OK;
+}
+void* fmq_shard_base(fmq_handle* h) { return h ? (void*)h->d_xbuf : nullptr; }
+
+static int shard_attach_common(fmq_handle* h, int32_t rank, int32_t world) {
+    if (!h->d_xbuf) return set_err(h, FMQ_ERR_BAD_ARG, "call fmq_shard_alloc first");
+    if (world != h->xs_world || rank < 0 || rank >= world) return set_err(h, FMQ_ERR_BAD_ARG, "world must equal fmq_shard_alloc's and 0 <= rank < world");
+    if (h->xs_attached) return set_err(h, FMQ_ERR_BAD_ARG, "peers are attached already");
+    return FMQ_OK;
+}
+int32_t fmq_shard_attach(fmq_handle* h, int32_t rank, int32_t world, const void* const* peer_bases) {
+    if (!h || !peer_bases) return FMQ_ERR_BAD_ARG;
+    int s = shard_attach_common(h, rank, world); if (s) return s;
+    CU(h, cudaSetDevice(h->device));
+    for (int r = 0; r < world; ++r) {
+        char* b = (r == rank) ? h->d_xbuf : (char*)peer_bases[r];
+        if (!b) return set_err(h, FMQ_ERR_BAD_ARG, "null peer buffer");
+        if (r != rank) {                                                      // a buffer on another GPU of this process: make it reachable
+            cudaPointerAttributes at{};
+            if (cudaPointerGetAttributes(&at, b) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device != h->device) {
+                cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { h->err = std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e); return FMQ_ERR_CUDA; }
+            }
+            cudaGetLastError();
+        }
+        h->xs_base[r] = b; h->xs_ctl[r] = reinterpret_cast<XCtl*>(b);
+    }
+    h->xs_rank = rank; h->xs_attached = true;
+    return FMQ_OK;
+}
+int32_t fmq_shard_attach_ipc(fmq_handle* h, int32_t rank, int32_t world, const void* blobs) {
+    if (!h || !blobs) return FMQ_ERR_BAD_ARG;
+    int s = shard_attach_common(h, rank, world); if (s) return s;
+    CU(h, cudaSetDevice(h->device));
+    const void* bases[FMQ_MAX_PEERS] = {};
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) { bases[r] = h->d_xbuf; continue; }
+        cudaIpcMemHandle_t ih; memcpy(&ih, (const char*)blobs + (size_t)r * 64, 64);
+        void* p = nullptr;
+        CU(h, cudaIpcOpenMemHandle(&p, ih, cudaIpcMemLazyEnablePeerAccess));
+        h->xs_opened[r] = p; bases[r] = p;
+    }
+    return fmq_shard_attach(h, rank, world, bases);
+}
+
+int32_t fmq_shard_send(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val, size_t n, int32_t mem) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (!h->xs_attached) return set_err(h, FMQ_ERR_BAD_ARG, "call fmq_shard_attach first");
+    if (n > h->xs_seg_cap) return set_err(h, FMQ_ERR_BAD_ARG, "batch larger than fmq_shard_alloc's max_send");
+    if (n > 0 && (!ts || !key || !val)) return set_err(h, FMQ_ERR_BAD_ARG, "null column pointer");
+    if (mem != FMQ_MEM_HOST && mem != FMQ_MEM_DEVICE) return set_err(h, FMQ_ERR_BAD_ARG, "bad mem");
+    CU(h, cudaSetDevice(h->device));
+    cudaStream_t ss = h->send_stream;
+    const u64 seq = ++h->xs_send_seq; const u32 parity = (u32)(seq & 1);
+    const int W = h->xs_world, me = h->xs_rank;
+    const u64 *dts = (const u64*)ts, *dkey = (const u64*)key, *dval = (const u64*)val;
+    if (mem == FMQ_MEM_HOST && n > 0) {
+        if (!h->xs_stage) CU(h, dalloc(&h->xs_stage, 3 * h->xs_seg_cap));
+        // the previous send's kernels have read the staging columns before these copies overwrite them (same stream)
+        CU(h, cudaMemcpyAsync(h->xs_stage, ts, n * 8, cudaMemcpyHostToDevice, ss));
+        CU(h, cudaMemcpyAsync(h->xs_stage + h->xs_seg_cap, key, n * 8, cudaMemcpyHostToDevice, ss));
+        CU(h, cudaMemcpyAsync(h->xs_stage + 2 * h->xs_seg_cap, val, n * 8, cudaMemcpyHostToDevice, ss));
+        dts = h->xs_stage; dkey = h->xs_stage + h->xs_seg_cap; dval = h->xs_stage + 2 * h->xs_seg_cap;
+    }
+    // the peers must have consumed batch seq-2, the last one scattered into the segments of this parity
+    xs_wait_acks_kernel<<<1, 32, 0, ss>>>(h->xs_ctl[me], (u32)W, parity, seq >= 3 ? seq - 2 : 0, h->d_st, peer_timeout_ns()); LAUNCHED(h, "xs_wait_acks_kernel");
+    const u32 nchunks = xs_num_chunks(n);
+    if (n > 0) {
+        SplitDst dst{}; dst.col_stride = h->xs_seg_cap;
+        for (int d = 0; d < W; ++d) dst.ts[d] = xs_segment(h->xs_base[d], W, h->xs_seg_cap, parity, me);
+        cudaError_t e = owner_split(ss, SplitScratch{h->d_xcounts, h->d_xtiles}, dts, dkey, dval, n, (u32)W, h->cfg.key_mode == FMQ_KEYS_DENSE ? 1u : 0u, dst, true, h->d_send_max);
+        if (e != cudaSuccess) { h->err = std::string("owner split: ") + cudaGetErrorString(e); return FMQ_ERR_CUDA; }
+        h->launches += 5;
+    }
+    xs_publish_kernel<<<1, 32, 0, ss>>>(h->d_xcounts, nchunks, (u64)n, (u32)W, (u32)me, parity, seq, h->d_send_max, xs_peers(h)); LAUNCHED(h, "xs_publish_kernel");
+    if (mem == FMQ_MEM_HOST && n > 0) CU(h, cudaStreamSynchronize(ss));       // the caller owns host columns only until this call returns
+    return FMQ_OK;
+}
+
+}  // extern "C"
+
+template <typename V>
+static int shard_recv_t(fmq_handle* h, int64_t wm_after, size_t* n_received) {
+    const fmq_config& c = h->cfg;
+    const u64 seq = ++h->xs_recv_seq; const u32 parity = (u32)(seq & 1);
+    const int W = h->xs_world, me = h->xs_rank;
+    cudaEvent_t* tev = h->tev[h->pushes % fmq_handle::TIMING_RING];
+    CU(h, cudaEventRecord(tev[0], h->stream));
+    xs_gather_kernel<<<1, 32, 0, h->stream>>>(h->xs_ctl[me], (u32)W, parity, seq, h->d_seg_n, h->d_seg_n + FMQ_MAX_PEERS, h->d_st, peer_timeout_ns()); LAUNCHED(h, "xs_gather_kernel");
+    u64* seg0 = xs_segment(h->d_xbuf, W, h->xs_seg_cap, parity, 0);
+    SegIn seg; seg.nseg = (u32)W; seg.stride = 3 * h->xs_seg_cap; seg.seg_n = h->d_seg_n;
+    int s;
+    if (keyed_enabled(c) || n_received) {
+        // The keyed chain sizes its launches on the host: the one number it needs, the batch's event count, is read back.
+        CU(h, cudaMemcpyAsync(h->h_ntotal, h->d_seg_n + FMQ_MAX_PEERS, 8, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+        if (n_received) *n_received = (size_t)*h->h_ntotal;
+    }
+    if (keyed_enabled(c)) {
+        const size_t n = (size_t)*h->h_ntotal;
+        if (n > h->max_batch) return set_err(h, FMQ_ERR_BAD_ARG, "received more events than fmq_config.max_batch");
+        if (n > 0) {
+            xs_compact_kernel<<<(unsigned)h->num_sms * 4, 256, 0, h->stream>>>(seg0, seg.stride, h->xs_seg_cap, h->d_seg_n, (u32)W, (u64*)h->d_in_ts, h->d_in_key, h->d_in_val, h->max_batch);
+            LAUNCHED(h, "xs_compact_kernel");
+        }
+        s = stage_ingest<V>(h, h->d_in_ts, h->d_in_key, h->d_in_val, n); if (s) return s;
+        s = stage_fire<V>(h, n, wm_after, true); if (s) return s;
+    } else {
+        s = stage_ingest<V>(h, (const i64*)seg0, seg0 + h->xs_seg_cap, seg0 + 2 * h->xs_seg_cap, h->xs_seg_cap, seg); if (s) return s;
+        s = stage_fire<V>(h, 0, wm_after, true, seg, h->xs_seg_cap); if (s) return s;
+    }
+    xs_ack_kernel<<<1, 32, 0, h->stream>>>(xs_peers(h), (u32)W, (u32)me, parity, seq); LAUNCHED(h, "xs_ack_kernel");
+    CU(h, cudaEventRecord(tev[3], h->stream));
+    h->pushes++;
+    return FMQ_OK;
+}
+extern "C" {
+int32_t fmq_shard_recv(fmq_handle* h, int64_t watermark_after, size_t* n_received) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (!h->xs_attached) return set_err(h, FMQ_ERR_BAD_ARG, "call fmq_shard_attach first");
+    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "combiner peers attached: this handle does not take the exchange route");
+    if (h->xs_recv_seq >= h->xs_send_seq) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_shard_recv without a matching fmq_shard_send on this rank");
+    CU(h, cudaSetDevice(h->device));
+    return h->cfg.value_type == FMQ_VAL_F64 ? shard_recv_t<double>(h, watermark_after, n_received) : shard_recv_t<i64>(h, watermark_after, n_received);
+}
+}  // extern "C"
+
 // ---- owner split for callers that must not allocate ------------------------------------------------
 // Same stable multi-split as fmq_partition_by_owner, but its scratch (the per-chunk digit counters
 // and the scan's tile sums) lives in a fixed file-scope device array instead of a handle's
 // cudaMalloc'ed buffers, so the call performs no allocation of any kind.  See include/fmq_b200.h.
 namespace {
-constexpr size_t NOALLOC_MAX_CHUNKS = FMQ_NOALLOC_MAX_EVENTS / RS_CHUNK;                 // 2048
+constexpr size_t NOALLOC_MAX_CHUNKS = FMQ_NOALLOC_MAX_EVENTS / XS_CHUNK;                 // 2048
 constexpr size_t NOALLOC_COUNTS = (size_t)RS_DIGITS * NOALLOC_MAX_CHUNKS;                 // 524288 counters
 constexpr size_t NOALLOC_TILES = (NOALLOC_COUNTS + SCAN_TILE - 1) / SCAN_TILE;            // 128 tile sums
 // ~2 MB per GPU that loads this library, held until the process exits.
@@ -1350,18 +1558,9 @@ extern "C" int32_t fmq_partition_by_owner_noalloc(int32_t device, void* stream_,
     // Nothing in the scratch has to start at zero: the histogram kernel stores (not adds) every one
     // of the 256 x nchunks counters it owns and the scan stores every tile sum before reading it, so
     // whatever the previous call left behind is overwritten before it can be read.
-    const u32 nchunks = rs_num_chunks(n);
-    const u32 nblocks = (nchunks + RS_WARPS - 1) / RS_WARPS;
-    const size_t len = (size_t)RS_DIGITS * nchunks;
-    const u32 ntiles = (u32)((len + SCAN_TILE - 1) / SCAN_TILE);
-    OwnerDigit dg{(const u64*)key, world, 0u};
-    MoveEvent3 mv{(const u64*)ts, (const u64*)key, (const u64*)val, (u64*)ts_out, (u64*)key_out, (u64*)val_out, world, 0u};
-    rs_hist_kernel<<<nblocks, RS_THREADS, 0, stream>>>(n, nchunks, dg, d_counts);
-    scan_tile_sums<<<ntiles, SCAN_THREADS, 0, stream>>>(d_counts, len, d_tiles);
-    scan_tile_offsets<<<1, SCAN_THREADS, 0, stream>>>(d_tiles, ntiles);
-    scan_apply<<<ntiles, SCAN_THREADS, 0, stream>>>(d_counts, len, d_tiles);
-    rs_scatter_kernel<<<nblocks, RS_THREADS, 0, stream>>>(n, nchunks, dg, mv, d_counts);
-    NA_CU(cudaGetLastError());
+    const u32 nchunks = xs_num_chunks(n);
+    SplitDst dst{}; dst.out_ts = (u64*)ts_out; dst.out_key = (u64*)key_out; dst.out_val = (u64*)val_out;
+    NA_CU(owner_split(stream, SplitScratch{d_counts, d_tiles}, (const u64*)ts, (const u64*)key, (const u64*)val, n, world, 0u, dst, false, nullptr));
     u32 starts[RS_DIGITS];
     NA_CU(cudaMemcpy2DAsync(starts, 4, d_counts, (size_t)nchunks * 4, 4, world, cudaMemcpyDeviceToHost, stream));
     NA_CU(cudaStreamSynchronize(stream));

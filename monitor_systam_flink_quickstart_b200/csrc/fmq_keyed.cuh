@@ -6,6 +6,7 @@
 // then every run of equal slots is walked in order, seeded from / written back to the per-key state.
 #pragma once
 #include "fmq_device.cuh"
+#include "fmq_sort.cuh"
 
 namespace fmq {
 
@@ -139,19 +140,6 @@ constexpr int PS_IPT = PS_CHUNK / 256;          // items per thread
 #define FMQ_PS_MINB 3
 #endif
 
-// Lanes of `am` holding the same BITS-bit digit, from BITS ballots.  MATCH.ANY does this in one
-// instruction but was measured at ~150 cycles per warp instruction per SM on B200 (it bounded both
-// scatter kernels at ~0.3 ms per pass of 2^24 items); votes are cheap.
-template <int BITS>
-__device__ __forceinline__ unsigned match_digit(unsigned am, u32 d) {
-    unsigned m = am;
-#pragma unroll
-    for (int b = 0; b < BITS; ++b) {
-        const unsigned v = __ballot_sync(am, (d >> b) & 1u);
-        m &= ((d >> b) & 1u) ? v : ~v;
-    }
-    return m;
-}
 template <int BITS, typename KeyFn>
 __global__ void __launch_bounds__(256, FMQ_PS_MINB) ps_scatter_tile_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t n, u32 nchunks, u32 shift,
                                                               const u32* __restrict__ offsets, KeyFn keyfn) {

@@ -2,72 +2,184 @@
 //   * keyBy exchange (A4): split a batch into `world` owner buckets before the all-to-all;
 //   * keyed ValueState path (A7): LSD radix sort of (key slot -> arrival index) so that every
 //     key's records are contiguous AND in arrival order;
-// A warp owns a contiguous chunk of the input, so stability needs no cross-warp coordination:
-// counts[digit][chunk] is scanned digit-major and each warp then walks its chunk in order.
+// A block owns a contiguous chunk of the input: counts[digit][chunk] is scanned digit-major, and the block
+// then sorts its chunk in shared memory and copies every digit's run out in one piece.
 #pragma once
 #include "fmq_device.cuh"
 
 namespace fmq {
 
-constexpr int RS_THREADS = 256;                 // 8 warps per block
-constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_DIGITS = 256;
-constexpr u32 RS_CHUNK = 2048;                  // items per warp chunk
+constexpr int RS_DIGITS = 256;                  // largest world an owner split supports
+constexpr u32 XS_CHUNK = 2048;                  // events per block
+constexpr int XS_THREADS = 256;
+constexpr int XS_WARPS = XS_THREADS / 32;
+constexpr int XS_IPT = XS_CHUNK / XS_THREADS;   // 8 events per thread: a warp ranks 256 consecutive events, 32 per round
 
-__host__ __device__ inline u32 rs_num_chunks(size_t n) { return (u32)((n + RS_CHUNK - 1) / RS_CHUNK); }
+__host__ __device__ inline u32 xs_num_chunks(size_t n) { return (u32)((n + XS_CHUNK - 1) / XS_CHUNK); }
 
-// DigitFn: u32 operator()(size_t i) -> [0, 256)
-template <typename DigitFn>
-__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(size_t n, u32 nchunks, DigitFn digit, u32* __restrict__ counts) {
-    __shared__ u32 cnt[RS_WARPS][RS_DIGITS];
-    const u32 wl = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const u32 chunk = blockIdx.x * RS_WARPS + wl;
-    for (int d = lane; d < RS_DIGITS; d += 32) cnt[wl][d] = 0;
-    __syncwarp();
-    if (chunk < nchunks) {
-        const size_t lo = (size_t)chunk * RS_CHUNK;
-        const size_t hi = (lo + RS_CHUNK < n) ? lo + RS_CHUNK : n;
-        for (size_t i0 = lo; i0 < hi; i0 += 32) {
-            const size_t i = i0 + lane;
-            const bool act = i < hi;
-            const unsigned am = __ballot_sync(0xffffffffu, act);
-            if (act) {
-                const u32 d = digit(i);
-                const unsigned m = __match_any_sync(am, d);
-                if ((int)lane == __ffs(m) - 1) cnt[wl][d] += __popc(m);
-            }
-            __syncwarp();
-        }
-        for (int d = lane; d < RS_DIGITS; d += 32) counts[(size_t)d * nchunks + chunk] = cnt[wl][d];
+// keyBy routing on the GPU (A4): hashed keys -> mix64(key) % world; dense ids -> id % world
+__device__ __forceinline__ u32 owner_digit(u64 key, u32 world, u32 dense) { return (u32)((dense ? key : mix64(key)) % world); }
+
+// Lanes of `am` holding the same BITS-bit digit, from BITS ballots.  MATCH.ANY does this in one
+// instruction but was measured at ~150 cycles per warp instruction per SM on B200; votes are cheap.
+template <int BITS>
+__device__ __forceinline__ unsigned match_digit(unsigned am, u32 d) {
+    unsigned m = am;
+#pragma unroll
+    for (int b = 0; b < BITS; ++b) {
+        const unsigned v = __ballot_sync(am, (d >> b) & 1u);
+        m &= ((d >> b) & 1u) ? v : ~v;
     }
+    return m;
 }
 
-// Emit: void operator()(size_t src, size_t dst) — moves item src to position dst.
-template <typename DigitFn, typename Emit>
-__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(size_t n, u32 nchunks, DigitFn digit, Emit emit, const u32* __restrict__ offsets) {
-    __shared__ u32 off[RS_WARPS][RS_DIGITS];
-    const u32 wl = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const u32 chunk = blockIdx.x * RS_WARPS + wl;
-    if (chunk >= nchunks) return;
-    for (int d = lane; d < RS_DIGITS; d += 32) off[wl][d] = offsets[(size_t)d * nchunks + chunk];
-    __syncwarp();
-    const size_t lo = (size_t)chunk * RS_CHUNK;
-    const size_t hi = (lo + RS_CHUNK < n) ? lo + RS_CHUNK : n;
-    for (size_t i0 = lo; i0 < hi; i0 += 32) {
-        const size_t i = i0 + lane;
-        const bool act = i < hi;
+// Counting half of the owner split: one block per chunk of XS_CHUNK events, counts[digit][chunk].
+// Every one of the 2^BITS x nchunks counters is STORED (nothing has to start at zero).
+template <int BITS>
+__global__ void __launch_bounds__(XS_THREADS) xs_hist_kernel(const u64* __restrict__ key, size_t n, u32 nchunks, u32 world, u32 dense, u32* __restrict__ counts) {
+    constexpr u32 NB = 1u << BITS;
+    __shared__ u32 cnt[NB];
+    const u32 tid = threadIdx.x;
+    const u32 chunk = blockIdx.x;
+    for (u32 d = tid; d < NB; d += XS_THREADS) cnt[d] = 0;
+    __syncthreads();
+    const size_t lo = (size_t)chunk * XS_CHUNK;
+    const size_t hi = (lo + XS_CHUNK < n) ? lo + XS_CHUNK : n;
+    u64 kk[XS_IPT];
+#pragma unroll
+    for (int r = 0; r < XS_IPT; ++r) { const size_t i = lo + (size_t)r * XS_THREADS + tid; kk[r] = i < hi ? ldg_stream(key + i) : 0; }
+#pragma unroll
+    for (int r = 0; r < XS_IPT; ++r) {
+        const bool act = lo + (size_t)r * XS_THREADS + tid < hi;
         const unsigned am = __ballot_sync(0xffffffffu, act);
         if (act) {
-            const u32 d = digit(i);
-            const unsigned m = __match_any_sync(am, d);
+            const u32 d = owner_digit(kk[r], world, dense);
+            const unsigned m = match_digit<BITS>(am, d);
+            if ((int)(tid & 31) == __ffs(m) - 1) atomicAdd(&cnt[d], (u32)__popc(m));      // one shared atomic per distinct digit of the warp round
+        }
+    }
+    __syncthreads();
+    for (u32 d = tid; d < NB; d += XS_THREADS) counts[(size_t)d * nchunks + chunk] = cnt[d];
+}
+
+// Scatter half: the block sorts its chunk by owner in shared memory (stable: warp w ranks its 256 consecutive
+// events round by round, a cross-warp prefix per owner orders the warps) and copies every owner's run out with
+// consecutive threads writing consecutive addresses — 2 KB runs per column at world = 8 instead of lone 8-byte
+// stores.  The destination of owner d is either one shared set of output columns (plain partition: the buckets lie
+// one after the other) or that owner's OWN columns (keyBy exchange: dst[d] is a segment of rank d's receive
+// buffer, local or mapped over NVLink — the scatter IS the transfer).  Dense ids become the owner's local id
+// (id / world).  The largest timestamp of the batch is reduced on the way (one atomic per block).
+struct SplitDst {
+    u64* ts[FMQ_MAX_PEERS]; size_t col_stride;     // per-owner mode: key column = ts + col_stride, value column = ts + 2 * col_stride
+    u64* out_ts; u64* out_key; u64* out_val;       // single-output mode
+};
+struct SplitArgs {
+    const u64* ts; const u64* key; const u64* val; size_t n; u32 nchunks; u32 world; u32 dense;
+    const u32* offsets;                            // counts[digit][chunk] after the exclusive scan (digit-major)
+    SplitDst dst; i64* max_ts;                     // max_ts may be null
+};
+constexpr size_t xs_scatter_smem(u32 nb) { return (size_t)3 * XS_CHUNK * 8 + XS_CHUNK * 2 + (size_t)XS_WARPS * nb * 2 + nb * 4 * 2; }
+
+template <int BITS, bool PER_OWNER>
+__global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_constant__ SplitArgs a) {
+    constexpr u32 NB = 1u << BITS;
+    extern __shared__ __align__(16) unsigned char xs_smem[];
+    u64* ev_s = reinterpret_cast<u64*>(xs_smem);                                  // [3][XS_CHUNK]
+    unsigned short* dig_s = reinterpret_cast<unsigned short*>(ev_s + 3 * XS_CHUNK);   // [XS_CHUNK] owner of every sorted position
+    unsigned short* wcnt = dig_s + XS_CHUNK;                                      // [XS_WARPS][NB] per-warp counts, then exclusive prefixes
+    u32* dbase = reinterpret_cast<u32*>(wcnt + XS_WARPS * NB);                    // [NB] start of the owner's run inside the sorted chunk
+    u32* goff = dbase + NB;                                                       // [NB] where that run goes in the owner's destination
+    __shared__ u32 scan_ws[XS_WARPS];
+    __shared__ i64 max_ws[XS_WARPS];
+    const u32 tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+    const u32 chunk = blockIdx.x;
+    const size_t lo = (size_t)chunk * XS_CHUNK;
+    const size_t hi = (lo + XS_CHUNK < a.n) ? lo + XS_CHUNK : a.n;
+    for (u32 i = tid; i < XS_WARPS * NB; i += XS_THREADS) wcnt[i] = 0;
+    for (u32 d = tid; d < NB; d += XS_THREADS) {
+        const u32 o = a.offsets[(size_t)d * a.nchunks + chunk];
+        goff[d] = PER_OWNER ? o - a.offsets[(size_t)d * a.nchunks] : o;           // per-owner destinations start at 0
+    }
+    __syncthreads();
+    // phase 1: rank inside the warp's 256 consecutive events, in arrival order
+    u64 kk[XS_IPT]; unsigned short dg[XS_IPT], rk[XS_IPT];
+    const size_t wlo = lo + (size_t)w * (XS_CHUNK / XS_WARPS);
+#pragma unroll
+    for (int r = 0; r < XS_IPT; ++r) { const size_t i = wlo + r * 32 + lane; kk[r] = i < hi ? ldg_stream(a.key + i) : 0; }
+#pragma unroll
+    for (int r = 0; r < XS_IPT; ++r) {
+        const bool act = wlo + r * 32 + lane < hi;
+        const unsigned am = __ballot_sync(0xffffffffu, act);
+        dg[r] = 0; rk[r] = 0;
+        if (act) {
+            const u32 d = owner_digit(kk[r], a.world, a.dense);
+            const unsigned m = match_digit<BITS>(am, d);
             const int leader = __ffs(m) - 1;
             u32 base = 0;
-            if ((int)lane == leader) { base = off[wl][d]; off[wl][d] = base + __popc(m); }
+            if ((int)lane == leader) { base = wcnt[w * NB + d]; wcnt[w * NB + d] = (unsigned short)(base + __popc(m)); }
             base = __shfl_sync(m, base, leader);
-            emit(i, (size_t)base + __popc(m & ((1u << lane) - 1)));
+            dg[r] = (unsigned short)d; rk[r] = (unsigned short)(base + __popc(m & ((1u << lane) - 1)));
         }
         __syncwarp();
     }
+    __syncthreads();
+    // phase 2: per owner, exclusive prefix over the warps; then exclusive prefix over the owners
+    constexpr u32 DPT = NB / XS_THREADS ? NB / XS_THREADS : 1;
+    u32 tot_local = 0, dtot[DPT];
+#pragma unroll
+    for (u32 q = 0; q < DPT; ++q) {
+        const u32 d = tid * DPT + q;
+        u32 run = 0;
+        if (d < NB) for (int ww = 0; ww < XS_WARPS; ++ww) { const u32 c = wcnt[ww * NB + d]; wcnt[ww * NB + d] = (unsigned short)run; run += c; }
+        dtot[q] = run; tot_local += run;
+    }
+    u32 inc = tot_local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, inc, o); if ((int)lane >= o) inc += x; }
+    if (lane == 31) scan_ws[w] = inc;
+    __syncthreads();
+    u32 wb = 0;
+    for (u32 i = 0; i < w; ++i) wb += scan_ws[i];
+    u32 run = wb + inc - tot_local;
+#pragma unroll
+    for (u32 q = 0; q < DPT; ++q) { const u32 d = tid * DPT + q; if (d < NB) dbase[d] = run; run += dtot[q]; }
+    __syncthreads();
+    // phase 3: the three columns of every event go to its sorted position (timestamps and values are read here,
+    // coalesced like the keys were, so that they do not sit in registers through the ranking)
+    i64 tmax = I64_MIN_;
+#pragma unroll
+    for (int r = 0; r < XS_IPT; ++r) {
+        const size_t i = wlo + r * 32 + lane;
+        if (i < hi) {
+            const u32 pos = dbase[dg[r]] + wcnt[w * NB + dg[r]] + rk[r];
+            const u64 t = ldg_stream(a.ts + i), k = kk[r];
+            tmax = (i64)t > tmax ? (i64)t : tmax;
+            ev_s[pos] = t;
+            ev_s[XS_CHUNK + pos] = (a.dense && k != KEY_EMPTY) ? k / a.world : k;
+            ev_s[2 * XS_CHUNK + pos] = ldg_stream(a.val + i);
+            dig_s[pos] = dg[r];
+        }
+    }
+    if (a.max_ts) { tmax = warp_max_i64(tmax); if (lane == 0) max_ws[w] = tmax; }
+    __syncthreads();
+    if (a.max_ts && tid == 0) {
+        i64 m = max_ws[0];
+        for (int i = 1; i < XS_WARPS; ++i) m = max_ws[i] > m ? max_ws[i] : m;
+        if (m != I64_MIN_) atomicMax(reinterpret_cast<long long*>(a.max_ts), (long long)m);
+    }
+    // phase 4: copy out; consecutive threads -> consecutive positions -> consecutive addresses inside a run
+    const u32 cnt = (u32)(hi - lo);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        for (u32 pos = tid; pos < cnt; pos += XS_THREADS) {
+            const u32 d = dig_s[pos];
+            const size_t o = (size_t)goff[d] + (pos - dbase[d]);
+            u64* dstc = PER_OWNER ? a.dst.ts[d] + (size_t)c * a.dst.col_stride : (c == 0 ? a.dst.out_ts : (c == 1 ? a.dst.out_key : a.dst.out_val));
+            dstc[o] = ev_s[c * XS_CHUNK + pos];
+        }
+    }
+    // stores to a peer's memory must have landed before a later kernel of this stream raises that peer's flag
+    if (PER_OWNER) __threadfence_system();
 }
 
 // ---- exclusive scan over u32 (three small kernels; the counter matrix is tiny next to the data) ----
@@ -127,26 +239,5 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply(u32* __restrict__ dat
 #pragma unroll
     for (int k = 0; k < SCAN_IPT; ++k) { if (base + k < n) data[base + k] = ex; ex += v[k]; }
 }
-
-// ---- digit / emit functors -----------------------------------------------------------------------
-struct OwnerDigit {      // keyBy routing on the GPU (A4): hashed keys -> mix64(key) % world; dense ids -> id % world
-    const u64* key; u32 world; u32 dense;
-    __device__ __forceinline__ u32 operator()(size_t i) const { return (u32)((dense ? key[i] : mix64(key[i])) % world); }
-};
-struct MoveEvent3 {      // moves one 24 B event (three 8 B columns); dense ids become the owner's local id (id / world)
-    const u64* ts; const u64* key; const u64* val; u64* ts_o; u64* key_o; u64* val_o; u32 world; u32 dense;
-    __device__ __forceinline__ void operator()(size_t s, size_t d) const {
-        const u64 k = key[s];
-        ts_o[d] = ts[s]; key_o[d] = (dense && k != KEY_EMPTY) ? k / world : k; val_o[d] = val[s];
-    }
-};
-struct SlotDigit {       // one 8-bit digit of the key-directory slot
-    const u32* slot; u32 shift;
-    __device__ __forceinline__ u32 operator()(size_t i) const { return (slot[i] >> shift) & 0xFFu; }
-};
-struct MovePair {        // (slot, arrival index) pair
-    const u32* slot; const u32* idx; u32* slot_o; u32* idx_o;
-    __device__ __forceinline__ void operator()(size_t s, size_t d) const { slot_o[d] = slot[s]; idx_o[d] = idx[s]; }
-};
 
 }  // namespace fmq

@@ -257,7 +257,9 @@ __device__ __forceinline__ u32 filter_events(const IngestArgs& a, DevState* st, 
 // kernel is launched first and returns immediately unless its preconditions hold, and vice versa.
 __device__ __forceinline__ bool ingest_fast_ok(const DevState* st, const WindowGeom& g, int window_enabled = 1) {
     if (!window_enabled) return true;                            // filter-only jobs (chapter1) need no pane origin
-    return st->anchored && g.slide32 != 0 && (u64)(g.ring_mask + 1) * g.slide32 < 0x100000000ull;
+    // 32-bit pane offsets and 32-bit cell indices: ring * slide < 2^32 ms and fewer than 2^31 accumulator cells (64 GB)
+    return st->anchored && g.slide32 != 0 && (u64)(g.ring_mask + 1) * g.slide32 < 0x100000000ull &&
+           (u64)(g.ring_mask + 1) * g.capacity < 0x80000000ull;
 }
 
 // ---- segmented input ---------------------------------------------------------------------------------
@@ -280,6 +282,11 @@ __device__ __forceinline__ void seg_tab_fill(const IngestArgs& a, SegTab* t, Dev
 // tile index -> element offset of its first event (same for every column) and number of events in it
 template <int TILE>
 __device__ __forceinline__ size_t seg_locate(const IngestArgs& a, const SegTab& t, u64 tile, u32& cnt) {
+    if (a.nseg <= 1) {                                           // one plain batch
+        const u64 first = tile * TILE, rem = t.n[0] - first;
+        cnt = rem < (u64)TILE ? (u32)rem : (u32)TILE;
+        return (size_t)first;
+    }
     u32 s = 0;
     while (tile >= t.tile_end[s]) ++s;                           // <= 8 steps, uniform across the warp
     const u64 first = (tile - (s ? t.tile_end[s - 1] : 0)) * TILE, rem = t.n[s] - first;
@@ -327,10 +334,23 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
 struct IngestRun {            // per-thread running scalars of one batch
     u64 late = 0, nea = 0; i64 dmax = I64_MIN_; u32 pmin = 0xFFFFFFFFu, pmax = 0; u32 err = 0;
     u32 dup[2] = {0, 0};
+    u32 dumin = 0xFFFFFFFFu, dumax = 0;     // lean core: smallest / largest (ts - origin) among the accumulated events
 };
 struct IngestConst {
     i64 origin_ts, origin_pane; u32 origin_ring, slide, recip; u64 span, nbuckets; bool combine;
+    // lean core
+    u32 cap32, m32; bool exact32; u64 keep_policy;
 };
+// pane quotient of a 32-bit offset: one multiply when ring * slide^2 <= 2^32 (ceil(2^32/slide) is then exact for every
+// offset inside the ring), else the estimate-and-correct form
+__device__ __forceinline__ u32 pane_quotient(u32 du, const IngestConst& k) {
+    if (k.exact32) return __umulhi(du, k.m32);
+    u32 q = __umulhi(du, k.recip);                                 // q <= du / slide <= q + 2
+    u32 rem = du - q * k.slide;
+    if (rem >= k.slide) { q++; rem -= k.slide; }
+    if (rem >= k.slide) { q++; }
+    return q;
+}
 
 // The window part of one tile (A1 max-ts, A3 late test, A2 pane, A5 accumulate) for the four events held by
 // this lane.  Must be reached by all 32 lanes of the warp.  Returns which of the four were late / accumulated,
@@ -383,6 +403,89 @@ __device__ __forceinline__ void ingest_core(const IngestArgs& a, DevState* st, c
         V v; memcpy(&v, &vb_[e], 8);
         accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask, k.combine, e == 0 && sample, r.dup, hot);
         slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
+    }
+}
+
+// ---- lean core (warp-ring kernel, no warp-level combining) ------------------------------------------------
+// ncu of the first warp-ring kernel: 264 instructions per event and lane, issue slots 52 % busy with 16 warps per
+// SM, lg_throttle 0 — the kernel was bound by its own instruction count, not by the L2 (profiles/r02_notes.md).
+// This form does the same work in 32-bit arithmetic wherever the geometry allows it: one unsigned compare is the
+// late AND the ring test, the pane quotient is one multiply, a cell is a 32-bit index (tables < 2^31 cells), the
+// pair-lane exchange moves three words, and the order-preserving max / min encoding is three logic operations.
+template <typename V>
+__device__ __forceinline__ void red_half(char* acc_half, u32 c, u32 lo, u32 hi, bool odd, u32 oddmask, bool want, u64 policy) {
+    if (c == 0xFFFFFFFFu) return;
+    char* p = acc_half + (u64)c * 32u;
+    if constexpr (IsF64<V>::value) {
+        const double addv = odd ? __hiloint2double((int)hi, (int)lo) : 1.0;
+        asm volatile("red.global.add.L2::cache_hint.f64 [%0], %1, %2;" :: "l"(p), "d"(addv), "l"(policy) : "memory");
+    } else {
+        const u64 addv = odd ? (((u64)hi << 32) | lo) : 1ull;
+        asm volatile("red.global.add.L2::cache_hint.u64 [%0], %1, %2;" :: "l"(p), "l"(addv), "l"(policy) : "memory");
+    }
+    if (want) {
+        u32 uh, ul;
+        if constexpr (IsF64<V>::value) {
+            const u32 m = (u32)((int)hi >> 31);                       // all ones for negative values
+            uh = hi ^ (m | 0x80000000u) ^ oddmask; ul = lo ^ m ^ oddmask;   // order_f64, complemented on the min lanes
+            const double v = __hiloint2double((int)hi, (int)lo);
+            if (v != v) { uh = 0xFFFFFFFFu; ul = 0xFFFFFFFFu; }      // NaN wins both max and min (Math.max / Math.min)
+        } else {
+            uh = hi ^ 0x80000000u ^ oddmask; ul = lo ^ oddmask;
+        }
+        const u64 x = ((u64)uh << 32) | ul;
+        asm volatile("red.global.max.L2::cache_hint.u64 [%0], %1, %2;" :: "l"(p + 16), "l"(x), "l"(policy) : "memory");
+    }
+}
+// A5 for one event per lane: cw = cell index or 0xFFFFFFFF (nothing to add).  Must be reached by all 32 lanes.
+template <typename V>
+__device__ __forceinline__ void accumulate_lean32(char* acc_half, u32 cw, u64 vb, bool odd, u32 oddmask, bool want, u64 policy) {
+    const u32 lo = (u32)vb, hi = (u32)(vb >> 32);
+    const u32 cw_p = __shfl_xor_sync(0xffffffffu, cw, 1), lo_p = __shfl_xor_sync(0xffffffffu, lo, 1), hi_p = __shfl_xor_sync(0xffffffffu, hi, 1);
+    // first the even lane's event (both halves in one instruction = one sector request), then the odd lane's
+    red_half<V>(acc_half, odd ? cw_p : cw, odd ? lo_p : lo, odd ? hi_p : hi, odd, oddmask, want, policy);
+    red_half<V>(acc_half, odd ? cw : cw_p, odd ? lo : lo_p, odd ? hi : hi_p, odd, oddmask, want, policy);
+}
+
+template <typename V, bool DENSE>
+__device__ __forceinline__ void ingest_core_lean(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
+                                                 const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 in_mask,
+                                                 u32& late_mask, u32& vmask, u32 (&q_)[INGEST_EPT], u32 (&slot_)[INGEST_EPT]) {
+    const bool odd = threadIdx.x & 1;
+    const u32 oddmask = odd ? 0xFFFFFFFFu : 0u;
+    const bool want = odd ? (a.g.agg_mask & 4u) != 0 : (a.g.agg_mask & 8u) != 0;
+    char* acc_half = reinterpret_cast<char*>(a.acc) + (odd ? 8 : 0);
+    u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0;
+    late_mask = 0; vmask = 0;
+#pragma unroll
+    for (int e = 0; e < INGEST_EPT; ++e) {
+        const bool in = (in_mask >> e) & 1u;
+        const i64 d = ts_[e] - k.origin_ts;
+        const bool inr = (u64)d < k.span;                          // A3 + ring test: late (negative) and beyond-the-ring offsets both fail
+        bool good = in && ts_[e] >= 0;
+        if (DENSE) good = good && key_[e] < (u64)k.cap32; else good = good && key_[e] != KEY_EMPTY;
+        const bool act = good && inr;
+        const u32 du = (u32)d;
+        q_[e] = pane_quotient(du, k);                              // A2
+        r.dumin = min(r.dumin, act ? du : 0xFFFFFFFFu); r.dumax = max(r.dumax, act ? du : 0u);   // A1 and the live pane range, divided once at the end
+        if (in && !act) {                                          // rare: late record, bad input, or a span the ring cannot hold
+            if (!good) r.err |= ERRB_BAD_INPUT;
+            else { r.dmax = d > r.dmax ? d : r.dmax; if (d < 0) { r.late++; late_mask |= 1u << e; } else r.err |= ERRB_RING; }
+        }
+        if (!DENSE) { hb_[e] = dir_home_bucket(key_[e], k.nbuckets); if (act) kv_[e] = ld_bucket(a.dkeys + hb_[e] * 4); }
+        act_mask |= act ? (1u << e) : 0u;
+    }
+#pragma unroll
+    for (int e = 0; e < INGEST_EPT; ++e) {
+        bool valid = (act_mask >> e) & 1u;
+        u32 slot = (u32)key_[e];
+        if (!DENSE) {
+            if (valid) slot = dir_resolve_inline(a.dkeys, k.nbuckets, key_[e], hb_[e], kv_[e], st);
+            valid = valid && slot != SLOT_INVALID;
+        }
+        const u32 cell = ((k.origin_ring + q_[e]) & a.g.ring_mask) * k.cap32 + slot;
+        slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
+        accumulate_lean32<V>(acc_half, valid ? cell : 0xFFFFFFFFu, vb_[e], odd, oddmask, want, k.keep_policy);
     }
 }
 
@@ -598,7 +701,10 @@ __device__ __forceinline__ void wr_flush(WarpRows& w, u64* counter, u64 cap, T0*
     w.n = 0;
 }
 
-template <typename V, bool DENSE, bool EXTRAS>
+// COMBINE: warp-level pre-aggregation of lanes that hit the same cell (skewed keys).  The host picks the variant
+// from a hint the plan kernel leaves in pinned host memory (it may lag by a batch: the choice only changes the
+// order of additions, never the result beyond the double-sum tolerance).
+template <typename V, bool DENSE, bool EXTRAS, bool COMBINE>
 __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(const __grid_constant__ IngestArgs a) {
     extern __shared__ __align__(128) unsigned char iw_smem[];
     __shared__ __align__(8) u64 bars[IW_WARPS][IW_STAGES];
@@ -611,16 +717,20 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
     if (a.window_enabled) {
         k.origin_ts = st->origin_ts;
         k.origin_pane = st->origin_pane;
-        k.combine = st->combine_dups != 0;
+        k.combine = COMBINE;
         k.origin_ring = (u32)st->origin_pane & a.g.ring_mask;
         k.slide = a.g.slide32;
         k.recip = 0xFFFFFFFFu / k.slide;
         k.span = (u64)(a.g.ring_mask + 1 - st->pending_clear) * k.slide;
         k.nbuckets = a.g.capacity >> 2;
+        k.cap32 = (u32)a.g.capacity;
+        k.exact32 = k.slide >= 2 && (u64)(a.g.ring_mask + 1) * k.slide * k.slide <= 0x100000000ull;
+        k.m32 = k.exact32 ? (u32)((0x100000000ull + k.slide - 1) / k.slide) : 0u;
+        k.keep_policy = l2_keep_policy();
     }
     IngestRun r;
     if (threadIdx.x == 0) seg_tab_fill<IW_TILE>(a, &seg, st);
-    if (k.combine) hot_init(&hot_tab);
+    if (COMBINE) hot_init(&hot_tab);
     if (lane == 0) {
         for (int s = 0; s < IW_STAGES; ++s) mbar_init(&bars[wl][s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -649,10 +759,13 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
     };
     if (lane == 0)
         for (int s = 0; s < IW_STAGES; ++s) { const u64 t = gw + (u64)s * nw; if (t < ntiles) issue(t, s); }
-    u64 it = 0;
-    for (u64 t = gw; t < ntiles; t += nw, ++it) {
-        const int s = (int)(it % IW_STAGES);
-        mbar_wait(&bars[wl][s], (u32)((it / IW_STAGES) & 1));
+    // per-event filter A6-i (Main.java:31) as one comparison: LT / LE compare the negated operands
+    const bool f_flip = a.efilter_op == 1 || a.efilter_op == 3, f_strict = a.efilter_op < 2;
+    const double f_thr = f_flip ? -a.efilter_thr : a.efilter_thr;
+    u32 nea_w = 0;                                               // rows this warp produced (uniform)
+    int s = 0; u32 phase = 0;
+    for (u64 t = gw; t < ntiles; t += nw) {
+        mbar_wait(&bars[wl][s], phase);
         u32 cnt; const size_t off = seg_locate<IW_TILE>(a, seg, t, cnt);
         // lane x takes events x, x+32, x+64, x+96 of the tile: conflict-free 8-byte shared loads
         i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; u32 in_mask = 0xFu;
@@ -676,25 +789,41 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
             const u64 tn = t + (u64)IW_STAGES * nw;
             if (tn < ntiles) issue(tn, s);
         }
-        u32 ok_mask = 0;
-#pragma unroll
-        for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
-        if ((ok_mask & in_mask) != in_mask) r.err |= ERRB_BAD_INPUT;
-        ok_mask &= in_mask;
-        if (a.efilter_enabled) {                                 // A6-i (Main.java:31)
+        if (++s == IW_STAGES) { s = 0; phase ^= 1u; }
+        if (a.efilter_enabled) {
 #pragma unroll
             for (int e = 0; e < INGEST_EPT; ++e) {
                 V v; memcpy(&v, &vb_[e], 8);
-                const bool hit = (ok_mask & (1u << e)) && cmp_op((double)v, a.efilter_op, a.efilter_thr);
+                const double x = f_flip ? -(double)v : (double)v;
+                const bool hit = ((in_mask >> e) & 1u) && ts_[e] >= 0 && key_[e] != KEY_EMPTY && (f_strict ? x > f_thr : x >= f_thr);
                 if (ea.n + 32 > IW_ROWS) wr_flush(ea, &st->n_ealert, a.ea_cap, a.ea_ts, a.ea_key, a.ea_val, r.err);
                 const u32 before = ea.n;
                 wr_push(ea, hit, (u64)ts_[e], key_[e], vb_[e]);
-                if (lane == 0) r.nea += ea.n - before;
+                nea_w += ea.n - before;
             }
         }
-        if (!a.window_enabled) continue;
+        if (!a.window_enabled) {                                 // filter-only job: input validity is still checked
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e) if (((in_mask >> e) & 1u) && (ts_[e] < 0 || key_[e] == KEY_EMPTY)) r.err |= ERRB_BAD_INPUT;
+            continue;
+        }
         u32 late_mask, vmask, q_[INGEST_EPT], slot_[INGEST_EPT];
-        ingest_core<V, DENSE>(a, st, k, r, ts_, key_, vb_, ok_mask, &hot_tab, wl == 0, late_mask, vmask, q_, slot_);
+        if constexpr (!COMBINE) {
+            ingest_core_lean<V, DENSE>(a, st, k, r, ts_, key_, vb_, in_mask, late_mask, vmask, q_, slot_);
+            if (wl == 0 && (((t - gw) / nw) & 3u) == 0) {        // skew sample (one warp per block, every 4th tile): lanes sharing their cell with another lane
+                const bool v0 = vmask & 1u;
+                const u64 c0 = ((u64)((k.origin_ring + q_[0]) & a.g.ring_mask) << 32) | slot_[0];
+                const unsigned m = __match_any_sync(0xffffffffu, v0 ? c0 : (0xFFFF000000000000ull | lane));
+                r.dup[0] += __popc(__ballot_sync(0xffffffffu, v0)); r.dup[1] += __popc(__ballot_sync(0xffffffffu, v0 && (m & (m - 1)) != 0));
+            }
+        } else {
+            u32 ok_mask = 0;
+#pragma unroll
+            for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
+            if ((ok_mask & in_mask) != in_mask) r.err |= ERRB_BAD_INPUT;
+            ok_mask &= in_mask;
+            ingest_core<V, DENSE>(a, st, k, r, ts_, key_, vb_, ok_mask, &hot_tab, wl == 0, late_mask, vmask, q_, slot_);
+        }
         if (EXTRAS && a.lt_cap) {                                // late side output (chapter3/README.md:213-228, option 3)
 #pragma unroll
             for (int e = 0; e < INGEST_EPT; ++e) {
@@ -713,11 +842,17 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
     if (a.efilter_enabled) wr_flush(ea, &st->n_ealert, a.ea_cap, a.ea_ts, a.ea_key, a.ea_val, r.err);
     if (EXTRAS && a.lt_cap) wr_flush(lt, &st->n_late, a.lt_cap, a.lt_ts, a.lt_key, a.lt_val, r.err);
     if (EXTRAS && a.mlog_enabled) wr_flush(ml, &st->n_mlog, a.ml_cap, a.ml_pane, a.ml_slot, a.ml_val, r.err);
-    if (k.combine && a.window_enabled) { __syncthreads(); hot_flush<V>(&hot_tab, a.acc, a.g.agg_mask); }
+    if (COMBINE && a.window_enabled) { __syncthreads(); hot_flush<V>(&hot_tab, a.acc, a.g.agg_mask); }
     // ---- per-warp reduction of the batch scalars, one atomic each per warp ----
-    r.nea = warp_sum_u64(r.nea);
+    r.nea = nea_w;                                               // uniform: lane 0 reports it
     for (int o = 16; o > 0; o >>= 1) r.err |= __shfl_xor_sync(0xffffffffu, r.err, o);
     if (a.window_enabled) {
+        // lean core: the extreme offsets become the extreme panes and the largest timestamp here, once per lane
+        if (r.dumin <= r.dumax) {
+            const u32 qlo = pane_quotient(r.dumin, k), qhi = pane_quotient(r.dumax, k);
+            r.pmin = qlo < r.pmin ? qlo : r.pmin; r.pmax = qhi > r.pmax ? qhi : r.pmax;
+            r.dmax = (i64)r.dumax > r.dmax ? (i64)r.dumax : r.dmax;
+        }
         r.late = warp_sum_u64(r.late); r.dmax = warp_max_i64(r.dmax);
         r.pmin = __reduce_min_sync(0xffffffffu, r.pmin); r.pmax = __reduce_max_sync(0xffffffffu, r.pmax);
     }
@@ -829,6 +964,7 @@ struct PlanArgs {
     DevState* st; WindowGeom g; i64 bound; i64 watermark_after; u64 n_events; int window_enabled; int is_auto;
     int is_keep;      // FMQ_WM_KEEP: bookkeeping only, the watermark stays where it is
     const u64* seg_n; u32 nseg; u64 seg_cap;   // segmented input: the event count lives in device memory (n_events is then ignored)
+    u32* combine_hint;                         // pinned host word: the skew decision, for the host's choice of ingest kernel
     int overlap;      // combiner mode with fire / retire on a second stream: the next ingest starts before the expired panes are cleared
 };
 
@@ -842,7 +978,10 @@ __global__ void plan_kernel(const PlanArgs a) {
     if (!a.window_enabled) return;
     // skew adaptation for the next batch: pre-aggregate inside warps when > 3 % of the sampled lanes
     // shared their cell with another lane of the same warp
-    if (st->dup_sampled >= 4096) { st->combine_dups = (st->dup_found * 32 > st->dup_sampled) ? 1u : 0u; st->dup_sampled = 0; st->dup_found = 0; }
+    if (st->dup_sampled >= 4096) {
+        st->combine_dups = (st->dup_found * 32 > st->dup_sampled) ? 1u : 0u; st->dup_sampled = 0; st->dup_found = 0;
+        if (a.combine_hint) *a.combine_hint = st->combine_dups;
+    }
     // A1: BoundedOutOfOrdernessTimestampExtractor (chapter3/README.md:379-396)
     if (st->batch_max_ts > st->cur_max_ts) st->cur_max_ts = st->batch_max_ts;
     st->batch_max_ts = I64_MIN_;

@@ -268,3 +268,43 @@ class PeerPullOperator:
 
     def flush(self, wm: int = capi.FMQ_WM_FINAL):
         self.engine.flush(wm)
+
+
+class ExchangeOperator:
+    """keyBy exchange inside the library (include/fmq_b200.h, fmq_shard_*): the reference's structure — a hash
+    exchange in front of owner-held keyed state (BandwidthMonitorWithEventTime.java:45-47) — with nothing but kernel
+    launches per micro-batch.  Each rank's scatter kernel writes every owner's events straight into that owner's
+    receive segment over NVLink, counts and the batch's largest timestamp travel as peer stores behind a flag, and
+    the receiving rank's kernels wait on those flags on the device.  Every operator, both key modes, per-key arrival
+    order.  `torch.distributed` (or any other transport) is used ONCE, at set-up, to hand the 64-byte IPC blobs
+    around; pass `bases` instead to attach engines living in this process."""
+
+    def __init__(self, engine, rank: int, world: int, max_send: int, group=None, bases=None):
+        self.engine, self.rank, self.world = engine, rank, world
+        self.dense = engine.cfg.key_mode == capi.FMQ_KEYS_DENSE
+        if bases is not None:                                # same process: (engines already shard_alloc'ed)
+            engine.shard_attach(rank, world, bases)
+            return
+        import torch.distributed as dist
+        blob = engine.shard_alloc(world, max_send)
+        blobs = [None] * world
+        dist.all_gather_object(blobs, blob, group=group)
+        engine.shard_attach_ipc(rank, world, blobs)
+        dist.barrier(group=group)                            # every rank has mapped every buffer before the first store
+
+    def global_keys(self, local_keys: np.ndarray) -> np.ndarray:
+        return local_keys * np.uint64(self.world) + np.uint64(self.rank) if self.dense else local_keys
+
+    def send(self, ts, key, val):
+        self.engine.shard_send(ts, key, val)
+
+    def recv(self, watermark_after: int = capi.FMQ_WM_AUTO, want_count: bool = False):
+        return self.engine.shard_recv(watermark_after, want_count)
+
+    def process_batch(self, ts, key, val, watermark_after: int = capi.FMQ_WM_AUTO):
+        """send + recv of one micro-batch; the send of the next batch overlaps this one's kernels on its own stream."""
+        self.engine.shard_send(ts, key, val)
+        self.engine.shard_recv(watermark_after)
+
+    def flush(self, wm: int = capi.FMQ_WM_FINAL):
+        self.engine.flush(wm)

@@ -56,8 +56,10 @@ def _assert_rows(got_cols, want_cols, order, names, f64_cols=()):
 
 def _compare(gpu, cpu, f64):
     f, o = gpu.poll_fired(chunk=BIG), cpu.poll_fired(chunk=BIG)
-    fcols = lambda r: [r.key, r.window_end, r.count, r.sum, r.min, r.max]
-    _assert_rows(fcols(f), fcols(o), [0, 1], ["key", "window_end", "count", "sum", "min", "max"], f64_cols=(3,) if f64 else ())
+    m = gpu.cfg.agg_mask                                        # columns the job did not ask for are not defined: left out
+    names = ["key", "window_end", "count"] + [n for n, bit in (("sum", capi.FMQ_AGG_SUM), ("min", capi.FMQ_AGG_MIN), ("max", capi.FMQ_AGG_MAX)) if m & bit]
+    fcols = lambda r: [getattr(r, n) for n in names]  # noqa: E731
+    _assert_rows(fcols(f), fcols(o), [0, 1], names, f64_cols=(names.index("sum"),) if (f64 and "sum" in names) else ())
     if gpu.cfg.walert_source:
         a, b = gpu.poll_window_alerts(chunk=BIG), cpu.poll_window_alerts(chunk=BIG)
         _assert_rows([a.key, a.window_end, a.value], [b.key, b.window_end, b.value], [0, 1], ["alert key", "alert window_end", "alert value"], f64_cols=(2,))
