@@ -179,9 +179,11 @@ def main():
     ap.add_argument("--cpu-sample-log2", type=int, default=23, help="events per step of the CPU baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--multi", default="combiner", choices=["combiner", "alltoall", "peerpull"],
+    ap.add_argument("--multi", default="combiner", choices=["combiner", "exchange", "alltoall", "peerpull"],
                     help="N>1: combiner = local accumulate + peer-memory fire (no event shuffle; dense ids); "
-                         "alltoall = owner split + NCCL all-to-all of the events")
+                         "exchange = keyBy exchange inside the library (scatter over NVLink + device flags); "
+                         "alltoall / peerpull = round 1's host-driven exchanges (NCCL all-to-all / copies out of peer memory)")
+    ap.add_argument("--no-verify", action="store_true", help="N>1: skip the comparison of the ranks' outputs with the CPU oracle")
     ap.add_argument("--no-variants", action="store_true")
     ap.add_argument("--no-clocks", action="store_true", help="experiment: do not sample nvidia-smi during the timed region")
     ap.add_argument("--keys", type=int, default=N_KEYS, help="experiment: number of distinct hosts")
@@ -265,25 +267,28 @@ def main():
         start = (step * world + rank) * B
         ts, key, val = generate_torch(spec, start, B, device=f"cuda:{local_rank}")
         return ts.contiguous(), key.contiguous(), val.contiguous()
-    batches = [dev_batch(s) for s in range(W + K)]
+    default_batches = batches = [dev_batch(s) for s in range(W + K)]
     torch.cuda.synchronize()
 
     host_issue_ms = [0.0]
 
-    def measure(kw, with_clocks):
+    def make_operator(eng, kw, multi):
+        from monitor_systam_flink_quickstart_b200.shard import CombinerOperator, ExchangeOperator, PeerPullOperator, ShardedOperator
+        if multi == "combiner" and kw.get("key_mode") == capi.FMQ_KEYS_DENSE:
+            return CombinerOperator(eng, rank, world)
+        if multi in ("exchange", "combiner"):
+            return ExchangeOperator(eng, rank, world, B)
+        if multi == "peerpull":
+            return PeerPullOperator(eng, rank, world, BOUND_MS)
+        return ShardedOperator(eng, rank, world, BOUND_MS)
+
+    def measure(kw, with_clocks, multi=args.multi, batches=None, K=K):
         """W warm-up + K timed steps with device-resident inputs; CUDA events on the engine's stream
         (every kernel, copy and collective of a step is ordered on it)."""
+        batches = batches if batches is not None else default_batches
         eng = capi.Engine(**kw)
         stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local_rank))
-        sharded = None
-        if world > 1:
-            from monitor_systam_flink_quickstart_b200.shard import CombinerOperator, PeerPullOperator, ShardedOperator
-            if args.multi == "combiner" and kw.get("key_mode") == capi.FMQ_KEYS_DENSE:
-                sharded = CombinerOperator(eng, rank, world)
-            elif args.multi == "peerpull":
-                sharded = PeerPullOperator(eng, rank, world, BOUND_MS)
-            else:
-                sharded = ShardedOperator(eng, rank, world, BOUND_MS)
+        sharded = make_operator(eng, kw, multi) if world > 1 else None
 
         def step(b):
             if sharded:
@@ -389,11 +394,91 @@ def main():
             "value": B / (float(np.mean(t_c2)) * 1e-3), "unit": "events/s", "ms_per_step": float(np.mean(t_c2)), "gpu_launches": int(c2_launches),
             "timing": "CUDA events on the engine stream around each push (library-recorded), inputs resident in HBM"}
 
+    def job_max(x):
+        if not dist:
+            return x
+        t = torch.tensor([x], device=f"cuda:{local_rank}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    verify = None
+    if world > 1 and not args.no_variants:
+        variants = {}
+        nv_bytes = 24.0 * B * (world - 1) / world            # what one GPU sends (and receives) over NVLink per step
+        # (a) the headline workload through the reference's own structure: a keyBy exchange in front of owner-held state
+        kwx = dict(kw)
+        if args.key_mode == "dense":
+            kwx["table_capacity"] = (args.keys + world - 1) // world
+        msx, ingx, firex, dx, _ = measure(kwx, False, multi="exchange")
+        msx = job_max(msx)
+        variants["route=keyBy exchange inside the library (scatter over NVLink + device flags), same C3 workload"] = {
+            "value": world * B * K / (msx * 1e-3), "unit": "events/s", "ms_per_step": msx / K,
+            "nvlink_GBps_per_gpu_each_direction": nv_bytes / (msx / K * 1e-3) / 1e9, "nvlink_frac_of_900": nv_bytes / (msx / K * 1e-3) / 1e9 / 900.0,
+            "events_over_nvlink_per_step_per_gpu": B * (world - 1) // world}
+        # (b) BASELINE.json configs[3] in its named form: 60 s / 10 s sliding sum per (host << 32 | metric), 10 M keys, int64, hashed keys
+        K4 = min(K, 8)
+        spec4 = StreamSpec(n_keys=10_000_000, events_per_ms=10_000 * world, jitter_ms=4000, late_frac_ppm=0, value_type="i64", key_kind="host_metric")
+        keys_rank = 10_000_000 // world
+        kw4 = dict(value_type=capi.FMQ_VAL_I64, window_enabled=1, agg_mask=15, window_size_ms=60_000, window_slide_ms=10_000, max_out_of_orderness_ms=5000,
+                   walert_source=capi.FMQ_ALERT_SUM, walert_op=capi.FMQ_CMP_LT, walert_mul=8.0, walert_div0=60.0, walert_div1=1024.0, walert_div2=1024.0,
+                   walert_threshold=0.05, table_capacity=int(keys_rank * 1.6) + 1024, pane_ring=16, max_batch=2 * B, device=local_rank,
+                   fired_capacity=8 * keys_rank + (1 << 20), walert_capacity=8 * keys_rank + (1 << 20))
+        batches4 = [tuple(t.contiguous() for t in generate_torch(spec4, (s_ * world + rank) * B, B, device=f"cuda:{local_rank}")) for s_ in range(W + K4)]
+        torch.cuda.synchronize()
+        ms4, ing4, fire4, d4, _ = measure(kw4, False, multi="exchange", batches=batches4, K=K4)
+        ms4 = job_max(ms4)
+        del batches4
+        variants["workload=configs[3]: 60s/10s sliding per (host,metric), 10M keys, hashed, through the keyBy exchange"] = {
+            "value": world * B * K4 / (ms4 * 1e-3), "unit": "events/s", "ms_per_step": ms4 / K4, "steps": K4,
+            "nvlink_GBps_per_gpu_each_direction": nv_bytes / (ms4 / K4 * 1e-3) / 1e9, "nvlink_frac_of_900": nv_bytes / (ms4 / K4 * 1e-3) / 1e9 / 900.0}
+
+    if world > 1 and not args.no_verify:
+        # Outside every timed region: V steps of the headline route into fresh engines; the union of the ranks' rows
+        # against the CPU oracle fed the same global batches, as order-independent sums over the rows.
+        V = 2
+        engv = capi.Engine(**kw)
+        opv = make_operator(engv, kw, args.multi)
+        for b in range(V):
+            opv.process_batch(*default_batches[b])
+        engv.synchronize()
+        opv.flush()
+        engv.synchronize()
+
+        def row_sums(f, a, e, late, gk):
+            M = np.uint64(0x9E3779B97F4A7C15)
+            hf = ((gk(f.key) * M) ^ (f.window_end.view(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F)) ^ f.count.view(np.uint64)).sum(dtype=np.uint64)
+            he = ((e.ts.view(np.uint64) * M) ^ gk(e.key) ^ e.val.view(np.uint64)).sum(dtype=np.uint64)
+            s64 = lambda u: int(np.array(u, dtype=np.uint64).astype(np.int64))  # noqa: E731
+            return [len(f), int(f.count.sum()), s64(hf), len(a), len(e), s64(he), int(late)]
+        gk = opv.global_keys if hasattr(opv, "global_keys") else (lambda k: k)
+        mine = row_sums(engv.poll_fired(chunk=1 << 24), engv.poll_window_alerts(chunk=1 << 24), engv.poll_event_alerts(chunk=1 << 24),
+                        engv.counters()["late_dropped"], gk)
+        engv.close()
+        tot = torch.tensor(mine, device=f"cuda:{local_rank}", dtype=torch.int64)
+        dist.all_reduce(tot)                                   # int64 sums wrap like the uint64 sums they stand for
+        if rank == 0:
+            subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
+            from oracle_lib import ParallelOracle
+            okw = {k_: v_ for k_, v_ in kw.items() if k_ != "device"}
+            orc = ParallelOracle(threads=os.cpu_count() or 1, **okw)
+            for b in range(V):
+                parts = [generate_numpy(spec, (b * world + r) * B, B) for r in range(world)]
+                orc.push_batch(*[np.concatenate([p_[j] for p_ in parts]) for j in range(3)])
+                del parts
+            orc.flush()
+            want = row_sums(orc.poll_fired(chunk=1 << 26), orc.poll_window_alerts(chunk=1 << 26), orc.poll_event_alerts(chunk=1 << 26),
+                            orc.counters()["late_dropped"], lambda k: k)
+            orc.close()
+            got = [int(x) for x in tot.tolist()]
+            names = ["fired_rows", "sum_of_counts", "fired_row_hash", "window_alert_rows", "event_alert_rows", "event_alert_hash", "late_dropped"]
+            verify = {"steps": V, "events": V * world * B, "route": args.multi, "oracle": "oracle/cpu_parallel.cpp (ParallelOracle)",
+                      "equal": got == want, "got": dict(zip(names, got)), "want": dict(zip(names, want))}
+
     # -------- roofline of the dominant kernel (ingest), this rank --------
     peak, peak_src = measured_peak()
     alg_bytes = 24.0 * events_rank + 24.0 * ealert_rank
     achieved = alg_bytes / (ing_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "ingest_fast_kernel<double,%s>" % args.key_mode, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+    roofline = {"bound": "hbm", "kernel": "ingest_ring_kernel<double,%s>" % args.key_mode, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": ncu_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                 "avg_launch_ms": ing_ms, "fire_chain_ms": fire_ms, "share_of_step": ing_ms * K / ms,
                 "host_issue_ms_per_step": issue_ms}
@@ -531,11 +616,11 @@ def main():
                        "events_per_step_per_gpu": B, "global_events_per_ms": spec.events_per_ms, "keys": args.keys, "key_mode": args.key_mode, "window_ms": WINDOW_MS, "bound_ms": BOUND_MS,
                        "l2": "inputs larger than L2 (each batch = 24 B x 2^%d = %.0f MB, read once)" % (args.batch_log2, 24 * B / 1e6),
                        "parallelism": "1 GPU" if world == 1 else (
-                           f"{world} GPUs, combiner: local accumulate + 32 B all-reduce per batch + fire over NVLink peer memory, fire/retire of batch k overlapped with the ingest of batch k+1"
+                           f"{world} GPUs, combiner: local accumulate + 32 B of batch scalars exchanged by peer stores behind device flags + fire over NVLink peer memory, fire/retire of batch k overlapped with the ingest of batch k+1"
                            if (args.multi == "combiner" and args.key_mode == "dense") else (
-                               f"keyBy sharded over {world} GPUs, buckets pulled from peer memory over NVLink" if args.multi == "peerpull"
+                               f"keyBy exchange over {world} GPUs inside the library: owner runs scattered over NVLink, device flags" if args.multi == "exchange" else f"keyBy sharded over {world} GPUs, buckets pulled from peer memory over NVLink" if args.multi == "peerpull"
                                else f"keyBy hash-sharded over {world} GPUs, NCCL all-to-all"))},
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "e2e_packed": e2e_packed, "gpu_launches": int(launches), "clocks": clocks, "variants": variants,
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "e2e_packed": e2e_packed, "gpu_launches": int(launches), "clocks": clocks, "variants": variants, "verify_vs_oracle": verify,
             "step_counts": {"event_alert_rows": int(n_ealert), "late_dropped": int(n_late), "fired_rows": int(n_fired)}}
     print(json.dumps(line))
     if dist:

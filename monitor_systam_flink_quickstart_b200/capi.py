@@ -194,6 +194,7 @@ def _declare(lib, p: str, has_mem: bool = True, side_outputs: Optional[bool] = N
         sig("shard_attach_ipc", [vp, i32, i32, vp])
         sig("shard_send", [vp, vp, vp, vp, sz, i32])
         sig("shard_recv", [vp, i64, psz])
+        sig("combiner_use_flags", [vp, i32])
 
 
 def _ptr(a) -> int:
@@ -539,6 +540,9 @@ class Engine(EngineBase):
 
     def combiner_overlap(self, enable: bool = True):
         self._check(self._lib.fmq_combiner_overlap(self._h, 1 if enable else 0))
+
+    def combiner_use_flags(self, enable: bool = True):
+        self._check(self._lib.fmq_combiner_use_flags(self._h, 1 if enable else 0))
 
     @property
     def fire_stream(self) -> int:

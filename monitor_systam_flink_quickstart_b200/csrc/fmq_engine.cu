@@ -750,6 +750,9 @@ static int push_cols(fmq_handle* h, const InCols& c, size_t n, int64_t wm_after,
     return h->cfg.value_type == FMQ_VAL_F64 ? push_cols_t<double>(h, c, n, wm_after, mem) : push_cols_t<i64>(h, c, n, wm_after, mem);
 }
 
+static u64 peer_timeout_ns();
+static XPeers xs_peers(const fmq_handle* h);
+
 // combiner mode, stage 1 (fmq_push_local / fmq_push_local_packed)
 static int push_local_cols(fmq_handle* h, const InCols& c, size_t n, int32_t mem) {
     int s = check_cols(h, c, n, mem); if (s) return s;
@@ -758,7 +761,13 @@ static int push_local_cols(fmq_handle* h, const InCols& c, size_t n, int32_t mem
     cudaEvent_t wait_copy = nullptr;
     s = h->cfg.value_type == FMQ_VAL_F64 ? ingest_cols<double>(h, c, n, mem, &wait_copy) : ingest_cols<i64>(h, c, n, mem, &wait_copy);
     if (s) return s;
-    pack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "pack_scalars_kernel");
+    if (h->cmb_flags) {
+        // this rank's batch scalars go straight into every peer's control block, behind the batch number
+        const u64 seq = ++h->cmb_seq;
+        cmb_publish_kernel<<<1, 32, 0, h->stream>>>(h->d_st, xs_peers(h), (u32)h->world, (u32)h->rank, (u32)(seq & 1), seq); LAUNCHED(h, "cmb_publish_kernel");
+    } else {
+        pack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "pack_scalars_kernel");
+    }
     h->pending_n += n;
     if (wait_copy) CU(h, cudaEventSynchronize(wait_copy));
     return FMQ_OK;
@@ -1019,10 +1028,20 @@ int32_t fmq_fire_global(fmq_handle* h, int64_t watermark_after) {
     if (h->sticky) return FMQ_ERR_POISONED;
     CU(h, cudaSetDevice(h->device));
     if (h->overlap) CU(h, cudaStreamWaitEvent(h->stream, h->ev_bdone, 0));     // the previous batch's retire / commit
-    unpack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "unpack_scalars_kernel");
+    if (h->cmb_flags) {
+        if (h->cmb_seq == 0) return set_err(h, FMQ_ERR_BAD_ARG, "with device flags every fmq_fire_global follows an fmq_push_local (n = 0 for a flush)");
+        // waits, on the device, until every rank has published this batch's scalars (= "every rank has ingested") and takes their maximum
+        cmb_reduce_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->xs_ctl[h->rank], (u32)h->world, (u32)(h->cmb_seq & 1), h->cmb_seq, peer_timeout_ns()); LAUNCHED(h, "cmb_reduce_kernel");
+    } else {
+        unpack_scalars_kernel<<<1, 32, 0, h->stream>>>(h->d_st, h->d_xchg); LAUNCHED(h, "unpack_scalars_kernel");
+    }
     int s = (h->cfg.value_type == FMQ_VAL_F64) ? stage_fire<double>(h, h->pending_n, watermark_after, false)
                                                : stage_fire<i64>(h, h->pending_n, watermark_after, false);
     if (s) return s;
+    if (h->cmb_flags) {                                            // "this rank has finished reading its peers' tables", after the fire kernel
+        cudaStream_t fs = h->overlap ? h->fire_stream : h->stream;
+        cmb_done_kernel<<<1, 32, 0, fs>>>(xs_peers(h), (u32)h->world, (u32)h->rank, (u32)(h->cmb_seq & 1), h->cmb_seq); LAUNCHED(h, "cmb_done_kernel");
+    }
     h->pending_n = 0;
     return FMQ_OK;
 }
@@ -1031,6 +1050,9 @@ int32_t fmq_retire(fmq_handle* h) {
     if (h->sticky) return FMQ_ERR_POISONED;
     CU(h, cudaSetDevice(h->device));
     cudaStream_t fs = h->overlap ? h->fire_stream : h->stream;
+    if (h->cmb_flags) {                                            // every rank has finished reading this rank's table
+        cmb_wait_done_kernel<<<1, 32, 0, fs>>>(h->xs_ctl[h->rank], (u32)h->world, (u32)(h->cmb_seq & 1), h->cmb_seq, h->d_st, peer_timeout_ns()); LAUNCHED(h, "cmb_wait_done_kernel");
+    }
     retire_kernel<<<(unsigned)h->num_sms * 4, 256, 0, fs>>>(h->d_st, h->d_acc, h->capacity, h->g.ring_mask); LAUNCHED(h, "retire_kernel");
     if (h->overlap) {
         commit_overlapped_kernel<<<1, 32, 0, fs>>>(h->d_st); LAUNCHED(h, "commit_overlapped_kernel");
@@ -1038,7 +1060,7 @@ int32_t fmq_retire(fmq_handle* h) {
     } else {
         commit_kernel<<<1, 32, 0, fs>>>(h->d_st); LAUNCHED(h, "commit_kernel");
         // pre-arm the exchange buffer so that a fire with no preceding local push contributes nothing
-        pack_scalars_kernel<<<1, 32, 0, fs>>>(h->d_st, h->d_xchg); LAUNCHED(h, "pack_scalars_kernel");
+        if (!h->cmb_flags) { pack_scalars_kernel<<<1, 32, 0, fs>>>(h->d_st, h->d_xchg); LAUNCHED(h, "pack_scalars_kernel"); }
     }
     CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][3], fs));
     h->pushes++;
@@ -1061,6 +1083,20 @@ int32_t fmq_combiner_overlap(fmq_handle* h, int32_t enable) {
     return FMQ_OK;
 }
 void* fmq_fire_stream(fmq_handle* h) { return h ? (void*)(h->overlap ? h->fire_stream : h->stream) : nullptr; }
+int32_t fmq_combiner_use_flags(fmq_handle* h, int32_t enable) {
+    if (!h) return FMQ_ERR_BAD_ARG;
+    if (h->sticky) return FMQ_ERR_POISONED;
+    if (enable) {
+        if (h->world < 2) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_combiner_use_flags follows fmq_attach_peers");
+        if (!h->xs_attached || h->xs_world != h->world || h->xs_rank != h->rank)
+            return set_err(h, FMQ_ERR_BAD_ARG, "the control blocks of all ranks must be attached first (fmq_shard_alloc + fmq_shard_attach[_ipc], same rank and world)");
+    }
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaStreamSynchronize(h->stream));
+    if (h->fire_stream) CU(h, cudaStreamSynchronize(h->fire_stream));
+    h->cmb_flags = enable != 0;
+    return FMQ_OK;
+}
 
 // ---- text ingest ------------------------------------------------------------------------------------
 uint64_t fmq_text_key_hash(const char* s, size_t len) {

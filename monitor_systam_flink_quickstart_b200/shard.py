@@ -161,12 +161,16 @@ class CombinerOperator:
     :class:`ShardedOperator`.
     """
 
-    def __init__(self, engine, rank: int, world: int, group=None, overlap=None):
+    def __init__(self, engine, rank: int, world: int, group=None, overlap=None, flags: bool = True):
         """overlap (default: on for tumbling windows): fire / barrier / retire of batch k run on a second
-        stream with a second communicator while batch k+1 is ingested (fmq_combiner_overlap)."""
+        stream while batch k+1 is ingested (fmq_combiner_overlap).
+        flags (default): the 32 bytes of batch scalars and both barriers travel as peer stores behind device flags
+        inside the library (fmq_combiner_use_flags) — no collective is called per batch, `torch.distributed` only
+        hands the IPC blobs around at set-up.  flags=False: the round-1 schedule with two NCCL all-reduces per batch."""
         import torch
         import torch.distributed as dist
         self.dist, self.engine, self.rank, self.world, self.group = dist, engine, rank, world, group
+        self.flags = bool(flags)
         dev = torch.device("cuda", torch.cuda.current_device())
         blobs = [None] * world
         dist.all_gather_object(blobs, engine.ipc_export(), group=group)
@@ -174,6 +178,17 @@ class CombinerOperator:
         engine.attach_peers(rank, world, tables)
         tumbling = engine.cfg.window_size_ms == engine.cfg.window_slide_ms
         self.overlap = tumbling if overlap is None else bool(overlap)
+        if self.flags:
+            cblobs = [None] * world
+            dist.all_gather_object(cblobs, engine.shard_alloc(world, 4), group=group)
+            engine.shard_attach_ipc(rank, world, cblobs)
+            if self.overlap:
+                engine.combiner_overlap(True)
+            engine.combiner_use_flags(True)
+            self._empty = (np.zeros(0, np.int64), np.zeros(0, np.uint64), np.zeros(0, np.float64 if engine.cfg.value_type == capi.FMQ_VAL_F64 else np.int64))
+            self._ext = self._ext2 = None
+            dist.barrier(group=group)                        # every rank has mapped every table and control block
+            return
         self._ext = torch.cuda.ExternalStream(engine.stream, device=dev)
         self._ext2, self.group2 = self._ext, group
         if self.overlap:
@@ -187,6 +202,10 @@ class CombinerOperator:
         dist.barrier(group=group)
 
     def _fire(self, watermark_after):
+        if self.flags:                                       # kernels only: the device-side flags order the ranks
+            self.engine.fire_global(watermark_after)
+            self.engine.retire()
+            return
         import torch
         dist = self.dist
         with torch.cuda.stream(self._ext):
@@ -199,13 +218,17 @@ class CombinerOperator:
     def process_batch(self, ts, key, val, watermark_after: int = capi.FMQ_WM_AUTO, ts_base: int = 0):
         """One micro-batch: everything below is queued on the engine's streams, no host round trip
         (host columns: the call returns once they are copied in)."""
+        if self.flags:
+            self.engine.push_local(ts, key, val, ts_base)
+            self._fire(watermark_after)
+            return
         import torch
         with torch.cuda.stream(self._ext):
             self.engine.push_local(ts, key, val, ts_base)
         self._fire(watermark_after)
 
     def flush(self, wm: int = capi.FMQ_WM_FINAL):
-        if self.overlap:                      # the exchange buffer is not pre-armed by retire in this mode
+        if self.overlap or self.flags:        # the exchange is not pre-armed by retire in these modes
             self.engine.push_local(*self._empty)
         self._fire(wm)
 
@@ -213,9 +236,12 @@ class CombinerOperator:
         """Order the engine's main stream after everything queued on the fire stream (timing, hand-over)."""
         if self.overlap:
             import torch
+            dev = torch.device("cuda", torch.cuda.current_device())
+            e1 = torch.cuda.ExternalStream(self.engine.stream, device=dev)
+            e2 = torch.cuda.ExternalStream(self.engine.fire_stream, device=dev)
             ev = torch.cuda.Event()
-            ev.record(self._ext2)
-            self._ext.wait_event(ev)
+            ev.record(e2)
+            e1.wait_event(ev)
 
 
 class PeerPullOperator:

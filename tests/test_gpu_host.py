@@ -115,9 +115,12 @@ CKW = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms
 @pytest.mark.parametrize("world", [2, 3])
 @pytest.mark.parametrize("vt", ["f64", "i64"])
 @pytest.mark.parametrize("overlap", [0, 1])
-def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt, overlap):
+@pytest.mark.parametrize("flags", [0, 1])
+def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt, overlap, flags):
     """`world` engines in ONE process on one GPU play the ranks (their tables are attached to each other
-    as plain device pointers); the two collectives are done by hand between synchronised streams.
+    as plain device pointers).  flags=0: the two collectives are done by hand between synchronised streams (what a
+    caller with its own collective library does); flags=1: the library exchanges the batch scalars and both
+    barriers itself through device flags in the peers' control blocks, nothing is synchronised by the host.
     Union of the ranks' outputs == oracle over the whole stream."""
     import torch
     from monitor_systam_flink_quickstart_b200.shard import exchange_tensor
@@ -135,6 +138,12 @@ def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt, overlap):
         e.attach_peers(r, world, [x.table_ptr for x in engs])
         if overlap:
             e.combiner_overlap(True)
+    if flags:
+        for e in engs:
+            e.shard_alloc(world, 4)
+        for r, e in enumerate(engs):
+            e.shard_attach(r, world, [x.shard_base for x in engs])
+            e.combiner_use_flags(True)
     xs = [exchange_tensor(e, "cuda:0") for e in engs]
     ref = OracleEngine(**{k: v for k, v in kw.items()})
     nb, b = 6, 7001
@@ -148,6 +157,12 @@ def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt, overlap):
         torch.cuda.synchronize()
 
     def fire(wm):
+        if flags:                                 # every rank's step is queued before the next step of any rank: no spin waits on unsubmitted work
+            for e in engs:
+                e.fire_global(wm)
+            for e in engs:
+                e.retire()
+            return
         collective_max()
         for e in engs:
             e.fire_global(wm)
@@ -171,10 +186,11 @@ def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt, overlap):
                 e.push_local((ts_n - base).astype(np.uint32), key_n.astype(np.uint32), val_n, base)
             else:                                                 # host columns as they are
                 e.push_local(*parts[-1])
-            e.synchronize()
+            if not flags:
+                e.synchronize()
         fire(capi.FMQ_WM_AUTO)
         ref.push_batch(*[np.concatenate([p[j] for p in parts]) for j in range(3)])
-    if overlap:                                   # this mode does not pre-arm the exchange buffer in retire
+    if overlap or flags:                          # these modes do not pre-arm the exchange in retire: a flush starts with an empty local push
         for e in engs:
             e.push_local(np.zeros(0, np.int64), np.zeros(0, np.uint64), np.zeros(0, np.float64 if vt == "f64" else np.int64))
     fire(capi.FMQ_WM_FINAL)
@@ -196,7 +212,7 @@ def test_combiner_mode_emulated_ranks_on_one_gpu(world, vt, overlap):
         assert len(x["fired"]) > 0 and x["fired"].key.min() >= per * r and x["fired"].key.max() < per * (r + 1)
 
 
-def _combiner_worker(rank, world, port, outdir, tumbling=False):
+def _combiner_worker(rank, world, port, outdir, tumbling=False, flags=True):
     import torch
     import torch.distributed as dist
     from monitor_systam_flink_quickstart_b200.shard import CombinerOperator
@@ -207,7 +223,7 @@ def _combiner_worker(rank, world, port, outdir, tumbling=False):
     spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
     kw = dict(CKW, window_slide_ms=CKW["window_size_ms"]) if tumbling else CKW
     eng = capi.Engine(device=rank, **kw)
-    op = CombinerOperator(eng, rank, world)
+    op = CombinerOperator(eng, rank, world, flags=flags)
     assert op.overlap == tumbling
     cols = [generate_torch(spec, (b * world + rank) * B, B, device=f"cuda:{rank}") for b in range(NBC)]
     torch.cuda.synchronize()
@@ -222,15 +238,16 @@ def _combiner_worker(rank, world, port, outdir, tumbling=False):
 
 
 @pytest.mark.parametrize("tumbling", [False, True])       # True: fire / retire overlapped with the next batch's ingest
-def test_two_gpu_combiner_over_nvlink_equals_oracle(tumbling):
+@pytest.mark.parametrize("world,flags", [(2, False), (2, True), (4, True), (8, True)])   # flags: device flags instead of NCCL all-reduces
+def test_two_gpu_combiner_over_nvlink_equals_oracle(tumbling, world, flags):
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
     from monitor_systam_flink_quickstart_b200.stream import StreamSpec, generate_numpy
-    world, port = 2, 29700 + os.getpid() % 2000
+    port = 29700 + os.getpid() % 2000 + 7 * world + int(flags) + 2 * int(tumbling)
     with tempfile.TemporaryDirectory() as d:
-        mp.spawn(_combiner_worker, args=(world, port, d, tumbling), nprocs=world, join=True)
+        mp.spawn(_combiner_worker, args=(world, port, d, tumbling, flags), nprocs=world, join=True)
         res = [pickle.load(open(os.path.join(d, f"r{r}.pkl"), "rb")) for r in range(world)]
     spec = StreamSpec(n_keys=900, events_per_ms=4, jitter_ms=3000, late_frac_ppm=30000, late_extra_ms=20000)
     ref = OracleEngine(**dict(CKW, window_slide_ms=CKW["window_size_ms"] if tumbling else CKW["window_slide_ms"]))

@@ -9,8 +9,8 @@ B="--steps 20 --warmup 3"
 timeout -s KILL 600 python bench.py $B > gpurun_out/a_bench_n1.json 2> gpurun_out/a_bench_n1.err; echo "bench rc=$?"
 Q="$B --no-e2e --no-cpu-baseline --no-variants"
 FMQ_INGEST_LEGACY=1 timeout -s KILL 300 python bench.py $Q > gpurun_out/a_bench_legacy.json 2>&1
-for v in w4s4b3 w8s2b3 w4s2b6; do
-  FMQ_LIB_PATH=$PWD/build/variants/libfmq_$v.so timeout -s KILL 300 python bench.py $Q > gpurun_out/a_bench_$v.json 2>&1
+for v in w4s2b5 w8s2b3 w4s2b6; do
+  FMQ_LIB_PATH=$PWD/build/variants/libfmq_$v.so FMQ_SKIP_BUILD=1 timeout -s KILL 300 python bench.py $Q > gpurun_out/a_bench_$v.json 2>&1
 done
 timeout -s KILL 300 python bench.py $Q --key-mode hashed > gpurun_out/a_bench_hashed.json 2>&1
 python - <<'PY'
