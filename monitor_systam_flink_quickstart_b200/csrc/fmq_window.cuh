@@ -355,15 +355,15 @@ __device__ __forceinline__ u32 pane_quotient(u32 du, const IngestConst& k) {
 // The window part of one tile (A1 max-ts, A3 late test, A2 pane, A5 accumulate) for the four events held by
 // this lane.  Must be reached by all 32 lanes of the warp.  Returns which of the four were late / accumulated,
 // their pane quotient and slot (for the side outputs the callers append in their own way).
-template <typename V, bool DENSE>
+template <typename V, bool DENSE, int EPT>
 __device__ __forceinline__ void ingest_core(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
-                                            const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 ok_mask,
-                                            HotTable* hot, bool sample, u32& late_mask, u32& vmask, u32 (&q_)[INGEST_EPT], u32 (&slot_)[INGEST_EPT]) {
+                                            const i64 (&ts_)[EPT], const u64 (&key_)[EPT], const u64 (&vb_)[EPT], u32 ok_mask,
+                                            HotTable* hot, bool sample, u32& late_mask, u32& vmask, u32 (&q_)[EPT], u32 (&slot_)[EPT]) {
     // ---- per event: A1 max-ts, A3 late test, A2 pane, and (hashed keys) the home-bucket load:
     //      all four directory loads are in flight before any of them is consumed ----
-    u32 ring_[INGEST_EPT]; u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0; late_mask = 0;
+    u32 ring_[EPT]; u64 hb_[EPT]; ulonglong4 kv_[EPT]; u32 act_mask = 0; late_mask = 0;
 #pragma unroll
-    for (int e = 0; e < INGEST_EPT; ++e) {
+    for (int e = 0; e < EPT; ++e) {
         const bool ok = ok_mask & (1u << e);
         const i64 d = ts_[e] - k.origin_ts;
         r.dmax = (ok && d > r.dmax) ? d : r.dmax;                  // A1 (ts = origin + d)
@@ -392,7 +392,7 @@ __device__ __forceinline__ void ingest_core(const IngestArgs& a, DevState* st, c
     // ---- A5: slot -> pair-lane accumulate ----
     vmask = 0;
 #pragma unroll
-    for (int e = 0; e < INGEST_EPT; ++e) {
+    for (int e = 0; e < EPT; ++e) {
         bool valid = act_mask & (1u << e);
         u32 slot = (u32)key_[e];                                   // dense ids index the table directly
         if (!DENSE) {
@@ -412,45 +412,53 @@ __device__ __forceinline__ void ingest_core(const IngestArgs& a, DevState* st, c
 // This form does the same work in 32-bit arithmetic wherever the geometry allows it: one unsigned compare is the
 // late AND the ring test, the pane quotient is one multiply, a cell is a 32-bit index (tables < 2^31 cells), the
 // pair-lane exchange moves three words, and the order-preserving max / min encoding is three logic operations.
-// One half (this lane's 8 bytes of the add pair and of the max pair) of the update of cell c, both REDs predicated
-// rather than branched around: c == 0xFFFFFFFF = nothing to add.
 template <typename V>
 __device__ __forceinline__ void red_half(char* acc_half, u32 c, u32 lo, u32 hi, bool odd, u32 oddmask, bool want, u64 policy) {
-    const u32 ok = c != 0xFFFFFFFFu, okm = ok && want;
+    if (c == 0xFFFFFFFFu) return;
     char* p = acc_half + (u64)c * 32u;
-    u32 uh, ul;
     if constexpr (IsF64<V>::value) {
-        const u32 m = (u32)((int)hi >> 31);                           // all ones for negative values
-        uh = hi ^ (m | 0x80000000u) ^ oddmask; ul = lo ^ m ^ oddmask;   // order_f64, complemented on the min lanes
-        const double v = __hiloint2double((int)hi, (int)lo);
-        if (v != v) { uh = 0xFFFFFFFFu; ul = 0xFFFFFFFFu; }          // NaN wins both max and min (Math.max / Math.min)
-        const double addv = odd ? v : 1.0;
-        asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %0, 0;\n\tsetp.ne.u32 q, %1, 0;\n\t"
-                     "@p red.global.add.L2::cache_hint.f64 [%2], %3, %5;\n\t"
-                     "@q red.global.max.L2::cache_hint.u64 [%2+16], %4, %5;\n\t}"
-                     :: "r"(ok), "r"(okm), "l"(p), "d"(addv), "l"(((u64)uh << 32) | ul), "l"(policy) : "memory");
+        const double addv = odd ? __hiloint2double((int)hi, (int)lo) : 1.0;
+        asm volatile("red.global.add.L2::cache_hint.f64 [%0], %1, %2;" :: "l"(p), "d"(addv), "l"(policy) : "memory");
     } else {
-        uh = hi ^ 0x80000000u ^ oddmask; ul = lo ^ oddmask;
         const u64 addv = odd ? (((u64)hi << 32) | lo) : 1ull;
-        asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %0, 0;\n\tsetp.ne.u32 q, %1, 0;\n\t"
-                     "@p red.global.add.L2::cache_hint.u64 [%2], %3, %5;\n\t"
-                     "@q red.global.max.L2::cache_hint.u64 [%2+16], %4, %5;\n\t}"
-                     :: "r"(ok), "r"(okm), "l"(p), "l"(addv), "l"(((u64)uh << 32) | ul), "l"(policy) : "memory");
+        asm volatile("red.global.add.L2::cache_hint.u64 [%0], %1, %2;" :: "l"(p), "l"(addv), "l"(policy) : "memory");
+    }
+    if (want) {
+        u32 uh, ul;
+        if constexpr (IsF64<V>::value) {
+            const u32 m = (u32)((int)hi >> 31);                       // all ones for negative values
+            uh = hi ^ (m | 0x80000000u) ^ oddmask; ul = lo ^ m ^ oddmask;   // order_f64, complemented on the min lanes
+            const double v = __hiloint2double((int)hi, (int)lo);
+            if (v != v) { uh = 0xFFFFFFFFu; ul = 0xFFFFFFFFu; }      // NaN wins both max and min (Math.max / Math.min)
+        } else {
+            uh = hi ^ 0x80000000u ^ oddmask; ul = lo ^ oddmask;
+        }
+        const u64 x = ((u64)uh << 32) | ul;
+        asm volatile("red.global.max.L2::cache_hint.u64 [%0], %1, %2;" :: "l"(p + 16), "l"(x), "l"(policy) : "memory");
     }
 }
+// A5 for one event per lane: cw = cell index or 0xFFFFFFFF (nothing to add).  Must be reached by all 32 lanes.
+template <typename V>
+__device__ __forceinline__ void accumulate_lean32(char* acc_half, u32 cw, u64 vb, bool odd, u32 oddmask, bool want, u64 policy) {
+    const u32 lo = (u32)vb, hi = (u32)(vb >> 32);
+    const u32 cw_p = __shfl_xor_sync(0xffffffffu, cw, 1), lo_p = __shfl_xor_sync(0xffffffffu, lo, 1), hi_p = __shfl_xor_sync(0xffffffffu, hi, 1);
+    // first the even lane's event (both halves in one instruction = one sector request), then the odd lane's
+    red_half<V>(acc_half, odd ? cw_p : cw, odd ? lo_p : lo, odd ? hi_p : hi, odd, oddmask, want, policy);
+    red_half<V>(acc_half, odd ? cw : cw_p, odd ? lo : lo_p, odd ? hi : hi_p, odd, oddmask, want, policy);
+}
 
-template <typename V, bool DENSE>
+template <typename V, bool DENSE, int EPT>
 __device__ __forceinline__ void ingest_core_lean(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
-                                                 const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 in_mask,
-                                                 u32& late_mask, u32& vmask, u32 (&q_)[INGEST_EPT], u32 (&slot_)[INGEST_EPT]) {
+                                                 const i64 (&ts_)[EPT], const u64 (&key_)[EPT], const u64 (&vb_)[EPT], u32 in_mask,
+                                                 u32& late_mask, u32& vmask, u32 (&q_)[EPT], u32 (&slot_)[EPT]) {
     const bool odd = threadIdx.x & 1;
     const u32 oddmask = odd ? 0xFFFFFFFFu : 0u;
     const bool want = odd ? (a.g.agg_mask & 4u) != 0 : (a.g.agg_mask & 8u) != 0;
     char* acc_half = reinterpret_cast<char*>(a.acc) + (odd ? 8 : 0);
-    u64 hb_[INGEST_EPT]; ulonglong4 kv_[INGEST_EPT]; u32 act_mask = 0, cw_[INGEST_EPT];
+    u64 hb_[EPT]; ulonglong4 kv_[EPT]; u32 act_mask = 0;
     late_mask = 0; vmask = 0;
 #pragma unroll
-    for (int e = 0; e < INGEST_EPT; ++e) {
+    for (int e = 0; e < EPT; ++e) {
         const bool in = (in_mask >> e) & 1u;
         const i64 d = ts_[e] - k.origin_ts;
         const bool inr = (u64)d < k.span;                          // A3 + ring test: late (negative) and beyond-the-ring offsets both fail
@@ -468,7 +476,7 @@ __device__ __forceinline__ void ingest_core_lean(const IngestArgs& a, DevState* 
         act_mask |= act ? (1u << e) : 0u;
     }
 #pragma unroll
-    for (int e = 0; e < INGEST_EPT; ++e) {
+    for (int e = 0; e < EPT; ++e) {
         bool valid = (act_mask >> e) & 1u;
         u32 slot = (u32)key_[e];
         if (!DENSE) {
@@ -477,22 +485,7 @@ __device__ __forceinline__ void ingest_core_lean(const IngestArgs& a, DevState* 
         }
         const u32 cell = ((k.origin_ring + q_[e]) & a.g.ring_mask) * k.cap32 + slot;
         slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
-        cw_[e] = valid ? cell : 0xFFFFFFFFu;
-    }
-    // A5, pair-lane: the partner's cell and value (three words per event), all twelve exchanges issued before the
-    // first is consumed; then per event first the even lane's update (both halves in ONE instruction = one sector
-    // request at the L2), then the odd lane's
-    u32 cwp_[INGEST_EPT], lop_[INGEST_EPT], hip_[INGEST_EPT];
-#pragma unroll
-    for (int e = 0; e < INGEST_EPT; ++e) {
-        cwp_[e] = __shfl_xor_sync(0xffffffffu, cw_[e], 1);
-        lop_[e] = __shfl_xor_sync(0xffffffffu, (u32)vb_[e], 1); hip_[e] = __shfl_xor_sync(0xffffffffu, (u32)(vb_[e] >> 32), 1);
-    }
-#pragma unroll
-    for (int e = 0; e < INGEST_EPT; ++e) {
-        const u32 lo = (u32)vb_[e], hi = (u32)(vb_[e] >> 32);
-        red_half<V>(acc_half, odd ? cwp_[e] : cw_[e], odd ? lop_[e] : lo, odd ? hip_[e] : hi, odd, oddmask, want, k.keep_policy);
-        red_half<V>(acc_half, odd ? cw_[e] : cwp_[e], odd ? lo : lop_[e], odd ? hi : hip_[e], odd, oddmask, want, k.keep_policy);
+        accumulate_lean32<V>(acc_half, valid ? cell : 0xFFFFFFFFu, vb_[e], odd, oddmask, want, k.keep_policy);
     }
 }
 
@@ -509,7 +502,7 @@ __device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, c
     if (a.efilter_enabled && do_filter) r.nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
     if (!a.window_enabled) return;
     u32 late_mask, vmask, q_[INGEST_EPT], slot_[INGEST_EPT];
-    ingest_core<V, DENSE>(a, st, k, r, ts_, key_, vb_, ok_mask, hot, threadIdx.x < 32, late_mask, vmask, q_, slot_);
+    ingest_core<V, DENSE, INGEST_EPT>(a, st, k, r, ts_, key_, vb_, ok_mask, hot, threadIdx.x < 32, late_mask, vmask, q_, slot_);
     // ---- late side output (chapter3/README.md:213-228, option 3: "a separate stream of the late data") ----
     if (EXTRAS && a.lt_cap) {
         u64 row = block_append<INGEST_THREADS>(__popc(late_mask), &st->n_late, a.lt_cap, st);
@@ -674,11 +667,18 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
 #ifndef FMQ_IW_BLOCKS
 #define FMQ_IW_BLOCKS 4
 #endif
+#ifndef FMQ_IW_EPT
+#define FMQ_IW_EPT 4
+#endif
+#ifndef FMQ_IW_ROWS
+#define FMQ_IW_ROWS 128
+#endif
 constexpr int IW_WARPS = FMQ_IW_WARPS, IW_STAGES = FMQ_IW_STAGES, IW_THREADS = IW_WARPS * 32;
-constexpr int IW_TILE = 32 * INGEST_EPT;                    // 128 events per warp tile
-constexpr int IW_STAGE_BYTES = 3 * IW_TILE * 8;             // 3 KB
-constexpr int IW_ROWS = 128;                                // rows a warp stages before it reserves output space
-constexpr int IW_ROWBUF_BYTES = 3 * IW_ROWS * 8;            // 3 KB
+constexpr int IW_EPT = FMQ_IW_EPT;                          // events per lane per tile
+constexpr int IW_TILE = 32 * IW_EPT;                        // events per warp tile
+constexpr int IW_STAGE_BYTES = 3 * IW_TILE * 8;
+constexpr int IW_ROWS = FMQ_IW_ROWS;                        // rows a warp stages before it reserves output space (>= 64)
+constexpr int IW_ROWBUF_BYTES = 3 * IW_ROWS * 8;
 __host__ __device__ constexpr int iw_warp_bytes(bool extras) { return IW_STAGES * IW_STAGE_BYTES + (extras ? 3 : 1) * IW_ROWBUF_BYTES; }
 __host__ __device__ constexpr int iw_smem_bytes(bool extras) { return IW_WARPS * iw_warp_bytes(extras); }
 
@@ -686,46 +686,26 @@ __device__ __forceinline__ void mbar_arrive(u64* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-// Rows (3 x 8 B) staged by one warp in a ring of IW_ROWS, written out behind ONE reservation per ~half ring.  The
-// reservation (a same-address atomic with a return value: microseconds under load) is issued one drain AHEAD of the
-// copy-out that needs it: ncu of the version that reserved and copied in one go had 13 % of all warp samples sitting
-// on that return value.  head / tail count rows pushed / written out (warp-uniform); rows [tail, tail + res_n) are
-// the ones the reservation in flight covers, res_base (lane 0) is where they go.
-struct WarpRows { u64* buf; u32 head, tail, res_n; u64 res_base; };
-__device__ __forceinline__ void wr_init(WarpRows& w, u64* buf) { w.buf = buf; w.head = 0; w.tail = 0; w.res_n = 0; w.res_base = 0; }
+// rows (3 x 8 B) staged by one warp; n is warp-uniform
+struct WarpRows { u64* buf; u32 n; };
 __device__ __forceinline__ void wr_push(WarpRows& w, bool pred, u64 c0, u64 c1, u64 c2) {      // all 32 lanes; needs room for 32 rows
     const u32 lane = threadIdx.x & 31;
     const unsigned m = __ballot_sync(0xffffffffu, pred);
-    if (pred) { const u32 i = (w.head + __popc(m & ((1u << lane) - 1))) & (IW_ROWS - 1); w.buf[i] = c0; w.buf[IW_ROWS + i] = c1; w.buf[2 * IW_ROWS + i] = c2; }
-    w.head += __popc(m);
+    if (pred) { const u32 i = w.n + __popc(m & ((1u << lane) - 1)); w.buf[i] = c0; w.buf[IW_ROWS + i] = c1; w.buf[2 * IW_ROWS + i] = c2; }
+    w.n += __popc(m);
 }
-// writes out the rows of the reservation in flight (if any), then reserves space for everything staged since
 template <typename T0, typename T1>
-__device__ __forceinline__ void wr_drain(WarpRows& w, u64* counter, u64 cap, T0* d0, T1* d1, u64* d2, u32& err) {   // all 32 lanes
+__device__ __forceinline__ void wr_flush(WarpRows& w, u64* counter, u64 cap, T0* d0, T1* d1, u64* d2, u32& err) {   // all 32 lanes
+    if (w.n == 0) return;
     const u32 lane = threadIdx.x & 31;
     __syncwarp();
-    if (w.res_n) {
-        const u64 base = __shfl_sync(0xffffffffu, w.res_base, 0);
-        if (base + w.res_n > cap) err |= ERRB_OUTPUT;
-        else for (u32 i = lane; i < w.res_n; i += 32) {
-            const u32 j = (w.tail + i) & (IW_ROWS - 1);
-            d0[base + i] = (T0)w.buf[j]; d1[base + i] = (T1)w.buf[IW_ROWS + j]; d2[base + i] = w.buf[2 * IW_ROWS + j];
-        }
-        w.tail += w.res_n;
-        __syncwarp();
-    }
-    w.res_n = w.head - w.tail;
-    if (w.res_n && lane == 0) w.res_base = atomicAdd(counter, (u64)w.res_n);      // consumed by the NEXT drain
-}
-// room for another 32 rows?  Normally one drain makes it (the reservation in flight covers about half the ring).
-template <typename T0, typename T1>
-__device__ __forceinline__ void wr_make_room(WarpRows& w, u64* counter, u64 cap, T0* d0, T1* d1, u64* d2, u32& err) {
-    if (w.res_n == 0 && w.head - w.tail >= IW_ROWS / 3) wr_drain(w, counter, cap, d0, d1, d2, err);   // first reservation, early
-    while (w.head - w.tail + 32 > IW_ROWS) wr_drain(w, counter, cap, d0, d1, d2, err);
-}
-template <typename T0, typename T1>
-__device__ __forceinline__ void wr_finish(WarpRows& w, u64* counter, u64 cap, T0* d0, T1* d1, u64* d2, u32& err) {
-    while (w.head != w.tail) wr_drain(w, counter, cap, d0, d1, d2, err);
+    u64 base = 0;
+    if (lane == 0) base = atomicAdd(counter, (u64)w.n);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base + w.n > cap) err |= ERRB_OUTPUT;
+    else for (u32 i = lane; i < w.n; i += 32) { d0[base + i] = (T0)w.buf[i]; d1[base + i] = (T1)w.buf[IW_ROWS + i]; d2[base + i] = w.buf[2 * IW_ROWS + i]; }
+    __syncwarp();
+    w.n = 0;
 }
 
 // COMBINE: warp-level pre-aggregation of lanes that hit the same cell (skewed keys).  The host picks the variant
@@ -766,10 +746,9 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
     const u64 ntiles = seg.tile_end[FMQ_MAX_PEERS - 1];
     const u64 gw = (u64)blockIdx.x * IW_WARPS + wl, nw = (u64)gridDim.x * IW_WARPS;
     unsigned char* wbase = iw_smem + (size_t)wl * iw_warp_bytes(EXTRAS);
-    WarpRows ea, lt, ml;
-    wr_init(ea, reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES));
-    wr_init(lt, reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES + IW_ROWBUF_BYTES));
-    wr_init(ml, reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES + 2 * IW_ROWBUF_BYTES));
+    WarpRows ea{reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES), 0};
+    WarpRows lt{reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES + IW_ROWBUF_BYTES), 0};
+    WarpRows ml{reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES + 2 * IW_ROWBUF_BYTES), 0};
     const u64* cts = reinterpret_cast<const u64*>(a.ts); const u64* cval = static_cast<const u64*>(a.val);
     u64 policy;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
@@ -790,20 +769,21 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
     // per-event filter A6-i (Main.java:31) as one comparison: LT / LE compare the negated operands
     const bool f_flip = a.efilter_op == 1 || a.efilter_op == 3, f_strict = a.efilter_op < 2;
     const double f_thr = f_flip ? -a.efilter_thr : a.efilter_thr;
+    u32 nea_w = 0;                                               // rows this warp produced (uniform)
     int s = 0; u32 phase = 0;
     for (u64 t = gw; t < ntiles; t += nw) {
         mbar_wait(&bars[wl][s], phase);
         u32 cnt; const size_t off = seg_locate<IW_TILE>(a, seg, t, cnt);
         // lane x takes events x, x+32, x+64, x+96 of the tile: conflict-free 8-byte shared loads
-        i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; u32 in_mask = 0xFu;
+        i64 ts_[IW_EPT]; u64 key_[IW_EPT]; u64 vb_[IW_EPT]; u32 in_mask = (1u << IW_EPT) - 1u;
         if (a.vec32 && cnt == IW_TILE) {
             const u64 *sts = stage_col(s, 0), *skey = stage_col(s, 1), *sval = stage_col(s, 2);
 #pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e) { ts_[e] = (i64)sts[lane + 32 * e]; key_[e] = skey[lane + 32 * e]; vb_[e] = sval[lane + 32 * e]; }
+            for (int e = 0; e < IW_EPT; ++e) { ts_[e] = (i64)sts[lane + 32 * e]; key_[e] = skey[lane + 32 * e]; vb_[e] = sval[lane + 32 * e]; }
         } else {
             in_mask = 0;
 #pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e) {
+            for (int e = 0; e < IW_EPT; ++e) {
                 const u32 i = lane + 32 * e; const bool in = i < cnt;
                 in_mask |= in ? (1u << e) : 0u;
                 ts_[e] = in ? (i64)ldg_stream(cts + off + i) : 0; key_[e] = in ? ldg_stream(a.key + off + i) : 0; vb_[e] = in ? ldg_stream(cval + off + i) : 0;
@@ -819,22 +799,24 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
         if (++s == IW_STAGES) { s = 0; phase ^= 1u; }
         if (a.efilter_enabled) {
 #pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e) {
+            for (int e = 0; e < IW_EPT; ++e) {
                 V v; memcpy(&v, &vb_[e], 8);
                 const double x = f_flip ? -(double)v : (double)v;
                 const bool hit = ((in_mask >> e) & 1u) && ts_[e] >= 0 && key_[e] != KEY_EMPTY && (f_strict ? x > f_thr : x >= f_thr);
-                wr_make_room(ea, &st->n_ealert, a.ea_cap, a.ea_ts, a.ea_key, a.ea_val, r.err);
+                if (ea.n + 32 > IW_ROWS) wr_flush(ea, &st->n_ealert, a.ea_cap, a.ea_ts, a.ea_key, a.ea_val, r.err);
+                const u32 before = ea.n;
                 wr_push(ea, hit, (u64)ts_[e], key_[e], vb_[e]);
+                nea_w += ea.n - before;
             }
         }
         if (!a.window_enabled) {                                 // filter-only job: input validity is still checked
 #pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e) if (((in_mask >> e) & 1u) && (ts_[e] < 0 || key_[e] == KEY_EMPTY)) r.err |= ERRB_BAD_INPUT;
+            for (int e = 0; e < IW_EPT; ++e) if (((in_mask >> e) & 1u) && (ts_[e] < 0 || key_[e] == KEY_EMPTY)) r.err |= ERRB_BAD_INPUT;
             continue;
         }
-        u32 late_mask, vmask, q_[INGEST_EPT], slot_[INGEST_EPT];
+        u32 late_mask, vmask, q_[IW_EPT], slot_[IW_EPT];
         if constexpr (!COMBINE) {
-            ingest_core_lean<V, DENSE>(a, st, k, r, ts_, key_, vb_, in_mask, late_mask, vmask, q_, slot_);
+            ingest_core_lean<V, DENSE, IW_EPT>(a, st, k, r, ts_, key_, vb_, in_mask, late_mask, vmask, q_, slot_);
             if (wl == 0 && (((t - gw) / nw) & 3u) == 0) {        // skew sample (one warp per block, every 4th tile): lanes sharing their cell with another lane
                 const bool v0 = vmask & 1u;
                 const u64 c0 = ((u64)((k.origin_ring + q_[0]) & a.g.ring_mask) << 32) | slot_[0];
@@ -844,32 +826,32 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
         } else {
             u32 ok_mask = 0;
 #pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
+            for (int e = 0; e < IW_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
             if ((ok_mask & in_mask) != in_mask) r.err |= ERRB_BAD_INPUT;
             ok_mask &= in_mask;
-            ingest_core<V, DENSE>(a, st, k, r, ts_, key_, vb_, ok_mask, &hot_tab, wl == 0, late_mask, vmask, q_, slot_);
+            ingest_core<V, DENSE, IW_EPT>(a, st, k, r, ts_, key_, vb_, ok_mask, &hot_tab, wl == 0, late_mask, vmask, q_, slot_);
         }
         if (EXTRAS && a.lt_cap) {                                // late side output (chapter3/README.md:213-228, option 3)
 #pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e) {
-                wr_make_room(lt, &st->n_late, a.lt_cap, a.lt_ts, a.lt_key, a.lt_val, r.err);
+            for (int e = 0; e < IW_EPT; ++e) {
+                if (lt.n + 32 > IW_ROWS) wr_flush(lt, &st->n_late, a.lt_cap, a.lt_ts, a.lt_key, a.lt_val, r.err);
                 wr_push(lt, (late_mask >> e) & 1u, (u64)ts_[e], key_[e], vb_[e]);
             }
         }
         if (EXTRAS && a.mlog_enabled) {                          // N3: every accepted value is logged (ComputeCpuMiddle.java:36-38)
 #pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e) {
-                wr_make_room(ml, &st->n_mlog, a.ml_cap, a.ml_pane, a.ml_slot, a.ml_val, r.err);
+            for (int e = 0; e < IW_EPT; ++e) {
+                if (ml.n + 32 > IW_ROWS) wr_flush(ml, &st->n_mlog, a.ml_cap, a.ml_pane, a.ml_slot, a.ml_val, r.err);
                 wr_push(ml, (vmask >> e) & 1u, (u64)(k.origin_pane + (i64)q_[e]), (u64)slot_[e], vb_[e]);
             }
         }
     }
-    if (a.efilter_enabled) wr_finish(ea, &st->n_ealert, a.ea_cap, a.ea_ts, a.ea_key, a.ea_val, r.err);
-    if (EXTRAS && a.lt_cap) wr_finish(lt, &st->n_late, a.lt_cap, a.lt_ts, a.lt_key, a.lt_val, r.err);
-    if (EXTRAS && a.mlog_enabled) wr_finish(ml, &st->n_mlog, a.ml_cap, a.ml_pane, a.ml_slot, a.ml_val, r.err);
+    if (a.efilter_enabled) wr_flush(ea, &st->n_ealert, a.ea_cap, a.ea_ts, a.ea_key, a.ea_val, r.err);
+    if (EXTRAS && a.lt_cap) wr_flush(lt, &st->n_late, a.lt_cap, a.lt_ts, a.lt_key, a.lt_val, r.err);
+    if (EXTRAS && a.mlog_enabled) wr_flush(ml, &st->n_mlog, a.ml_cap, a.ml_pane, a.ml_slot, a.ml_val, r.err);
     if (COMBINE && a.window_enabled) { __syncthreads(); hot_flush<V>(&hot_tab, a.acc, a.g.agg_mask); }
     // ---- per-warp reduction of the batch scalars, one atomic each per warp ----
-    r.nea = ea.head;                                             // rows this warp produced (uniform: lane 0 reports it)
+    r.nea = nea_w;                                               // uniform: lane 0 reports it
     for (int o = 16; o > 0; o >>= 1) r.err |= __shfl_xor_sync(0xffffffffu, r.err, o);
     if (a.window_enabled) {
         // lean core: the extreme offsets become the extreme panes and the largest timestamp here, once per lane

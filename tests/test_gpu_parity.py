@@ -156,7 +156,8 @@ def test_window_parity_skewed_keys_switch_on_warp_combining(vt):
     """Zipf(1.2) keys: after the first batch the engine pre-aggregates same-cell lanes inside a warp
     (skew adaptation).  Counts, integer sums, min/max stay bit-exact; double sums within 1e-9."""
     kw = dict(value_type=capi.FMQ_VAL_F64 if vt == "f64" else capi.FMQ_VAL_I64, window_enabled=1, agg_mask=15, window_size_ms=10_000,
-XX, jitter_ms=3000, late_frac_ppm=5000, late_extra_ms=20_000, value_type=vt)
+              window_slide_ms=5000, max_out_of_orderness_ms=3000, table_capacity=1 << 19, pane_ring=64, max_batch=1 << 19, fired_capacity=1 << 22)
+    spec = StreamSpec(n_keys=1_000_000, events_per_ms=50, key_kind="zipf", jitter_ms=3000, late_frac_ppm=5000, late_extra_ms=20_000, value_type=vt)
     gpu, cpu = pair(**kw)
     for b in range(4):
         ts, key, val = generate_numpy(spec, b * 300_000, 300_000)
