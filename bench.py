@@ -432,6 +432,21 @@ def main():
             "value": world * B * K4 / (ms4 * 1e-3), "unit": "events/s", "ms_per_step": ms4 / K4, "steps": K4,
             "nvlink_GBps_per_gpu_each_direction": nv_bytes / (ms4 / K4 * 1e-3) / 1e9, "nvlink_frac_of_900": nv_bytes / (ms4 / K4 * 1e-3) / 1e9 / 900.0}
 
+        # (c) BASELINE.json configs[4]: Zipf(1.2) over 10^8 ids (one id carries 18 % of the stream, so does its owner rank),
+        #     tumbling windows plus the consecutive-readings rule (order-dependent keyed state: stable exchange), hashed keys
+        spec5 = StreamSpec(n_keys=100_000_000, events_per_ms=1000 * world, jitter_ms=3000, late_frac_ppm=500, late_extra_ms=20_000, key_kind="zipf")
+        kw5 = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=10_000, max_out_of_orderness_ms=3000,
+                   consec_n=3, consec_threshold=50.0, consec_reset_on_fire=1, table_capacity=6_000_000, pane_ring=16, max_batch=3 * B, device=local_rank,
+                   fired_capacity=16_000_000, calert_capacity=3 * B // 4)
+        batches5 = [tuple(t.contiguous() for t in generate_torch(spec5, (s_ * world + rank) * B, B, device=f"cuda:{local_rank}")) for s_ in range(W + K4)]
+        torch.cuda.synchronize()
+        ms5, ing5, fire5, d5, _ = measure(kw5, False, multi="exchange", batches=batches5, K=K4)
+        ms5 = job_max(ms5)
+        del batches5
+        variants["workload=configs[4]: Zipf(1.2) over 1e8 ids, tumbling window + 3 consecutive readings > 50, hashed, through the keyBy exchange"] = {
+            "value": world * B * K4 / (ms5 * 1e-3), "unit": "events/s", "ms_per_step": ms5 / K4, "steps": K4,
+            "note": "the hottest id's owner receives ~18 % of all events on top of its share: the step time is that rank's"}
+
     if world > 1 and not args.no_verify:
         # Outside every timed region: V steps of the headline route into fresh engines; the union of the ranks' rows
         # against the CPU oracle fed the same global batches, as order-independent sums over the rows.

@@ -80,6 +80,7 @@ struct fmq_handle {
     char* d_xbuf = nullptr; size_t xs_seg_cap = 0; int xs_world = 0, xs_rank = -1; bool xs_attached = false;
     XCtl* xs_ctl[FMQ_MAX_PEERS] = {}; char* xs_base[FMQ_MAX_PEERS] = {}; void* xs_opened[FMQ_MAX_PEERS] = {};
     cudaStream_t send_stream = nullptr; u32* d_xcounts = nullptr; u32* d_xtiles = nullptr; i64* d_send_max = nullptr;
+    unsigned long long* d_xfill = nullptr;   // [FMQ_MAX_PEERS] events placed so far in each owner's segment (unordered scatter)
     u64* d_seg_n = nullptr;              // [FMQ_MAX_PEERS] counts of the batch being received + [1] their sum
     u64* h_ntotal = nullptr;             // pinned: the sum read back for the keyed chain (which sizes its launches on the host)
     u64* xs_stage = nullptr;             // 3 x seg_cap: host columns of a send are copied here first
@@ -130,7 +131,7 @@ static void free_all(fmq_handle* h) {
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : h->alt_out) if (p) cudaFree(p);
     for (void* p : h->xs_opened) if (p) cudaIpcCloseMemHandle(p);
-    { void* xs[] = {h->d_xbuf, h->d_xcounts, h->d_xtiles, h->d_send_max, h->d_seg_n, h->xs_stage}; for (void* p : xs) if (p) cudaFree(p); }
+    { void* xs[] = {h->d_xbuf, h->d_xcounts, h->d_xtiles, h->d_send_max, h->d_seg_n, h->xs_stage, h->d_xfill}; for (void* p : xs) if (p) cudaFree(p); }
     if (h->h_ntotal) cudaFreeHost(h->h_ntotal);
     if (h->send_stream) { cudaStreamSynchronize(h->send_stream); cudaStreamDestroy(h->send_stream); }
     for (int i = 0; i < fmq_handle::HOST_SETS; ++i) {
@@ -310,15 +311,19 @@ static int exclusive_scan_counts(fmq_handle* h, size_t len) {
 // start of owner d's bucket (single-output mode) or what precedes owner d's events in digit-major order.
 struct SplitScratch { u32* counts; u32* tiles; };
 static cudaError_t owner_split(cudaStream_t stream, const SplitScratch& sc, const u64* ts, const u64* key, const u64* val, size_t n, u32 world, u32 dense,
-                               const SplitDst& dst, bool per_owner, i64* max_ts) {
+                               const SplitDst& dst, bool per_owner, i64* max_ts, unsigned long long* fill = nullptr, u32 max_blocks = 0) {
     const u32 nchunks = xs_num_chunks(n);
-    SplitArgs a{ts, key, val, n, nchunks, world, dense, sc.counts, dst, max_ts};
+    SplitArgs a{ts, key, val, n, nchunks, world, dense, sc.counts, dst, max_ts, per_owner ? fill : nullptr};
+    const u32 grid = (max_blocks && max_blocks < nchunks) ? max_blocks : nchunks;      // the scatter is persistent over chunks
     auto run = [&](auto hist, auto scat_single, auto scat_owner, u32 nb) -> cudaError_t {
-        hist<<<nchunks, XS_THREADS, 0, stream>>>(key, n, nchunks, world, dense, sc.counts);
-        cudaError_t e = scan_counts_on(stream, sc.counts, sc.tiles, (size_t)nb * nchunks); if (e != cudaSuccess) return e;
+        cudaError_t e;
+        if (!a.fill) {                                                                // stable form: count, scan, then scatter
+            hist<<<nchunks, XS_THREADS, 0, stream>>>(key, n, nchunks, world, dense, sc.counts);
+            e = scan_counts_on(stream, sc.counts, sc.tiles, (size_t)nb * nchunks); if (e != cudaSuccess) return e;
+        }
         const size_t smem = xs_scatter_smem(nb);
-        if (per_owner) { e = cudaFuncSetAttribute(scat_owner, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_owner<<<nchunks, XS_THREADS, smem, stream>>>(a); }
-        else           { e = cudaFuncSetAttribute(scat_single, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_single<<<nchunks, XS_THREADS, smem, stream>>>(a); }
+        if (per_owner) { e = cudaFuncSetAttribute(scat_owner, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_owner<<<grid, XS_THREADS, smem, stream>>>(a); }
+        else           { e = cudaFuncSetAttribute(scat_single, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_single<<<grid, XS_THREADS, smem, stream>>>(a); }
         return cudaGetLastError();
     };
     if (world <= 8) return run(xs_hist_kernel<3>, xs_scatter_kernel<3, false>, xs_scatter_kernel<3, true>, 8u);
@@ -467,7 +472,8 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         if (fast_geom && !ingest_legacy()) {
             // persistent grid: every warp streams its own ring of 128-event tiles
             size_t blocks = (n * (seg.nseg ? seg.nseg : 1) + (size_t)IW_TILE * IW_WARPS - 1) / ((size_t)IW_TILE * IW_WARPS);
-            const size_t maxb = (size_t)h->num_sms * FMQ_IW_BLOCKS;
+            // a rank of the keyBy exchange leaves room on every SM for the scatter of the next batch (one block of ~53 KB)
+            const size_t maxb = (size_t)h->num_sms * ((h->xs_attached && !h->cmb_flags && FMQ_IW_BLOCKS > 3) ? 3 : FMQ_IW_BLOCKS);
             if (blocks > maxb) blocks = maxb;
             const bool comb = c.window_enabled && h->h_hint && *(volatile u32*)h->h_hint != 0;     // skew seen by an earlier batch's sample
             auto pick = [&](auto lean, auto combining) { return comb ? combining : lean; };
@@ -1379,6 +1385,10 @@ static u64 peer_timeout_ns() {
     static const u64 v = [] { const char* e = getenv("FMQ_PEER_TIMEOUT_MS"); const long ms = e ? atol(e) : 20000; return (u64)(ms < 1 ? 1 : ms) * 1000000ull; }();
     return v;
 }
+static u32 xs_blocks_per_sm() {
+    static const u32 v = [] { const char* e = getenv("FMQ_XS_BLOCKS_PER_SM"); const int b = e ? atoi(e) : 1; return (u32)(b < 1 ? 1 : (b > 4 ? 4 : b)); }();
+    return v;
+}
 static u64* xs_segment(char* base, int world, size_t seg_cap, u32 parity, int src) {
     return reinterpret_cast<u64*>(base + XCTL_BYTES) + ((size_t)parity * world + src) * 3 * seg_cap;
 }
@@ -1399,6 +1409,7 @@ int32_t fmq_shard_alloc(fmq_handle* h, int32_t world, size_t max_send, void* han
     const size_t nc = (size_t)8 * xs_num_chunks(h->xs_seg_cap);
     CU(h, dalloc(&h->d_xcounts, nc)); CU(h, dalloc(&h->d_xtiles, (nc + SCAN_TILE - 1) / SCAN_TILE + 1));
     CU(h, dalloc(&h->d_send_max, 1)); CU(h, dalloc(&h->d_seg_n, FMQ_MAX_PEERS + 1));
+    CU(h, dalloc(&h->d_xfill, FMQ_MAX_PEERS)); CU(h, cudaMemset(h->d_xfill, 0, FMQ_MAX_PEERS * 8));
     const i64 imin = I64_MIN_;
     CU(h, cudaMemcpy(h->d_send_max, &imin, 8, cudaMemcpyHostToDevice));
     CU(h, cudaMemset(h->d_seg_n, 0, (FMQ_MAX_PEERS + 1) * 8));
@@ -1477,11 +1488,17 @@ int32_t fmq_shard_send(fmq_handle* h, const int64_t* ts, const uint64_t* key, co
     if (n > 0) {
         SplitDst dst{}; dst.col_stride = h->xs_seg_cap;
         for (int d = 0; d < W; ++d) dst.ts[d] = xs_segment(h->xs_base[d], W, h->xs_seg_cap, parity, me);
-        cudaError_t e = owner_split(ss, SplitScratch{h->d_xcounts, h->d_xtiles}, dts, dkey, dval, n, (u32)W, h->cfg.key_mode == FMQ_KEYS_DENSE ? 1u : 0u, dst, true, h->d_send_max);
+        // Order-dependent keyed state needs every key's events in arrival order: stable two-pass split.  Window aggregates
+        // and the filter are commutative: one pass, runs placed in completion order.  Either way the scatter takes at
+        // most xs_blocks_per_sm blocks per SM, so that the ingest of the previous batch keeps running beside it.
+        unsigned long long* fill = (keyed_enabled(h->cfg) || h->ml_cap) ? nullptr : h->d_xfill;
+        cudaError_t e = owner_split(ss, SplitScratch{h->d_xcounts, h->d_xtiles}, dts, dkey, dval, n, (u32)W, h->cfg.key_mode == FMQ_KEYS_DENSE ? 1u : 0u, dst, true, h->d_send_max,
+                                    fill, (u32)h->num_sms * xs_blocks_per_sm());
         if (e != cudaSuccess) { h->err = std::string("owner split: ") + cudaGetErrorString(e); return FMQ_ERR_CUDA; }
-        h->launches += 5;
+        h->launches += fill ? 1 : 5;
     }
-    xs_publish_kernel<<<1, 32, 0, ss>>>(h->d_xcounts, nchunks, (u64)n, (u32)W, (u32)me, parity, seq, h->d_send_max, xs_peers(h)); LAUNCHED(h, "xs_publish_kernel");
+    xs_publish_kernel<<<1, 32, 0, ss>>>(h->d_xcounts, nchunks, (u64)n, (n > 0 && !(keyed_enabled(h->cfg) || h->ml_cap)) ? h->d_xfill : nullptr, (u32)W, (u32)me, parity, seq,
+                                        h->d_send_max, xs_peers(h)); LAUNCHED(h, "xs_publish_kernel");
     if (mem == FMQ_MEM_HOST && n > 0) CU(h, cudaStreamSynchronize(ss));       // the caller owns host columns only until this call returns
     return FMQ_OK;
 }

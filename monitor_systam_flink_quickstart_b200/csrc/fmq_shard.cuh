@@ -58,14 +58,16 @@ __global__ void xs_wait_acks_kernel(const XCtl* ctl, u32 world, u32 parity, u64 
 
 // SEND last step: tell every owner how many events of mine lie in its segment, and my slice's largest timestamp
 struct XPeers { XCtl* ctl[FMQ_MAX_PEERS]; };
-__global__ void xs_publish_kernel(const u32* __restrict__ offsets, u32 nchunks, u64 n, u32 world, u32 rank, u32 parity, u64 seq, i64* max_ts, XPeers peers) {
+__global__ void xs_publish_kernel(const u32* __restrict__ offsets, u32 nchunks, u64 n, unsigned long long* fill, u32 world, u32 rank, u32 parity, u64 seq, i64* max_ts, XPeers peers) {
     const u32 d = threadIdx.x;
     const i64 m = *max_ts;
     __syncwarp();
     if (d < world) {
-        const u64 lo = n ? offsets[(size_t)d * nchunks] : 0, hi = n ? (d + 1 < world ? offsets[(size_t)(d + 1) * nchunks] : n) : 0;
+        u64 cnt;
+        if (fill) { cnt = fill[d]; fill[d] = 0; }                      // unordered scatter: the owners' fill counters are the counts
+        else { const u64 lo = n ? offsets[(size_t)d * nchunks] : 0, hi = n ? (d + 1 < world ? offsets[(size_t)(d + 1) * nchunks] : n) : 0; cnt = hi - lo; }
         XPub* p = &peers.ctl[d]->pub[parity][rank];
-        p->count = hi - lo; p->max_ts = m;
+        p->count = cnt; p->max_ts = m;
         __threadfence_system();                      // the record, and the scatter kernel's stores before it in stream order, before the flag
         st_release_sys(&p->seq, seq);
     }

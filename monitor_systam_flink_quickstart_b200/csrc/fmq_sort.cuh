@@ -75,8 +75,12 @@ struct SplitDst {
 };
 struct SplitArgs {
     const u64* ts; const u64* key; const u64* val; size_t n; u32 nchunks; u32 world; u32 dense;
-    const u32* offsets;                            // counts[digit][chunk] after the exclusive scan (digit-major)
+    const u32* offsets;                            // counts[digit][chunk] after the exclusive scan (digit-major); unused when `fill` is set
     SplitDst dst; i64* max_ts;                     // max_ts may be null
+    // Unordered mode (per-owner destinations only): no counting pass and no scan; a block reserves the place of each of
+    // its runs with one atomic on fill[owner].  Runs of different blocks then land in completion order, which is
+    // all a commutative aggregate needs; jobs with order-dependent keyed state use the stable two-pass form.
+    unsigned long long* fill;
 };
 constexpr size_t xs_scatter_smem(u32 nb) { return (size_t)3 * XS_CHUNK * 8 + XS_CHUNK * 2 + (size_t)XS_WARPS * nb * 2 + nb * 4 * 2; }
 
@@ -92,11 +96,15 @@ __global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_
     __shared__ u32 scan_ws[XS_WARPS];
     __shared__ i64 max_ws[XS_WARPS];
     const u32 tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-    const u32 chunk = blockIdx.x;
+    i64 tmax = I64_MIN_;
+    // persistent over chunks: the grid may be much smaller than the number of chunks (the keyBy exchange runs this kernel
+    // beside the ingest of the previous batch and leaves it most of every SM)
+    for (u32 chunk = blockIdx.x; chunk < a.nchunks; chunk += gridDim.x) {
     const size_t lo = (size_t)chunk * XS_CHUNK;
     const size_t hi = (lo + XS_CHUNK < a.n) ? lo + XS_CHUNK : a.n;
+    const bool unordered = PER_OWNER && a.fill != nullptr;
     for (u32 i = tid; i < XS_WARPS * NB; i += XS_THREADS) wcnt[i] = 0;
-    for (u32 d = tid; d < NB; d += XS_THREADS) {
+    if (!unordered) for (u32 d = tid; d < NB; d += XS_THREADS) {
         const u32 o = a.offsets[(size_t)d * a.nchunks + chunk];
         goff[d] = PER_OWNER ? o - a.offsets[(size_t)d * a.nchunks] : o;           // per-owner destinations start at 0
     }
@@ -142,11 +150,17 @@ __global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_
     for (u32 i = 0; i < w; ++i) wb += scan_ws[i];
     u32 run = wb + inc - tot_local;
 #pragma unroll
-    for (u32 q = 0; q < DPT; ++q) { const u32 d = tid * DPT + q; if (d < NB) dbase[d] = run; run += dtot[q]; }
+    for (u32 q = 0; q < DPT; ++q) {
+        const u32 d = tid * DPT + q;
+        if (d < NB) {
+            dbase[d] = run;
+            if (unordered) goff[d] = dtot[q] ? (u32)atomicAdd(&a.fill[d], (unsigned long long)dtot[q]) : 0u;   // this block's run of owner d
+        }
+        run += dtot[q];
+    }
     __syncthreads();
     // phase 3: the three columns of every event go to its sorted position (timestamps and values are read here,
     // coalesced like the keys were, so that they do not sit in registers through the ranking)
-    i64 tmax = I64_MIN_;
 #pragma unroll
     for (int r = 0; r < XS_IPT; ++r) {
         const size_t i = wlo + r * 32 + lane;
@@ -160,13 +174,7 @@ __global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_
             dig_s[pos] = dg[r];
         }
     }
-    if (a.max_ts) { tmax = warp_max_i64(tmax); if (lane == 0) max_ws[w] = tmax; }
     __syncthreads();
-    if (a.max_ts && tid == 0) {
-        i64 m = max_ws[0];
-        for (int i = 1; i < XS_WARPS; ++i) m = max_ws[i] > m ? max_ws[i] : m;
-        if (m != I64_MIN_) atomicMax(reinterpret_cast<long long*>(a.max_ts), (long long)m);
-    }
     // phase 4: copy out; consecutive threads -> consecutive positions -> consecutive addresses inside a run
     const u32 cnt = (u32)(hi - lo);
 #pragma unroll
@@ -176,6 +184,17 @@ __global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_
             const size_t o = (size_t)goff[d] + (pos - dbase[d]);
             u64* dstc = PER_OWNER ? a.dst.ts[d] + (size_t)c * a.dst.col_stride : (c == 0 ? a.dst.out_ts : (c == 1 ? a.dst.out_key : a.dst.out_val));
             dstc[o] = ev_s[c * XS_CHUNK + pos];
+        }
+    }
+    __syncthreads();                               // the staging area is reused by the next chunk
+    }
+    if (a.max_ts) {                                // one atomic per block for the batch's largest timestamp
+        tmax = warp_max_i64(tmax); if (lane == 0) max_ws[w] = tmax;
+        __syncthreads();
+        if (tid == 0) {
+            i64 m = max_ws[0];
+            for (int i = 1; i < XS_WARPS; ++i) m = max_ws[i] > m ? max_ws[i] : m;
+            if (m != I64_MIN_) atomicMax(reinterpret_cast<long long*>(a.max_ts), (long long)m);
         }
     }
     // stores to a peer's memory must have landed before a later kernel of this stream raises that peer's flag
