@@ -436,14 +436,14 @@ def main():
         #     tumbling windows plus the consecutive-readings rule (order-dependent keyed state: stable exchange), hashed keys
         spec5 = StreamSpec(n_keys=100_000_000, events_per_ms=1000 * world, jitter_ms=3000, late_frac_ppm=500, late_extra_ms=20_000, key_kind="zipf")
         kw5 = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=10_000, max_out_of_orderness_ms=3000,
-                   consec_n=3, consec_threshold=50.0, consec_reset_on_fire=1, table_capacity=6_000_000, pane_ring=16, max_batch=3 * B, device=local_rank,
-                   fired_capacity=16_000_000, calert_capacity=3 * B // 4)
+                   consec_n=3, consec_threshold=90.0, consec_reset_on_fire=1, table_capacity=6_000_000, pane_ring=16, max_batch=3 * B, device=local_rank,
+                   fired_capacity=24_000_000, calert_capacity=3 * B)
         batches5 = [tuple(t.contiguous() for t in generate_torch(spec5, (s_ * world + rank) * B, B, device=f"cuda:{local_rank}")) for s_ in range(W + K4)]
         torch.cuda.synchronize()
         ms5, ing5, fire5, d5, _ = measure(kw5, False, multi="exchange", batches=batches5, K=K4)
         ms5 = job_max(ms5)
         del batches5
-        variants["workload=configs[4]: Zipf(1.2) over 1e8 ids, tumbling window + 3 consecutive readings > 50, hashed, through the keyBy exchange"] = {
+        variants["workload=configs[4]: Zipf(1.2) over 1e8 ids, tumbling window + 3 consecutive readings > 90, hashed, through the keyBy exchange"] = {
             "value": world * B * K4 / (ms5 * 1e-3), "unit": "events/s", "ms_per_step": ms5 / K4, "steps": K4,
             "note": "the hottest id's owner receives ~18 % of all events on top of its share: the step time is that rank's"}
 

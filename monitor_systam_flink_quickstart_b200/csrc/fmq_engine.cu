@@ -448,6 +448,8 @@ static bool ingest_legacy() {
 }
 
 // stage 1 of a push: everything that touches only this handle's own events
+static u64 peer_timeout_ns();
+static u32 xs_ingest_blocks();
 struct SegIn { u32 nseg = 0; size_t stride = 0; const u64* seg_n = nullptr; };   // segmented input with device-side counts (keyBy exchange)
 template <typename V>
 static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n, const SegIn& seg = SegIn()) {
@@ -473,7 +475,7 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
             // persistent grid: every warp streams its own ring of 128-event tiles
             size_t blocks = (n * (seg.nseg ? seg.nseg : 1) + (size_t)IW_TILE * IW_WARPS - 1) / ((size_t)IW_TILE * IW_WARPS);
             // a rank of the keyBy exchange leaves room on every SM for the scatter of the next batch (one block of ~53 KB)
-            const size_t maxb = (size_t)h->num_sms * ((h->xs_attached && !h->cmb_flags && FMQ_IW_BLOCKS > 3) ? 3 : FMQ_IW_BLOCKS);
+            const size_t maxb = (size_t)h->num_sms * ((h->xs_attached && !h->cmb_flags) ? xs_ingest_blocks() : FMQ_IW_BLOCKS);
             if (blocks > maxb) blocks = maxb;
             const bool comb = c.window_enabled && h->h_hint && *(volatile u32*)h->h_hint != 0;     // skew seen by an earlier batch's sample
             auto pick = [&](auto lean, auto combining) { return comb ? combining : lean; };
@@ -756,7 +758,7 @@ static int push_cols(fmq_handle* h, const InCols& c, size_t n, int64_t wm_after,
     return h->cfg.value_type == FMQ_VAL_F64 ? push_cols_t<double>(h, c, n, wm_after, mem) : push_cols_t<i64>(h, c, n, wm_after, mem);
 }
 
-static u64 peer_timeout_ns();
+static u32 xs_ingest_blocks();
 static XPeers xs_peers(const fmq_handle* h);
 
 // combiner mode, stage 1 (fmq_push_local / fmq_push_local_packed)
@@ -1385,8 +1387,14 @@ static u64 peer_timeout_ns() {
     static const u64 v = [] { const char* e = getenv("FMQ_PEER_TIMEOUT_MS"); const long ms = e ? atol(e) : 20000; return (u64)(ms < 1 ? 1 : ms) * 1000000ull; }();
     return v;
 }
+// How the SMs are shared between the scatter of batch b+1 and the ingest of batch b (measurement knobs):
+// scatter blocks per SM (0 = one block per chunk, i.e. whatever fits) and ingest blocks per SM while a rank of the exchange.
 static u32 xs_blocks_per_sm() {
-    static const u32 v = [] { const char* e = getenv("FMQ_XS_BLOCKS_PER_SM"); const int b = e ? atoi(e) : 1; return (u32)(b < 1 ? 1 : (b > 4 ? 4 : b)); }();
+    static const u32 v = [] { const char* e = getenv("FMQ_XS_BLOCKS_PER_SM"); const int b = e ? atoi(e) : 2; return (u32)(b < 0 ? 0 : (b > 4 ? 4 : b)); }();
+    return v;
+}
+static u32 xs_ingest_blocks() {
+    static const u32 v = [] { const char* e = getenv("FMQ_XS_INGEST_BLOCKS"); const int b = e ? atoi(e) : 2; return (u32)(b < 1 ? 1 : (b > FMQ_IW_BLOCKS ? FMQ_IW_BLOCKS : b)); }();
     return v;
 }
 static u64* xs_segment(char* base, int world, size_t seg_cap, u32 parity, int src) {
