@@ -426,6 +426,49 @@ int32_t fmq_exchange_split(fmq_handle* h, const int64_t* ts, const uint64_t* key
 int32_t fmq_exchange_pull_push(fmq_handle* h, int32_t parity, const uint64_t* matrix,
                                int64_t watermark_after, size_t* n_received);
 
+/* ---- keyBy exchange inside the library (A4; SURVEY.md §8b: rank / world and the peers' memory belong to the boundary) ----
+ * Replaces: the keyBy network exchange in front of the keyed operator — KeyGroupStreamPartitioner + the Netty / local
+ * channels behind BandwidthMonitorWithEventTime.java:45 (`.keyBy(1)`), in front of :46-47 (window + reduce on the owning
+ * subtask) — for ranks on one NVSwitch node, with no collective library and no host round trip per micro-batch.
+ * Every rank owns a receive buffer the peers map (2 parities x `world` segments of three 8-byte columns).  Set-up, once:
+ *     fmq_shard_alloc(h, world, max_send, blob64)   allocate; blob64 = 64-byte CUDA IPC handle to give to the peers
+ *                                                   (any transport: Flink's own RPC, a file, a collective)
+ *     fmq_shard_attach_ipc(h, rank, world, blobs)   blobs = world x 64 bytes in rank order (own entry ignored); or, for
+ *     fmq_shard_attach(h, rank, world, bases)       handles living in one process, the fmq_shard_base() pointers
+ *     -- a barrier of the caller's: every rank has attached before the first send --
+ * Per micro-batch, on every rank (same order of batches everywhere):
+ *     fmq_shard_send(h, ts, key, val, n, mem)       this rank's slice (n <= max_send; host or device columns): the owner
+ *                                                   split's scatter kernel writes every owner's run straight into that
+ *                                                   owner's segment — local stores or NVLink peer stores — then tells
+ *                                                   each owner {count, largest timestamp of the slice} behind a flag.
+ *                                                   Runs on its own stream, beside the previous batch's kernels.
+ *     fmq_shard_recv(h, watermark_after, n_recv)    waits ON THE DEVICE for all `world` flags, then runs the operator
+ *                                                   chain on the segments in source-rank order (per-key arrival order
+ *                                                   as fmq_push_batch on the concatenated slices would see it) and
+ *                                                   acknowledges.  FMQ_WM_AUTO derives the watermark from the largest
+ *                                                   timestamp of the WHOLE batch (one assigner for the job,
+ *                                                   BandwidthMonitorWithEventTime.java:30-45), so all ranks agree.
+ *                                                   n_recv may be NULL; non-NULL reads the count back (synchronises).
+ * Routing and key rewriting are those of fmq_partition_by_owner.  Works for every operator and both key modes; jobs with
+ * order-dependent keyed state (A7) use the stable two-pass split and read one 8-byte count back per batch (their sort
+ * sizes its launches on the host), all others a single-pass split and nothing at all.  fmq_config.max_batch must cover
+ * what a rank can RECEIVE (keyed jobs).  A peer that does not show up within FMQ_PEER_TIMEOUT_MS (environment, default
+ * 20000) poisons the handle with FMQ_ERR_PEER_TIMEOUT instead of hanging the GPU.  Results are polled as usual; a DENSE
+ * handle's rows carry the rank-local id (global id = local * world + rank). */
+int32_t fmq_shard_alloc(fmq_handle* h, int32_t world, size_t max_send, void* handle64);
+void*   fmq_shard_base(fmq_handle* h);
+int32_t fmq_shard_attach(fmq_handle* h, int32_t rank, int32_t world, const void* const* peer_bases);
+int32_t fmq_shard_attach_ipc(fmq_handle* h, int32_t rank, int32_t world, const void* blobs64);
+int32_t fmq_shard_send(fmq_handle* h, const int64_t* ts, const uint64_t* key, const void* val, size_t n, int32_t mem);
+int32_t fmq_shard_recv(fmq_handle* h, int64_t watermark_after, size_t* n_received);
+
+/* Combiner mode without a collective library: after fmq_attach_peers AND fmq_shard_alloc(h, world, 1, ..) +
+ * fmq_shard_attach[_ipc] (the control block at the head of that buffer is all that is used), the 32 bytes of batch
+ * scalars and both barriers of the call sequence above travel as peer stores behind device flags inside
+ * fmq_push_local / fmq_fire_global / fmq_retire: the caller issues no all-reduce and no barrier.  Every
+ * fmq_fire_global then follows an fmq_push_local (n = 0 for an end-of-input flush).  No reference counterpart. */
+int32_t fmq_combiner_use_flags(fmq_handle* h, int32_t enable);
+
 /* Largest batch fmq_partition_by_owner_noalloc accepts (events). */
 #define FMQ_NOALLOC_MAX_EVENTS 4194304
 

@@ -286,6 +286,31 @@ __device__ __forceinline__ void block_append2(bool pa, bool pb, u64* ctr_a, u64 
     if (tb) { if (base2[1] + tb > cap_b) { if (threadIdx.x == 0) atomicOr(&st->err_flags, ERRB_OUTPUT); } else if (pb) row_b = base2[1] + (ex >> 16); }
 }
 
+// Same with small per-thread counts (each <= 255): the thread's rows of list A start at row_a, of list B at row_b.
+template <int THREADS>
+__device__ __forceinline__ void block_append2n(u32 na, u32 nb, u64* ctr_a, u64 cap_a, u64* ctr_b, u64 cap_b, DevState* st, u64& row_a, u64& row_b) {
+    __shared__ u32 wsum2n[THREADS / 32];
+    __shared__ u64 base2n[2];
+    const u32 lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const u32 cnt = na | (nb << 16);
+    u32 inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { u32 t = __shfl_up_sync(0xffffffffu, inc, o); if ((int)lane >= o) inc += t; }
+    if (lane == 31) wsum2n[w] = inc;
+    __syncthreads();
+    u32 wbase = 0, total = 0;
+#pragma unroll
+    for (int i = 0; i < THREADS / 32; ++i) { const u32 x = wsum2n[i]; if (i < (int)w) wbase += x; total += x; }
+    const u32 ta = total & 0xFFFFu, tb = total >> 16;
+    if (threadIdx.x == 0) base2n[0] = ta ? atomicAdd(ctr_a, (u64)ta) : 0;
+    if (threadIdx.x == 32) base2n[1] = tb ? atomicAdd(ctr_b, (u64)tb) : 0;
+    __syncthreads();
+    const u32 ex = wbase + inc - cnt;
+    row_a = ~0ull; row_b = ~0ull;
+    if (ta) { if (base2n[0] + ta > cap_a) { if (threadIdx.x == 0) atomicOr(&st->err_flags, ERRB_OUTPUT); } else if (na) row_a = base2n[0] + (ex & 0xFFFFu); }
+    if (tb) { if (base2n[1] + tb > cap_b) { if (threadIdx.x == 0) atomicOr(&st->err_flags, ERRB_OUTPUT); } else if (nb) row_b = base2n[1] + (ex >> 16); }
+}
+
 __device__ __forceinline__ i64 warp_max_i64(i64 v) {
     for (int o = 16; o > 0; o >>= 1) { i64 t = __shfl_xor_sync(0xffffffffu, v, o); v = t > v ? t : v; }
     return v;

@@ -597,7 +597,7 @@ static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now
         f.slot_lo = per * h->rank < h->capacity ? per * h->rank : h->capacity;
         f.slot_hi = f.slot_lo + per < h->capacity ? f.slot_lo + per : h->capacity;
         for (int r = 0; r < h->world; ++r) f.peer_acc[r] = h->peer_acc[r];
-        size_t blocks = (f.slot_hi - f.slot_lo + FIRE_THREADS - 1) / FIRE_THREADS; const size_t maxb = (size_t)h->num_sms * 8;
+        size_t blocks = (f.slot_hi - f.slot_lo + FIRE_THREADS * FIRE_SPT - 1) / (FIRE_THREADS * FIRE_SPT); const size_t maxb = (size_t)h->num_sms * 8;
         if (blocks > maxb) blocks = maxb;
         if (blocks == 0) blocks = 1;
         if (h->world > 1) fire_kernel<V, true><<<(unsigned)blocks, FIRE_THREADS, 0, fs>>>(f);

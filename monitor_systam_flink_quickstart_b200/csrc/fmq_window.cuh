@@ -1107,8 +1107,16 @@ __global__ void __launch_bounds__(256) retire_kernel(DevState* st, Acc32* acc, u
     }
 }
 
+// Geometry of the windows being fired is the same for every key: a few threads work it out once per block
+// (64-bit divisions) and leave it in shared memory; ncu of the first version counted 630 instructions per key slot,
+// most of them this arithmetic repeated by every thread.
+constexpr int FIRE_MAXW = 32;             // windows per pass over the slots
+constexpr int FIRE_SPT = 2;               // key slots per thread: both slots' cells are requested before either is used
+struct FireWin { i64 wend; u32 p0; u32 np; };     // first pane (low 32 bits: only its ring index is needed) and number of panes holding data
+
 template <typename V, bool PEERS>
 __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constant__ FireArgs a) {
+    __shared__ FireWin wins[FIRE_MAXW];
     DevState* st = a.st;
     const i64 nfire = st->fire_count;
     const i64 x_lo = st->expire_lo, x_hi = st->expire_hi;
@@ -1118,82 +1126,125 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
     const i64 size = a.g.size, slide = a.g.slide, off = a.g.off;
     const u64 C = a.g.capacity;
     constexpr bool is_f64 = IsF64<V>::value;
+    const bool want_mx = a.g.agg_mask & 8u, want_mn = a.g.agg_mask & 4u;
     u64 fired_local = 0, alerts_local = 0;
-    const u64 nslots_rounded = (a.slot_hi - a.slot_lo + FIRE_THREADS - 1) / FIRE_THREADS * FIRE_THREADS;   // block-uniform trip count
-    for (u64 sidx = (u64)blockIdx.x * blockDim.x + threadIdx.x; sidx < nslots_rounded; sidx += (u64)gridDim.x * blockDim.x) {
-        const u64 slot = a.slot_lo + sidx;
-        const u64 key = slot < a.slot_hi ? (a.dense_keys ? slot : a.dkeys[slot]) : KEY_EMPTY;
-        const bool live = key != KEY_EMPTY;
-        for (i64 j = 0; j < nfire; ++j) {
-            const i64 wend = first_end + j * slide;
+    const u64 nslots = a.slot_hi - a.slot_lo;
+    const u64 tile = (u64)FIRE_THREADS * FIRE_SPT;
+    const u64 ntiles = (nslots + tile - 1) / tile;                   // block-uniform trip count
+    for (i64 j0 = 0; j0 < nfire || j0 == 0; j0 += FIRE_MAXW) {
+        const int nw = (int)((nfire - j0) < FIRE_MAXW ? (nfire - j0) : FIRE_MAXW);
+        const bool last_pass = j0 + FIRE_MAXW >= nfire;
+        __syncthreads();
+        if ((int)threadIdx.x < nw) {
+            const i64 wend = first_end + (j0 + threadIdx.x) * slide;
             // panes of [wend - size, wend): absolute indices, clipped to the panes holding data
             i64 p0 = (wend - size - off) / slide, p1 = (wend - off) / slide - 1;   // exact: wend == off (mod slide)
             if (p0 < pmin) p0 = pmin;
             if (p1 > pmax) p1 = pmax;
-            u64 cnt_i = 0; double cnt_d = 0.0; u64 sum_i = 0; double sum_d = 0.0; u64 mx = 0, mn = 0;
-            if (live) {
-                for (i64 p = p0; p <= p1; ++p) {
-                    const u64 cell = (u64)((u32)p & a.g.ring_mask) * C + slot;
-                    if constexpr (!PEERS) {
-                        const ulonglong4 q = *reinterpret_cast<const ulonglong4*>(a.acc + cell);
-                        if (is_f64) { cnt_d += __longlong_as_double((i64)q.x); sum_d += __longlong_as_double((i64)q.y); }
-                        else        { cnt_i += q.x; sum_i += q.y; }
-                        mx = q.z > mx ? q.z : mx; mn = q.w > mn ? q.w : mn;
-                    } else {
-                        // every peer's cell is requested before the first one is used: over NVLink a load takes
-                        // microseconds, and a dependent chain of `world` of them per thread was what made the
-                        // fire chain grow with the GPU count
-                        ulonglong4 q[FMQ_MAX_PEERS];
+            wins[threadIdx.x] = FireWin{wend, (u32)p0, p1 >= p0 ? (u32)(p1 - p0 + 1) : 0u};
+        }
+        __syncthreads();
+        for (u64 t = blockIdx.x; t < ntiles; t += gridDim.x) {
+            u64 slot_[FIRE_SPT], key_[FIRE_SPT]; bool live_[FIRE_SPT];
 #pragma unroll
-                        for (int r = 0; r < FMQ_MAX_PEERS; ++r)
-                            q[r] = r < a.world ? *reinterpret_cast<const ulonglong4*>(a.peer_acc[r] + cell) : make_ulonglong4(0, 0, 0, 0);
+            for (int q = 0; q < FIRE_SPT; ++q) {
+                slot_[q] = a.slot_lo + t * tile + (u64)q * FIRE_THREADS + threadIdx.x;
+                key_[q] = slot_[q] < a.slot_hi ? (a.dense_keys ? slot_[q] : a.dkeys[slot_[q]]) : KEY_EMPTY;
+                live_[q] = key_[q] != KEY_EMPTY;
+            }
+            for (int j = 0; j < nw; ++j) {
+                const FireWin w = wins[j];
+                i64 count_[FIRE_SPT]; u64 sum_[FIRE_SPT], mx_[FIRE_SPT], mn_[FIRE_SPT]; double v_[FIRE_SPT]; bool fired_[FIRE_SPT], hit_[FIRE_SPT];
+                if (!PEERS && w.np == 1) {
+                    // tumbling windows (and the common sliding case of one pane with data): one cell per slot, all requested first
+                    ulonglong4 c_[FIRE_SPT];
 #pragma unroll
-                        for (int r = 0; r < FMQ_MAX_PEERS; ++r) {          // fixed rank order: deterministic double sums
-                            if (r >= a.world) break;
-                            if (is_f64) { cnt_d += __longlong_as_double((i64)q[r].x); sum_d += __longlong_as_double((i64)q[r].y); }
-                            else        { cnt_i += q[r].x; sum_i += q[r].y; }
-                            mx = q[r].z > mx ? q[r].z : mx; mn = q[r].w > mn ? q[r].w : mn;
+                    for (int q = 0; q < FIRE_SPT; ++q)
+                        c_[q] = live_[q] ? *reinterpret_cast<const ulonglong4*>(a.acc + (u64)(w.p0 & a.g.ring_mask) * C + slot_[q]) : make_ulonglong4(0, 0, 0, 0);
+#pragma unroll
+                    for (int q = 0; q < FIRE_SPT; ++q) {
+                        count_[q] = is_f64 ? (i64)__longlong_as_double((i64)c_[q].x) : (i64)c_[q].x;
+                        sum_[q] = c_[q].y; mx_[q] = c_[q].z; mn_[q] = c_[q].w;
+                    }
+                } else {
+#pragma unroll
+                    for (int q = 0; q < FIRE_SPT; ++q) {
+                        u64 cnt_i = 0; double cnt_d = 0.0; u64 sum_i = 0; double sum_d = 0.0; u64 mx = 0, mn = 0;
+                        if (live_[q]) {
+                            for (u32 pi = 0; pi < w.np; ++pi) {
+                                const u64 cell = (u64)((w.p0 + pi) & a.g.ring_mask) * C + slot_[q];
+                                if constexpr (!PEERS) {
+                                    const ulonglong4 c = *reinterpret_cast<const ulonglong4*>(a.acc + cell);
+                                    if (is_f64) { cnt_d += __longlong_as_double((i64)c.x); sum_d += __longlong_as_double((i64)c.y); }
+                                    else        { cnt_i += c.x; sum_i += c.y; }
+                                    mx = c.z > mx ? c.z : mx; mn = c.w > mn ? c.w : mn;
+                                } else {
+                                    // every peer's cell is requested before the first one is used: over NVLink a load takes
+                                    // microseconds, and a dependent chain of `world` of them per thread was what made the
+                                    // fire chain grow with the GPU count
+                                    ulonglong4 c[FMQ_MAX_PEERS];
+#pragma unroll
+                                    for (int r = 0; r < FMQ_MAX_PEERS; ++r)
+                                        c[r] = r < a.world ? *reinterpret_cast<const ulonglong4*>(a.peer_acc[r] + cell) : make_ulonglong4(0, 0, 0, 0);
+#pragma unroll
+                                    for (int r = 0; r < FMQ_MAX_PEERS; ++r) {          // fixed rank order: deterministic double sums
+                                        if (r >= a.world) break;
+                                        if (is_f64) { cnt_d += __longlong_as_double((i64)c[r].x); sum_d += __longlong_as_double((i64)c[r].y); }
+                                        else        { cnt_i += c[r].x; sum_i += c[r].y; }
+                                        mx = c[r].z > mx ? c[r].z : mx; mn = c[r].w > mn ? c[r].w : mn;
+                                    }
+                                }
+                            }
                         }
+                        count_[q] = is_f64 ? (i64)cnt_d : (i64)cnt_i;
+                        sum_[q] = is_f64 ? (u64)__double_as_longlong(sum_d) : sum_i; mx_[q] = mx; mn_[q] = mn;
                     }
                 }
-            }
-            const i64 count = is_f64 ? (i64)cnt_d : (i64)cnt_i;
-            const bool fired = live && count > 0;
-            const u64 sum_bits = is_f64 ? (u64)__double_as_longlong(sum_d) : sum_i;
-            if (fired) fired_local++;
-            // A6-ii/iii: ((double)sum * 8.0 / 60 / 1024 / 1024) < 100, evaluated left to right
-            double v = 0.0; bool hit = false;
-            if (a.walert_source != 0 && fired) {
-                if (a.walert_source == 2) {
-                    v = Codec<V>::as_double(sum_bits) / (double)count;            // ComputeCpuAvg.java:49
-                } else {
-                    double src;
-                    if (a.walert_source == 1) src = Codec<V>::as_double(sum_bits);
-                    else if (a.walert_source == 3) src = Codec<V>::as_double(Codec<V>::dec_min(mn));
-                    else if (a.walert_source == 4) src = Codec<V>::as_double(Codec<V>::dec_max(mx));
-                    else src = (double)count;
-                    v = src * a.mul / a.d0 / a.d1 / a.d2;
+                u32 nf = 0, na = 0;
+#pragma unroll
+                for (int q = 0; q < FIRE_SPT; ++q) {
+                    fired_[q] = live_[q] && count_[q] > 0;
+                    // A6-ii/iii: ((double)sum * 8.0 / 60 / 1024 / 1024) < 100, evaluated left to right
+                    double v = 0.0; bool hit = false;
+                    if (a.walert_source != 0 && fired_[q]) {
+                        if (a.walert_source == 2) {
+                            v = Codec<V>::as_double(sum_[q]) / (double)count_[q];            // ComputeCpuAvg.java:49
+                        } else {
+                            double src;
+                            if (a.walert_source == 1) src = Codec<V>::as_double(sum_[q]);
+                            else if (a.walert_source == 3) src = Codec<V>::as_double(Codec<V>::dec_min(mn_[q]));
+                            else if (a.walert_source == 4) src = Codec<V>::as_double(Codec<V>::dec_max(mx_[q]));
+                            else src = (double)count_[q];
+                            v = src * a.mul / a.d0 / a.d1 / a.d2;
+                        }
+                        hit = cmp_op(v, a.walert_op, a.thr);
+                    }
+                    v_[q] = v; hit_[q] = hit;
+                    nf += fired_[q] ? 1u : 0u; na += hit ? 1u : 0u;
                 }
-                hit = cmp_op(v, a.walert_op, a.thr);
+                fired_local += nf; alerts_local += na;
+                // A5f: compaction of the fired rows and of the alert rows behind one pair of block barriers
+                u64 row_f = ~0ull, row_a = ~0ull;
+                block_append2n<FIRE_THREADS>(a.emit_fired ? nf : 0u, a.walert_source != 0 ? na : 0u, &st->n_fired, a.f_cap, &st->n_walert, a.wa_cap, st, row_f, row_a);
+#pragma unroll
+                for (int q = 0; q < FIRE_SPT; ++q) {
+                    if (fired_[q] && row_f != ~0ull) {
+                        a.f_key[row_f] = key_[q]; a.f_wend[row_f] = w.wend; a.f_count[row_f] = count_[q]; a.f_sum[row_f] = sum_[q];
+                        a.f_min[row_f] = want_mn ? Codec<V>::dec_min(mn_[q]) : 0;
+                        a.f_max[row_f] = want_mx ? Codec<V>::dec_max(mx_[q]) : 0;
+                        ++row_f;
+                    }
+                    if (hit_[q] && row_a != ~0ull) { a.wa_key[row_a] = key_[q]; a.wa_wend[row_a] = w.wend; a.wa_val[row_a] = v_[q]; ++row_a; }
+                }
             }
-            if (hit) alerts_local++;
-            // A5f: compaction of the fired row and of the alert row behind one pair of block barriers
-            u64 row_f = ~0ull, row_a = ~0ull;
-            if (a.emit_fired && a.walert_source != 0) block_append2<FIRE_THREADS>(fired, hit, &st->n_fired, a.f_cap, &st->n_walert, a.wa_cap, st, row_f, row_a);
-            else if (a.emit_fired) { const u64 r_ = block_append<FIRE_THREADS>(fired ? 1u : 0u, &st->n_fired, a.f_cap, st); if (fired) row_f = r_; }
-            else if (a.walert_source != 0) { const u64 r_ = block_append<FIRE_THREADS>(hit ? 1u : 0u, &st->n_walert, a.wa_cap, st); if (hit) row_a = r_; }
-            if (row_f != ~0ull) {
-                a.f_key[row_f] = key; a.f_wend[row_f] = wend; a.f_count[row_f] = count; a.f_sum[row_f] = sum_bits;
-                a.f_min[row_f] = (a.g.agg_mask & 4u) ? Codec<V>::dec_min(mn) : 0;
-                a.f_max[row_f] = (a.g.agg_mask & 8u) ? Codec<V>::dec_max(mx) : 0;
+            // cleanup: WindowOperator.clearAllState for panes whose last window has fired
+            if (a.clear_in_fire && last_pass) {
+                const ulonglong4 z = make_ulonglong4(0, 0, 0, 0);
+#pragma unroll
+                for (int q = 0; q < FIRE_SPT; ++q)
+                    if (live_[q]) for (i64 p = x_lo; p <= x_hi; ++p)
+                        *reinterpret_cast<ulonglong4*>(&a.acc[(u64)((u32)p & a.g.ring_mask) * C + slot_[q]]) = z;
             }
-            if (row_a != ~0ull) { a.wa_key[row_a] = key; a.wa_wend[row_a] = wend; a.wa_val[row_a] = v; }
-        }
-        // cleanup: WindowOperator.clearAllState for panes whose last window has fired
-        if (live && a.clear_in_fire) {
-            const ulonglong4 z = make_ulonglong4(0, 0, 0, 0);
-            for (i64 p = x_lo; p <= x_hi; ++p)
-                *reinterpret_cast<ulonglong4*>(&a.acc[(u64)((u32)p & a.g.ring_mask) * C + slot]) = z;
         }
     }
     fired_local = warp_sum_u64(fired_local); alerts_local = warp_sum_u64(alerts_local);

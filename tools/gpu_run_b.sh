@@ -11,6 +11,7 @@ B="--steps 20 --warmup 3"
 Q="$B --no-e2e --no-cpu-baseline --no-variants"
 if [ "$FULL_BENCH" = "1" ]; then timeout -s KILL 600 python bench.py $B > gpurun_out/b_bench_n1.json 2> gpurun_out/b_bench_n1.err; echo "bench rc=$?";
 else timeout -s KILL 300 python bench.py $Q > gpurun_out/b_bench_default.json 2>&1; fi
+shopt -s nullglob
 for f in build/variants/libfmq_*.so; do
   v=$(basename $f .so); v=${v#libfmq_}
   FMQ_LIB_PATH=$PWD/$f timeout -s KILL 300 python bench.py $Q $VARIANT_ARGS > gpurun_out/b_bench_$v.json 2>&1

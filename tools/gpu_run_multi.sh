@@ -6,7 +6,8 @@ mkdir -p gpurun_out
 nvidia-smi --query-gpu=index,name --format=csv,noheader | head -8
 timeout -s KILL 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/m${N}_smoke.log 2>&1 || { echo "SMOKE FAILED"; tail -30 gpurun_out/m${N}_smoke.log; exit 1; }
 if [ "$SKIP_TESTS" != "1" ]; then
-timeout -s KILL 1500 python -m pytest tests -m gpu -q --timeout 600 -rs ${PYTEST_K:+-k "$PYTEST_K"} > gpurun_out/m${N}_pytest.log 2>&1; echo "pytest rc=$?"; tail -25 gpurun_out/m${N}_pytest.log
+if [ -n "$PYTEST_IDS_FILE" ]; then mapfile -t IDS < "$PYTEST_IDS_FILE"; else IDS=(tests); fi
+timeout -s KILL 1500 python -m pytest "${IDS[@]}" -m gpu -v --timeout 600 -rs ${PYTEST_K:+-k "$PYTEST_K"} > gpurun_out/m${N}_pytest.log 2>&1; echo "pytest rc=$?"; tail -25 gpurun_out/m${N}_pytest.log
 fi
 run_bench () {   # $1 = tag, rest = bench args
   tag=$1; shift
