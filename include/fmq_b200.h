@@ -151,6 +151,14 @@ typedef struct fmq_config {
                                         (sideOutputLateData), this many rows between polls        */
     int32_t  overlapped_polls;       /* 1: second set of output columns for fmq_poll_all_begin/end */
     int32_t  reserved3;
+    int64_t  allowed_lateness_ms;    /* .allowedLateness(Time) — option 2 of the lateness handling the tutorial lists
+                                        (chapter3/README.md:211-212): a window's state is kept until
+                                        window_end - 1 + T <= watermark; a record that arrives for a window that has
+                                        fired but is still kept is added to it and the window fires AGAIN.  Flink
+                                        re-fires once per such record; here watermarks and outputs exist at micro-batch
+                                        boundaries only, so a (key, window) that took late records in a batch re-fires
+                                        ONCE at the end of that batch, with everything it holds by then.  Records
+                                        older than that are dropped / side-output as before.  0 = Flink's default.   */
 } fmq_config;
 
 /* one fired (key, window): 48 B per row */

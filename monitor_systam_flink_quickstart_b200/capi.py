@@ -49,6 +49,7 @@ class FmqConfig(C.Structure):
         ("ealert_capacity", C.c_uint64), ("calert_capacity", C.c_uint64),
         ("text_max_bytes", C.c_uint64), ("median_log_capacity", C.c_uint64), ("median_capacity", C.c_uint64),
         ("late_capacity", C.c_uint64), ("overlapped_polls", C.c_int32), ("reserved3", C.c_int32),
+        ("allowed_lateness_ms", C.c_int64),
     ]
 
 

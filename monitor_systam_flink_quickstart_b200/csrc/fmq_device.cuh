@@ -56,6 +56,7 @@ struct DevState {
     u64 dup_sampled, dup_found; u32 combine_dups;
     u32 pending_clear;               // panes whose clear is still in flight while the next batch is ingested (overlapped combiner mode)
     u64 n_late;                      // rows in the late side output
+    u64 n_dirty;                     // allowedLateness: (key, pane) cells that took a record after one of their windows had fired, this batch
     u64 n_mlog, n_mwork, n_median;   // median path: logged records, records selected for the window being fired, emitted rows
     u32 err_flags;
     u32 pad1;

@@ -45,6 +45,7 @@ struct fmq_handle {
     DevState* d_st = nullptr; DevState* h_st = nullptr;   // h_st: pinned mirror
     u32* h_hint = nullptr;                                // pinned word the plan kernel writes: skewed keys seen (picks the ingest variant)
     u64* d_keys = nullptr; Acc32* d_acc = nullptr; u32* d_kflags = nullptr; u64* d_kmax = nullptr;
+    u32* d_dirty = nullptr;              // allowedLateness: one bit per (ring pane, key slot)
     // staging for host-resident inputs
     i64* d_in_ts = nullptr; u64* d_in_key = nullptr; u64* d_in_val = nullptr;
     // host pushes: two staging sets filled on a copy stream, so that the copy-in of batch k+1 runs
@@ -122,7 +123,7 @@ const char* fmq_last_error(fmq_handle* h) { return h ? h->err.c_str() : g_create
 static void free_all(fmq_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
-    void* ptrs[] = {h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
+    void* ptrs[] = {h->d_dirty, h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
                     h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
                     h->d_pack[0], h->d_pack[1], h->kr_lead, h->kr_k, h->kr_fl, h->kr_in_c, h->kr_mk, h->kr_mb, h->kr_in_mk, h->kr_in_mb, h->d_counts, h->d_tiles, h->d_xchg, h->d_xsend, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad,
@@ -198,6 +199,15 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     h->g.slide32 = (cfg->window_slide_ms > 0 && cfg->window_slide_ms < 0x100000000ll) ? (u32)cfg->window_slide_ms : 0;
     h->g.panes_per_window = cfg->window_enabled ? (u32)(cfg->window_size_ms / cfg->window_slide_ms) : 0;
     if (cfg->window_enabled && h->g.panes_per_window >= h->ring) return fail(FMQ_ERR_BAD_ARG, "pane_ring must exceed window_size_ms / window_slide_ms");
+    if (cfg->allowed_lateness_ms < 0 || cfg->allowed_lateness_ms > (1ll << 40)) return fail(FMQ_ERR_BAD_ARG, "allowed_lateness_ms must be in [0, 2^40]");
+    if (cfg->allowed_lateness_ms > 0) {
+        if (!cfg->window_enabled) return fail(FMQ_ERR_BAD_ARG, "allowed_lateness_ms needs window_enabled");
+        if (cfg->median_log_capacity > 0) return fail(FMQ_ERR_BAD_ARG, "allowed_lateness_ms with the window median is not supported");
+        if ((uint64_t)(cfg->window_size_ms + cfg->allowed_lateness_ms) / (uint64_t)cfg->window_slide_ms + 1 >= h->ring)
+            return fail(FMQ_ERR_BAD_ARG, "pane_ring must exceed (window_size_ms + allowed_lateness_ms) / window_slide_ms + 1");
+        h->g.lateness = cfg->allowed_lateness_ms;
+        h->g.dirty_words = (h->capacity + 31) / 32;
+    }
 
     CUC(dalloc(&h->d_st, 1)); CUC(cudaMallocHost((void**)&h->h_st, sizeof(DevState)));
     CUC(cudaMallocHost((void**)&h->h_hint, 64)); memset(h->h_hint, 0, 64);
@@ -207,6 +217,10 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     CUC(cudaMemcpy(h->d_st, &init, sizeof(init), cudaMemcpyHostToDevice));
     CUC(dalloc(&h->d_keys, h->capacity)); CUC(cudaMemset(h->d_keys, 0xFF, h->capacity * 8));
     if (cfg->window_enabled) { CUC(dalloc(&h->d_acc, (size_t)h->ring * h->capacity)); CUC(cudaMemset(h->d_acc, 0, (size_t)h->ring * h->capacity * sizeof(Acc32))); }
+    if (h->g.lateness > 0) {
+        CUC(dalloc(&h->d_dirty, (size_t)h->ring * h->g.dirty_words)); CUC(cudaMemset(h->d_dirty, 0, (size_t)h->ring * h->g.dirty_words * 4));
+        h->g.dirty = h->d_dirty;
+    }
     CUC(dalloc(&h->d_in_ts, h->max_batch)); CUC(dalloc(&h->d_in_key, h->max_batch)); CUC(dalloc(&h->d_in_val, h->max_batch));
     if (cfg->window_enabled && cfg->emit_fired) {
         h->f_cap = cfg->fired_capacity ? cfg->fired_capacity : (2 * h->capacity > (1u << 20) ? 2 * h->capacity : (1u << 20));
@@ -574,6 +588,32 @@ static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now
     p.st = h->d_st; p.g = h->g; p.bound = c.max_out_of_orderness_ms; p.watermark_after = wm_after; p.n_events = (u64)n; p.window_enabled = c.window_enabled;
     p.is_auto = wm_after == FMQ_WM_AUTO; p.is_keep = wm_after == FMQ_WM_KEEP; p.overlap = h->overlap ? 1 : 0;
     p.combine_hint = h->h_hint;
+    auto fire_args = [&](bool refire) {
+        FireArgs f{};
+        f.st = h->d_st; f.dkeys = h->d_keys; f.acc = h->d_acc; f.g = h->g; f.dense_keys = c.key_mode == FMQ_KEYS_DENSE; f.emit_fired = c.emit_fired;
+        f.walert_source = c.walert_source; f.walert_op = c.walert_op;
+        f.mul = c.walert_mul == 0.0 ? 1.0 : c.walert_mul; f.d0 = c.walert_div0 == 0.0 ? 1.0 : c.walert_div0;
+        f.d1 = c.walert_div1 == 0.0 ? 1.0 : c.walert_div1; f.d2 = c.walert_div2 == 0.0 ? 1.0 : c.walert_div2; f.thr = c.walert_threshold;
+        f.f_key = h->f_key; f.f_wend = h->f_wend; f.f_count = h->f_count; f.f_sum = h->f_sum; f.f_min = h->f_min; f.f_max = h->f_max; f.f_cap = h->f_cap;
+        f.wa_key = h->wa_key; f.wa_wend = h->wa_wend; f.wa_val = h->wa_val; f.wa_cap = h->wa_cap;
+        f.world = h->world; f.clear_in_fire = (retire_now && !refire) ? 1 : 0; f.refire = refire ? 1 : 0;
+        const u64 per = (h->capacity + h->world - 1) / h->world;            // this rank fires a contiguous slot range
+        f.slot_lo = per * h->rank < h->capacity ? per * h->rank : h->capacity;
+        f.slot_hi = f.slot_lo + per < h->capacity ? f.slot_lo + per : h->capacity;
+        for (int r = 0; r < h->world; ++r) f.peer_acc[r] = h->peer_acc[r];
+        return f;
+    };
+    auto fire_blocks = [&](const FireArgs& f) {
+        size_t blocks = (f.slot_hi - f.slot_lo + FIRE_THREADS * FIRE_SPT - 1) / (FIRE_THREADS * FIRE_SPT); const size_t maxb = (size_t)h->num_sms * 8;
+        if (blocks > maxb) blocks = maxb;
+        return (unsigned)(blocks == 0 ? 1 : blocks);
+    };
+    if (c.window_enabled && h->g.lateness > 0) {
+        // allowedLateness: windows that had fired before this batch and took records in it fire again, under the watermark
+        // still in force, before the plan moves it (the kernel returns at once if the ingest marked nothing)
+        const FireArgs f = fire_args(true);
+        fire_kernel<V, false><<<fire_blocks(f), FIRE_THREADS, 0, h->stream>>>(f); LAUNCHED(h, "fire_kernel(refire)");
+    }
     plan_kernel<<<1, 32, 0, h->stream>>>(p); LAUNCHED(h, "plan_kernel");
     cudaStream_t fs = h->stream;
     if (h->overlap) {                                          // everything from the fire kernel on runs beside the next ingest
@@ -585,21 +625,8 @@ static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now
         wm_after >= INT64_MIN + c.window_size_ms + c.window_offset_ms + c.window_slide_ms + 2) h->anchored_known = true;
     if (c.window_enabled && h->ml_cap > 0) { int s_ = fire_medians(h); if (s_) return s_; }
     if (c.window_enabled) {
-        FireArgs f{};
-        f.st = h->d_st; f.dkeys = h->d_keys; f.acc = h->d_acc; f.g = h->g; f.dense_keys = c.key_mode == FMQ_KEYS_DENSE; f.emit_fired = c.emit_fired;
-        f.walert_source = c.walert_source; f.walert_op = c.walert_op;
-        f.mul = c.walert_mul == 0.0 ? 1.0 : c.walert_mul; f.d0 = c.walert_div0 == 0.0 ? 1.0 : c.walert_div0;
-        f.d1 = c.walert_div1 == 0.0 ? 1.0 : c.walert_div1; f.d2 = c.walert_div2 == 0.0 ? 1.0 : c.walert_div2; f.thr = c.walert_threshold;
-        f.f_key = h->f_key; f.f_wend = h->f_wend; f.f_count = h->f_count; f.f_sum = h->f_sum; f.f_min = h->f_min; f.f_max = h->f_max; f.f_cap = h->f_cap;
-        f.wa_key = h->wa_key; f.wa_wend = h->wa_wend; f.wa_val = h->wa_val; f.wa_cap = h->wa_cap;
-        f.world = h->world; f.clear_in_fire = retire_now ? 1 : 0;
-        const u64 per = (h->capacity + h->world - 1) / h->world;            // this rank fires a contiguous slot range
-        f.slot_lo = per * h->rank < h->capacity ? per * h->rank : h->capacity;
-        f.slot_hi = f.slot_lo + per < h->capacity ? f.slot_lo + per : h->capacity;
-        for (int r = 0; r < h->world; ++r) f.peer_acc[r] = h->peer_acc[r];
-        size_t blocks = (f.slot_hi - f.slot_lo + FIRE_THREADS * FIRE_SPT - 1) / (FIRE_THREADS * FIRE_SPT); const size_t maxb = (size_t)h->num_sms * 8;
-        if (blocks > maxb) blocks = maxb;
-        if (blocks == 0) blocks = 1;
+        const FireArgs f = fire_args(false);
+        const unsigned blocks = fire_blocks(f);
         if (h->world > 1) fire_kernel<V, true><<<(unsigned)blocks, FIRE_THREADS, 0, fs>>>(f);
         else              fire_kernel<V, false><<<(unsigned)blocks, FIRE_THREADS, 0, fs>>>(f);
         LAUNCHED(h, "fire_kernel");
@@ -1013,6 +1040,7 @@ int32_t fmq_attach_peers(fmq_handle* h, int32_t rank, int32_t world, const void*
     if (h->cfg.key_mode != FMQ_KEYS_DENSE) return set_err(h, FMQ_ERR_BAD_ARG, "combiner mode needs FMQ_KEYS_DENSE (slots must mean the same key on every rank)");
     if (h->ml_cap) return set_err(h, FMQ_ERR_BAD_ARG, "the window median needs every value of a key on one rank: route it through the all-to-all exchange instead");
     if (keyed_enabled(h->cfg)) return set_err(h, FMQ_ERR_BAD_ARG, "keyed ValueState operators depend on per-key order: route them through the all-to-all exchange instead");
+    if (h->g.lateness > 0) return set_err(h, FMQ_ERR_BAD_ARG, "allowed_lateness_ms is not supported in combiner mode: route the job through the keyBy exchange instead");
     for (int r = 0; r < world; ++r) {
         if (r != rank && !peer_tables[r]) return set_err(h, FMQ_ERR_BAD_ARG, "null peer table");
         h->peer_acc[r] = (r == rank) ? h->d_acc : static_cast<const Acc32*>(peer_tables[r]);

@@ -13,7 +13,30 @@ struct WindowGeom {
     u64 capacity;               // key slots per pane
     u32 slide32;                // slide if it fits 32 bits, else 0
     u32 panes_per_window;       // size / slide
+    i64 lateness;               // allowedLateness in ms (0: a window's state goes when it fires)
+    u32* dirty;                 // lateness > 0: one bit per (ring pane, key slot), dirty_words 32-bit words per pane
+    u64 dirty_words;
 };
+
+// allowedLateness: a record landed in a pane of which at least one window has fired already: that window must fire again.
+// Panes with relative index below `fired_panes` (counted from the pane origin) are such panes.
+__device__ __forceinline__ void mark_dirty(const WindowGeom& g, DevState* st, u32 ring_idx, u32 slot) {
+    const u32 bit = 1u << (slot & 31);
+    const u32 old = atomicOr(&g.dirty[(u64)ring_idx * g.dirty_words + (slot >> 5)], bit);
+    if (!(old & bit)) atomicAdd(&st->n_dirty, 1ull);
+}
+// Number of panes, counted from the pane origin, that belong to a window which has fired under the watermark in force
+// and is still kept.  Window ends are e = off (mod slide); fired: e <= wm + 1; kept: e > wm + 1 - lateness.  If such ends
+// exist, the panes concerned are exactly origin .. (largest fired end's index) - 1: the origin is the first pane whose
+// LAST window is still kept, and every pane up to there has a window inside the fired-and-kept range.
+__device__ __forceinline__ u32 fired_panes(const WindowGeom& g, const DevState* st) {
+    if (g.lateness <= 0 || !st->anchored) return 0u;
+    const i64 hi_idx = floor_div(st->wm + 1 - g.off, g.slide);                    // index of the largest end <= wm + 1
+    const i64 lo_idx = floor_div(st->wm + 1 - g.lateness - g.off, g.slide) + 1;   // index of the smallest end > wm + 1 - lateness
+    if (lo_idx > hi_idx) return 0u;
+    const i64 n = (hi_idx - 1) - st->origin_pane + 1;
+    return n <= 0 ? 0u : (n > 0x7FFFFFFF ? 0x7FFFFFFFu : (u32)n);
+}
 
 struct IngestArgs {
     const i64* ts; const u64* key; const void* val; size_t n;
@@ -340,6 +363,7 @@ struct IngestConst {
     i64 origin_ts, origin_pane; u32 origin_ring, slide, recip; u64 span, nbuckets; bool combine;
     // lean core
     u32 cap32, m32; bool exact32; u64 keep_policy;
+    u32 fired_n;                 // allowedLateness: relative panes below this have a fired window (0 = lateness off)
 };
 // pane quotient of a 32-bit offset: one multiply when ring * slide^2 <= 2^32 (ceil(2^32/slide) is then exact for every
 // offset inside the ring), else the estimate-and-correct form
@@ -401,6 +425,7 @@ __device__ __forceinline__ void ingest_core(const IngestArgs& a, DevState* st, c
         }
         const u64 idx = (u64)ring_[e] * a.g.capacity + slot;
         V v; memcpy(&v, &vb_[e], 8);
+        if (k.fired_n && valid && q_[e] < k.fired_n) mark_dirty(a.g, st, ring_[e], slot);
         accumulate_pair<V>(a.acc, valid, idx, v, a.g.agg_mask, k.combine, e == 0 && sample, r.dup, hot);
         slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
     }
@@ -485,6 +510,7 @@ __device__ __forceinline__ void ingest_core_lean(const IngestArgs& a, DevState* 
         }
         const u32 cell = ((k.origin_ring + q_[e]) & a.g.ring_mask) * k.cap32 + slot;
         slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
+        if (k.fired_n && valid && q_[e] < k.fired_n) mark_dirty(a.g, st, (k.origin_ring + q_[e]) & a.g.ring_mask, slot);
         accumulate_lean32<V>(acc_half, valid ? cell : 0xFFFFFFFFu, vb_[e], odd, oddmask, want, k.keep_policy);
     }
 }
@@ -542,6 +568,7 @@ __global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_
     // first d that falls outside the ring (< 2^32); panes still being cleared are not yet reusable
     k.span = (u64)(a.g.ring_mask + 1 - st->pending_clear) * k.slide;
     k.nbuckets = a.g.capacity >> 2;
+    k.fired_n = fired_panes(a.g, st);
     IngestRun r;
     if (k.combine) hot_init(&hot_tab);                           // ordered before its first use by the barrier after the prologue
 
@@ -734,6 +761,7 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
         k.exact32 = k.slide >= 2 && (u64)(a.g.ring_mask + 1) * k.slide * k.slide <= 0x100000000ull;
         k.m32 = k.exact32 ? (u32)((0x100000000ull + k.slide - 1) / k.slide) : 0u;
         k.keep_policy = l2_keep_policy();
+        k.fired_n = fired_panes(a.g, st);
     }
     IngestRun r;
     if (threadIdx.x == 0) seg_tab_fill<IW_TILE>(a, &seg, st);
@@ -889,6 +917,7 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
     const i64 origin_ts = anchored ? st->origin_ts : (a.g.off - a.g.slide);
     const i64 origin_pane = anchored ? st->origin_pane : -1;
     const u32 R = a.g.ring_mask + 1 - st->pending_clear;
+    const u32 gfired = fired_panes(a.g, st);
 
     u64 late = 0, nea = 0; i64 max_ts = I64_MIN_; i64 pmin = I64_MAX_, pmax = I64_MIN_; u32 err = 0;
 
@@ -928,7 +957,10 @@ __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __
                         u32 slot;
                         if (DENSE) { slot = key < a.g.capacity ? (u32)key : SLOT_INVALID; if (slot == SLOT_INVALID) err |= ERRB_BAD_INPUT; }
                         else slot = dir_find_or_insert(a.dkeys, a.g.capacity, key, st);
-                        if (slot != SLOT_INVALID) { valid = true; idx = (u64)((u32)p & a.g.ring_mask) * a.g.capacity + slot; }
+                        if (slot != SLOT_INVALID) {
+                            valid = true; idx = (u64)((u32)p & a.g.ring_mask) * a.g.capacity + slot;
+                            if (gfired && prel < gfired) mark_dirty(a.g, st, (u32)p & a.g.ring_mask, slot);
+                        }
                     }
                 }
             }
@@ -982,6 +1014,7 @@ __global__ void plan_kernel(const PlanArgs a) {
     if (a.seg_n) { n_events = 0; for (u32 s = 0; s < a.nseg; ++s) n_events += a.seg_n[s] < a.seg_cap ? a.seg_n[s] : a.seg_cap; }
     st->events_in += n_events;
     st->fire_count = 0; st->expire_lo = 1; st->expire_hi = 0; st->pending_clear = 0;
+    st->n_dirty = 0;                                           // the re-fire pass of this batch has run (it precedes the plan)
     if (!a.window_enabled) return;
     // skew adaptation for the next batch: pre-aggregate inside warps when > 3 % of the sampled lanes
     // shared their cell with another lane of the same warp
@@ -1007,14 +1040,14 @@ __global__ void plan_kernel(const PlanArgs a) {
     st->wm = target;
     // a watermark this close to INT64_MIN cannot make anything late or fire anything (ts >= 0) and would
     // overflow the pane arithmetic below: it is recorded and otherwise leaves the stream un-anchored
-    const i64 wm_floor = I64_MIN_ + a.g.size + a.g.off + a.g.slide + 2;
+    const i64 wm_floor = I64_MIN_ + a.g.size + a.g.off + a.g.slide + a.g.lateness + 2;
     if (target < wm_floor) return;
     const i64 size = a.g.size, slide = a.g.slide, off = a.g.off;
     const bool final_wm = (target == I64_MAX_);
     // first pane that stays live: p*slide + off + size - 1 > target
     i64 new_lo;
     if (final_wm) new_lo = has_data ? st->max_pane + 1 : 0;
-    else          new_lo = floor_div(target + 1 - size - off, slide) + 1;
+    else          new_lo = floor_div(target - a.g.lateness + 1 - size - off, slide) + 1;   // allowedLateness keeps a window's panes that much longer
     if (has_data) {
         // windows whose end-1 lies in (wm_old, target], clipped to windows that can hold data
         const i64 e_data_lo = st->min_pane * slide + off + slide;      // window whose last pane is min_pane
@@ -1068,6 +1101,8 @@ struct FireArgs {
     // by reading that range of EVERY rank's table over NVLink peer memory and combining the cells.
     int world;                  // 1 = single GPU
     int clear_in_fire;          // 1: the firing thread also clears expired panes (single GPU)
+    int refire;                 // allowedLateness pass (runs BEFORE the plan): the windows that had fired under the watermark still
+                                // in force and are still kept fire again for the keys whose panes took records in this batch
     u64 slot_lo, slot_hi;
     const Acc32* peer_acc[FMQ_MAX_PEERS];
     int emit_fired; int walert_source, walert_op; double mul, d0, d1, d2, thr;
@@ -1118,12 +1153,22 @@ template <typename V, bool PEERS>
 __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constant__ FireArgs a) {
     __shared__ FireWin wins[FIRE_MAXW];
     DevState* st = a.st;
-    const i64 nfire = st->fire_count;
-    const i64 x_lo = st->expire_lo, x_hi = st->expire_hi;
-    if (nfire == 0 && (x_lo > x_hi || !a.clear_in_fire)) return;
-    const i64 first_end = st->fire_first_end;
-    const i64 pmin = st->min_pane, pmax = st->max_pane;
     const i64 size = a.g.size, slide = a.g.slide, off = a.g.off;
+    const i64 pmin = st->min_pane, pmax = st->max_pane;
+    i64 nfire = st->fire_count, first_end = st->fire_first_end;
+    const i64 x_lo = st->expire_lo, x_hi = st->expire_hi;
+    if (a.refire) {
+        // window ends e = off (mod slide) with e - 1 <= wm (fired) and e - 1 + lateness > wm (still kept), clipped to windows that can hold data
+        if (st->n_dirty == 0 || !st->anchored || pmin > pmax) return;
+        const i64 wm = st->wm;
+        i64 e_hi = floor_div(wm + 1 - off, slide) * slide + off;
+        i64 e_lo = (floor_div(wm + 1 - a.g.lateness - off, slide) + 1) * slide + off;
+        const i64 d_lo = pmin * slide + off + slide, d_hi = pmax * slide + off + size;
+        if (d_lo > e_lo) e_lo = d_lo;
+        if (d_hi < e_hi) e_hi = d_hi;
+        if (e_hi < e_lo) return;
+        first_end = e_lo; nfire = (e_hi - e_lo) / slide + 1;
+    } else if (nfire == 0 && (x_lo > x_hi || !a.clear_in_fire)) return;
     const u64 C = a.g.capacity;
     constexpr bool is_f64 = IsF64<V>::value;
     const bool want_mx = a.g.agg_mask & 8u, want_mn = a.g.agg_mask & 4u;
@@ -1204,6 +1249,12 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
 #pragma unroll
                 for (int q = 0; q < FIRE_SPT; ++q) {
                     fired_[q] = live_[q] && count_[q] > 0;
+                    if (a.refire && fired_[q]) {                  // only the keys whose panes of this window took records in this batch
+                        bool any = false;
+                        for (u32 pi = 0; pi < w.np; ++pi)
+                            any = any || ((a.g.dirty[(u64)((w.p0 + pi) & a.g.ring_mask) * a.g.dirty_words + (slot_[q] >> 5)] >> (slot_[q] & 31)) & 1u);
+                        fired_[q] = any;
+                    }
                     // A6-ii/iii: ((double)sum * 8.0 / 60 / 1024 / 1024) < 100, evaluated left to right
                     double v = 0.0; bool hit = false;
                     if (a.walert_source != 0 && fired_[q]) {
@@ -1237,8 +1288,19 @@ __global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constan
                     if (hit_[q] && row_a != ~0ull) { a.wa_key[row_a] = key_[q]; a.wa_wend[row_a] = w.wend; a.wa_val[row_a] = v_[q]; ++row_a; }
                 }
             }
+            if (a.refire && last_pass) {                          // the marks of this batch are spent
+                const i64 r0 = (first_end - size - off) / slide, r1 = (first_end + (nfire - 1) * slide - off) / slide - 1;
+                const i64 c0 = r0 < pmin ? pmin : r0, c1 = r1 > pmax ? pmax : r1;
+#pragma unroll
+                for (int q = 0; q < FIRE_SPT; ++q)
+                    if (live_[q]) for (i64 p = c0; p <= c1; ++p) {
+                        u32* wd = &a.g.dirty[(u64)((u32)p & a.g.ring_mask) * a.g.dirty_words + (slot_[q] >> 5)];
+                        const u32 bit = 1u << (slot_[q] & 31);
+                        if (*wd & bit) atomicAnd(wd, ~bit);
+                    }
+            }
             // cleanup: WindowOperator.clearAllState for panes whose last window has fired
-            if (a.clear_in_fire && last_pass) {
+            if (a.clear_in_fire && !a.refire && last_pass) {
                 const ulonglong4 z = make_ulonglong4(0, 0, 0, 0);
 #pragma unroll
                 for (int q = 0; q < FIRE_SPT; ++q)

@@ -202,6 +202,7 @@ template <typename Row, typename F> size_t drain(std::vector<Row>& v, size_t cap
 extern "C" {
 int32_t orcp_create(const fmq_config* cfg, int32_t threads, void** out) {
     if (!cfg || !out || cfg->struct_size != sizeof(fmq_config) || threads < 1) return FMQ_ERR_BAD_ARG;
+    if (cfg->allowed_lateness_ms != 0) return FMQ_ERR_BAD_ARG;      // restated in flink_literal.cpp only
     if (cfg->value_type == FMQ_VAL_F64) *out = new Par<double>(*cfg, threads); else *out = new Par<int64_t>(*cfg, threads);
     return FMQ_OK;
 }

@@ -90,6 +90,8 @@ struct Oracle : OracleBase {
     std::map<WKey, Acc<V>> wstate;                             // Heap{Reducing,Aggregating}State
     std::map<WKey, std::vector<V>> wlist;                      // HeapListState: ComputeCpuMiddle.java:34 (process(...))
     std::set<std::tuple<int64_t, uint64_t, int64_t>> timers;   // (timestamp, key, window start)
+    std::set<std::tuple<int64_t, uint64_t, int64_t>> cleanup;  // allowedLateness > 0: (maxTimestamp + lateness, key, window start)
+    std::set<std::pair<int64_t, uint64_t>> refire;             // (window start, key) that took a record after having fired, this batch
     int64_t current_wm = INT64_MIN;                            // InternalTimerServiceImpl.currentWatermark
     // BoundedOutOfOrdernessTimestampExtractor (chapter3/README.md:342-397)
     int64_t current_max_ts; int64_t last_emitted_wm = INT64_MIN;
@@ -130,11 +132,12 @@ struct Oracle : OracleBase {
         if (ts > current_max_ts) current_max_ts = ts;
         // --- WindowOperator.processElement, non-merging branch (Appendix A.3, A.4) ---
         const int64_t size = cfg.window_size_ms, slide = cfg.window_slide_ms, off = cfg.window_offset_ms;
+        const int64_t lateness = cfg.allowed_lateness_ms;
         bool skipped = true;
         int64_t last_start = window_start(ts, off, slide);
         for (int64_t s = last_start; s > ts - size; s -= slide) {
             int64_t max_ts = s + size - 1;                       // TimeWindow.maxTimestamp()
-            if (max_ts + 0 <= current_wm) continue;              // isWindowLate, allowedLateness = 0
+            if (max_ts + lateness <= current_wm) continue;       // isWindowLate: cleanupTime(window) <= currentWatermark
             skipped = false;
             auto it = wstate.find({key, s});
             if (it == wstate.end()) {
@@ -145,9 +148,14 @@ struct Oracle : OracleBase {
                 a.mn = java_min(a.mn, val); a.mx = java_max(a.mx, val);
             }
             if (cfg.median_log_capacity > 0) wlist[{key, s}].push_back(val);
-            timers.insert({max_ts, key, s});                     // EventTimeTrigger.onElement (+ cleanup timer, same ts)
+            // EventTimeTrigger.onElement: a window whose maxTimestamp has passed FIREs at once (allowedLateness > 0
+            // only: otherwise such a window is late).  Here outputs exist at micro-batch boundaries, so the window
+            // re-fires once at the end of this batch (see fmq_config.allowed_lateness_ms).
+            if (max_ts <= current_wm) refire.insert({s, key});
+            else timers.insert({max_ts, key, s});                // registerEventTimeTimer(maxTimestamp)
+            if (lateness > 0) cleanup.insert({max_ts + lateness, key, s});   // registerCleanupTimer
         }
-        if (skipped && ts + 0 <= current_wm) {                   // numLateRecordsDropped / sideOutput(lateDataOutputTag, element)
+        if (skipped && ts + lateness <= current_wm) {                   // numLateRecordsDropped / sideOutput(lateDataOutputTag, element)
             ctr.late_dropped++;
             if (cfg.late_capacity > 0) late.push_back({ts, key, bits_of(val)});
         }
@@ -166,6 +174,25 @@ struct Oracle : OracleBase {
         return src * one_if_zero(cfg.walert_mul) / one_if_zero(cfg.walert_div0) / one_if_zero(cfg.walert_div1) / one_if_zero(cfg.walert_div2);
     }
 
+    // emitWindowContents for one (key, window): the fired row and the alert evaluated on it
+    void emit_window(uint64_t key, int64_t s, const Acc<V>& a) {
+        const int64_t wend = s + cfg.window_size_ms;
+        ctr.windows_fired++;
+        if (cfg.emit_fired) fired.push_back({key, wend, a.count, bits_of(a.sum), bits_of(a.mn), bits_of(a.mx)});
+        if (cfg.walert_source != FMQ_ALERT_NONE) {
+            double v = alert_value(a);
+            if (cmp(v, cfg.walert_op, cfg.walert_threshold)) { walerts.push_back({key, wend, v}); ctr.window_alerts++; }
+        }
+    }
+    // windows that had fired already and took records in this batch: one more firing each, before the next watermark
+    void refire_pending() {
+        for (const auto& r : refire) {
+            auto it = wstate.find({r.second, r.first});
+            if (it != wstate.end()) emit_window(r.second, r.first, it->second);
+        }
+        refire.clear();
+    }
+
     void advance_watermark(int64_t wm) {
         if (wm <= current_wm) return;
         current_wm = wm; ctr.watermark = wm;
@@ -177,13 +204,7 @@ struct Oracle : OracleBase {
             if (tts != wend - 1) continue;                       // EventTimeTrigger.onEventTime
             auto it = wstate.find({key, s});
             if (it == wstate.end()) continue;
-            const Acc<V>& a = it->second;
-            ctr.windows_fired++;
-            if (cfg.emit_fired) fired.push_back({key, wend, a.count, bits_of(a.sum), bits_of(a.mn), bits_of(a.mx)});
-            if (cfg.walert_source != FMQ_ALERT_NONE) {
-                double v = alert_value(a);
-                if (cmp(v, cfg.walert_op, cfg.walert_threshold)) { walerts.push_back({key, wend, v}); ctr.window_alerts++; }
-            }
+            emit_window(key, s, it->second);
             if (cfg.median_log_capacity > 0) {
                 // ComputeCpuMiddle.java:36-47: copy, Collections.sort (Double.compareTo), middle element(s)
                 std::vector<V>& vals = wlist[{key, s}];
@@ -193,7 +214,12 @@ struct Oracle : OracleBase {
                 medians.push_back({key, wend, med});
                 wlist.erase({key, s});
             }
-            wstate.erase(it);                                    // clearAllState at cleanup time
+            if (cfg.allowed_lateness_ms == 0) wstate.erase(it);  // clearAllState: cleanup time == fire time
+        }
+        // cleanup timers (maxTimestamp + allowedLateness): the window's state goes, later records for it are late
+        while (!cleanup.empty() && std::get<0>(*cleanup.begin()) <= wm) {
+            auto t = *cleanup.begin(); cleanup.erase(cleanup.begin());
+            wstate.erase({std::get<1>(t), std::get<2>(t)});
         }
     }
 
@@ -211,6 +237,7 @@ struct Oracle : OracleBase {
             process_element(ts[i], key[i], v[i]);
         }
         // FMQ_WM_KEEP: no Watermark element follows these records (WindowOperator#processElement never moves time)
+        if (cfg.window_enabled) refire_pending();
         if (cfg.window_enabled && wm_after != FMQ_WM_KEEP) advance_watermark(wm_after == FMQ_WM_AUTO ? auto_watermark() : wm_after);
         ctr.keys = kstate.size();
         return FMQ_OK;

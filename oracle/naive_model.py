@@ -83,6 +83,9 @@ class NaiveFlinkModel:
         self.window = bool(g("window_enabled", 0))
         self.size, self.slide, self.off = g("window_size_ms", 0), g("window_slide_ms", 0), g("window_offset_ms", 0)
         self.bound = g("max_out_of_orderness_ms", 0)
+        self.lateness = g("allowed_lateness_ms", 0)
+        self.cleanup = []          # heap of (maxTimestamp + lateness, key, window_start)
+        self.refire = set()        # (key, window_start) that took a record after having fired, this batch
         self.emit_fired = g("emit_fired", 1)
         self.wsrc, self.wop, self.wthr = g("walert_source", 0), g("walert_op", 0), g("walert_threshold", 0.0)
         self.scale = [g(k, 0.0) or 1.0 for k in ("walert_mul", "walert_div0", "walert_div1", "walert_div2")]
@@ -126,7 +129,7 @@ class NaiveFlinkModel:
         skipped = True
         s = last_start
         while s > ts - self.size:
-            if not (s + self.size - 1 <= self.wm):
+            if not (s + self.size - 1 + self.lateness <= self.wm):
                 skipped = False
                 a = self.state.get((key, s))
                 if a is None:
@@ -136,11 +139,15 @@ class NaiveFlinkModel:
                     a[1] = a[1] + val if self.is_f64 else _wrap64(a[1] + val)
                     a[2], a[3] = _jmin(a[2], val), _jmax(a[3], val)
                 t = (s + self.size - 1, key, s)
-                if t not in self.timer_set:
+                if t[0] <= self.wm:
+                    self.refire.add((key, s))          # fired already, still kept: fires again at the end of this batch
+                elif t not in self.timer_set:
                     self.timer_set.add(t)
                     heapq.heappush(self.timers, t)
+                    if self.lateness > 0:
+                        heapq.heappush(self.cleanup, (t[0] + self.lateness, key, s))
             s -= self.slide
-        if skipped and ts <= self.wm:
+        if skipped and ts + self.lateness <= self.wm:
             self.late_dropped += 1
 
     def _alert_value(self, a):
@@ -153,6 +160,23 @@ class NaiveFlinkModel:
             v = v / d
         return v
 
+    def _emit(self, key, s, a):
+        self.windows_fired += 1
+        wend = s + self.size
+        if self.emit_fired:
+            self.fired.append((key, wend, a[0], a[1], a[2], a[3]))
+        if self.wsrc:
+            v = self._alert_value(a)
+            if _CMP[self.wop](v, self.wthr):
+                self.walerts.append((key, wend, v))
+
+    def _refire_pending(self):
+        for key, s in sorted(self.refire):
+            a = self.state.get((key, s))
+            if a is not None:
+                self._emit(key, s, a)
+        self.refire = set()
+
     def _advance(self, wm):
         if wm <= self.wm:
             return
@@ -161,23 +185,20 @@ class NaiveFlinkModel:
             t = heapq.heappop(self.timers)
             self.timer_set.discard(t)
             _, key, s = t
-            a = self.state.pop((key, s), None)
+            a = self.state.get((key, s)) if self.lateness > 0 else self.state.pop((key, s), None)
             if a is None:
                 continue
-            self.windows_fired += 1
-            wend = s + self.size
-            if self.emit_fired:
-                self.fired.append((key, wend, a[0], a[1], a[2], a[3]))
-            if self.wsrc:
-                v = self._alert_value(a)
-                if _CMP[self.wop](v, self.wthr):
-                    self.walerts.append((key, wend, v))
+            self._emit(key, s, a)
+        while self.cleanup and self.cleanup[0][0] <= wm:
+            _, key, s = heapq.heappop(self.cleanup)
+            self.state.pop((key, s), None)
 
     def push_batch(self, ts, key, val, watermark_after=I64_MIN):
         self.rolling = []
         for t, k, v in zip(ts, key, val):
             self._element(int(t), int(k), float(v) if self.is_f64 else int(v))
         if self.window:
+            self._refire_pending()
             if watermark_after == I64_MIN + 1:       # FMQ_WM_KEEP: no watermark follows this batch
                 return
             if watermark_after == I64_MIN:

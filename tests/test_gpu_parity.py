@@ -200,6 +200,61 @@ def test_keep_before_any_watermark_leaves_the_stream_unanchored():
     compare_all(gpu, cpu)
 
 
+# ---- .allowedLateness(T): option 2 of the lateness handling the tutorial lists (chapter3/README.md:211-212) ----------
+def test_allowed_lateness_known_answer():
+    """One 10 s window, T = 5 s: two records, the window fires; a third record arrives late but within T: the window
+    fires again with all three; after the watermark passes window end - 1 + T a fourth record is dropped."""
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=10_000, allowed_lateness_ms=5000, late_capacity=16, **SMALL)
+    e = capi.Engine(**kw)
+    one = lambda t, v: (np.array([t], np.int64), np.array([7], np.uint64), np.array([v], np.float64))  # noqa: E731
+    e.push_batch(np.array([1000, 2000], np.int64), np.array([7, 7], np.uint64), np.array([1.0, 2.0]), 12_000)
+    f = e.poll_fired(); assert (f.window_end.tolist(), f.count.tolist(), f.sum.tolist()) == ([10_000], [2], [3.0])
+    e.push_batch(*one(3000, 4.0), capi.FMQ_WM_KEEP)                        # late, but the window is still kept: it fires again
+    f = e.poll_fired(); assert (f.window_end.tolist(), f.count.tolist(), f.sum.tolist(), f.max.tolist()) == ([10_000], [3], [7.0], [4.0])
+    e.push_batch(*one(3500, 8.0), 14_998)                                   # window end - 1 + T = 14 999 > 14 998: still kept
+    f = e.poll_fired(); assert (f.count.tolist(), f.sum.tolist()) == ([4], [15.0])
+    e.push_batch(*one(4000, 16.0), 14_999)                                  # judged against 14 998: accepted, re-fired, then the state goes
+    f = e.poll_fired(); assert (f.count.tolist(), f.sum.tolist()) == ([5], [31.0])
+    e.push_batch(*one(5000, 32.0), capi.FMQ_WM_KEEP)                        # the window is gone: dropped
+    assert len(e.poll_fired()) == 0 and e.counters()["late_dropped"] == 1 and e.poll_late().ts.tolist() == [5000]
+    e.flush()
+    assert len(e.poll_fired()) == 0 and e.counters()["windows_fired"] == 4
+
+
+@pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
+@pytest.mark.parametrize("name", ["tumbling_f64", "sliding_i64", "sliding_offset_short_T"])
+def test_allowed_lateness_parity(name, key_mode):
+    """Streams with a heavy late tail (some of it within T, some beyond), automatic / explicit / absent watermarks:
+    fired rows (first firings and re-firings), alerts, the late side output and every counter against the oracle."""
+    cfgs = {
+        "tumbling_f64": (dict(window_size_ms=10_000, window_slide_ms=10_000, max_out_of_orderness_ms=3000, allowed_lateness_ms=15_000,
+                              walert_source=capi.FMQ_ALERT_AVG, walert_op=capi.FMQ_CMP_GT, walert_threshold=55.0), "f64"),
+        "sliding_i64": (dict(value_type=capi.FMQ_VAL_I64, window_size_ms=30_000, window_slide_ms=10_000, window_offset_ms=3000, max_out_of_orderness_ms=5000,
+                             allowed_lateness_ms=25_000, walert_source=capi.FMQ_ALERT_SUM, walert_op=capi.FMQ_CMP_LT, walert_mul=8.0, walert_div0=60.0,
+                             walert_div1=1024.0, walert_div2=1024.0, walert_threshold=0.5), "i64"),
+        "sliding_offset_short_T": (dict(window_size_ms=20_000, window_slide_ms=5000, window_offset_ms=1234, max_out_of_orderness_ms=2000, allowed_lateness_ms=3000), "f64"),
+    }
+    c, vt = cfgs[name]
+    kw = dict(window_enabled=1, agg_mask=15, late_capacity=1 << 17, key_mode=key_mode, table_capacity=1 << 12, pane_ring=64, max_batch=1 << 16, **c)
+    gpu, cpu = pair(**kw)
+    spec = StreamSpec(n_keys=700, events_per_ms=2, jitter_ms=4000, late_frac_ppm=150_000, late_extra_ms=40_000, value_type=vt)
+    t0 = spec.t0
+    wms = [capi.FMQ_WM_AUTO, capi.FMQ_WM_AUTO, capi.FMQ_WM_KEEP, capi.FMQ_WM_AUTO, t0 + 70_000, capi.FMQ_WM_KEEP, capi.FMQ_WM_AUTO, capi.FMQ_WM_AUTO]
+    for i, wm in enumerate(wms):
+        ts, key, val = generate_numpy(spec, i * 30_000, 30_000 if i != 5 else 777)
+        for e in (gpu, cpu):
+            e.push_batch(ts, key, val, wm)
+        if i % 3 == 1:
+            compare_all(gpu, cpu)
+    compare_all(gpu, cpu)
+    for e in (gpu, cpu):
+        e.flush()
+    compare_all(gpu, cpu)
+    c = cpu.counters()
+    assert c["windows_fired"] > 0 and (name == "sliding_i64" or c["late_dropped"] > 0)     # sliding_i64 keeps everything this stream brings
+    f = cpu.poll_fired()
+
+
 def test_explicit_watermarks_and_empty_batches():
     kw = dict(window_enabled=1, agg_mask=15, window_size_ms=5000, window_slide_ms=5000, **SMALL)
     gpu, cpu = pair(**kw)

@@ -23,6 +23,13 @@ CFGS = {
                         walert_source=capi.FMQ_ALERT_SUM, walert_op=capi.FMQ_CMP_LT, walert_mul=8.0, walert_div0=60.0,
                         walert_div1=1024.0, walert_div2=1024.0, walert_threshold=0.5,
                         consec_n=2, consec_threshold=500000.0, consec_reset_on_fire=0),
+    # .allowedLateness(T): windows kept T ms after they fired, re-fired once per batch that added records to them
+    "tumbling_late_f64": dict(window_enabled=1, agg_mask=15, window_size_ms=10_000, window_slide_ms=10_000, max_out_of_orderness_ms=3000,
+                              allowed_lateness_ms=15_000, walert_source=capi.FMQ_ALERT_AVG, walert_op=capi.FMQ_CMP_GT, walert_threshold=55.0),
+    "sliding_late_i64": dict(value_type=capi.FMQ_VAL_I64, window_enabled=1, agg_mask=15, window_size_ms=30_000, window_slide_ms=10_000,
+                             window_offset_ms=3000, max_out_of_orderness_ms=5000, allowed_lateness_ms=25_000,
+                             walert_source=capi.FMQ_ALERT_SUM, walert_op=capi.FMQ_CMP_LT, walert_mul=8.0, walert_div0=60.0,
+                             walert_div1=1024.0, walert_div2=1024.0, walert_threshold=0.5),
 }
 
 
