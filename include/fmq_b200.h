@@ -151,6 +151,11 @@ typedef struct fmq_config {
                                         (sideOutputLateData), this many rows between polls        */
     int32_t  overlapped_polls;       /* 1: second set of output columns for fmq_poll_all_begin/end */
     int32_t  reserved3;
+    uint64_t text_dict_capacity;     /* > 0: fmq_parse_text / fmq_push_text dictionary-encode the host / channel strings on the
+                                        device: the key column carries dense ids 0, 1, 2, ... in order of first sight (what
+                                        FMQ_KEYS_DENSE wants), this many distinct strings at most; names come back through
+                                        fmq_dict_lookup.  0: the key column carries fmq_text_key_hash(string)           */
+    uint64_t text_dict_arena_bytes;  /* bytes kept for the strings themselves (default 32 per entry)                   */
     int64_t  allowed_lateness_ms;    /* .allowedLateness(Time) — option 2 of the lateness handling the tutorial lists
                                         (chapter3/README.md:211-212): a window's state is kept until
                                         window_end - 1 + T <= watermark; a record that arrives for a window that has
@@ -319,12 +324,19 @@ int32_t fmq_get_key_state(fmq_handle* h, const uint64_t* keys, size_t n, int32_t
 #define FMQ_TEXT_OK 0u
 #define FMQ_TEXT_MALFORMED 1u
 #define FMQ_TEXT_VALUE_ON_HOST 2u
+#define FMQ_TEXT_KEY_ON_HOST 3u      /* dictionary mode: the string shares its 64-bit hash with another one, or the dictionary is full */
 uint64_t fmq_text_key_hash(const char* s, size_t len);
 int32_t fmq_parse_text(fmq_handle* h, const char* text, size_t bytes, int32_t text_mem, int32_t format,
                        int32_t utc_offset_hours, int64_t* ts_out, uint64_t* key_out, void* val_out,
                        uint32_t* status_out, size_t cap, int32_t out_mem, size_t* n_lines, size_t* n_bad);
 int32_t fmq_push_text(fmq_handle* h, const char* text, size_t bytes, int32_t text_mem, int32_t format,
                       int32_t utc_offset_hours, int64_t watermark_after, size_t* n_lines);
+/* Replaces: the String the reference prints with every result (`value.f0` / `value.f1` in the sinks, e.g.
+ * BandwidthMonitorWithEventTime.java:55) — the names behind dictionary ids (fmq_config.text_dict_capacity > 0).
+ * fmq_dict_size: number of ids handed out so far.  fmq_dict_lookup: names of n ids into host rows of `stride` bytes
+ * (zero padded, truncated if longer); lens[i] = the name's full length, UINT32_MAX for an id never handed out. */
+int32_t fmq_dict_size(fmq_handle* h, size_t* n_ids);
+int32_t fmq_dict_lookup(fmq_handle* h, const uint64_t* ids, size_t n, char* names_out, size_t stride, uint32_t* lens_out);
 
 /* Replaces: AbstractStreamOperator#snapshotState / #initializeState (the checkpoint hooks the
  * tutorial's promised-but-unwritten next chapter is about, chapter3/README.md:454-456).  A snapshot is

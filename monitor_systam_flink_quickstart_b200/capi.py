@@ -19,7 +19,7 @@ FMQ_VAL_F64, FMQ_VAL_I64 = 0, 1
 FMQ_MEM_HOST, FMQ_MEM_DEVICE = 0, 1
 FMQ_KEYS_HASHED, FMQ_KEYS_DENSE = 0, 1
 FMQ_TEXT_CPU, FMQ_TEXT_FLOW = 0, 1
-FMQ_TEXT_OK, FMQ_TEXT_MALFORMED, FMQ_TEXT_VALUE_ON_HOST = 0, 1, 2
+FMQ_TEXT_OK, FMQ_TEXT_MALFORMED, FMQ_TEXT_VALUE_ON_HOST, FMQ_TEXT_KEY_ON_HOST = 0, 1, 2, 3
 FMQ_CMP_GT, FMQ_CMP_LT, FMQ_CMP_GE, FMQ_CMP_LE = 0, 1, 2, 3
 FMQ_AGG_COUNT, FMQ_AGG_SUM, FMQ_AGG_MIN, FMQ_AGG_MAX = 1, 2, 4, 8
 FMQ_ALERT_NONE, FMQ_ALERT_SUM, FMQ_ALERT_AVG, FMQ_ALERT_MIN, FMQ_ALERT_MAX, FMQ_ALERT_COUNT = range(6)
@@ -49,6 +49,7 @@ class FmqConfig(C.Structure):
         ("ealert_capacity", C.c_uint64), ("calert_capacity", C.c_uint64),
         ("text_max_bytes", C.c_uint64), ("median_log_capacity", C.c_uint64), ("median_capacity", C.c_uint64),
         ("late_capacity", C.c_uint64), ("overlapped_polls", C.c_int32), ("reserved3", C.c_int32),
+        ("text_dict_capacity", C.c_uint64), ("text_dict_arena_bytes", C.c_uint64),
         ("allowed_lateness_ms", C.c_int64),
     ]
 
@@ -165,6 +166,8 @@ def _declare(lib, p: str, has_mem: bool = True, side_outputs: Optional[bool] = N
         sig("text_key_hash", [C.c_char_p, sz], C.c_uint64)
         sig("parse_text", [vp, vp, sz, i32, i32, i32, vp, vp, vp, vp, sz, i32, psz, psz])
         sig("push_text", [vp, vp, sz, i32, i32, i32, i64, psz])
+        sig("dict_size", [vp, psz])
+        sig("dict_lookup", [vp, vp, sz, vp, sz, vp])
         sig("poll_all_begin", [vp, C.POINTER(FmqFiredCols), sz, C.POINTER(FmqWAlertCols), sz, C.POINTER(FmqEventCols), sz, psz])
         sig("poll_all_end", [vp])
         sig("snapshot_size", [vp, psz])
@@ -491,6 +494,20 @@ class Engine(EngineBase):
         n = C.c_size_t(0)
         self._check(self._lib.fmq_push_text(self._h, text, len(text), FMQ_MEM_HOST, fmt, utc_offset_hours, watermark_after, C.byref(n)))
         return n.value
+
+    def dict_size(self) -> int:
+        n = C.c_size_t(0)
+        self._check(self._lib.fmq_dict_size(self._h, C.byref(n)))
+        return n.value
+
+    def dict_lookup(self, ids, stride: int = 64):
+        """Names behind dictionary ids (text_dict_capacity > 0) -> list of str (None for an id never handed out)."""
+        ids = np.ascontiguousarray(ids, dtype=np.uint64)
+        n = len(ids)
+        out = np.zeros((n, stride), np.uint8); lens = np.zeros(n, np.uint32)
+        if n:
+            self._check(self._lib.fmq_dict_lookup(self._h, ids.ctypes.data, n, out.ctypes.data, stride, lens.ctypes.data))
+        return [None if l == 0xFFFFFFFF else bytes(out[i, :min(int(l), stride)]).decode("utf-8", "replace") for i, l in enumerate(lens)]
 
     # ---- checkpointing (snapshotState / initializeState) ------------------------------------------
     def snapshot(self) -> np.ndarray:

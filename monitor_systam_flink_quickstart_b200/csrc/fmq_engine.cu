@@ -96,6 +96,9 @@ struct fmq_handle {
     u64* md_key = nullptr; i64* md_wend = nullptr; double* md_val = nullptr; u64 md_cap = 0; size_t cur_median = 0;
     // text ingest
     char* d_text = nullptr; u64* d_line_start = nullptr; u32* d_txt_status = nullptr; unsigned long long* d_txt_bad = nullptr;
+    // device dictionary (text_dict_capacity > 0): hash table, names, where every line's key field lies
+    u64* dt_hash = nullptr; u32* dt_id = nullptr; u64 dt_mask = 0; u64* dn_off = nullptr; u32* dn_len = nullptr; char* dn_arena = nullptr; u64 dn_arena_cap = 0;
+    unsigned long long* dt_counters = nullptr; u64* d_key_off = nullptr; u32* d_key_len = nullptr;
 };
 
 #define CU(h, call)                                                                                   \
@@ -123,7 +126,7 @@ const char* fmq_last_error(fmq_handle* h) { return h ? h->err.c_str() : g_create
 static void free_all(fmq_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
-    void* ptrs[] = {h->d_dirty, h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
+    void* ptrs[] = {h->dt_hash, h->dt_id, h->dn_off, h->dn_len, h->dn_arena, h->dt_counters, h->d_key_off, h->d_key_len, h->d_dirty, h->d_st, h->d_keys, h->d_acc, h->d_kflags, h->d_kmax, h->d_in_ts, h->d_in_key, h->d_in_val,
                     h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
                     h->d_pack[0], h->d_pack[1], h->kr_lead, h->kr_k, h->kr_fl, h->kr_in_c, h->kr_mk, h->kr_mb, h->kr_in_mk, h->kr_in_mb, h->d_counts, h->d_tiles, h->d_xchg, h->d_xsend, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad,
@@ -276,6 +279,18 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     if (cfg->text_max_bytes > 0) {
         CUC(dalloc(&h->d_text, cfg->text_max_bytes + 64)); CUC(dalloc(&h->d_line_start, h->max_batch + 2));
         CUC(dalloc(&h->d_txt_status, h->max_batch)); CUC(dalloc(&h->d_txt_bad, 1));
+        if (cfg->text_dict_capacity > 0) {
+            if (cfg->text_dict_capacity >= 0xFFFFFFF0ull) return fail(FMQ_ERR_BAD_ARG, "text_dict_capacity must be < 2^32");
+            if (cfg->key_mode == FMQ_KEYS_DENSE && cfg->text_dict_capacity > h->capacity) return fail(FMQ_ERR_BAD_ARG, "text_dict_capacity cannot exceed table_capacity of a FMQ_KEYS_DENSE handle (ids index the table)");
+            u64 slots = 64; while (slots < 2 * cfg->text_dict_capacity) slots <<= 1;
+            h->dt_mask = slots - 1;
+            h->dn_arena_cap = cfg->text_dict_arena_bytes ? cfg->text_dict_arena_bytes : 32 * cfg->text_dict_capacity;
+            CUC(dalloc(&h->dt_hash, slots)); CUC(cudaMemset(h->dt_hash, 0xFF, slots * 8));
+            CUC(dalloc(&h->dt_id, slots)); CUC(cudaMemset(h->dt_id, 0xFF, slots * 4));
+            CUC(dalloc(&h->dn_off, cfg->text_dict_capacity)); CUC(dalloc(&h->dn_len, cfg->text_dict_capacity));
+            CUC(dalloc(&h->dn_arena, h->dn_arena_cap)); CUC(dalloc(&h->dt_counters, 4)); CUC(cudaMemset(h->dt_counters, 0, 32));
+            CUC(dalloc(&h->d_key_off, h->max_batch)); CUC(dalloc(&h->d_key_len, h->max_batch));
+        }
         const size_t nb = (cfg->text_max_bytes + TXT_CHUNK - 1) / TXT_CHUNK + 1;
         if (nb > h->counts_len) return fail(FMQ_ERR_BAD_ARG, "text_max_bytes too large for this max_batch (raise max_batch)");
     }
@@ -1166,8 +1181,14 @@ static int parse_text_to_staging(fmq_handle* h, const char* text, size_t bytes, 
     txt_mark_kernel<<<nblocks, TXT_THREADS, 0, h->stream>>>(d, bytes, h->d_counts, h->d_line_start, h->max_batch + 2); LAUNCHED(h, "txt_mark_kernel");
     if (last != '\n') { const u64 end = bytes; CU(h, cudaMemcpyAsync(h->d_line_start + lines, &end, 8, cudaMemcpyHostToDevice, h->stream)); }
     CU(h, cudaMemsetAsync(h->d_txt_bad, 0, 8, h->stream));
-    TextArgs a{d, bytes, h->d_line_start, lines, format, utc, h->d_in_ts, h->d_in_key, h->d_in_val, h->d_txt_status, h->d_txt_bad};
+    TextArgs a{d, bytes, h->d_line_start, lines, format, utc, h->d_in_ts, h->d_in_key, h->d_in_val, h->d_txt_status, h->d_txt_bad, h->d_key_off, h->d_key_len};
     txt_parse_kernel<<<(unsigned)((lines + 255) / 256), 256, 0, h->stream>>>(a); LAUNCHED(h, "txt_parse_kernel");
+    if (h->dt_hash && lines > 0) {                                         // strings -> dense ids, in order of first sight
+        DictArgs da{h->dt_hash, h->dt_id, h->dt_mask, h->dn_off, h->dn_len, h->dn_arena, h->dn_arena_cap, h->cfg.text_dict_capacity, h->dt_counters,
+                    d, h->d_key_off, h->d_key_len, lines, h->d_in_key, h->d_txt_status, h->d_txt_bad};
+        dict_insert_kernel<<<(unsigned)((lines + 255) / 256), 256, 0, h->stream>>>(da); LAUNCHED(h, "dict_insert_kernel");
+        dict_lookup_kernel<<<(unsigned)((lines + 255) / 256), 256, 0, h->stream>>>(da); LAUNCHED(h, "dict_lookup_kernel");
+    }
     unsigned long long bad = 0;
     CU(h, cudaMemcpyAsync(&bad, h->d_txt_bad, 8, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
@@ -1197,6 +1218,34 @@ int32_t fmq_push_text(fmq_handle* h, const char* text, size_t bytes, int32_t tex
     int s = parse_text_to_staging(h, text, bytes, text_mem, format, utc, n_lines, &bad); if (s) return s;
     if (bad) { h->err = std::to_string(bad) + " line(s) are malformed or need a host-side value parse: use fmq_parse_text and fix them"; return FMQ_ERR_BAD_ARG; }
     return fmq_push_batch(h, (const int64_t*)h->d_in_ts, (const uint64_t*)h->d_in_key, h->d_in_val, *n_lines, wm_after, FMQ_MEM_DEVICE);
+}
+
+int32_t fmq_dict_size(fmq_handle* h, size_t* n_ids) {
+    if (!h || !n_ids) return FMQ_ERR_BAD_ARG;
+    if (!h->dt_hash) return set_err(h, FMQ_ERR_BAD_ARG, "the device dictionary is not enabled (fmq_config.text_dict_capacity)");
+    CU(h, cudaSetDevice(h->device));
+    unsigned long long c[4];
+    CU(h, cudaMemcpyAsync(c, h->dt_counters, 32, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    *n_ids = (size_t)(c[0] < h->cfg.text_dict_capacity ? c[0] : h->cfg.text_dict_capacity);
+    return FMQ_OK;
+}
+int32_t fmq_dict_lookup(fmq_handle* h, const uint64_t* ids, size_t n, char* names_out, size_t stride, uint32_t* lens_out) {
+    if (!h || (n && (!ids || !names_out || !lens_out)) || stride == 0) return FMQ_ERR_BAD_ARG;
+    if (!h->dt_hash) return set_err(h, FMQ_ERR_BAD_ARG, "the device dictionary is not enabled (fmq_config.text_dict_capacity)");
+    if (n == 0) return FMQ_OK;
+    size_t n_ids = 0;
+    int s = fmq_dict_size(h, &n_ids); if (s) return s;
+    struct Tmp { void* p = nullptr; ~Tmp() { if (p) cudaFree(p); } } tmp;
+    const size_t bytes = n * 8 + n * 4 + n * stride;
+    CU(h, cudaMalloc(&tmp.p, bytes));
+    u64* d_ids = static_cast<u64*>(tmp.p); u32* d_lens = reinterpret_cast<u32*>(d_ids + n); char* d_rows = reinterpret_cast<char*>(d_lens + n);
+    CU(h, cudaMemcpyAsync(d_ids, ids, n * 8, cudaMemcpyHostToDevice, h->stream));
+    dict_names_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(d_ids, n, h->dn_off, h->dn_len, h->dn_arena, (u64)n_ids, d_rows, stride, d_lens); LAUNCHED(h, "dict_names_kernel");
+    CU(h, cudaMemcpyAsync(lens_out, d_lens, n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaMemcpyAsync(names_out, d_rows, n * stride, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return FMQ_OK;
 }
 
 // ---- snapshot / restore (Flink snapshotState / initializeState) --------------------

@@ -13,7 +13,7 @@ constexpr u32 TXT_CHUNK = 4096;          // bytes per block in the newline passe
 constexpr int TXT_THREADS = 128;         // 32 bytes per thread
 
 // per-line status written to `status_out`
-constexpr u32 TXT_OK = 0, TXT_MALFORMED = 1, TXT_VALUE_ON_HOST = 2;
+constexpr u32 TXT_OK = 0, TXT_MALFORMED = 1, TXT_VALUE_ON_HOST = 2, TXT_KEY_ON_HOST = 3;
 
 __global__ void __launch_bounds__(TXT_THREADS) txt_count_kernel(const char* __restrict__ text, size_t bytes, u32* __restrict__ counts) {
     __shared__ u32 wsum[TXT_THREADS / 32];
@@ -126,6 +126,7 @@ struct TextArgs {
     int format;                 // 0: "<epoch-s> <host> <cpu> <usage>" -> f64;  1: "<ISO> <channel> <flow>" -> i64
     int utc_offset_hours;       // the reference uses ZoneOffset.ofHours(8)
     i64* ts; u64* key; u64* val; u32* status; unsigned long long* n_bad;
+    u64* key_off; u32* key_len;     // optional: where the key field of every line lies in the text (device dictionary)
 };
 
 __global__ void __launch_bounds__(256) txt_parse_kernel(const TextArgs a) {
@@ -164,7 +165,80 @@ __global__ void __launch_bounds__(256) txt_parse_kernel(const TextArgs a) {
         }
     }
     a.ts[li] = ts; a.key[li] = key; a.val[li] = vb; a.status[li] = st;
+    if (a.key_off) { a.key_off[li] = lo + (size_t)fs[1]; a.key_len[li] = (nf > 1 && fl[1] > 0) ? (u32)fl[1] : 0u; }
     if (st != TXT_OK) atomicAdd(a.n_bad, 1ull);
+}
+
+// ---- device dictionary: host / channel strings -> dense ids 0, 1, 2, ... -------------------------
+// What the reference's `map` + keyBy(String) amounts to for the state behind it (Main.java:21-25,
+// BandwidthMonitorWithEventTime.java:39-45): every distinct string gets the next free id the first time it is
+// seen, the id indexes the FMQ_KEYS_DENSE tables directly, and the string is kept in an arena so that rows can be
+// printed with the name again (fmq_dict_lookup).  Open addressing on the 64-bit FNV/mix hash of the string; the
+// strings themselves are compared on lookup, so two strings that share a hash are told apart (the second one is
+// handed back to the host, TXT_KEY_ON_HOST, rather than merged).
+// Two kernels, so that nobody ever waits for another thread: `insert` claims hash slots (the CAS winner allocates
+// the id and copies the string), `lookup` runs after it and reads only published entries.
+struct DictArgs {
+    u64* hash; u32* id; u64 mask;                       // table of mask + 1 slots (a power of two), KEY_EMPTY = free
+    u64* name_off; u32* name_len; char* arena; u64 arena_cap; u64 id_cap;
+    unsigned long long* counters;                       // [0] next id, [1] arena bytes used, [2] error flags (1 = ids, 2 = arena)
+    const char* text; const u64* key_off; const u32* key_len; size_t n_lines;
+    u64* key; u32* status; unsigned long long* n_bad;
+};
+__global__ void __launch_bounds__(256) dict_insert_kernel(const DictArgs a) {
+    const size_t li = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= a.n_lines || a.status[li] == TXT_MALFORMED) return;
+    const u64 h = a.key[li];
+    for (u64 s = h & a.mask, probe = 0; probe <= a.mask; ++probe, s = (s + 1) & a.mask) {
+        u64 cur = a.hash[s];
+        if (cur == KEY_EMPTY) cur = atomicCAS(&a.hash[s], KEY_EMPTY, h);
+        if (cur == KEY_EMPTY) {                                            // first sight of this hash: this thread enters the string
+            const u64 id = atomicAdd(&a.counters[0], 1ull);
+            const u32 len = a.key_len[li];
+            const u64 off = atomicAdd(&a.counters[1], (unsigned long long)len);
+            if (id >= a.id_cap) { atomicOr(&a.counters[2], 1ull); a.id[s] = 0xFFFFFFFFu; return; }
+            if (off + len > a.arena_cap) { atomicOr(&a.counters[2], 2ull); a.id[s] = 0xFFFFFFFFu; return; }
+            const char* src = a.text + a.key_off[li];
+            for (u32 i = 0; i < len; ++i) a.arena[off + i] = src[i];
+            a.name_off[id] = off; a.name_len[id] = len; a.id[s] = (u32)id;
+            return;
+        }
+        if (cur == h) return;                                              // known (or being entered by the winner right now)
+    }
+    atomicOr(&a.counters[2], 1ull);
+}
+__global__ void __launch_bounds__(256) dict_lookup_kernel(const DictArgs a) {
+    const size_t li = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= a.n_lines || a.status[li] == TXT_MALFORMED) return;
+    const u64 h = a.key[li];
+    u64 out = KEY_EMPTY;
+    for (u64 s = h & a.mask, probe = 0; probe <= a.mask; ++probe, s = (s + 1) & a.mask) {
+        const u64 cur = a.hash[s];
+        if (cur == KEY_EMPTY) break;
+        if (cur != h) continue;
+        const u32 id = a.id[s];
+        if (id == 0xFFFFFFFFu) break;                                      // dictionary full
+        const u32 len = a.key_len[li];
+        bool same = a.name_len[id] == len;
+        const char* x = a.arena + a.name_off[id]; const char* y = a.text + a.key_off[li];
+        for (u32 i = 0; same && i < len; ++i) same = x[i] == y[i];
+        if (same) out = id;
+        break;                                                             // same hash, another string: not merged, the host takes it
+    }
+    if (out == KEY_EMPTY) { if (a.status[li] == TXT_OK) atomicAdd(a.n_bad, 1ull); a.status[li] = TXT_KEY_ON_HOST; out = 0; }
+    a.key[li] = out;
+}
+// names of `n` ids into rows of `stride` bytes (zero padded); lens[i] = full length, 0xFFFFFFFF for an unknown id
+__global__ void __launch_bounds__(256) dict_names_kernel(const u64* ids, size_t n, const u64* name_off, const u32* name_len, const char* arena, u64 n_ids,
+                                                         char* out, size_t stride, u32* lens) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u64 id = ids[i];
+    char* row = out + i * stride;
+    if (id >= n_ids) { lens[i] = 0xFFFFFFFFu; for (size_t j = 0; j < stride; ++j) row[j] = 0; return; }
+    const u32 len = name_len[id]; lens[i] = len;
+    const char* src = arena + name_off[id];
+    for (size_t j = 0; j < stride; ++j) row[j] = j < len ? src[j] : 0;
 }
 
 }  // namespace fmq
