@@ -557,30 +557,38 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
 
 __global__ void set_mlog_kernel(DevState* st) { st->n_mlog = st->n_mwork; }
 
-// N3: for every window the plan says is firing, select its records from the value log, sort them by
-// (slot, value) and emit one median per key; then drop the records of expired panes from the log.
-// The sizes of these steps are data-dependent, so this (slow by nature) path reads the plan back.
+// N3: the records of every window the plan says is firing are selected from the value log — all windows of the
+// fire in one pass (in groups only when their (record, window) pairs would not fit the work buffer) — sorted by value
+// (Collections.sort order) and then, stably, by (window, key), and one thread per (window, key) picks the middle.
+// One read-back of the plan per push sizes the launches; nothing is synchronised per window.
 static int sync_state(fmq_handle* h);
 static int fire_medians(fmq_handle* h) {
     int s = sync_state(h); if (s) return s;
     const DevState d = *h->h_st;
-    const i64 size = h->g.size, slide = h->g.slide, off = h->g.off;
+    const i64 size = h->g.size, slide = h->g.slide, off = h->g.off, k = size / slide;
     const size_t off_mwork = offsetof(DevState, n_mwork);
     const unsigned grid = (unsigned)h->num_sms * 4;
-    for (i64 j = 0; j < d.fire_count && d.n_mlog > 0; ++j) {
-        const i64 wend = d.fire_first_end + j * slide;
-        const i64 p0 = (wend - size - off) / slide, p1 = (wend - off) / slide - 1;
-        CU(h, cudaMemsetAsync((char*)h->d_st + off_mwork, 0, 8, h->stream));
-        median_select_kernel<<<grid, MED_THREADS, 0, h->stream>>>(h->ml_pane[h->ml_cur], h->ml_slot[h->ml_cur], h->ml_val[h->ml_cur], h->d_st, p0, p1,
-                                                                 h->mw_items[0], h->mw_vals, h->ml_cap); LAUNCHED(h, "median_select_kernel");
-        s = sync_state(h); if (s) return s;
-        const size_t nsel = (size_t)h->h_st->n_mwork;
-        if (nsel == 0) continue;
-        int cur = 0;
-        s = sort_items(h, h->mw_items, nsel, 64, F64ValueKey{h->mw_vals}, &cur); if (s) return s;      // Collections.sort order
-        s = sort_items(h, h->mw_items, nsel, h->slot_bits, SlotKey{}, &cur); if (s) return s;           // stable: groups by key
-        MedianEmitArgs m{h->mw_items[cur], h->mw_vals, nsel, h->d_keys, h->cfg.key_mode == FMQ_KEYS_DENSE, wend, h->d_st, h->md_key, h->md_wend, h->md_val, h->md_cap};
-        median_emit_kernel<<<grid, MED_THREADS, 0, h->stream>>>(m); LAUNCHED(h, "median_emit_kernel");
+    if (d.fire_count > 0 && d.n_mlog > 0) {
+        // windows per group: every record lies in at most min(G, k) of G consecutive windows
+        i64 G = d.fire_count;
+        const u64 per = (u64)(G < k ? G : k);
+        if (d.n_mlog * per > h->ml_cap) { G = (i64)(h->ml_cap / d.n_mlog); if (G > k) G = k; if (G < 1) G = 1; }
+        u32 jbits = 1; while ((1ll << jbits) <= G) ++jbits;                  // 2^jbits > G: a real group key is never all ones
+        if (jbits + h->slot_bits > 32) return set_err(h, FMQ_ERR_BAD_ARG, "window median: too many windows fire at once for this table size (advance the watermark in smaller steps)");
+        for (i64 j0 = 0; j0 < d.fire_count; j0 += G) {
+            const i64 nj = d.fire_count - j0 < G ? d.fire_count - j0 : G;
+            u64 bound = d.n_mlog * (u64)(nj < k ? nj : k); if (bound > h->ml_cap) bound = h->ml_cap;
+            CU(h, cudaMemsetAsync((char*)h->d_st + off_mwork, 0, 8, h->stream));
+            CU(h, cudaMemsetAsync(h->mw_items[0], 0xFF, bound * 8, h->stream));
+            median_select_all_kernel<<<grid, MED_THREADS, 0, h->stream>>>(h->ml_pane[h->ml_cur], h->ml_slot[h->ml_cur], h->ml_val[h->ml_cur], h->d_st, size, slide, off, j0, nj,
+                                                                         h->slot_bits, h->mw_items[0], h->mw_vals, bound); LAUNCHED(h, "median_select_all_kernel");
+            int cur = 0;
+            s = sort_items(h, h->mw_items, (size_t)bound, 64, F64ValueKey{h->mw_vals, bound}, &cur); if (s) return s;      // Collections.sort order
+            s = sort_items(h, h->mw_items, (size_t)bound, h->slot_bits + jbits, SlotKey{}, &cur); if (s) return s;          // stable: groups by (window, key)
+            MedianEmitArgs m{h->mw_items[cur], h->mw_vals, bound, h->d_keys, h->cfg.key_mode == FMQ_KEYS_DENSE, d.fire_first_end + j0 * slide, h->d_st,
+                             h->md_key, h->md_wend, h->md_val, h->md_cap, h->slot_bits, slide};
+            median_emit_kernel<<<grid, MED_THREADS, 0, h->stream>>>(m); LAUNCHED(h, "median_emit_kernel");
+        }
     }
     if (d.expire_lo <= d.expire_hi && d.n_mlog > 0) {
         CU(h, cudaMemsetAsync((char*)h->d_st + off_mwork, 0, 8, h->stream));
@@ -1260,6 +1268,7 @@ size_t snap_bytes(const fmq_handle* h) {
     size_t b = sizeof(SnapHeader) + sizeof(DevState) + h->capacity * 8;
     if (h->cfg.window_enabled) b += (size_t)h->ring * h->capacity * sizeof(Acc32);
     if (keyed_enabled(h->cfg)) b += h->capacity * 4 + h->capacity * 8;
+    if (h->ml_cap) b += (size_t)h->ml_cap * 20;                  // the window median's value log (pane, slot, value)
     return b;
 }
 bool same_job(const fmq_config& a, const fmq_config& b) {
@@ -1279,7 +1288,6 @@ int32_t fmq_snapshot(fmq_handle* h, void* buf, size_t cap, size_t* written) {
     if (!h || !buf || !written) return FMQ_ERR_BAD_ARG;
     if (h->sticky) return FMQ_ERR_POISONED;
     if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "snapshot of a combiner-mode handle is not supported");
-    if (h->ml_cap) return set_err(h, FMQ_ERR_BAD_ARG, "snapshot of a handle with the window median enabled is not supported yet");
     const size_t need = snap_bytes(h);
     if (cap < need) return set_err(h, FMQ_ERR_BAD_ARG, "snapshot buffer too small (see fmq_snapshot_size)");
     int st = sync_state(h); if (st) return st;
@@ -1295,6 +1303,12 @@ int32_t fmq_snapshot(fmq_handle* h, void* buf, size_t cap, size_t* written) {
     if (hd.has_keyed) {
         CU(h, cudaMemcpyAsync(p, h->d_kflags, h->capacity * 4, cudaMemcpyDeviceToHost, h->stream)); p += h->capacity * 4;
         CU(h, cudaMemcpyAsync(p, h->d_kmax, h->capacity * 8, cudaMemcpyDeviceToHost, h->stream)); p += h->capacity * 8;
+    }
+    if (h->ml_cap) {
+        const int c = h->ml_cur;
+        CU(h, cudaMemcpyAsync(p, h->ml_pane[c], h->ml_cap * 8, cudaMemcpyDeviceToHost, h->stream)); p += h->ml_cap * 8;
+        CU(h, cudaMemcpyAsync(p, h->ml_val[c], h->ml_cap * 8, cudaMemcpyDeviceToHost, h->stream)); p += h->ml_cap * 8;
+        CU(h, cudaMemcpyAsync(p, h->ml_slot[c], h->ml_cap * 4, cudaMemcpyDeviceToHost, h->stream)); p += h->ml_cap * 4;
     }
     CU(h, cudaStreamSynchronize(h->stream));
     *written = need;
@@ -1315,13 +1329,20 @@ int32_t fmq_restore(fmq_handle* h, const void* buf, size_t bytes) {
     if (h->copy_stream) CU(h, cudaStreamSynchronize(h->copy_stream));
     const char* p = static_cast<const char*>(buf) + sizeof(SnapHeader);
     DevState d; memcpy(&d, p, sizeof(d)); p += sizeof(d);
-    d.n_fired = d.n_walert = d.n_ealert = d.n_calert = 0; d.n_late = 0; d.n_median = 0; d.n_mlog = 0; d.n_mwork = 0; d.err_flags = 0;
+    d.n_fired = d.n_walert = d.n_ealert = d.n_calert = 0; d.n_late = 0; d.n_median = 0; d.n_mwork = 0; d.n_dirty = 0; d.err_flags = 0;
+    if (!h->ml_cap) d.n_mlog = 0;
     CU(h, cudaMemcpyAsync(h->d_st, &d, sizeof(d), cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaMemcpyAsync(h->d_keys, p, h->capacity * 8, cudaMemcpyHostToDevice, h->stream)); p += h->capacity * 8;
     if (hd.has_window) { const size_t b = (size_t)h->ring * h->capacity * sizeof(Acc32); CU(h, cudaMemcpyAsync(h->d_acc, p, b, cudaMemcpyHostToDevice, h->stream)); p += b; }
     if (hd.has_keyed) {
         CU(h, cudaMemcpyAsync(h->d_kflags, p, h->capacity * 4, cudaMemcpyHostToDevice, h->stream)); p += h->capacity * 4;
         CU(h, cudaMemcpyAsync(h->d_kmax, p, h->capacity * 8, cudaMemcpyHostToDevice, h->stream)); p += h->capacity * 8;
+    }
+    if (h->ml_cap) {
+        h->ml_cur = 0;
+        CU(h, cudaMemcpyAsync(h->ml_pane[0], p, h->ml_cap * 8, cudaMemcpyHostToDevice, h->stream)); p += h->ml_cap * 8;
+        CU(h, cudaMemcpyAsync(h->ml_val[0], p, h->ml_cap * 8, cudaMemcpyHostToDevice, h->stream)); p += h->ml_cap * 8;
+        CU(h, cudaMemcpyAsync(h->ml_slot[0], p, h->ml_cap * 4, cudaMemcpyHostToDevice, h->stream)); p += h->ml_cap * 4;
     }
     CU(h, cudaStreamSynchronize(h->stream));
     h->cur_fired = h->cur_walert = h->cur_ealert = h->cur_calert = 0; h->cur_late = 0; h->cur_median = 0;

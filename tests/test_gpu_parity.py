@@ -465,6 +465,35 @@ def test_window_median_parity(key_mode, slide):
     assert_fired_equal(gpu.poll_fired(), cpu.poll_fired())
 
 
+def test_window_median_many_windows_per_fire_small_work_buffer_and_snapshot():
+    """Watermarks that jump: a dozen sliding windows fire in one push (all of them selected and sorted in one pass, or in
+    groups when the (record, window) pairs would not fit the work buffer: the log capacity here is barely above the
+    log's size), and a snapshot taken in the middle carries the value log along."""
+    kw = dict(window_enabled=1, agg_mask=15, window_size_ms=20_000, window_slide_ms=5000, max_out_of_orderness_ms=2000,
+              median_log_capacity=70_000, **SMALL)
+    gpu, cpu = pair(**kw)
+    spec = StreamSpec(n_keys=500, events_per_ms=1, jitter_ms=2000, late_frac_ppm=10000, late_extra_ms=15000)
+    med = []
+    wms = [capi.FMQ_WM_KEEP, capi.FMQ_WM_KEEP, capi.FMQ_WM_AUTO, capi.FMQ_WM_KEEP, capi.FMQ_WM_AUTO, capi.FMQ_WM_AUTO]
+    for b, wm in enumerate(wms):
+        ts, key, val = generate_numpy(spec, b * 20_000, 20_000)
+        gpu.push_batch(ts, key, val, wm); cpu.push_batch(ts, key, val, wm)
+        if b == 3:
+            med.append(gpu.poll_medians()); fired_before = gpu.poll_fired()
+            snap = gpu.snapshot()
+            gpu.close()
+            gpu = capi.Engine(**kw)
+            gpu.restore(snap)
+    gpu.flush(); cpu.flush()
+    med.append(gpu.poll_medians())
+    a = sort_walerts(capi.WindowAlerts(*[np.concatenate([getattr(m, f) for m in med]) for f in ("key", "window_end", "value")])); w = sort_walerts(cpu.poll_medians())
+    assert len(w) > 5000
+    np.testing.assert_array_equal(a.key, w.key); np.testing.assert_array_equal(a.window_end, w.window_end)
+    np.testing.assert_array_equal(a.value.view(np.uint64), w.value.view(np.uint64))
+    f2 = gpu.poll_fired()
+    assert_fired_equal(capi.Fired(*[np.concatenate([getattr(x, f) for x in (fired_before, f2)]) for f in ("key", "window_end", "count", "sum", "min", "max")]), cpu.poll_fired())
+
+
 # ---- checkpoint / restore (SURVEY §8f N4) ---------------------------------------------------------
 @pytest.mark.parametrize("key_mode", [capi.FMQ_KEYS_HASHED, capi.FMQ_KEYS_DENSE])
 def test_snapshot_restore_continues_exactly(key_mode):
