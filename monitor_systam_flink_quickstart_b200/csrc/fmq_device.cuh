@@ -160,20 +160,17 @@ __device__ __forceinline__ int bucket_match(const ulonglong4& kv, u64 key) {
     return j;
 }
 
-// Same as dir_resolve below but inlined into the ingest loop.
+__device__ __noinline__ u32 dir_resolve(u64* __restrict__ dkeys, u64 nbuckets, u64 key, u64 b, ulonglong4 kv, DevState* st);
+// The lookup inlined into the ingest loop: the key is in a bucket of its probe sequence (every event of a running
+// job).  A bucket with a free slot means first sight of the key: the claim (a compare-and-swap ladder) lives out of
+// line — ncu of the hashed ingest kernel had `no_instruction` as its top stall (3 per issue): four inlined copies of
+// that ladder per tile made the streaming loop larger than the instruction cache.
 __device__ __forceinline__ u32 dir_resolve_inline(u64* __restrict__ dkeys, u64 nbuckets, u64 key, u64 b, ulonglong4 kv, DevState* st) {
+#pragma unroll 1
     for (u64 probe = 0; probe < nbuckets; ++probe) {
         const int j = bucket_match(kv, key);
         if (j >= 0) return (u32)(b * 4 + j);
-        const u64 k4[4] = {kv.x, kv.y, kv.z, kv.w};
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            if (k4[q] == KEY_EMPTY) {                                   // first sight of this key: claim the slot
-                const u64 old = atomicCAS(dkeys + b * 4 + q, KEY_EMPTY, key);
-                if (old == KEY_EMPTY) { atomicAdd(&st->keys, 1ull); return (u32)(b * 4 + q); }
-                if (old == key) return (u32)(b * 4 + q);
-            }
-        }
+        if (kv.x == KEY_EMPTY || kv.y == KEY_EMPTY || kv.z == KEY_EMPTY || kv.w == KEY_EMPTY) return dir_resolve(dkeys, nbuckets, key, b, kv, st);
         b = (b + 1 == nbuckets) ? 0 : b + 1;
         kv = ld_bucket(dkeys + b * 4);
     }

@@ -2,7 +2,7 @@
 # single-GPU run: smoke, GPU test suite, bench of the default build and of every library under build/variants
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out; rm -f gpurun_out/b_*
-timeout -s KILL 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/b_smoke.log 2>&1 || { echo "SMOKE FAILED"; tail -30 gpurun_out/b_smoke.log; exit 1; }
+timeout -s KILL 120 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/b_smoke.log 2>&1 || { echo "SMOKE FAILED"; tail -30 gpurun_out/b_smoke.log; exit 1; }
 echo "smoke ok"
 if [ "$SKIP_TESTS" != "1" ]; then
 timeout -s KILL 1800 python -m pytest tests -m gpu -q --timeout 900 ${PYTEST_ARGS:--x} > gpurun_out/b_pytest.log 2>&1; echo "pytest rc=$?"; tail -${PYTEST_TAIL:-15} gpurun_out/b_pytest.log

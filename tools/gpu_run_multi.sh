@@ -4,7 +4,7 @@ cd "$(dirname "$0")/.."
 N=${N:-2}
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=index,name --format=csv,noheader | head -8
-timeout -s KILL 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/m${N}_smoke.log 2>&1 || { echo "SMOKE FAILED"; tail -30 gpurun_out/m${N}_smoke.log; exit 1; }
+timeout -s KILL 120 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/m${N}_smoke.log 2>&1 || { echo "SMOKE FAILED"; tail -30 gpurun_out/m${N}_smoke.log; exit 1; }
 if [ "$SKIP_TESTS" != "1" ]; then
 if [ -n "$PYTEST_IDS_FILE" ]; then mapfile -t IDS < "$PYTEST_IDS_FILE"; else IDS=(tests); fi
 timeout -s KILL 1500 python -m pytest "${IDS[@]}" -m gpu -v --timeout 600 -rs ${PYTEST_K:+-k "$PYTEST_K"} > gpurun_out/m${N}_pytest.log 2>&1; echo "pytest rc=$?"; tail -25 gpurun_out/m${N}_pytest.log
