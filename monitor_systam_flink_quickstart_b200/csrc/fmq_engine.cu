@@ -470,12 +470,6 @@ static int stage_keyed(fmq_handle* h, const i64* ts, const u64* key, const V* va
     return FMQ_OK;
 }
 
-// A/B switch for measurements: FMQ_INGEST_LEGACY=1 runs round 1's block-staged ingest kernel instead of the warp-ring one
-static bool ingest_legacy() {
-    static const bool v = [] { const char* e = getenv("FMQ_INGEST_LEGACY"); return e && e[0] == '1'; }();
-    return v;
-}
-
 // stage 1 of a push: everything that touches only this handle's own events
 static u64 peer_timeout_ns();
 static u32 xs_ingest_blocks();
@@ -500,7 +494,7 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
                                                      (u64)h->ring * h->capacity < 0x80000000ull);
         const bool dense = c.key_mode == FMQ_KEYS_DENSE;
         const bool extras = h->ml_cap > 0 || h->lt_cap > 0;
-        if (fast_geom && !ingest_legacy()) {
+        if (fast_geom) {
             // persistent grid: every warp streams its own ring of 128-event tiles
             size_t blocks = (n * (seg.nseg ? seg.nseg : 1) + (size_t)IW_TILE * IW_WARPS - 1) / ((size_t)IW_TILE * IW_WARPS);
             // a rank of the keyBy exchange leaves room on every SM for the scatter of the next batch (one block of ~53 KB)
@@ -520,16 +514,8 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         const size_t tile = (size_t)INGEST_THREADS * INGEST_EPT;
         size_t blocks = (n * (seg.nseg ? seg.nseg : 1) + tile - 1) / tile; const size_t maxb = (size_t)h->num_sms * FMQ_INGEST_MIN_BLOCKS;   // persistent: resident blocks only
         if (blocks > maxb) blocks = maxb;
-        if (c.window_enabled && fast_geom && ingest_legacy() && seg.nseg <= 1) {          // A/B: the block-staged kernel of round 1
-            auto kfn = dense ? (extras ? ingest_fast_kernel<V, true, true> : ingest_fast_kernel<V, true, false>)
-                             : (extras ? ingest_fast_kernel<V, false, true> : ingest_fast_kernel<V, false, false>);
-            CU(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, INGEST_SMEM_BYTES));
-            kfn<<<(unsigned)blocks, INGEST_THREADS, INGEST_SMEM_BYTES, h->stream>>>(a);
-            LAUNCHED(h, "ingest_fast_kernel");
-        }
-        if ((c.window_enabled && (!fast_geom || !h->anchored_known)) || (!c.window_enabled && ingest_legacy())) {
+        if (c.window_enabled && (!fast_geom || !h->anchored_known)) {
             IngestArgs g = a;
-            g.force_generic = c.window_enabled ? 0 : 1;          // (legacy A/B only: filter-only jobs went through this kernel)
             if (dense) ingest_generic_kernel<V, true><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(g);
             else       ingest_generic_kernel<V, false><<<(unsigned)blocks, INGEST_THREADS, 0, h->stream>>>(g);
             LAUNCHED(h, "ingest_generic_kernel");

@@ -44,7 +44,6 @@ struct IngestArgs {
     // segment s of every column starts seg_stride elements after segment s-1 and holds seg_n[s] events,
     // a count that lives in device memory (n is then the capacity of a segment).  nseg <= 1: one plain batch of n.
     u32 nseg; size_t seg_stride; const u64* seg_n;
-    int force_generic;          // the generic kernel runs whatever the stream position says
     DevState* st;
     u64* dkeys;
     Acc32* acc;
@@ -317,20 +316,12 @@ __device__ __forceinline__ size_t seg_locate(const IngestArgs& a, const SegTab& 
     return (size_t)s * a.seg_stride + first;
 }
 
-// ---- ingest, fast kernel --------------------------------------------------------------------------
+// ---- ingest, fast path ------------------------------------------------------------------------------
 // Preconditions (checked on the device): the stream is anchored (a watermark exists, so the pane
-// origin is known) and pane_ring * slide < 2^32, so the pane of a record is a 32-bit quotient of
-// (ts - origin).  Per event the late test, the pane and the accumulate are predicated, not branched.
-//
-// Staging: the three event columns are streamed into shared memory by the TMA engine
-// (cp.async.bulk 1-D copies completing on an mbarrier, L2 evict-first policy) through a ring of
-// INGEST_STAGES tiles per block, issued INGEST_STAGES tiles ahead by one thread.  The compute
-// threads therefore never wait on HBM latency themselves: their only global-memory traffic is the
-// directory bucket load (hashed keys) and the fire-and-forget RED updates.
-constexpr int INGEST_STAGES = 3;
-constexpr int INGEST_TILE = INGEST_THREADS * INGEST_EPT;                       // 1024 events = 3 x 8 KB
-constexpr int INGEST_SMEM_BYTES = INGEST_STAGES * 3 * INGEST_TILE * 8;         // 72 KB of dynamic shared memory
-
+// origin is known), pane_ring * slide < 2^32, so the pane of a record is a 32-bit quotient of
+// (ts - origin), and the table has fewer than 2^31 cells.  Per event the late test, the pane and the
+// accumulate are predicated, not branched.  The event columns are streamed into shared memory by the
+// TMA engine (cp.async.bulk 1-D copies completing on an mbarrier, L2 evict-first policy).
 __device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(u64* bar, u32 count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -512,167 +503,6 @@ __device__ __forceinline__ void ingest_core_lean(const IngestArgs& a, DevState* 
         slot_[e] = slot; vmask |= valid ? (1u << e) : 0u;
         if (k.fired_n && valid && q_[e] < k.fired_n) mark_dirty(a.g, st, (k.origin_ring + q_[e]) & a.g.ring_mask, slot);
         accumulate_lean32<V>(acc_half, valid ? cell : 0xFFFFFFFFu, vb_[e], odd, oddmask, want, k.keep_policy);
-    }
-}
-
-// One tile of the block-staged fast path: the four events held by this thread.  Called by every thread of the block.
-template <typename V, bool DENSE, bool EXTRAS>      // EXTRAS: late side output and/or the median value log are enabled
-__device__ __forceinline__ void ingest_tile(const IngestArgs& a, DevState* st, const IngestConst& k, IngestRun& r,
-                                            const i64 (&ts_)[INGEST_EPT], const u64 (&key_)[INGEST_EPT], const u64 (&vb_)[INGEST_EPT], u32 in_mask,
-                                            HotTable* hot, bool do_filter = true) {
-    u32 ok_mask = 0;
-#pragma unroll
-    for (int e = 0; e < INGEST_EPT; ++e) ok_mask |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY) ? 1u : 0u) << e;
-    if ((ok_mask & in_mask) != in_mask) r.err |= ERRB_BAD_INPUT;
-    ok_mask &= in_mask;
-    if (a.efilter_enabled && do_filter) r.nea += filter_events<V>(a, st, ts_, key_, vb_, ok_mask);
-    if (!a.window_enabled) return;
-    u32 late_mask, vmask, q_[INGEST_EPT], slot_[INGEST_EPT];
-    ingest_core<V, DENSE, INGEST_EPT>(a, st, k, r, ts_, key_, vb_, ok_mask, hot, threadIdx.x < 32, late_mask, vmask, q_, slot_);
-    // ---- late side output (chapter3/README.md:213-228, option 3: "a separate stream of the late data") ----
-    if (EXTRAS && a.lt_cap) {
-        u64 row = block_append<INGEST_THREADS>(__popc(late_mask), &st->n_late, a.lt_cap, st);
-        if (row != ~0ull) {
-#pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e)
-                if (late_mask & (1u << e)) { a.lt_ts[row] = ts_[e]; a.lt_key[row] = key_[e]; a.lt_val[row] = vb_[e]; ++row; }
-        }
-    }
-    // ---- N3: non-incremental window functions keep every value (ComputeCpuMiddle.java:36-38) ----
-    if (EXTRAS && a.mlog_enabled) {
-        u64 row = block_append<INGEST_THREADS>(__popc(vmask), &st->n_mlog, a.ml_cap, st);
-        if (row != ~0ull) {
-#pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e)
-                if (vmask & (1u << e)) { a.ml_pane[row] = k.origin_pane + (i64)q_[e]; a.ml_slot[row] = slot_[e]; a.ml_val[row] = vb_[e]; ++row; }
-        }
-    }
-}
-
-template <typename V, bool DENSE, bool EXTRAS>
-__global__ void __launch_bounds__(INGEST_THREADS, FMQ_INGEST_MIN_BLOCKS) ingest_fast_kernel(const __grid_constant__ IngestArgs a) {
-    extern __shared__ __align__(128) unsigned char ingest_smem[];
-    __shared__ __align__(8) u64 bars[INGEST_STAGES];
-    __shared__ u32 f_wsum[INGEST_THREADS / 32];
-    __shared__ u64 f_base;
-    __shared__ HotTable hot_tab;
-    DevState* st = a.st;
-    if (!ingest_fast_ok(st, a.g)) return;                        // the generic kernel handles this batch
-    IngestConst k;
-    k.origin_ts = st->origin_ts;
-    k.origin_pane = st->origin_pane;
-    k.combine = st->combine_dups != 0;
-    k.origin_ring = (u32)st->origin_pane & a.g.ring_mask;
-    k.slide = a.g.slide32;
-    k.recip = 0xFFFFFFFFu / k.slide;                             // floor((2^32-1)/slide): quotient estimate, never too big
-    // first d that falls outside the ring (< 2^32); panes still being cleared are not yet reusable
-    k.span = (u64)(a.g.ring_mask + 1 - st->pending_clear) * k.slide;
-    k.nbuckets = a.g.capacity >> 2;
-    k.fired_n = fired_panes(a.g, st);
-    IngestRun r;
-    if (k.combine) hot_init(&hot_tab);                           // ordered before its first use by the barrier after the prologue
-
-    const V* __restrict__ val = static_cast<const V*>(a.val);
-    // bulk copies need 16-byte aligned, whole tiles; the (at most one) ragged tile goes the direct way
-    const size_t full_tiles = a.vec32 ? a.n / INGEST_TILE : 0;
-    u64 policy;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
-    auto stage_ptr = [&](int s, int col) { return reinterpret_cast<u64*>(ingest_smem + ((size_t)(s * 3 + col) * INGEST_TILE) * 8); };
-    auto issue = [&](size_t t, int s) {                          // one thread: arm the barrier, start 3 x 8 KB copies
-        mbar_expect_tx(&bars[s], 3u * INGEST_TILE * 8u);
-        tma_load_1d(stage_ptr(s, 0), a.ts + t * INGEST_TILE, INGEST_TILE * 8u, &bars[s], policy);
-        tma_load_1d(stage_ptr(s, 1), a.key + t * INGEST_TILE, INGEST_TILE * 8u, &bars[s], policy);
-        tma_load_1d(stage_ptr(s, 2), val + t * INGEST_TILE, INGEST_TILE * 8u, &bars[s], policy);
-    };
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < INGEST_STAGES; ++s) mbar_init(&bars[s], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        for (int s = 0; s < INGEST_STAGES; ++s) {
-            const size_t t = blockIdx.x + (size_t)s * gridDim.x;
-            if (t < full_tiles) issue(t, s);
-        }
-    }
-    __syncthreads();
-    size_t it = 0;
-    for (size_t t = blockIdx.x; t < full_tiles; t += gridDim.x, ++it) {
-        const int s = (int)(it % INGEST_STAGES);
-        mbar_wait(&bars[s], (u32)((it / INGEST_STAGES) & 1));
-        // thread x takes events x, x+256, x+512, x+768 of the tile: conflict-free 8-byte shared loads
-        i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT];
-        const u64 *sts = stage_ptr(s, 0), *skey = stage_ptr(s, 1), *sval = stage_ptr(s, 2);
-#pragma unroll
-        for (int e = 0; e < INGEST_EPT; ++e) {
-            ts_[e] = (i64)sts[threadIdx.x + e * INGEST_THREADS]; key_[e] = skey[threadIdx.x + e * INGEST_THREADS]; vb_[e] = sval[threadIdx.x + e * INGEST_THREADS];
-        }
-        // A6-i, first half: hit mask and the warp-level prefix, BEFORE the barrier that frees the stage, so that
-        // this one barrier also publishes the per-warp totals (saves a block barrier per tile)
-        u32 hits = 0, inc = 0;
-        if (a.efilter_enabled) {
-#pragma unroll
-            for (int e = 0; e < INGEST_EPT; ++e) {
-                V v; memcpy(&v, &vb_[e], 8);
-                hits |= ((ts_[e] >= 0 && key_[e] != KEY_EMPTY && cmp_op((double)v, a.efilter_op, a.efilter_thr)) ? 1u : 0u) << e;
-            }
-            inc = __popc(hits);
-            const u32 lane = threadIdx.x & 31;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, inc, o); if ((int)lane >= o) inc += x; }
-            if (lane == 31) f_wsum[threadIdx.x >> 5] = inc;
-        }
-        __syncthreads();                                         // every thread has its events in registers: the stage is free
-        if (threadIdx.x == 0) {
-            // The stage was just read through the generic proxy (by every thread, ordered by the barrier
-            // above); the bulk copy below overwrites it through the async proxy.  Without this
-            // cross-proxy fence the copy can overtake those reads: measured as a rare wrong value column
-            // (counts conserved, sums not) once blocks reuse a stage (tests/test_gpu_fullsize.py).
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            const size_t tn = t + (size_t)INGEST_STAGES * gridDim.x;
-            if (tn < full_tiles) issue(tn, s);
-        }
-        if (a.efilter_enabled) {                                 // second half: one reservation per tile, rows in thread order
-            u32 wbase = 0, total = 0;
-#pragma unroll
-            for (int i = 0; i < INGEST_THREADS / 32; ++i) { const u32 x = f_wsum[i]; if (i < (int)(threadIdx.x >> 5)) wbase += x; total += x; }
-            if (threadIdx.x == 0) f_base = total ? atomicAdd(&st->n_ealert, (u64)total) : 0;
-            __syncthreads();
-            if (total) {
-                u64 row = f_base + wbase + (inc - __popc(hits));
-                if (f_base + total > a.ea_cap) { if (threadIdx.x == 0) r.err |= ERRB_OUTPUT; }
-                else {
-#pragma unroll
-                    for (int e = 0; e < INGEST_EPT; ++e)
-                        if (hits & (1u << e)) { a.ea_ts[row] = ts_[e]; a.ea_key[row] = key_[e]; a.ea_val[row] = vb_[e]; ++row; }
-                }
-            }
-            r.nea += __popc(hits);
-        }
-        ingest_tile<V, DENSE, EXTRAS>(a, st, k, r, ts_, key_, vb_, 0xFu, &hot_tab, false);
-    }
-    // ragged tail (and unaligned columns): direct 8-byte loads
-    const size_t tail_tiles = (a.n - full_tiles * INGEST_TILE + INGEST_TILE - 1) / INGEST_TILE;
-    for (size_t t = blockIdx.x; t < tail_tiles; t += gridDim.x) {
-        const size_t i = (full_tiles + t) * INGEST_TILE + (size_t)threadIdx.x * INGEST_EPT;
-        i64 ts_[INGEST_EPT]; u64 key_[INGEST_EPT]; u64 vb_[INGEST_EPT]; u32 in_mask;
-        load_events<V>(a, i, ts_, key_, vb_, in_mask);
-        ingest_tile<V, DENSE, EXTRAS>(a, st, k, r, ts_, key_, vb_, in_mask, &hot_tab);
-    }
-    if (k.combine && a.window_enabled) { __syncthreads(); hot_flush<V>(&hot_tab, a.acc, a.g.agg_mask); }
-    // ---- per-warp reduction of the batch scalars, one atomic each per warp ----
-    r.nea = warp_sum_u64(r.nea);
-    for (int o = 16; o > 0; o >>= 1) r.err |= __shfl_xor_sync(0xffffffffu, r.err, o);
-    if (a.window_enabled) {
-        r.late = warp_sum_u64(r.late); r.dmax = warp_max_i64(r.dmax);
-        r.pmin = __reduce_min_sync(0xffffffffu, r.pmin); r.pmax = __reduce_max_sync(0xffffffffu, r.pmax);
-    }
-    if (threadIdx.x == 0 && r.dup[0]) { atomicAdd(&st->dup_sampled, (u64)r.dup[0]); atomicAdd(&st->dup_found, (u64)r.dup[1]); }
-    if ((threadIdx.x & 31) == 0) {
-        if (r.nea) atomicAdd(&st->event_alerts, r.nea);
-        if (r.err) atomicOr(&st->err_flags, r.err);
-        if (a.window_enabled) {
-            if (r.late) atomicAdd(&st->late_dropped, r.late);
-            if (r.dmax != I64_MIN_) atomicMax(&st->batch_max_ts, k.origin_ts + r.dmax);
-            if (r.pmin <= r.pmax) { atomicMin(&st->min_pane, st->origin_pane + (i64)r.pmin); atomicMax(&st->max_pane, st->origin_pane + (i64)r.pmax); }
-        }
     }
 }
 
@@ -910,7 +740,7 @@ template <typename V, bool DENSE>
 __global__ void __launch_bounds__(INGEST_THREADS) ingest_generic_kernel(const __grid_constant__ IngestArgs a) {
     DevState* st = a.st;
     __shared__ SegTab seg;
-    if (!a.force_generic && ingest_fast_ok(st, a.g, a.window_enabled)) return;       // the fast kernel handles this batch
+    if (ingest_fast_ok(st, a.g, a.window_enabled)) return;       // the fast kernel handles this batch
     if (threadIdx.x == 0) seg_tab_fill<INGEST_THREADS * INGEST_EPT>(a, &seg, st);
     __syncthreads();
     const int anchored = st->anchored;

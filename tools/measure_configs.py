@@ -46,6 +46,20 @@ run("N3 10 s tumbling median, 1 M keys, dense", StreamSpec(n_keys=1_000_000, eve
     agg_mask=1, table_capacity=1_000_000, key_mode=1, fired_capacity=1 << 23, median_log_capacity=3 * B, median_capacity=1 << 23, **W10)
 print("\n| config | step ms | ingest | keyed | plan+fire | Gev/s | 24 B x ev/s over 6550.7 GB/s |\n|---|---|---|---|---|---|---|")
 print("\n".join(rows))
+# A4: the owner split by itself (count + scan + block-staged scatter into one output), device time on the handle's stream
+eng = capi.Engine(efilter_enabled=1, max_batch=B)
+cols = generate_torch(StreamSpec(n_keys=1_000_000), 0, B)
+outs = [torch.empty_like(c) for c in cols]
+ext = torch.cuda.ExternalStream(eng.stream)
+torch.cuda.synchronize()
+for world in (2, 8, 64):
+    ts_ = []
+    for i in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(ext); eng.partition_by_owner(cols[0], cols[1], cols[2], world, *outs); e1.record(ext); torch.cuda.synchronize()
+        if i >= 2: ts_.append(e0.elapsed_time(e1))
+    print(f"A4 owner split, world {world}: {np.mean(ts_):.3f} ms per 2^{int(np.log2(B))} events (incl. the 1 KB read-back of the bucket starts) = {24 * B / np.mean(ts_) / 1e6:.0f} GB/s of events")
+eng.close()
 # N2: text ingest
 lines = [f"{1563452000 + i // 1000} 10.{(i * 7919) % 250}.{(i * 104729) % 250}.{i % 250} cpu{i % 8} {((i * 2654435761) % 100000) / 1000:.3f}" for i in range(1 << 20)]
 text = ("\n".join(lines) + "\n").encode() * 4
