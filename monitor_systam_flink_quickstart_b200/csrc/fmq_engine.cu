@@ -350,13 +350,13 @@ static cudaError_t owner_split(cudaStream_t stream, const SplitScratch& sc, cons
             hist<<<nchunks, XS_THREADS, 0, stream>>>(key, n, nchunks, world, dense, sc.counts);
             e = scan_counts_on(stream, sc.counts, sc.tiles, (size_t)nb * nchunks); if (e != cudaSuccess) return e;
         }
-        const size_t smem = xs_scatter_smem(nb);
-        if (per_owner) { e = cudaFuncSetAttribute(scat_owner, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_owner<<<grid, XS_THREADS, smem, stream>>>(a); }
-        else           { e = cudaFuncSetAttribute(scat_single, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_single<<<grid, XS_THREADS, smem, stream>>>(a); }
+        // beside the ingest of the previous batch (keyBy exchange): 256-thread blocks; by itself: 512-thread blocks
+        if (per_owner) { const size_t smem = xs_scatter_smem(nb, XS_THREADS); e = cudaFuncSetAttribute(scat_owner, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_owner<<<grid, XS_THREADS, smem, stream>>>(a); }
+        else           { const size_t smem = xs_scatter_smem(nb, XS_THREADS_WIDE); e = cudaFuncSetAttribute(scat_single, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_single<<<grid, XS_THREADS_WIDE, smem, stream>>>(a); }
         return cudaGetLastError();
     };
-    if (world <= 8) return run(xs_hist_kernel<3>, xs_scatter_kernel<3, false>, xs_scatter_kernel<3, true>, 8u);
-    return run(xs_hist_kernel<8>, xs_scatter_kernel<8, false>, xs_scatter_kernel<8, false>, 256u);
+    if (world <= 8) return run(xs_hist_kernel<3>, xs_scatter_kernel<3, false, XS_THREADS_WIDE>, xs_scatter_kernel<3, true, XS_THREADS>, 8u);
+    return run(xs_hist_kernel<8>, xs_scatter_kernel<8, false, XS_THREADS_WIDE>, xs_scatter_kernel<8, false, XS_THREADS_WIDE>, 256u);
 }
 static u32 split_digits(u32 world) { return world <= 8 ? 8u : 256u; }
 

@@ -11,9 +11,10 @@ namespace fmq {
 
 constexpr int RS_DIGITS = 256;                  // largest world an owner split supports
 constexpr u32 XS_CHUNK = 2048;                  // events per block
-constexpr int XS_THREADS = 256;
+constexpr int XS_THREADS = 256;                 // counting kernel, and the scatter when it shares the SMs with the ingest (keyBy exchange)
 constexpr int XS_WARPS = XS_THREADS / 32;
-constexpr int XS_IPT = XS_CHUNK / XS_THREADS;   // 8 events per thread: a warp ranks 256 consecutive events, 32 per round
+constexpr int XS_IPT = XS_CHUNK / XS_THREADS;   // 8 events per thread
+constexpr int XS_THREADS_WIDE = 512;            // the scatter by itself: 4 events per thread, all three columns requested at once
 
 __host__ __device__ inline u32 xs_num_chunks(size_t n) { return (u32)((n + XS_CHUNK - 1) / XS_CHUNK); }
 
@@ -82,19 +83,21 @@ struct SplitArgs {
     // all a commutative aggregate needs; jobs with order-dependent keyed state use the stable two-pass form.
     unsigned long long* fill;
 };
-constexpr size_t xs_scatter_smem(u32 nb) { return (size_t)3 * XS_CHUNK * 8 + XS_CHUNK * 2 + (size_t)XS_WARPS * nb * 2 + nb * 4 * 2; }
+constexpr size_t xs_scatter_smem(u32 nb, int threads) { return (size_t)3 * XS_CHUNK * 8 + XS_CHUNK * 2 + (size_t)(threads / 32) * nb * 2 + nb * 4 * 2; }
 
-template <int BITS, bool PER_OWNER>
-__global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_constant__ SplitArgs a) {
+template <int BITS, bool PER_OWNER, int THREADS>
+__global__ void __launch_bounds__(THREADS, THREADS == 256 ? 4 : 2) xs_scatter_kernel(const __grid_constant__ SplitArgs a) {
+    constexpr int WARPS = THREADS / 32, IPT = (int)XS_CHUNK / THREADS;
+    constexpr bool EARLY = THREADS > 256;         // enough registers to hold all three columns through the ranking
     constexpr u32 NB = 1u << BITS;
     extern __shared__ __align__(16) unsigned char xs_smem[];
     u64* ev_s = reinterpret_cast<u64*>(xs_smem);                                  // [3][XS_CHUNK]
     unsigned short* dig_s = reinterpret_cast<unsigned short*>(ev_s + 3 * XS_CHUNK);   // [XS_CHUNK] owner of every sorted position
-    unsigned short* wcnt = dig_s + XS_CHUNK;                                      // [XS_WARPS][NB] per-warp counts, then exclusive prefixes
-    u32* dbase = reinterpret_cast<u32*>(wcnt + XS_WARPS * NB);                    // [NB] start of the owner's run inside the sorted chunk
+    unsigned short* wcnt = dig_s + XS_CHUNK;                                      // [WARPS][NB] per-warp counts, then exclusive prefixes
+    u32* dbase = reinterpret_cast<u32*>(wcnt + WARPS * NB);                    // [NB] start of the owner's run inside the sorted chunk
     u32* goff = dbase + NB;                                                       // [NB] where that run goes in the owner's destination
-    __shared__ u32 scan_ws[XS_WARPS];
-    __shared__ i64 max_ws[XS_WARPS];
+    __shared__ u32 scan_ws[WARPS];
+    __shared__ i64 max_ws[WARPS];
     const u32 tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     i64 tmax = I64_MIN_;
     // persistent over chunks: the grid may be much smaller than the number of chunks (the keyBy exchange runs this kernel
@@ -103,19 +106,24 @@ __global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_
     const size_t lo = (size_t)chunk * XS_CHUNK;
     const size_t hi = (lo + XS_CHUNK < a.n) ? lo + XS_CHUNK : a.n;
     const bool unordered = PER_OWNER && a.fill != nullptr;
-    for (u32 i = tid; i < XS_WARPS * NB; i += XS_THREADS) wcnt[i] = 0;
-    if (!unordered) for (u32 d = tid; d < NB; d += XS_THREADS) {
+    for (u32 i = tid; i < WARPS * NB; i += THREADS) wcnt[i] = 0;
+    if (!unordered) for (u32 d = tid; d < NB; d += THREADS) {
         const u32 o = a.offsets[(size_t)d * a.nchunks + chunk];
         goff[d] = PER_OWNER ? o - a.offsets[(size_t)d * a.nchunks] : o;           // per-owner destinations start at 0
     }
     __syncthreads();
     // phase 1: rank inside the warp's 256 consecutive events, in arrival order
-    u64 kk[XS_IPT]; unsigned short dg[XS_IPT], rk[XS_IPT];
-    const size_t wlo = lo + (size_t)w * (XS_CHUNK / XS_WARPS);
+    // all three columns of the thread's events are requested at once (one memory round trip per chunk, not two)
+    u64 kk[IPT], tt[EARLY ? IPT : 1], vv[EARLY ? IPT : 1]; unsigned short dg[IPT], rk[IPT];
+    const size_t wlo = lo + (size_t)w * (XS_CHUNK / WARPS);
 #pragma unroll
-    for (int r = 0; r < XS_IPT; ++r) { const size_t i = wlo + r * 32 + lane; kk[r] = i < hi ? ldg_stream(a.key + i) : 0; }
+    for (int r = 0; r < IPT; ++r) {
+        const size_t i = wlo + r * 32 + lane; const bool in = i < hi;
+        kk[r] = in ? ldg_stream(a.key + i) : 0;
+        if constexpr (EARLY) { tt[r] = in ? ldg_stream(a.ts + i) : 0; vv[r] = in ? ldg_stream(a.val + i) : 0; }
+    }
 #pragma unroll
-    for (int r = 0; r < XS_IPT; ++r) {
+    for (int r = 0; r < IPT; ++r) {
         const bool act = wlo + r * 32 + lane < hi;
         const unsigned am = __ballot_sync(0xffffffffu, act);
         dg[r] = 0; rk[r] = 0;
@@ -132,13 +140,13 @@ __global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_
     }
     __syncthreads();
     // phase 2: per owner, exclusive prefix over the warps; then exclusive prefix over the owners
-    constexpr u32 DPT = NB / XS_THREADS ? NB / XS_THREADS : 1;
+    constexpr u32 DPT = NB / THREADS ? NB / THREADS : 1;
     u32 tot_local = 0, dtot[DPT];
 #pragma unroll
     for (u32 q = 0; q < DPT; ++q) {
         const u32 d = tid * DPT + q;
         u32 run = 0;
-        if (d < NB) for (int ww = 0; ww < XS_WARPS; ++ww) { const u32 c = wcnt[ww * NB + d]; wcnt[ww * NB + d] = (unsigned short)run; run += c; }
+        if (d < NB) for (int ww = 0; ww < WARPS; ++ww) { const u32 c = wcnt[ww * NB + d]; wcnt[ww * NB + d] = (unsigned short)run; run += c; }
         dtot[q] = run; tot_local += run;
     }
     u32 inc = tot_local;
@@ -159,18 +167,18 @@ __global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_
         run += dtot[q];
     }
     __syncthreads();
-    // phase 3: the three columns of every event go to its sorted position (timestamps and values are read here,
-    // coalesced like the keys were, so that they do not sit in registers through the ranking)
+    // phase 3: the three columns of every event go to its sorted position
 #pragma unroll
-    for (int r = 0; r < XS_IPT; ++r) {
+    for (int r = 0; r < IPT; ++r) {
         const size_t i = wlo + r * 32 + lane;
         if (i < hi) {
             const u32 pos = dbase[dg[r]] + wcnt[w * NB + dg[r]] + rk[r];
-            const u64 t = ldg_stream(a.ts + i), k = kk[r];
+            u64 t, v; const u64 k = kk[r];
+            if constexpr (EARLY) { t = tt[r]; v = vv[r]; } else { t = ldg_stream(a.ts + i); v = ldg_stream(a.val + i); }
             tmax = (i64)t > tmax ? (i64)t : tmax;
             ev_s[pos] = t;
             ev_s[XS_CHUNK + pos] = (a.dense && k != KEY_EMPTY) ? k / a.world : k;
-            ev_s[2 * XS_CHUNK + pos] = ldg_stream(a.val + i);
+            ev_s[2 * XS_CHUNK + pos] = v;
             dig_s[pos] = dg[r];
         }
     }
@@ -179,7 +187,7 @@ __global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_
     const u32 cnt = (u32)(hi - lo);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        for (u32 pos = tid; pos < cnt; pos += XS_THREADS) {
+        for (u32 pos = tid; pos < cnt; pos += THREADS) {
             const u32 d = dig_s[pos];
             const size_t o = (size_t)goff[d] + (pos - dbase[d]);
             u64* dstc = PER_OWNER ? a.dst.ts[d] + (size_t)c * a.dst.col_stride : (c == 0 ? a.dst.out_ts : (c == 1 ? a.dst.out_key : a.dst.out_val));
@@ -193,7 +201,7 @@ __global__ void __launch_bounds__(XS_THREADS, 4) xs_scatter_kernel(const __grid_
         __syncthreads();
         if (tid == 0) {
             i64 m = max_ws[0];
-            for (int i = 1; i < XS_WARPS; ++i) m = max_ws[i] > m ? max_ws[i] : m;
+            for (int i = 1; i < WARPS; ++i) m = max_ws[i] > m ? max_ws[i] : m;
             if (m != I64_MIN_) atomicMax(reinterpret_cast<long long*>(a.max_ts), (long long)m);
         }
     }
