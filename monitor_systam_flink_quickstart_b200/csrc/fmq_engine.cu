@@ -1700,9 +1700,9 @@ extern "C" int32_t fmq_partition_by_owner_noalloc(int32_t device, void* stream_,
     int st = noalloc_scratch_for(device, &scratch); if (st) return st;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     u32* d_counts = scratch; u32* d_tiles = scratch + NOALLOC_COUNTS;
-    // Nothing in the scratch has to start at zero: the histogram kernel stores (not adds) every one
-    // of the 256 x nchunks counters it owns and the scan stores every tile sum before reading it, so
-    // whatever the previous call left behind is overwritten before it can be read.
+    // Nothing in the scratch has to start at zero: the counting kernel stores (not adds) every one of the
+    // digits x nchunks counters it owns (8 digits up to world = 8, 256 beyond) and the scan stores every tile
+    // sum before reading it, so whatever the previous call left behind is overwritten before it can be read.
     const u32 nchunks = xs_num_chunks(n);
     SplitDst dst{}; dst.out_ts = (u64*)ts_out; dst.out_key = (u64*)key_out; dst.out_val = (u64*)val_out;
     NA_CU(owner_split(stream, SplitScratch{d_counts, d_tiles}, (const u64*)ts, (const u64*)key, (const u64*)val, n, world, 0u, dst, false, nullptr));
