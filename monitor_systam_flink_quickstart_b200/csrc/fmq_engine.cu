@@ -473,6 +473,7 @@ static int stage_keyed(fmq_handle* h, const i64* ts, const u64* key, const V* va
 // stage 1 of a push: everything that touches only this handle's own events
 static u64 peer_timeout_ns();
 static u32 xs_ingest_blocks();
+static u32 cmb_ingest_blocks();
 struct SegIn { u32 nseg = 0; size_t stride = 0; const u64* seg_n = nullptr; };   // segmented input with device-side counts (keyBy exchange)
 template <typename V>
 static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void* val, size_t n, const SegIn& seg = SegIn()) {
@@ -498,7 +499,8 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
             // persistent grid: every warp streams its own ring of 128-event tiles
             size_t blocks = (n * (seg.nseg ? seg.nseg : 1) + (size_t)IW_TILE * IW_WARPS - 1) / ((size_t)IW_TILE * IW_WARPS);
             // a rank of the keyBy exchange leaves room on every SM for the scatter of the next batch (one block of ~53 KB)
-            const size_t maxb = (size_t)h->num_sms * ((h->xs_attached && !h->cmb_flags) ? xs_ingest_blocks() : FMQ_IW_BLOCKS);
+            // (overlapped combiner: the fire kernel of the previous batch runs beside this ingest; FMQ_CMB_INGEST_BLOCKS leaves it room)
+            const size_t maxb = (size_t)h->num_sms * ((h->xs_attached && !h->cmb_flags) ? xs_ingest_blocks() : (h->overlap ? cmb_ingest_blocks() : FMQ_IW_BLOCKS));
             if (blocks > maxb) blocks = maxb;
             const bool comb = c.window_enabled && h->h_hint && *(volatile u32*)h->h_hint != 0;     // skew seen by an earlier batch's sample
             auto pick = [&](auto lean, auto combining) { return comb ? combining : lean; };
@@ -613,7 +615,7 @@ static int stage_fire(fmq_handle* h, size_t n, int64_t wm_after, bool retire_now
         return f;
     };
     auto fire_blocks = [&](const FireArgs& f) {
-        size_t blocks = (f.slot_hi - f.slot_lo + FIRE_THREADS * FIRE_SPT - 1) / (FIRE_THREADS * FIRE_SPT); const size_t maxb = (size_t)h->num_sms * 8;
+        size_t blocks = (f.slot_hi - f.slot_lo + FIRE_THREADS * FIRE_SPT - 1) / (FIRE_THREADS * FIRE_SPT); const size_t maxb = (size_t)h->num_sms * FMQ_FIRE_GRID;
         if (blocks > maxb) blocks = maxb;
         return (unsigned)(blocks == 0 ? 1 : blocks);
     };
@@ -1475,6 +1477,10 @@ static u64 peer_timeout_ns() {
 // scatter blocks per SM (0 = one block per chunk, i.e. whatever fits) and ingest blocks per SM while a rank of the exchange.
 static u32 xs_blocks_per_sm() {
     static const u32 v = [] { const char* e = getenv("FMQ_XS_BLOCKS_PER_SM"); const int b = e ? atoi(e) : 2; return (u32)(b < 0 ? 0 : (b > 4 ? 4 : b)); }();
+    return v;
+}
+static u32 cmb_ingest_blocks() {
+    static const u32 v = [] { const char* e = getenv("FMQ_CMB_INGEST_BLOCKS"); const int b = e ? atoi(e) : FMQ_IW_BLOCKS; return (u32)(b < 1 ? 1 : (b > FMQ_IW_BLOCKS ? FMQ_IW_BLOCKS : b)); }();
     return v;
 }
 static u32 xs_ingest_blocks() {

@@ -940,7 +940,19 @@ struct FireArgs {
     u64* wa_key; i64* wa_wend; double* wa_val; u64 wa_cap;
 };
 
-constexpr int FIRE_THREADS = 256;
+#ifndef FMQ_FIRE_THREADS
+#define FMQ_FIRE_THREADS 256
+#endif
+#ifndef FMQ_FIRE_SPT
+#define FMQ_FIRE_SPT 2
+#endif
+#ifndef FMQ_FIRE_MINB
+#define FMQ_FIRE_MINB 4
+#endif
+#ifndef FMQ_FIRE_GRID
+#define FMQ_FIRE_GRID 8
+#endif
+constexpr int FIRE_THREADS = FMQ_FIRE_THREADS;
 
 // [batch max ts, -(min pane), max pane, 0]: the three batch scalars every rank must agree on,
 // laid out so that ONE all-reduce(MAX) over int64 makes them global (combiner mode).
@@ -976,11 +988,11 @@ __global__ void __launch_bounds__(256) retire_kernel(DevState* st, Acc32* acc, u
 // (64-bit divisions) and leave it in shared memory; ncu of the first version counted 630 instructions per key slot,
 // most of them this arithmetic repeated by every thread.
 constexpr int FIRE_MAXW = 32;             // windows per pass over the slots
-constexpr int FIRE_SPT = 2;               // key slots per thread: both slots' cells are requested before either is used
+constexpr int FIRE_SPT = FMQ_FIRE_SPT;     // key slots per thread: both slots' cells are requested before either is used
 struct FireWin { i64 wend; u32 p0; u32 np; };     // first pane (low 32 bits: only its ring index is needed) and number of panes holding data
 
 template <typename V, bool PEERS>
-__global__ void __launch_bounds__(FIRE_THREADS) fire_kernel(const __grid_constant__ FireArgs a) {
+__global__ void __launch_bounds__(FIRE_THREADS, FMQ_FIRE_MINB) fire_kernel(const __grid_constant__ FireArgs a) {
     __shared__ FireWin wins[FIRE_MAXW];
     DevState* st = a.st;
     const i64 size = a.g.size, slide = a.g.slide, off = a.g.off;
