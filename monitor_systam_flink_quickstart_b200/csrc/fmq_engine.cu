@@ -92,7 +92,7 @@ struct fmq_handle {
     i64* lt_ts = nullptr; u64 *lt_key = nullptr, *lt_val = nullptr; u64 lt_cap = 0; size_t cur_late = 0;
     // median path (N3)
     i64* ml_pane[2] = {nullptr, nullptr}; u32* ml_slot[2] = {nullptr, nullptr}; u64* ml_val[2] = {nullptr, nullptr}; int ml_cur = 0; u64 ml_cap = 0;
-    u64* mw_items[2] = {nullptr, nullptr}; u64* mw_vals = nullptr;
+    u64* mw_items[2] = {nullptr, nullptr}; u64* mw_vals = nullptr; u64* mw_big = nullptr; u64 mw_big_cap = 0;
     u64* md_key = nullptr; i64* md_wend = nullptr; double* md_val = nullptr; u64 md_cap = 0; size_t cur_median = 0;
     // text ingest
     char* d_text = nullptr; u64* d_line_start = nullptr; u32* d_txt_status = nullptr; unsigned long long* d_txt_bad = nullptr;
@@ -130,7 +130,7 @@ static void free_all(fmq_handle* h) {
                     h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
                     h->d_pack[0], h->d_pack[1], h->kr_lead, h->kr_k, h->kr_fl, h->kr_in_c, h->kr_mk, h->kr_mb, h->kr_in_mk, h->kr_in_mb, h->d_counts, h->d_tiles, h->d_xchg, h->d_xsend, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad,
-                    h->ml_pane[0], h->ml_pane[1], h->ml_slot[0], h->ml_slot[1], h->ml_val[0], h->ml_val[1], h->mw_items[0], h->mw_items[1], h->mw_vals,
+                    h->ml_pane[0], h->ml_pane[1], h->ml_slot[0], h->ml_slot[1], h->ml_val[0], h->ml_val[1], h->mw_items[0], h->mw_items[1], h->mw_vals, h->mw_big,
                     h->md_key, h->md_wend, h->md_val, h->lt_ts, h->lt_key, h->lt_val};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : h->alt_out) if (p) cudaFree(p);
@@ -273,6 +273,8 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
         h->ml_cap = cfg->median_log_capacity;
         for (int k = 0; k < 2; ++k) { CUC(dalloc(&h->ml_pane[k], h->ml_cap)); CUC(dalloc(&h->ml_slot[k], h->ml_cap)); CUC(dalloc(&h->ml_val[k], h->ml_cap)); CUC(dalloc(&h->mw_items[k], h->ml_cap)); }
         CUC(dalloc(&h->mw_vals, h->ml_cap));
+        h->mw_big_cap = h->ml_cap / (MED_SMALL + 1) + 1;                    // runs longer than MED_SMALL values: (start, length) pairs behind a counter
+        CUC(dalloc(&h->mw_big, 2 + 2 * h->mw_big_cap));
         h->md_cap = cfg->median_capacity ? cfg->median_capacity : (2 * h->capacity > (1u << 20) ? 2 * h->capacity : (1u << 20));
         CUC(dalloc(&h->md_key, h->md_cap)); CUC(dalloc(&h->md_wend, h->md_cap)); CUC(dalloc(&h->md_val, h->md_cap));
     }
@@ -358,7 +360,6 @@ static cudaError_t owner_split(cudaStream_t stream, const SplitScratch& sc, cons
     if (world <= 8) return run(xs_hist_kernel<3>, xs_scatter_kernel<3, false, XS_THREADS_WIDE>, xs_scatter_kernel<3, true, XS_THREADS>, 8u);
     return run(xs_hist_kernel<8>, xs_scatter_kernel<8, false, XS_THREADS_WIDE>, xs_scatter_kernel<8, false, XS_THREADS_WIDE>, 256u);
 }
-static u32 split_digits(u32 world) { return world <= 8 ? 8u : 256u; }
 
 static int status_from_flags(fmq_handle* h, u32 flags) {
     if (!flags) return FMQ_OK;
@@ -546,8 +547,9 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
 __global__ void set_mlog_kernel(DevState* st) { st->n_mlog = st->n_mwork; }
 
 // N3: the records of every window the plan says is firing are selected from the value log — all windows of the
-// fire in one pass (in groups only when their (record, window) pairs would not fit the work buffer) — sorted by value
-// (Collections.sort order) and then, stably, by (window, key), and one thread per (window, key) picks the middle.
+// fire in one pass (in groups only when their (record, window) pairs would not fit the work buffer) — grouped by
+// (window, key) with two or three radix passes; each run's middle value(s) are then found where the run lies
+// (csrc/fmq_median.cuh: one thread for a short run, a block's radix select for a long one).
 // One read-back of the plan per push sizes the launches; nothing is synchronised per window.
 static int sync_state(fmq_handle* h);
 static int fire_medians(fmq_handle* h) {
@@ -571,11 +573,12 @@ static int fire_medians(fmq_handle* h) {
             median_select_all_kernel<<<grid, MED_THREADS, 0, h->stream>>>(h->ml_pane[h->ml_cur], h->ml_slot[h->ml_cur], h->ml_val[h->ml_cur], h->d_st, size, slide, off, j0, nj,
                                                                          h->slot_bits, h->mw_items[0], h->mw_vals, bound); LAUNCHED(h, "median_select_all_kernel");
             int cur = 0;
-            s = sort_items(h, h->mw_items, (size_t)bound, 64, F64ValueKey{h->mw_vals, bound}, &cur); if (s) return s;      // Collections.sort order
-            s = sort_items(h, h->mw_items, (size_t)bound, h->slot_bits + jbits, SlotKey{}, &cur); if (s) return s;          // stable: groups by (window, key)
-            MedianEmitArgs m{h->mw_items[cur], h->mw_vals, bound, h->d_keys, h->cfg.key_mode == FMQ_KEYS_DENSE, d.fire_first_end + j0 * slide, h->d_st,
-                             h->md_key, h->md_wend, h->md_val, h->md_cap, h->slot_bits, slide};
-            median_emit_kernel<<<grid, MED_THREADS, 0, h->stream>>>(m); LAUNCHED(h, "median_emit_kernel");
+            s = sort_items(h, h->mw_items, (size_t)bound, h->slot_bits + jbits, SlotKey{}, &cur); if (s) return s;          // groups by (window, key)
+            CU(h, cudaMemsetAsync(h->mw_big, 0, 8, h->stream));
+            MedianPickArgs m{h->mw_items[cur], h->mw_items[cur ^ 1], h->mw_vals, bound, h->d_keys, h->cfg.key_mode == FMQ_KEYS_DENSE, d.fire_first_end + j0 * slide, h->d_st,
+                             h->md_key, h->md_wend, h->md_val, h->md_cap, h->slot_bits, slide, h->mw_big, h->mw_big_cap};
+            median_pick_kernel<<<(unsigned)h->num_sms * 8, MED_THREADS, 0, h->stream>>>(m); LAUNCHED(h, "median_pick_kernel");   // runs of up to MED_SMALL values
+            median_long_kernel<<<grid, MED_THREADS, 0, h->stream>>>(m); LAUNCHED(h, "median_long_kernel");      // the others (returns at once if there are none)
         }
     }
     if (d.expire_lo <= d.expire_hi && d.n_mlog > 0) {

@@ -38,10 +38,6 @@ __host__ __device__ inline u32 ps_pass_bits(u32 key_bits) { const u32 passes = (
 struct SlotKey {            // item = (slot << 32 | index): sort by slot
     __device__ __forceinline__ u64 operator()(u64 item) const { return item >> 32; }
 };
-struct F64ValueKey {        // item = (group << 32 | index into vals): sort by vals[index] in Double.compareTo order
-    const u64* vals; u64 n; // items whose index lies beyond n are padding
-    __device__ __forceinline__ u64 operator()(u64 item) const { const u32 i = (u32)item; return i < n ? Codec<double>::cmp_key(__longlong_as_double((i64)vals[i])) : 0ull; }
-};
 
 template <int BITS, bool SCATTER, typename KeyFn>
 __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t n, u32 nchunks, u32 shift,

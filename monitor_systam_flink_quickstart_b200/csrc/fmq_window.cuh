@@ -565,6 +565,43 @@ __device__ __forceinline__ void wr_flush(WarpRows& w, u64* counter, u64 cap, T0*
     w.n = 0;
 }
 
+// The value log (N3) takes a row for EVERY accepted record: one reservation per 128 staged rows was 1.3 x 10^5 atomics with
+// a return value on one address per 2^24 records, which serialise in their L2 slice (+0.43 ms per batch, measured).  A warp
+// therefore reserves up to ML_CHUNK rows at a time — never more than it can still produce — and fills what it did not use
+// (records dropped as late, ragged tiles) with rows of pane ML_PANE_NONE, which belong to no window and are dropped
+// by the next compaction.
+constexpr u32 ML_CHUNK = 2048;
+constexpr i64 ML_PANE_NONE = -(1ll << 62);
+struct LogSpace { u64 base; u32 left; };                    // warp-uniform
+__device__ __forceinline__ void ml_flush(WarpRows& w, LogSpace& sp, u64 future, const IngestArgs& a, DevState* st, u32& err) {   // all 32 lanes
+    if (w.n == 0) return;
+    const u32 lane = threadIdx.x & 31;
+    __syncwarp();
+    u32 done = 0;
+    while (done < w.n) {
+        if (sp.left == 0) {
+            const u64 most = (u64)(w.n - done) + future;
+            const u32 want = most < ML_CHUNK ? (u32)most : ML_CHUNK;
+            u64 b = 0;
+            if (lane == 0) b = atomicAdd(&st->n_mlog, (u64)want);
+            b = __shfl_sync(0xffffffffu, b, 0);
+            if (b + want > a.ml_cap) { err |= ERRB_OUTPUT; break; }
+            sp.base = b; sp.left = want;
+        }
+        const u32 m = sp.left < w.n - done ? sp.left : w.n - done;
+        for (u32 i = lane; i < m; i += 32) {
+            a.ml_pane[sp.base + i] = (i64)w.buf[done + i]; a.ml_slot[sp.base + i] = (u32)w.buf[IW_ROWS + done + i]; a.ml_val[sp.base + i] = w.buf[2 * IW_ROWS + done + i];
+        }
+        sp.base += m; sp.left -= m; done += m;
+    }
+    __syncwarp();
+    w.n = 0;
+}
+__device__ __forceinline__ void ml_finish(LogSpace& sp, const IngestArgs& a) {
+    for (u32 i = threadIdx.x & 31; i < sp.left; i += 32) { a.ml_pane[sp.base + i] = ML_PANE_NONE; a.ml_slot[sp.base + i] = 0u; a.ml_val[sp.base + i] = 0ull; }
+    sp.left = 0;
+}
+
 // COMBINE: warp-level pre-aggregation of lanes that hit the same cell (skewed keys).  The host picks the variant
 // from a hint the plan kernel leaves in pinned host memory (it may lag by a batch: the choice only changes the
 // order of additions, never the result beyond the double-sum tolerance).
@@ -607,6 +644,7 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
     WarpRows ea{reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES), 0};
     WarpRows lt{reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES + IW_ROWBUF_BYTES), 0};
     WarpRows ml{reinterpret_cast<u64*>(wbase + IW_STAGES * IW_STAGE_BYTES + 2 * IW_ROWBUF_BYTES), 0};
+    LogSpace ml_space{0, 0};
     const u64* cts = reinterpret_cast<const u64*>(a.ts); const u64* cval = static_cast<const u64*>(a.val);
     u64 policy;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
@@ -699,14 +737,15 @@ __global__ void __launch_bounds__(IW_THREADS, FMQ_IW_BLOCKS) ingest_ring_kernel(
         if (EXTRAS && a.mlog_enabled) {                          // N3: every accepted value is logged (ComputeCpuMiddle.java:36-38)
 #pragma unroll
             for (int e = 0; e < IW_EPT; ++e) {
-                if (ml.n + 32 > IW_ROWS) wr_flush(ml, &st->n_mlog, a.ml_cap, a.ml_pane, a.ml_slot, a.ml_val, r.err);
+                // rows this warp can still produce: the rest of this tile and its later tiles
+                if (ml.n + 32 > IW_ROWS) ml_flush(ml, ml_space, (u64)(IW_EPT - e) * 32u + (u64)IW_TILE * ((ntiles - 1 - t) / nw), a, st, r.err);
                 wr_push(ml, (vmask >> e) & 1u, (u64)(k.origin_pane + (i64)q_[e]), (u64)slot_[e], vb_[e]);
             }
         }
     }
     if (a.efilter_enabled) wr_flush(ea, &st->n_ealert, a.ea_cap, a.ea_ts, a.ea_key, a.ea_val, r.err);
     if (EXTRAS && a.lt_cap) wr_flush(lt, &st->n_late, a.lt_cap, a.lt_ts, a.lt_key, a.lt_val, r.err);
-    if (EXTRAS && a.mlog_enabled) wr_flush(ml, &st->n_mlog, a.ml_cap, a.ml_pane, a.ml_slot, a.ml_val, r.err);
+    if (EXTRAS && a.mlog_enabled) { ml_flush(ml, ml_space, 0, a, st, r.err); ml_finish(ml_space, a); }
     if (COMBINE && a.window_enabled) { __syncthreads(); hot_flush<V>(&hot_tab, a.acc, a.g.agg_mask); }
     // ---- per-warp reduction of the batch scalars, one atomic each per warp ----
     r.nea = nea_w;                                               // uniform: lane 0 reports it

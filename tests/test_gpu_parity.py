@@ -465,6 +465,28 @@ def test_window_median_parity(key_mode, slide):
     assert_fired_equal(gpu.poll_fired(), cpu.poll_fired())
 
 
+def test_window_median_run_lengths_around_the_short_long_boundary():
+    """Runs of 1 .. 34 values are ordered by one thread, longer ones by a block's radix select (csrc/fmq_median.cuh):
+    every length around the boundary, even and odd, one run of 10^5 values, ties, both zeros and both infinities."""
+    kw = dict(window_enabled=1, agg_mask=1, window_size_ms=10_000, window_slide_ms=10_000, max_out_of_orderness_ms=0,
+              median_log_capacity=500_000, **dict(SMALL, max_batch=1 << 18))
+    gpu, cpu = pair(**kw)
+    lens = list(range(1, 36)) + [63, 64, 65, 255, 256, 257, 1000, 4097, 100_001, 100_000]
+    rng = np.random.default_rng(5)
+    key = np.repeat(np.arange(len(lens), dtype=np.uint64) + 1, lens)
+    perm = rng.permutation(len(key)); key = key[perm]
+    for w in range(2):
+        val = np.round(rng.normal(0, 3, len(key)), 1 if w == 0 else 12)
+        val[::53] = -0.0; val[1::53] = 0.0; val[7::211] = np.inf; val[11::223] = -np.inf
+        ts = 1_600_000_000_000 + w * 10_000 + rng.integers(0, 10_000, len(key)).astype(np.int64)
+        gpu.push_batch(ts, key, val, capi.FMQ_WM_KEEP); cpu.push_batch(ts, key, val, capi.FMQ_WM_KEEP)
+    gpu.flush(); cpu.flush()
+    a, w = sort_walerts(gpu.poll_medians()), sort_walerts(cpu.poll_medians())
+    assert len(w) == 2 * len(lens)
+    np.testing.assert_array_equal(a.key, w.key); np.testing.assert_array_equal(a.window_end, w.window_end)
+    np.testing.assert_array_equal(a.value.view(np.uint64), w.value.view(np.uint64))
+
+
 def test_window_median_many_windows_per_fire_small_work_buffer_and_snapshot():
     """Watermarks that jump: a dozen sliding windows fire in one push (all of them selected and sorted in one pass, or in
     groups when the (record, window) pairs would not fit the work buffer: the log capacity here is barely above the
