@@ -92,6 +92,7 @@ struct fmq_handle {
     i64* lt_ts = nullptr; u64 *lt_key = nullptr, *lt_val = nullptr; u64 lt_cap = 0; size_t cur_late = 0;
     // median path (N3)
     i64* ml_pane[2] = {nullptr, nullptr}; u32* ml_slot[2] = {nullptr, nullptr}; u64* ml_val[2] = {nullptr, nullptr}; int ml_cur = 0; u64 ml_cap = 0;
+    u64* d_loc[3] = {nullptr, nullptr, nullptr}; u32 loc_parts = 0;     // hash-range partition in front of the ingest (tables much larger than the L2)
     u64* mw_items[2] = {nullptr, nullptr}; u64* mw_vals = nullptr; u64* mw_big = nullptr; u64 mw_big_cap = 0;
     u64* md_key = nullptr; i64* md_wend = nullptr; double* md_val = nullptr; u64 md_cap = 0; size_t cur_median = 0;
     // text ingest
@@ -130,7 +131,7 @@ static void free_all(fmq_handle* h) {
                     h->f_key, h->f_sum, h->f_min, h->f_max, h->f_wend, h->f_count, h->wa_key, h->wa_wend, h->wa_val,
                     h->ea_ts, h->ea_key, h->ea_val, h->ca_ts, h->ca_key, h->ca_val, h->d_rolling,
                     h->d_pack[0], h->d_pack[1], h->kr_lead, h->kr_k, h->kr_fl, h->kr_in_c, h->kr_mk, h->kr_mb, h->kr_in_mk, h->kr_in_mb, h->d_counts, h->d_tiles, h->d_xchg, h->d_xsend, h->d_text, h->d_line_start, h->d_txt_status, h->d_txt_bad,
-                    h->ml_pane[0], h->ml_pane[1], h->ml_slot[0], h->ml_slot[1], h->ml_val[0], h->ml_val[1], h->mw_items[0], h->mw_items[1], h->mw_vals, h->mw_big,
+                    h->ml_pane[0], h->ml_pane[1], h->ml_slot[0], h->ml_slot[1], h->ml_val[0], h->ml_val[1], h->mw_items[0], h->mw_items[1], h->mw_vals, h->mw_big, h->d_loc[0], h->d_loc[1], h->d_loc[2],
                     h->md_key, h->md_wend, h->md_val, h->lt_ts, h->lt_key, h->lt_val};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (void* p : h->alt_out) if (p) cudaFree(p);
@@ -158,6 +159,7 @@ static void free_all(fmq_handle* h) {
     delete h;
 }
 
+static size_t locality_min_mb();
 int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     if (!cfg || !out) return set_err(nullptr, FMQ_ERR_BAD_ARG, "null argument");
     *out = nullptr;
@@ -258,6 +260,19 @@ int32_t fmq_create(const fmq_config* cfg, fmq_handle** out) {
     h->tiles_len = (h->counts_len + SCAN_TILE - 1) / SCAN_TILE;
     CUC(dalloc(&h->d_counts, h->counts_len)); CUC(dalloc(&h->d_tiles, h->tiles_len));
     CUC(dalloc(&h->d_xchg, 4)); CUC(cudaMemset(h->d_xchg, 0, 32));
+    // Hashed keys over a table whose panes are much larger than the L2 (126 MB): every accumulator request would go to DRAM
+    // at random.  Such handles split each batch into ranges of the hash first (= ranges of directory buckets and of
+    // accumulator slots: ~24 MB of cells per range and pane), so that the ingest kernel sweeps the table range by range.
+    // Measured (profiles/r02_notes.md): configs[3], 480 MB per pane: 1.57 -> 1.35 ms per 2^24 events; a 128 MB pane under
+    // Zipf keys (configs[4]) loses more to the split than it gains (1.80 -> 1.96), hence the 256 MB default threshold.
+    if (cfg->window_enabled && cfg->key_mode == FMQ_KEYS_HASHED) {
+        const size_t pane_mb = (size_t)h->capacity * sizeof(Acc32) >> 20;
+        if (pane_mb >= locality_min_mb()) {
+            u32 p = 2; while (p < 32 && (size_t)p * 24 < pane_mb) p <<= 1;
+            h->loc_parts = p;
+            for (int k = 0; k < 3; ++k) CUC(dalloc(&h->d_loc[k], h->max_batch));
+        }
+    }
     if (cfg->overlapped_polls) {
         CUC(cudaStreamCreateWithFlags(&h->out_stream, cudaStreamNonBlocking)); CUC(cudaEventCreateWithFlags(&h->ev_out, cudaEventDisableTiming));
         const size_t caps[12] = {h->f_cap, h->f_cap, h->f_cap, h->f_cap, h->f_cap, h->f_cap, h->wa_cap, h->wa_cap, h->wa_cap, h->ea_cap, h->ea_cap, h->ea_cap};
@@ -322,6 +337,10 @@ static int launch_check(fmq_handle* h, const char* what) {
 }
 #define LAUNCHED(h, what) do { int s_ = launch_check(h, what); if (s_) return s_; } while (0)
 
+static size_t locality_min_mb() {              // FMQ_LOCALITY_MIN_MB=0 switches the hash-range split off
+    static const size_t v = [] { const char* e = getenv("FMQ_LOCALITY_MIN_MB"); const long m = e ? atol(e) : 256; return m <= 0 ? (size_t)1 << 40 : (size_t)m; }();
+    return v;
+}
 // exclusive scan of `len` u32 counters in place (three small kernels); `tiles` holds one partial sum per 4096 counters
 static cudaError_t scan_counts_on(cudaStream_t stream, u32* counts, u32* tiles, size_t len) {
     const u32 ntiles = (u32)((len + SCAN_TILE - 1) / SCAN_TILE);
@@ -358,6 +377,7 @@ static cudaError_t owner_split(cudaStream_t stream, const SplitScratch& sc, cons
         return cudaGetLastError();
     };
     if (world <= 8) return run(xs_hist_kernel<3>, xs_scatter_kernel<3, false, XS_THREADS_WIDE>, xs_scatter_kernel<3, true, XS_THREADS>, 8u);
+    if (world <= 32 && !per_owner) return run(xs_hist_kernel<5>, xs_scatter_kernel<5, false, XS_THREADS_WIDE>, xs_scatter_kernel<5, false, XS_THREADS_WIDE>, 32u);
     return run(xs_hist_kernel<8>, xs_scatter_kernel<8, false, XS_THREADS_WIDE>, xs_scatter_kernel<8, false, XS_THREADS_WIDE>, 256u);
 }
 
@@ -484,6 +504,12 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
         IngestArgs a{};
         a.nseg = seg.nseg; a.seg_stride = seg.stride; a.seg_n = seg.seg_n;
         a.ts = ts; a.key = key; a.val = val; a.n = n; a.st = h->d_st; a.dkeys = h->d_keys; a.acc = h->d_acc; a.g = h->g;
+        if (h->loc_parts && seg.nseg == 0 && n >= ((size_t)1 << 20)) {      // (small batches touch little of the table anyway)
+            SplitDst dst{}; dst.out_ts = h->d_loc[0]; dst.out_key = h->d_loc[1]; dst.out_val = h->d_loc[2];
+            CU(h, owner_split(h->stream, SplitScratch{h->d_counts, h->d_tiles}, reinterpret_cast<const u64*>(ts), key, static_cast<const u64*>(val), n, h->loc_parts, SPLIT_HASH_RANGE, dst, false, nullptr));
+            h->launches += 5;
+            a.ts = reinterpret_cast<const i64*>(h->d_loc[0]); a.key = h->d_loc[1]; a.val = h->d_loc[2];
+        }
         a.window_enabled = c.window_enabled; a.vec32 = ((((uintptr_t)ts | (uintptr_t)key | (uintptr_t)val) & 31) == 0);
         a.efilter_enabled = c.efilter_enabled; a.efilter_op = c.efilter_op; a.efilter_thr = c.efilter_threshold;
         a.ea_ts = h->ea_ts; a.ea_key = h->ea_key; a.ea_val = h->ea_val; a.ea_cap = h->ea_cap;

@@ -18,8 +18,14 @@ constexpr int XS_THREADS_WIDE = 512;            // the scatter by itself: 4 even
 
 __host__ __device__ inline u32 xs_num_chunks(size_t n) { return (u32)((n + XS_CHUNK - 1) / XS_CHUNK); }
 
-// keyBy routing on the GPU (A4): hashed keys -> mix64(key) % world; dense ids -> id % world
-__device__ __forceinline__ u32 owner_digit(u64 key, u32 world, u32 dense) { return (u32)((dense ? key : mix64(key)) % world); }
+// keyBy routing on the GPU (A4): hashed keys -> mix64(key) % world (mode 0); dense ids -> id % world (mode 1).
+// Mode 2 is not routing but locality: `world` equal ranges of the hash, i.e. of the key directory's home buckets
+// (dir_home_bucket = mulhi(hash, buckets) is monotone in the hash) and so of the accumulator slots behind them.
+constexpr u32 SPLIT_HASHED = 0, SPLIT_DENSE = 1, SPLIT_HASH_RANGE = 2;
+__device__ __forceinline__ u32 owner_digit(u64 key, u32 world, u32 mode) {
+    if (mode == SPLIT_HASH_RANGE) return (u32)__umul64hi(mix64(key), (u64)world);
+    return (u32)((mode == SPLIT_DENSE ? key : mix64(key)) % world);
+}
 
 // Lanes of `am` holding the same BITS-bit digit, from BITS ballots.  MATCH.ANY does this in one
 // instruction but was measured at ~150 cycles per warp instruction per SM on B200; votes are cheap.
@@ -177,7 +183,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 4 : 2) xs_scatter_ke
             if constexpr (EARLY) { t = tt[r]; v = vv[r]; } else { t = ldg_stream(a.ts + i); v = ldg_stream(a.val + i); }
             tmax = (i64)t > tmax ? (i64)t : tmax;
             ev_s[pos] = t;
-            ev_s[XS_CHUNK + pos] = (a.dense && k != KEY_EMPTY) ? k / a.world : k;
+            ev_s[XS_CHUNK + pos] = (a.dense == SPLIT_DENSE && k != KEY_EMPTY) ? k / a.world : k;
             ev_s[2 * XS_CHUNK + pos] = v;
             dig_s[pos] = dg[r];
         }
