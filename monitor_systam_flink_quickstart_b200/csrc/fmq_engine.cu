@@ -1145,7 +1145,7 @@ int32_t fmq_retire(fmq_handle* h) {
 int32_t fmq_combiner_overlap(fmq_handle* h, int32_t enable) {
     if (!h) return FMQ_ERR_BAD_ARG;
     if (h->sticky) return FMQ_ERR_POISONED;
-    if (h->world < 2) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_combiner_overlap follows fmq_attach_peers");
+    if (!h->peer_acc[h->rank]) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_combiner_overlap follows fmq_attach_peers");
     if (enable && h->g.size != h->g.slide) return set_err(h, FMQ_ERR_BAD_ARG, "only tumbling windows can fire beside the next ingest (a sliding window's panes are still being updated)");
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaStreamSynchronize(h->stream));
