@@ -420,7 +420,7 @@ static int sort_items(fmq_handle* h, u64* const* buf, size_t n, u32 key_bits, Ke
                 hist<<<nblocks, 256, smem, h->stream>>>(buf[*cur], nullptr, n, nchunks, shift, h->d_counts, keyfn); LAUNCHED(h, "ps_pass_kernel(hist)");
             }
             int s_ = exclusive_scan_counts(h, (size_t)(1u << bits) * nchunks); if (s_) return s_;
-            const size_t tsmem = (size_t)PS_CHUNK * 8 + (size_t)(1u << bits) * 8 + (size_t)8 * (1u << bits) * 2 + (size_t)PS_CHUNK * 2;
+            const size_t tsmem = ps_scatter_smem(1u << bits);
             CU(h, cudaFuncSetAttribute(scat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
             scat<<<nchunks, 256, tsmem, h->stream>>>(buf[*cur], buf[*cur ^ 1], n, nchunks, shift, h->d_counts, keyfn); LAUNCHED(h, "ps_scatter_tile_kernel");
             return FMQ_OK;

@@ -123,55 +123,66 @@ __global__ void __launch_bounds__(256) resolve_hist_kernel(const u64* __restrict
     for (u32 d = lane; d < NB; d += 32) counts[(size_t)d * nchunks + chunk] = bins[d];
 }
 
-// Scatter half of a radix pass, one BLOCK per chunk of PS_CHUNK items: the chunk is sorted by digit in
-// shared memory first (stable: warp w ranks its 512 consecutive items round by round, a cross-warp
-// scan per digit orders the warps) and then copied out position by position, so consecutive threads
-// write consecutive addresses of a digit's run.  The per-warp-chunk version above writes every item as
-// a lone 8-byte store; ncu showed those partial-sector writes congesting the memory system
-// (782 MB of DRAM traffic for 268 MB of payload, 455 us per pass of 2^24 items).
+// Scatter half of a radix pass, one BLOCK per chunk of PS_CHUNK items: the chunk is ranked by digit in shared memory
+// (stable: warp w ranks its 512 consecutive items round by round, a cross-warp scan per digit orders the warps) and then
+// copied out position by position, so consecutive threads write consecutive addresses of a digit's run (lone 8-byte
+// stores were 782 MB of DRAM traffic for 268 MB of payload).
+// The chunk arrives as ONE 32 KB bulk copy (TMA) into shared memory: with plain loads ptxas, short of registers, issued
+// each round's load two rounds before its use, and every one of the 16 ranking rounds waited on DRAM (ncu: long
+// scoreboard in every round, 59 % of all samples in the ranking phase).  Items are never held in registers: a round
+// reads its item from shared memory, and the sorted order is a 16-bit source index per position.
 constexpr int PS_IPT = PS_CHUNK / 256;          // items per thread
-// 3 resident blocks (<= 85 registers) measured best: 2 (123 registers, no spills) 0.19 ms per pass of 2^24
-// items, 3 -> 0.165 ms; re-reading the items in phase 3 to free 32 more registers gained nothing.
 #ifndef FMQ_PS_MINB
-#define FMQ_PS_MINB 3
+#define FMQ_PS_MINB 4
 #endif
+constexpr size_t ps_scatter_smem(u32 nb) { return (size_t)PS_CHUNK * 8 + (size_t)nb * 8 + (size_t)8 * nb * 2 + (size_t)PS_CHUNK * 2; }
 
 template <int BITS, typename KeyFn>
 __global__ void __launch_bounds__(256, FMQ_PS_MINB) ps_scatter_tile_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t n, u32 nchunks, u32 shift,
                                                               const u32* __restrict__ offsets, KeyFn keyfn) {
     constexpr u32 NB = 1u << BITS;
-    extern __shared__ __align__(16) unsigned char ps_tile_smem[];
-    u64* items_s = reinterpret_cast<u64*>(ps_tile_smem);                         // [PS_CHUNK]
-    u32* goff = reinterpret_cast<u32*>(items_s + PS_CHUNK);                      // [NB] global offset of (digit, this chunk)
+    extern __shared__ __align__(128) unsigned char ps_tile_smem[];
+    u64* in_s = reinterpret_cast<u64*>(ps_tile_smem);                            // [PS_CHUNK] the chunk as it arrived
+    u32* goff = reinterpret_cast<u32*>(in_s + PS_CHUNK);                         // [NB] global offset of (digit, this chunk)
     u32* dbase = goff + NB;                                                      // [NB] start of the digit inside the sorted chunk
     unsigned short* wcnt = reinterpret_cast<unsigned short*>(dbase + NB);        // [8][NB] per-warp counts, then exclusive prefixes
-    unsigned short* dig_s = wcnt + 8 * NB;                                       // [PS_CHUNK] digit of every sorted position
+    unsigned short* src_s = wcnt + 8 * NB;                                       // [PS_CHUNK] sorted position -> index in the chunk
     __shared__ u32 scan_ws[8];
+    __shared__ __align__(8) u64 bar;
     const u32 tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     const u32 chunk = blockIdx.x;
     const size_t lo = (size_t)chunk * PS_CHUNK;
     const size_t hi = (lo + PS_CHUNK < n) ? lo + PS_CHUNK : n;
+    const u32 cnt = (u32)(hi - lo);
+    const bool bulk = cnt == PS_CHUNK && ((uintptr_t)in & 15) == 0;
+    if (tid == 0 && bulk) {
+        mbar_init(&bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        u64 policy;
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+        mbar_expect_tx(&bar, PS_CHUNK * 8u);
+        tma_load_1d(in_s, in + lo, PS_CHUNK * 8u, &bar, policy);
+    }
+    if (!bulk) for (u32 i = tid; i < PS_CHUNK; i += 256) in_s[i] = i < cnt ? in[lo + i] : ~0ull;     // ragged last chunk
     for (u32 i = tid; i < 8 * NB; i += 256) wcnt[i] = 0;
     for (u32 d = tid; d < NB; d += 256) goff[d] = offsets[(size_t)d * nchunks + chunk];
     __syncthreads();
+    if (bulk) mbar_wait(&bar, 0);
     // phase 1: rank inside the warp's 512 consecutive items, in order
-    u64 it[PS_IPT]; unsigned short dg[PS_IPT], rk[PS_IPT];
-#pragma unroll
-    for (int r = 0; r < PS_IPT; ++r) { const size_t i = lo + (size_t)w * (PS_CHUNK / 8) + r * 32 + lane; it[r] = i < hi ? in[i] : ~0ull; }
+    unsigned short rk[PS_IPT];
+    const u32 wlo = w * (PS_CHUNK / 8);
 #pragma unroll
     for (int r = 0; r < PS_IPT; ++r) {
-        const bool act = lo + (size_t)w * (PS_CHUNK / 8) + r * 32 + lane < hi;
+        const u32 i = wlo + r * 32 + lane;
+        const bool act = i < cnt;
         const unsigned am = __ballot_sync(0xffffffffu, act);
-        dg[r] = 0; rk[r] = 0;
-        if (act) {
-            const u32 d = (u32)(keyfn(it[r]) >> shift) & (NB - 1);
-            const unsigned m = match_digit<BITS>(am, d);
-            const int leader = __ffs(m) - 1;
-            u32 base = 0;
-            if ((int)lane == leader) { base = wcnt[w * NB + d]; wcnt[w * NB + d] = (unsigned short)(base + __popc(m)); }
-            base = __shfl_sync(m, base, leader);
-            dg[r] = (unsigned short)d; rk[r] = (unsigned short)(base + __popc(m & ((1u << lane) - 1)));
-        }
+        const u32 d = (u32)(keyfn(in_s[i]) >> shift) & (NB - 1);                // (every lane takes part in the votes and the shuffle)
+        const unsigned m = match_digit<BITS>(am, d);
+        const int leader = (__ffs(m) - 1) & 31;
+        u32 base = 0;
+        if (act && (int)lane == leader) { base = wcnt[w * NB + d]; wcnt[w * NB + d] = (unsigned short)(base + __popc(m)); }
+        base = __shfl_sync(0xffffffffu, base, leader);
+        rk[r] = (unsigned short)(base + __popc(m & ((1u << lane) - 1)));
         __syncwarp();
     }
     __syncthreads();
@@ -197,18 +208,22 @@ __global__ void __launch_bounds__(256, FMQ_PS_MINB) ps_scatter_tile_kernel(const
 #pragma unroll
     for (u32 q = 0; q < DPT; ++q) { const u32 d = tid * DPT + q; if (d < NB) dbase[d] = run; run += dtot[q]; }
     __syncthreads();
-    // phase 3: place every item at its sorted position
+    // phase 3: the sorted position of every item
 #pragma unroll
     for (int r = 0; r < PS_IPT; ++r) {
-        if (lo + (size_t)w * (PS_CHUNK / 8) + r * 32 + lane < hi) {
-            const u32 pos = dbase[dg[r]] + wcnt[w * NB + dg[r]] + rk[r];
-            items_s[pos] = it[r]; dig_s[pos] = dg[r];
+        const u32 i = wlo + r * 32 + lane;
+        if (i < cnt) {
+            const u32 d = (u32)(keyfn(in_s[i]) >> shift) & (NB - 1);
+            src_s[dbase[d] + wcnt[w * NB + d] + rk[r]] = (unsigned short)i;
         }
     }
     __syncthreads();
     // phase 4: copy out; consecutive threads -> consecutive positions -> consecutive addresses inside a run
-    const u32 cnt = (u32)(hi - lo);
-    for (u32 pos = tid; pos < cnt; pos += 256) { const u32 d = dig_s[pos]; out[(size_t)goff[d] + (pos - dbase[d])] = items_s[pos]; }
+    for (u32 pos = tid; pos < cnt; pos += 256) {
+        const u64 item = in_s[src_s[pos]];
+        const u32 d = (u32)(keyfn(item) >> shift) & (NB - 1);
+        out[(size_t)goff[d] + (pos - dbase[d])] = item;
+    }
 }
 
 // ---- step 3: apply the operators along every key's run, in arrival order ---------------------------

@@ -29,12 +29,15 @@ __device__ __forceinline__ u32 owner_digit(u64 key, u32 world, u32 mode) {
 
 // Lanes of `am` holding the same BITS-bit digit, from BITS ballots.  MATCH.ANY does this in one
 // instruction but was measured at ~150 cycles per warp instruction per SM on B200; votes are cheap.
+// ALL 32 lanes call this, converged (lanes outside `am` pass any digit; their result is meaningless): a vote or
+// shuffle under a run-time mask inside a divergent branch compiles to WARPSYNC + MATCH.ANY on the mask itself —
+// the slow instruction again, 16 times per chunk (found in the SASS of the scatter kernels).
 template <int BITS>
 __device__ __forceinline__ unsigned match_digit(unsigned am, u32 d) {
     unsigned m = am;
 #pragma unroll
     for (int b = 0; b < BITS; ++b) {
-        const unsigned v = __ballot_sync(am, (d >> b) & 1u);
+        const unsigned v = __ballot_sync(0xffffffffu, (d >> b) & 1u);
         m &= ((d >> b) & 1u) ? v : ~v;
     }
     return m;
@@ -59,11 +62,9 @@ __global__ void __launch_bounds__(XS_THREADS) xs_hist_kernel(const u64* __restri
     for (int r = 0; r < XS_IPT; ++r) {
         const bool act = lo + (size_t)r * XS_THREADS + tid < hi;
         const unsigned am = __ballot_sync(0xffffffffu, act);
-        if (act) {
-            const u32 d = owner_digit(kk[r], world, dense);
-            const unsigned m = match_digit<BITS>(am, d);
-            if ((int)(tid & 31) == __ffs(m) - 1) atomicAdd(&cnt[d], (u32)__popc(m));      // one shared atomic per distinct digit of the warp round
-        }
+        const u32 d = act ? owner_digit(kk[r], world, dense) : 0u;
+        const unsigned m = match_digit<BITS>(am, d);
+        if (act && (int)(tid & 31) == __ffs(m) - 1) atomicAdd(&cnt[d], (u32)__popc(m));   // one shared atomic per distinct digit of the warp round
     }
     __syncthreads();
     for (u32 d = tid; d < NB; d += XS_THREADS) counts[(size_t)d * nchunks + chunk] = cnt[d];
@@ -132,16 +133,13 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 4 : 2) xs_scatter_ke
     for (int r = 0; r < IPT; ++r) {
         const bool act = wlo + r * 32 + lane < hi;
         const unsigned am = __ballot_sync(0xffffffffu, act);
-        dg[r] = 0; rk[r] = 0;
-        if (act) {
-            const u32 d = owner_digit(kk[r], a.world, a.dense);
-            const unsigned m = match_digit<BITS>(am, d);
-            const int leader = __ffs(m) - 1;
-            u32 base = 0;
-            if ((int)lane == leader) { base = wcnt[w * NB + d]; wcnt[w * NB + d] = (unsigned short)(base + __popc(m)); }
-            base = __shfl_sync(m, base, leader);
-            dg[r] = (unsigned short)d; rk[r] = (unsigned short)(base + __popc(m & ((1u << lane) - 1)));
-        }
+        const u32 d = act ? owner_digit(kk[r], a.world, a.dense) : 0u;           // (every lane takes part in the votes and the shuffle)
+        const unsigned m = match_digit<BITS>(am, d);
+        const int leader = (__ffs(m) - 1) & 31;
+        u32 base = 0;
+        if (act && (int)lane == leader) { base = wcnt[w * NB + d]; wcnt[w * NB + d] = (unsigned short)(base + __popc(m)); }
+        base = __shfl_sync(0xffffffffu, base, leader);
+        dg[r] = (unsigned short)d; rk[r] = act ? (unsigned short)(base + __popc(m & ((1u << lane) - 1))) : (unsigned short)0;
         __syncwarp();
     }
     __syncthreads();
