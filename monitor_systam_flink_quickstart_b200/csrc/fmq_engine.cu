@@ -372,7 +372,11 @@ static cudaError_t owner_split(cudaStream_t stream, const SplitScratch& sc, cons
             e = scan_counts_on(stream, sc.counts, sc.tiles, (size_t)nb * nchunks); if (e != cudaSuccess) return e;
         }
         // beside the ingest of the previous batch (keyBy exchange): 256-thread blocks; by itself: 512-thread blocks
-        if (per_owner) { const size_t smem = xs_scatter_smem(nb, XS_THREADS); e = cudaFuncSetAttribute(scat_owner, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_owner<<<grid, XS_THREADS, smem, stream>>>(a); }
+        if (per_owner) {
+            const size_t smem = xs_scatter_smem(nb, XS_THREADS); e = cudaFuncSetAttribute(scat_owner, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e;
+            e = cudaFuncSetAttribute(scat_owner, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared); if (e != cudaSuccess) return e;   // it shares the SMs with the ingest kernel
+            scat_owner<<<grid, XS_THREADS, smem, stream>>>(a);
+        }
         else           { const size_t smem = xs_scatter_smem(nb, XS_THREADS_WIDE); e = cudaFuncSetAttribute(scat_single, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; scat_single<<<grid, XS_THREADS_WIDE, smem, stream>>>(a); }
         return cudaGetLastError();
     };
@@ -537,6 +541,7 @@ static int stage_ingest(fmq_handle* h, const i64* ts, const u64* key, const void
                                        : pick(ingest_ring_kernel<V, false, false, false>, ingest_ring_kernel<V, false, false, true>));
             const int smem = iw_smem_bytes(extras);
             CU(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            if (h->xs_attached) CU(h, cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));   // beside the scatter of the next batch
             kfn<<<(unsigned)blocks, IW_THREADS, smem, h->stream>>>(a);
             LAUNCHED(h, "ingest_ring_kernel");
         }

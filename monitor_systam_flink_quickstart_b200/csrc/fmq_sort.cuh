@@ -30,6 +30,10 @@ __device__ __forceinline__ u32 mod_small(u64 x, u32 w) {
     const u32 c = (0xFFFFFFFFu % w + 1u) % w;                             // 2^32 % w
     return (((u32)(x >> 32) % w) * c + (u32)x % w) % w;
 }
+__device__ __forceinline__ u64 div_small(u64 x, u32 w) {                  // dense id -> the owner's local id
+    if ((w & (w - 1u)) == 0u) return x >> (31 - __clz((int)w));
+    return (x >> 32) ? x / w : (u64)((u32)x / w);
+}
 __device__ __forceinline__ u32 owner_digit(u64 key, u32 world, u32 mode) {
     if (mode == SPLIT_HASH_RANGE) return (u32)__umul64hi(mix64(key), (u64)world);
     return mod_small(mode == SPLIT_DENSE ? key : mix64(key), world);
@@ -121,69 +125,54 @@ struct SplitArgs {
     // all a commutative aggregate needs; jobs with order-dependent keyed state use the stable two-pass form.
     unsigned long long* fill;
 };
-constexpr size_t xs_scatter_smem(u32 nb, int threads) { return (size_t)3 * XS_CHUNK * 8 + XS_CHUNK * 2 * 2 + (size_t)(threads / 32) * nb * 2 + nb * 4 * 2; }
+// (Tried: the three columns as TMA bulk copies into shared memory and a 16-bit source index per sorted position, as in
+// ps_scatter_tile_kernel.  By itself the kernel did not change — 175 us per 2^24 events either way once the owner digit
+// lost its 64-bit division — and beside the ingest kernel (keyBy exchange, N = 2, same box) the step went from 0.533 to
+// 0.576 ms: 512 threads polling an mbarrier take issue slots from the ingest warps.  Kept: per-thread loads.)
+constexpr size_t xs_scatter_smem(u32 nb, int threads) { return (size_t)3 * XS_CHUNK * 8 + XS_CHUNK * 2 + (size_t)(threads / 32) * nb * 2 + nb * 4 * 2; }
 
-// The chunk's three columns arrive as three 16 KB bulk copies (TMA) into shared memory and stay where they landed: the
-// ranking reads the keys from there, the sorted order is a 16-bit source index per position, and the copy-out gathers
-// through it.  (Loading the columns with per-thread loads held them in registers through the ranking — 512-thread
-// blocks — or cost a second DRAM round trip after it — 256-thread blocks.)
 template <int BITS, bool PER_OWNER, int THREADS>
 __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 4 : 2) xs_scatter_kernel(const __grid_constant__ SplitArgs a) {
     constexpr int WARPS = THREADS / 32, IPT = (int)XS_CHUNK / THREADS;
+    constexpr bool EARLY = THREADS > 256;         // enough registers to hold all three columns through the ranking
     constexpr u32 NB = 1u << BITS;
-    extern __shared__ __align__(128) unsigned char xs_smem[];
-    u64* in_s = reinterpret_cast<u64*>(xs_smem);                                  // [3][XS_CHUNK] ts, key, value as they arrived
-    unsigned short* dig_s = reinterpret_cast<unsigned short*>(in_s + 3 * XS_CHUNK);   // [XS_CHUNK] owner of every sorted position
-    unsigned short* src_s = dig_s + XS_CHUNK;                                     // [XS_CHUNK] sorted position -> index in the chunk
-    unsigned short* wcnt = src_s + XS_CHUNK;                                      // [WARPS][NB] per-warp counts, then exclusive prefixes
+    extern __shared__ __align__(16) unsigned char xs_smem[];
+    u64* ev_s = reinterpret_cast<u64*>(xs_smem);                                  // [3][XS_CHUNK]
+    unsigned short* dig_s = reinterpret_cast<unsigned short*>(ev_s + 3 * XS_CHUNK);   // [XS_CHUNK] owner of every sorted position
+    unsigned short* wcnt = dig_s + XS_CHUNK;                                      // [WARPS][NB] per-warp counts, then exclusive prefixes
     u32* dbase = reinterpret_cast<u32*>(wcnt + WARPS * NB);                    // [NB] start of the owner's run inside the sorted chunk
     u32* goff = dbase + NB;                                                       // [NB] where that run goes in the owner's destination
     __shared__ u32 scan_ws[WARPS];
     __shared__ i64 max_ws[WARPS];
-    __shared__ __align__(8) u64 bar;
     const u32 tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     i64 tmax = I64_MIN_;
-    const bool aligned = ((((uintptr_t)a.ts) | ((uintptr_t)a.key) | ((uintptr_t)a.val)) & 15) == 0;
-    u64 policy;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
-    if (tid == 0) { mbar_init(&bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-    u32 phase = 0;
     // persistent over chunks: the grid may be much smaller than the number of chunks (the keyBy exchange runs this kernel
     // beside the ingest of the previous batch and leaves it most of every SM)
     for (u32 chunk = blockIdx.x; chunk < a.nchunks; chunk += gridDim.x) {
     const size_t lo = (size_t)chunk * XS_CHUNK;
     const size_t hi = (lo + XS_CHUNK < a.n) ? lo + XS_CHUNK : a.n;
-    const u32 cnt = (u32)(hi - lo);
-    const bool bulk = aligned && cnt == XS_CHUNK;
     const bool unordered = PER_OWNER && a.fill != nullptr;
-    __syncthreads();                               // the previous chunk has been copied out of the staging area (and the barrier is initialised)
-    if (bulk) {
-        if (tid == 0) {
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");          // generic-proxy reads of the staging area before the async-proxy refill
-            mbar_expect_tx(&bar, 3u * XS_CHUNK * 8u);
-            tma_load_1d(in_s, a.ts + lo, XS_CHUNK * 8u, &bar, policy);
-            tma_load_1d(in_s + XS_CHUNK, a.key + lo, XS_CHUNK * 8u, &bar, policy);
-            tma_load_1d(in_s + 2 * XS_CHUNK, a.val + lo, XS_CHUNK * 8u, &bar, policy);
-        }
-    } else {                                       // ragged last chunk, or columns that are not 16-byte aligned
-        for (u32 i = tid; i < cnt; i += THREADS) { in_s[i] = ldg_stream(a.ts + lo + i); in_s[XS_CHUNK + i] = ldg_stream(a.key + lo + i); in_s[2 * XS_CHUNK + i] = ldg_stream(a.val + lo + i); }
-    }
     for (u32 i = tid; i < WARPS * NB; i += THREADS) wcnt[i] = 0;
     if (!unordered) for (u32 d = tid; d < NB; d += THREADS) {
         const u32 o = a.offsets[(size_t)d * a.nchunks + chunk];
         goff[d] = PER_OWNER ? o - a.offsets[(size_t)d * a.nchunks] : o;           // per-owner destinations start at 0
     }
     __syncthreads();
-    if (bulk) { mbar_wait(&bar, phase); phase ^= 1u; }
-    // phase 1: rank inside the warp's consecutive events, in arrival order
-    unsigned short dg[IPT], rk[IPT];
-    const u32 wlo = w * (XS_CHUNK / WARPS);
+    // phase 1: rank inside the warp's 256 consecutive events, in arrival order
+    // all three columns of the thread's events are requested at once (one memory round trip per chunk, not two)
+    u64 kk[IPT], tt[EARLY ? IPT : 1], vv[EARLY ? IPT : 1]; unsigned short dg[IPT], rk[IPT];
+    const size_t wlo = lo + (size_t)w * (XS_CHUNK / WARPS);
 #pragma unroll
     for (int r = 0; r < IPT; ++r) {
-        const u32 i = wlo + r * 32 + lane; const bool act = i < cnt;
+        const size_t i = wlo + r * 32 + lane; const bool in = i < hi;
+        kk[r] = in ? ldg_stream(a.key + i) : 0;
+        if constexpr (EARLY) { tt[r] = in ? ldg_stream(a.ts + i) : 0; vv[r] = in ? ldg_stream(a.val + i) : 0; }
+    }
+#pragma unroll
+    for (int r = 0; r < IPT; ++r) {
+        const bool act = wlo + r * 32 + lane < hi;
         const unsigned am = __ballot_sync(0xffffffffu, act);
-        const u32 d = act ? owner_digit(in_s[XS_CHUNK + i], a.world, a.dense) : 0u;           // (every lane takes part in the votes and the shuffle)
-        if (act) { const i64 t = (i64)in_s[i]; tmax = t > tmax ? t : tmax; }
+        const u32 d = act ? owner_digit(kk[r], a.world, a.dense) : 0u;           // (every lane takes part in the votes and the shuffle)
         const unsigned m = match_digit<BITS>(am, d);
         const int leader = (__ffs(m) - 1) & 31;
         u32 base = 0;
@@ -221,25 +210,34 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 4 : 2) xs_scatter_ke
         run += dtot[q];
     }
     __syncthreads();
-    // phase 3: the sorted position of every event
+    // phase 3: the three columns of every event go to its sorted position
 #pragma unroll
     for (int r = 0; r < IPT; ++r) {
-        const u32 i = wlo + r * 32 + lane;
-        if (i < cnt) { const u32 pos = dbase[dg[r]] + wcnt[w * NB + dg[r]] + rk[r]; src_s[pos] = (unsigned short)i; dig_s[pos] = dg[r]; }
+        const size_t i = wlo + r * 32 + lane;
+        if (i < hi) {
+            const u32 pos = dbase[dg[r]] + wcnt[w * NB + dg[r]] + rk[r];
+            u64 t, v; const u64 k = kk[r];
+            if constexpr (EARLY) { t = tt[r]; v = vv[r]; } else { t = ldg_stream(a.ts + i); v = ldg_stream(a.val + i); }
+            tmax = (i64)t > tmax ? (i64)t : tmax;
+            ev_s[pos] = t;
+            ev_s[XS_CHUNK + pos] = (a.dense == SPLIT_DENSE && k != KEY_EMPTY) ? div_small(k, a.world) : k;
+            ev_s[2 * XS_CHUNK + pos] = v;
+            dig_s[pos] = dg[r];
+        }
     }
     __syncthreads();
     // phase 4: copy out; consecutive threads -> consecutive positions -> consecutive addresses inside a run
+    const u32 cnt = (u32)(hi - lo);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
         for (u32 pos = tid; pos < cnt; pos += THREADS) {
             const u32 d = dig_s[pos];
             const size_t o = (size_t)goff[d] + (pos - dbase[d]);
             u64* dstc = PER_OWNER ? a.dst.ts[d] + (size_t)c * a.dst.col_stride : (c == 0 ? a.dst.out_ts : (c == 1 ? a.dst.out_key : a.dst.out_val));
-            u64 x = in_s[c * XS_CHUNK + src_s[pos]];
-            if (c == 1 && a.dense == SPLIT_DENSE && x != KEY_EMPTY) x /= a.world;      // dense ids become the owner's local id
-            dstc[o] = x;
+            dstc[o] = ev_s[c * XS_CHUNK + pos];
         }
     }
+    __syncthreads();                               // the staging area is reused by the next chunk
     }
     if (a.max_ts) {                                // one atomic per block for the batch's largest timestamp
         tmax = warp_max_i64(tmax); if (lane == 0) max_ws[w] = tmax;
