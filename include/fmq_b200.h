@@ -424,6 +424,9 @@ int32_t fmq_retire(fmq_handle* h);
  *     fmq_retire(h)              [on fmq_fire_stream(h)]
  * A fire with no preceding local push (end-of-input flush) calls fmq_push_local with n = 0 first.
  * pane_ring must cover the live panes plus the panes that expire in one step (else FMQ_ERR_RING_OVERFLOW).
+ * Also accepted on a handle without peers (world = 1, fmq_push_local / fmq_fire_global / fmq_retire with no all-reduce):
+ * same rows, but no faster than fmq_push_batch — on one GPU the fire kernel and the ingest kernel load the same L2
+ * (tools/exp_overlap_1gpu.py, profiles/r02_notes.md).
  * No reference counterpart (Flink fires windows on the task thread between records). */
 int32_t fmq_combiner_overlap(fmq_handle* h, int32_t enable);
 void*   fmq_fire_stream(fmq_handle* h);

@@ -825,7 +825,7 @@ static int check_cols(fmq_handle* h, const InCols& c, size_t n, int32_t mem) {
 
 static int push_cols(fmq_handle* h, const InCols& c, size_t n, int64_t wm_after, int32_t mem) {
     int s = check_cols(h, c, n, mem); if (s) return s;
-    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: use fmq_push_local / fmq_fire_global / fmq_retire");
+    if (h->world > 1 || h->overlap) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached or overlapped schedule: use fmq_push_local / fmq_fire_global / fmq_retire");
     CU(h, cudaSetDevice(h->device));
     return h->cfg.value_type == FMQ_VAL_F64 ? push_cols_t<double>(h, c, n, wm_after, mem) : push_cols_t<i64>(h, c, n, wm_after, mem);
 }
@@ -893,7 +893,7 @@ int32_t fmq_flush(fmq_handle* h, int64_t watermark) {
     if (!h) return FMQ_ERR_BAD_ARG;
     if (h->sticky) return FMQ_ERR_POISONED;
     if (watermark == FMQ_WM_AUTO || watermark == FMQ_WM_KEEP) return set_err(h, FMQ_ERR_BAD_ARG, "flush needs an explicit watermark");
-    if (h->world > 1) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached: use fmq_fire_global / fmq_retire");
+    if (h->world > 1 || h->overlap) return set_err(h, FMQ_ERR_BAD_ARG, "peers attached or overlapped schedule: use fmq_fire_global / fmq_retire");
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaEventRecord(h->tev[h->pushes % fmq_handle::TIMING_RING][0], h->stream));
     int s = (h->cfg.value_type == FMQ_VAL_F64) ? run_chain<double>(h, nullptr, nullptr, nullptr, 0, watermark)
@@ -1150,7 +1150,6 @@ int32_t fmq_retire(fmq_handle* h) {
 int32_t fmq_combiner_overlap(fmq_handle* h, int32_t enable) {
     if (!h) return FMQ_ERR_BAD_ARG;
     if (h->sticky) return FMQ_ERR_POISONED;
-    if (!h->peer_acc[h->rank]) return set_err(h, FMQ_ERR_BAD_ARG, "fmq_combiner_overlap follows fmq_attach_peers");
     if (enable && h->g.size != h->g.slide) return set_err(h, FMQ_ERR_BAD_ARG, "only tumbling windows can fire beside the next ingest (a sliding window's panes are still being updated)");
     CU(h, cudaSetDevice(h->device));
     CU(h, cudaStreamSynchronize(h->stream));

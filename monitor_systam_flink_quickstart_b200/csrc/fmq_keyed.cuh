@@ -39,16 +39,20 @@ struct SlotKey {            // item = (slot << 32 | index): sort by slot
     __device__ __forceinline__ u64 operator()(u64 item) const { return item >> 32; }
 };
 
+// Counting half of a radix pass: every warp counts the digits of one chunk of PS_CHUNK items into its own bins
+// (counting needs no order: one shared-memory atomic per item), counts[digit][chunk].  `SCATTER` is kept in the
+// signature for the call sites; only the counting form exists (the scatter is ps_scatter_tile_kernel).
 template <int BITS, bool SCATTER, typename KeyFn>
-__global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t n, u32 nchunks, u32 shift,
-                                                      u32* __restrict__ counts /* hist: written; scatter: scanned offsets */, KeyFn keyfn) {
+__global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in, u64* __restrict__ /*out*/, size_t n, u32 nchunks, u32 shift,
+                                                      u32* __restrict__ counts, KeyFn keyfn) {
+    static_assert(!SCATTER, "the scatter half is ps_scatter_tile_kernel");
     extern __shared__ u32 ps_smem[];
     constexpr u32 NB = 1u << BITS;
     const u32 wl = threadIdx.x >> 5, lane = threadIdx.x & 31;
     u32* bins = ps_smem + wl * NB;
     const u32 chunk = blockIdx.x * 8 + wl;
     if (chunk >= nchunks) return;
-    for (u32 d = lane; d < NB; d += 32) bins[d] = SCATTER ? counts[(size_t)d * nchunks + chunk] : 0u;
+    for (u32 d = lane; d < NB; d += 32) bins[d] = 0u;
     __syncwarp();
     const size_t lo = (size_t)chunk * PS_CHUNK;
     const size_t hi = (lo + PS_CHUNK < n) ? lo + PS_CHUNK : n;
@@ -56,31 +60,12 @@ __global__ void __launch_bounds__(256) ps_pass_kernel(const u64* __restrict__ in
         u64 it[PS_AHEAD];
 #pragma unroll
         for (int r = 0; r < PS_AHEAD; ++r) { const size_t i = i0 + r * 32 + lane; it[r] = i < hi ? in[i] : ~0ull; }
-        if constexpr (!SCATTER) {
-            // counting needs no order: one shared-memory atomic per item on the warp's private bins
 #pragma unroll
-            for (int r = 0; r < PS_AHEAD; ++r)
-                if (i0 + r * 32 + lane < hi) atomicAdd(&bins[(u32)(keyfn(it[r]) >> shift) & (NB - 1)], 1u);
-        } else {
-#pragma unroll
-        for (int r = 0; r < PS_AHEAD; ++r) {
-            const bool act = i0 + r * 32 + lane < hi;
-            const unsigned am = __ballot_sync(0xffffffffu, act);
-            if (act) {
-                const u32 d = (u32)(keyfn(it[r]) >> shift) & (NB - 1);
-                const unsigned m = __match_any_sync(am, d);
-                const int leader = __ffs(m) - 1;
-                u32 base = 0;
-                if ((int)lane == leader) { base = bins[d]; bins[d] = base + __popc(m); }
-                base = __shfl_sync(m, base, leader);
-                out[(size_t)base + __popc(m & ((1u << lane) - 1))] = it[r];
-            }
-            __syncwarp();
-        }
-        }
+        for (int r = 0; r < PS_AHEAD; ++r)
+            if (i0 + r * 32 + lane < hi) atomicAdd(&bins[(u32)(keyfn(it[r]) >> shift) & (NB - 1)], 1u);
     }
     __syncwarp();
-    if (!SCATTER) for (u32 d = lane; d < NB; d += 32) counts[(size_t)d * nchunks + chunk] = bins[d];
+    for (u32 d = lane; d < NB; d += 32) counts[(size_t)d * nchunks + chunk] = bins[d];
 }
 
 // Step 1, fused with the counting half of the first radix pass: the warp that resolves a chunk of keys also
