@@ -596,7 +596,7 @@ def test_overlapped_polls_return_the_same_rows():
 
 
 # ---- keyBy exchange ------------------------------------------------------------------------------
-@pytest.mark.parametrize("world", [1, 2, 8])
+@pytest.mark.parametrize("world", [1, 2, 3, 7, 8, 24, 32, 64, 200])      # 3-bit digits up to 8 owners, 5-bit up to 32, 8-bit beyond; powers of two and not
 def test_partition_by_owner_is_a_stable_split(world):
     import torch
     e = capi.Engine(efilter_enabled=1, max_batch=1 << 17)
