@@ -103,3 +103,29 @@ def test_parallel_baseline_matches_literal_oracle(name, threads):
     assert ca["late_dropped"] == cb["late_dropped"] and ca["windows_fired"] == cb["windows_fired"] > 0
     if name == "tumbling_f64":
         assert ca["late_dropped"] > 0          # the stream's late tail really exercises the drop
+
+
+def test_oracle_median_against_numpy_for_every_run_length():
+    """The window median of the literal oracle (the ListState restatement of ComputeCpuMiddle.java:34-47) against
+    numpy.median, for run lengths 1..35 and a few long ones, with ties, both zeros and both infinities: the same
+    stream the GPU test `test_window_median_run_lengths_around_the_short_long_boundary` compares with this oracle."""
+    kw = dict(window_enabled=1, agg_mask=1, window_size_ms=10_000, window_slide_ms=10_000, max_out_of_orderness_ms=0,
+              median_log_capacity=500_000, table_capacity=1 << 12, pane_ring=128, max_batch=1 << 18)
+    cpu = OracleEngine(**kw)
+    lens = list(range(1, 36)) + [63, 64, 65, 255, 256, 257, 1000, 4097, 100_001, 100_000]
+    rng = np.random.default_rng(5)
+    key = np.repeat(np.arange(len(lens), dtype=np.uint64) + 1, lens)
+    key = key[rng.permutation(len(key))]
+    want = {}
+    for w in range(2):
+        val = np.round(rng.normal(0, 3, len(key)), 1 if w == 0 else 12)
+        val[::53] = -0.0; val[1::53] = 0.0; val[7::211] = np.inf; val[11::223] = -np.inf
+        ts = 1_600_000_000_000 + w * 10_000 + rng.integers(0, 10_000, len(key)).astype(np.int64)
+        cpu.push_batch(ts, key, val, capi.FMQ_WM_KEEP)
+        for k in np.unique(key):
+            want[(int(k), 1_600_000_000_000 + (w + 1) * 10_000)] = float(np.median(val[key == k]))
+    cpu.flush()
+    m = cpu.poll_medians()
+    got = {(int(k), int(e)): float(v) for k, e, v in zip(m.key, m.window_end, m.value)}
+    assert got.keys() == want.keys()
+    assert all(got[x] == want[x] for x in want), [x for x in want if got[x] != want[x]][:5]
