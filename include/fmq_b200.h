@@ -144,8 +144,11 @@ typedef struct fmq_config {
     uint64_t calert_capacity;        /* consecutive-breach alert rows buffered between polls     */
     uint64_t text_max_bytes;         /* > 0: device buffers for fmq_parse_text / fmq_push_text    */
     uint64_t median_log_capacity;    /* > 0: also compute the per-(key, window) median
-                                        (ComputeCpuMiddle.java:34-47); this many accepted records
-                                        can be buffered while their windows are open (f64 only)   */
+                                        (ComputeCpuMiddle.java:34-47); this many records can be
+                                        buffered while their windows are open (f64 only).  Size it
+                                        for every record pushed in that time, not only the accepted
+                                        ones: log space is reserved ahead, and what a dropped (late)
+                                        record would have used stays empty until the next expiry   */
     uint64_t median_capacity;        /* median rows buffered between polls                        */
     uint64_t late_capacity;          /* > 0: dropped late records are kept as a side output
                                         (sideOutputLateData), this many rows between polls        */
